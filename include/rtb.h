@@ -1,0 +1,141 @@
+/* rtb.h -- C ABI of the B200 ray-casting backend ("rtb").
+ *
+ * This is the drop-in boundary for ONE path of RichardHancock/OpenCL-Ray-Tracer: the per-frame
+ * primary-ray cast that the reference runs either on the CPU (MainState::executeRayTracerCPU,
+ * RayTrace/states/MainState.cpp:936-972) or through OpenCL (MainState::openCLInit :1181-1326 +
+ * MainState::executeRayTracerOpenCL :641-934 + the kernel RayTrace/resources/shaders/
+ * rayTracer.cl:111-202).  A third `Mode::CUDA` behind the same toggle (MainState.cpp:217-224)
+ * calls these entry points; INTEGRATION.md shows the binding.
+ *
+ * Conventions: plain C types only; every function returns RTB_OK (0) or an rtb_status code and
+ * never throws; the context is opaque and owned by the library; output buffers are owned by the
+ * caller; calls block until the result is where the caller asked for it (like the reference's
+ * blocking clEnqueueWriteBuffer / clEnqueueMapBuffer sequence); one context is used from one
+ * thread at a time.  There is no CPU fallback: without a CUDA device rtb_init fails with
+ * RTB_ERR_NO_DEVICE.
+ *
+ * Scene arrays have EXACTLY the layout of the OpenCL kernel's arguments (rayTracer.cl:111-114),
+ * i.e. the flattening done at MainState.cpp:646-655:
+ *   sphereOrigins  4*ns floats (x,y,z,w)      sphereRadius  ns floats     sphereColours 4*ns floats
+ *   cubeVertices   4*36*nc floats (12 triangles x 3 vertices per cube, Cube::getTriangles() order)
+ *   cubeColours    4*nc floats
+ * Colours are (r,g,b,255) with r,g,b in [0,1] as the reference stores them.
+ *
+ * Camera: the reference has one shared direction `rayDir` and an explicit origin per pixel,
+ * rayOrigins[y*W+x] = (x, y, 0, 1) (MainState.cpp:37-50).  The grid entry points take the origin
+ * grid in affine form origin(x,y) = origin0 + x*dU + y*dV (reference values: origin0=(0,0,0,1),
+ * dU=(1,0,0,0), dV=(0,1,0,0), rayDir=(0,0,-1,-1)); rtb_render_rays keeps the explicit form.
+ *
+ * Outputs (each nullable):
+ *   rgba8     4*N bytes   the (uint8_t)-narrowed frame of MainState.cpp:1023-1037, row-major, y down
+ *   prim_id   N int32     winning primitive: cubes 0..nc-1, spheres nc..nc+ns-1, -1 = miss (extension)
+ *   rgba_i32  4*N int32   the reference's `std::vector<int> pixels` stream (MainState.cpp:952-955,
+ *                         rayTracer.cl:198-201), for assignment straight into `pixels`
+ */
+#ifndef RTB_H_
+#define RTB_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rtb_ctx rtb_ctx;
+
+typedef enum rtb_status {
+    RTB_OK = 0,
+    RTB_ERR_INVALID_ARG = 1,  /* null pointer, non-positive size, ...                          */
+    RTB_ERR_NO_DEVICE = 2,    /* no usable CUDA device / device id out of range                */
+    RTB_ERR_CUDA = 3,         /* a CUDA runtime call failed; see rtb_last_error_message        */
+    RTB_ERR_NO_SCENE = 4,     /* render called before rtb_set_scene                            */
+    RTB_ERR_NOT_A_BOX = 5,    /* a cube's 36 vertices are not an affine image of Cube.cpp's    */
+    RTB_ERR_CAMERA = 6,       /* degenerate camera: dU, dV, rayDir do not span a ray grid      */
+    RTB_ERR_OUT_OF_MEMORY = 7,
+    RTB_ERR_UNSUPPORTED = 8   /* e.g. n_devices > 1 inside one process (use one process/GPU)   */
+} rtb_status;
+
+/* Replaces MainState::openCLInit (MainState.cpp:1181-1326: platform/device pick, context, queue,
+ * program build, kernel).  n_devices must be 1 (one process per GPU; multi-GPU frames are sharded
+ * by the caller with rtb_render_bands_device).  device_ids may be NULL
+ * (= device 0).  Unlike the reference, failures are reported, not printed and ignored. */
+int rtb_init(rtb_ctx** out, int n_devices, const int* device_ids);
+
+/* Replaces the four clRelease* calls of MainState::~MainState (MainState.cpp:75-78). */
+void rtb_shutdown(rtb_ctx* ctx);
+
+/* Replaces MainState::getErrorString (MainState.cpp:1101-1179). */
+const char* rtb_error_string(int status);
+
+/* Detail text of the last failure on this context (CUDA error string, offending cube index...). */
+const char* rtb_last_error_message(const rtb_ctx* ctx);
+
+/* Replaces the 6 clCreateBuffer + clEnqueueWriteBuffer pairs for the scene
+ * (MainState.cpp:677-839) and the clSetKernelArg calls 1-7 (:747-753).  The scene stays resident
+ * on the device until the next rtb_set_scene.  Arrays are copied; the caller may free them. */
+int rtb_set_scene(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins,
+                  const float* sphereRadius, const float* sphereColours, int numCubes,
+                  const float* cubeVertices, const float* cubeColours);
+
+/* Replaces the rest of MainState::executeRayTracerOpenCL (rays upload :841-851, launch :858-869,
+ * blocking read-back :876-886, pixels.assign :907): renders one width x height frame into HOST
+ * buffers.  kernel_ms (nullable) = device time of the ray-cast kernel alone; total_ms (nullable)
+ * = upload + kernel + download, the analogue of the reference's OpenCL timer (:662-894). */
+int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+               const float dV[4], const float rayDir[4], uint8_t* rgba8_out, int32_t* prim_id_out,
+               int32_t* rgba_i32_out, float* kernel_ms, float* total_ms);
+
+/* Explicit-origin form, argument-for-argument the OpenCL kernel's `rayOrigins` + `rayDir`
+ * (rayTracer.cl:111-114; MainState.cpp:841-851): n_rays origins of 4 floats each, host memory. */
+int rtb_render_rays(rtb_ctx* ctx, size_t n_rays, const float* rayOrigins, const float rayDir[4],
+                    uint8_t* rgba8_out, int32_t* prim_id_out, int32_t* rgba_i32_out,
+                    float* kernel_ms, float* total_ms);
+
+/* Device-resident variant for multi-GPU sharding and for kernel-only timing.  Renders the
+ * interleaved row bands owned by `band_rank` out of `band_world` (band b = rows
+ * [b*band_rows, (b+1)*band_rows) belongs to rank b % band_world) into PACKED device buffers:
+ * local row = (b / band_world)*band_rows + (y - b*band_rows).  band_world = 1 renders the whole
+ * frame.  band_rows must be a positive multiple of 4.  d_* are device pointers on this context's
+ * device (nullable); cuda_stream is a cudaStream_t (NULL = the context's own stream).  The call
+ * only enqueues work when cuda_stream != NULL; with the context's stream it also synchronises. */
+int rtb_render_bands_device(rtb_ctx* ctx, int width, int height, const float origin0[4],
+                            const float dU[4], const float dV[4], const float rayDir[4],
+                            int band_rows, int band_rank, int band_world, void* d_rgba8,
+                            void* d_prim_id, void* d_rgba_i32, void* cuda_stream);
+
+/* Number of local rows rank `band_rank` owns for a frame of `height` rows. */
+int rtb_band_local_rows(int height, int band_rows, int band_rank, int band_world);
+
+/* n_frames frames of the same scene with per-frame cameras (cameras = n_frames x 16 floats:
+ * origin0, dU, dV, rayDir), kept on the device: d_rgba8 receives n_frames packed frames
+ * (4*width*height bytes each).  Used for the orbit sequence (BASELINE.json config 5). */
+int rtb_render_sequence_device(rtb_ctx* ctx, int width, int height, int n_frames,
+                               const float* cameras, void* d_rgba8, float* kernel_ms_total);
+
+/* Pinned host allocations for the e2e path (pageable buffers work too, only slower). */
+int rtb_host_alloc(void** out, size_t bytes);
+void rtb_host_free(void* p);
+
+/* Introspection. */
+int rtb_device_info(const rtb_ctx* ctx, int* sm_count, int* sm_clock_khz, char* name, size_t name_cap);
+/* Kernel launches issued by this context so far (ray-cast + helper kernels). */
+unsigned long long rtb_launch_count(const rtb_ctx* ctx);
+/* Average device time (ms) of the ray-cast kernel launches since the last call with reset != 0;
+ * measured with CUDA events on the launching stream.  n_launches (nullable) receives the count. */
+float rtb_kernel_ms_avg(rtb_ctx* ctx, int reset, int* n_launches);
+
+/* Debug/test entry: runs only the host-side packer (double-precision camera-space precompute)
+ * and copies the packed records out.  cube_rec: 12 floats per cube, sphere_rec: 4 floats per
+ * sphere, cam: 8 floats.  No device work.  ctx may be NULL-device-free: see rtb_pack_only_new. */
+int rtb_debug_pack(int numSpheres, const float* sphereOrigins, const float* sphereRadius,
+                   int numCubes, const float* cubeVertices, const float origin0[4],
+                   const float dU[4], const float dV[4], const float rayDir[4], float* cube_rec,
+                   float* sphere_rec, float* cam, int* bad_cube_index);
+
+const char* rtb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTB_H_ */

@@ -1,0 +1,250 @@
+"""ctypes binding of the C ABI in include/rtb.h (librtb.so, built in-tree by build.sh).
+
+This is plumbing only: every render goes to the hand-written sm_100a kernels inside librtb.so.
+There is no fallback -- if the library is missing or no B200-class device is present the calls
+raise.  Nothing in this package imports oracle/.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "librtb.so")
+
+RTB_OK = 0
+STATUS_NAMES = {
+    0: "RTB_OK", 1: "RTB_ERR_INVALID_ARG", 2: "RTB_ERR_NO_DEVICE", 3: "RTB_ERR_CUDA",
+    4: "RTB_ERR_NO_SCENE", 5: "RTB_ERR_NOT_A_BOX", 6: "RTB_ERR_CAMERA",
+    7: "RTB_ERR_OUT_OF_MEMORY", 8: "RTB_ERR_UNSUPPORTED",
+}
+
+# every symbol include/rtb.h declares (tests check that the library exports all of them)
+EXPORTED_SYMBOLS = [
+    "rtb_init", "rtb_shutdown", "rtb_error_string", "rtb_last_error_message", "rtb_set_scene",
+    "rtb_render", "rtb_render_rays", "rtb_render_bands_device", "rtb_band_local_rows",
+    "rtb_render_sequence_device", "rtb_host_alloc", "rtb_host_free", "rtb_device_info",
+    "rtb_launch_count", "rtb_kernel_ms_avg", "rtb_debug_pack", "rtb_version",
+]
+
+
+class RtbError(RuntimeError):
+    def __init__(self, status, detail=""):
+        self.status = status
+        name = STATUS_NAMES.get(status, "RTB_ERR_%d" % status)
+        super().__init__("%s%s" % (name, (": " + detail) if detail else ""))
+
+
+_lib = None
+
+
+def load_library(path=None):
+    """Loads librtb.so; raises (loudly) when the CUDA extension has not been built."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.isfile(p):
+        raise RuntimeError("librtb.so not found at %s -- run opencl_ray_tracer_b200/build.sh "
+                           "(or __graft_entry__.build()); there is no CPU fallback" % p)
+    lib = C.CDLL(p)
+    fp, ip, vp = C.POINTER(C.c_float), C.POINTER(C.c_int32), C.c_void_p
+    lib.rtb_init.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(C.c_int)]
+    lib.rtb_shutdown.argtypes = [vp]
+    lib.rtb_shutdown.restype = None
+    lib.rtb_error_string.argtypes = [C.c_int]
+    lib.rtb_error_string.restype = C.c_char_p
+    lib.rtb_last_error_message.argtypes = [vp]
+    lib.rtb_last_error_message.restype = C.c_char_p
+    lib.rtb_set_scene.argtypes = [vp, C.c_int, fp, fp, fp, C.c_int, fp, fp]
+    lib.rtb_render.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, vp, vp, vp, fp, fp]
+    lib.rtb_render_rays.argtypes = [vp, C.c_size_t, fp, fp, vp, vp, vp, fp, fp]
+    lib.rtb_render_bands_device.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, C.c_int,
+                                            C.c_int, vp, vp, vp, vp]
+    lib.rtb_band_local_rows.argtypes = [C.c_int] * 4
+    lib.rtb_render_sequence_device.argtypes = [vp, C.c_int, C.c_int, C.c_int, fp, vp, fp]
+    lib.rtb_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
+    lib.rtb_host_free.argtypes = [vp]
+    lib.rtb_host_free.restype = None
+    lib.rtb_device_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_char_p, C.c_size_t]
+    lib.rtb_launch_count.argtypes = [vp]
+    lib.rtb_launch_count.restype = C.c_ulonglong
+    lib.rtb_kernel_ms_avg.argtypes = [vp, C.c_int, C.POINTER(C.c_int)]
+    lib.rtb_kernel_ms_avg.restype = C.c_float
+    lib.rtb_debug_pack.argtypes = [C.c_int, fp, fp, C.c_int, fp, fp, fp, fp, fp, fp, fp, fp,
+                                   C.POINTER(C.c_int)]
+    lib.rtb_version.restype = C.c_char_p
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float)) if a is not None else None
+
+
+def _vp(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else None
+
+
+# the reference's ray set-up, RayTrace/states/MainState.cpp:37-50
+REFERENCE_CAMERA = (
+    np.array([0, 0, 0, 1], np.float32),   # origin0
+    np.array([1, 0, 0, 0], np.float32),   # dU
+    np.array([0, 1, 0, 0], np.float32),   # dV
+    np.array([0, 0, -1, -1], np.float32),  # rayDir = perspective(45,4/3,0,100)*(0,0,1,1)
+)
+
+
+def debug_pack(sph_o, sph_r, cube_v, camera=REFERENCE_CAMERA):
+    """Host-side packer only (no device): returns (cube_rec[nc,3,4], sphere_rec[ns,4], cam[8])."""
+    lib = load_library()
+    sph_o, sph_r, cube_v = _f32(sph_o).reshape(-1, 4), _f32(sph_r).reshape(-1), _f32(cube_v).reshape(-1, 36, 4)
+    ns, nc = len(sph_r), len(cube_v)
+    cube_rec = np.zeros((nc, 3, 4), np.float32)
+    sph_rec = np.zeros((ns, 4), np.float32)
+    cam = np.zeros(8, np.float32)
+    bad = C.c_int(-1)
+    o0, du, dv, d = [_f32(v) for v in camera]
+    rc = lib.rtb_debug_pack(ns, _fp(sph_o), _fp(sph_r), nc, _fp(cube_v), _fp(o0), _fp(du), _fp(dv),
+                            _fp(d), _fp(cube_rec), _fp(sph_rec), _fp(cam), C.byref(bad))
+    if rc != RTB_OK:
+        raise RtbError(rc, "cube %d" % bad.value if bad.value >= 0 else "")
+    return cube_rec, sph_rec, cam
+
+
+class Context:
+    """One rtb_ctx on one device (one process per GPU)."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        self._h = C.c_void_p()
+        dev = (C.c_int * 1)(device)
+        rc = self.lib.rtb_init(C.byref(self._h), 1, dev)
+        if rc != RTB_OK:
+            self._h = C.c_void_p()
+            raise RtbError(rc, "rtb_init(device=%d)" % device)
+        self.device = device
+        self.ns = self.nc = 0
+
+    def _check(self, rc):
+        if rc != RTB_OK:
+            raise RtbError(rc, (self.lib.rtb_last_error_message(self._h) or b"").decode())
+
+    def close(self):
+        if self._h:
+            self.lib.rtb_shutdown(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def device_info(self):
+        sm, khz = C.c_int(), C.c_int()
+        name = C.create_string_buffer(128)
+        self._check(self.lib.rtb_device_info(self._h, C.byref(sm), C.byref(khz), name, 128))
+        return {"sm_count": sm.value, "sm_clock_khz": khz.value, "name": name.value.decode()}
+
+    def set_scene(self, sph_o, sph_r, sph_c, cube_v, cube_c):
+        sph_o, sph_r, sph_c = _f32(sph_o).reshape(-1, 4), _f32(sph_r).reshape(-1), _f32(sph_c).reshape(-1, 4)
+        cube_v, cube_c = _f32(cube_v).reshape(-1, 36, 4), _f32(cube_c).reshape(-1, 4)
+        self._check(self.lib.rtb_set_scene(self._h, len(sph_r), _fp(sph_o), _fp(sph_r), _fp(sph_c),
+                                           len(cube_c), _fp(cube_v), _fp(cube_c)))
+        self.ns, self.nc = len(sph_r), len(cube_c)
+
+    def render(self, width, height, camera=REFERENCE_CAMERA, want=("rgba8", "prim_id", "rgba_i32"),
+               out=None):
+        """Blocking host-buffer render (rtb_render).  Returns dict with the requested arrays plus
+        kernel_ms / total_ms.  `out` may hold preallocated arrays (e.g. pinned) keyed like `want`."""
+        o0, du, dv, d = [_f32(v) for v in camera]
+        out = dict(out or {})
+        if "rgba8" in want and "rgba8" not in out:
+            out["rgba8"] = np.empty((height, width, 4), np.uint8)
+        if "prim_id" in want and "prim_id" not in out:
+            out["prim_id"] = np.empty((height, width), np.int32)
+        if "rgba_i32" in want and "rgba_i32" not in out:
+            out["rgba_i32"] = np.empty((height, width, 4), np.int32)
+        kms, tms = C.c_float(), C.c_float()
+        self._check(self.lib.rtb_render(
+            self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d),
+            _vp(out.get("rgba8") if "rgba8" in want else None),
+            _vp(out.get("prim_id") if "prim_id" in want else None),
+            _vp(out.get("rgba_i32") if "rgba_i32" in want else None), C.byref(kms), C.byref(tms)))
+        out["kernel_ms"], out["total_ms"] = kms.value, tms.value
+        return out
+
+    def render_rays(self, origins, ray_dir, want=("rgba8", "prim_id", "rgba_i32")):
+        o = _f32(origins).reshape(-1, 4)
+        d = _f32(ray_dir)
+        n = len(o)
+        out = {}
+        if "rgba8" in want:
+            out["rgba8"] = np.empty((n, 4), np.uint8)
+        if "prim_id" in want:
+            out["prim_id"] = np.empty(n, np.int32)
+        if "rgba_i32" in want:
+            out["rgba_i32"] = np.empty((n, 4), np.int32)
+        kms, tms = C.c_float(), C.c_float()
+        self._check(self.lib.rtb_render_rays(self._h, n, _fp(o), _fp(d), _vp(out.get("rgba8")),
+                                             _vp(out.get("prim_id")), _vp(out.get("rgba_i32")),
+                                             C.byref(kms), C.byref(tms)))
+        out["kernel_ms"], out["total_ms"] = kms.value, tms.value
+        return out
+
+    def band_local_rows(self, height, band_rows, rank, world):
+        return self.lib.rtb_band_local_rows(height, band_rows, rank, world)
+
+    def render_bands_device(self, width, height, camera, band_rows, rank, world, d_rgba8=0,
+                            d_prim_id=0, d_rgba_i32=0, stream=0):
+        """Device-pointer render (ints from torch .data_ptr()); stream = cudaStream_t as int
+        (0 -> the context's own stream, synchronous)."""
+        o0, du, dv, d = [_f32(v) for v in camera]
+        self._check(self.lib.rtb_render_bands_device(
+            self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d), band_rows, rank, world,
+            C.c_void_p(d_rgba8 or None), C.c_void_p(d_prim_id or None), C.c_void_p(d_rgba_i32 or None),
+            C.c_void_p(stream or None)))
+
+    def render_sequence_device(self, width, height, cameras, d_rgba8):
+        cams = _f32(cameras).reshape(-1, 16)
+        kms = C.c_float()
+        self._check(self.lib.rtb_render_sequence_device(self._h, width, height, len(cams), _fp(cams),
+                                                        C.c_void_p(d_rgba8), C.byref(kms)))
+        return kms.value
+
+    def launch_count(self):
+        return int(self.lib.rtb_launch_count(self._h))
+
+    def kernel_ms_avg(self, reset=True):
+        n = C.c_int()
+        avg = self.lib.rtb_kernel_ms_avg(self._h, 1 if reset else 0, C.byref(n))
+        return float(avg), n.value
+
+
+def host_alloc(nbytes):
+    """Pinned host buffer as a uint8 numpy array (freed with host_free)."""
+    lib = load_library()
+    p = C.c_void_p()
+    rc = lib.rtb_host_alloc(C.byref(p), nbytes)
+    if rc != RTB_OK:
+        raise RtbError(rc, "rtb_host_alloc")
+    buf = (C.c_uint8 * nbytes).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=np.uint8)
+    arr_ptr = p.value
+    return arr, arr_ptr
+
+
+def host_free(ptr):
+    load_library().rtb_host_free(C.c_void_p(ptr))

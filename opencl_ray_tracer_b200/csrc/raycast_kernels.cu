@@ -1,0 +1,333 @@
+// raycast_kernels.cu -- hand-written sm_100a kernels of the ray-cast path.
+//
+// raycast_grid_kernel replaces the OpenCL kernel `rayTracer`
+// (RayTrace/resources/shaders/rayTracer.cl:111-202) and, result-wise, the CPU loop
+// MainState::executeRayTracerCPU -> collide (RayTrace/states/MainState.cpp:936-956, :330-408).
+//
+// Mapping: one warp = an 8x4 lane tile, each lane owns PX horizontally adjacent
+// pixels (one primary ray each), so a warp covers (8*PX) x 4 pixels and a lane's PX RGBA8 results
+// leave as 128-bit stores.  The packed primitive records (16 B each) are staged global->shared
+// in 12 KB chunks with 1-D TMA bulk copies (cp.async.bulk + mbarrier complete_tx), double
+// buffered, and read back as warp-uniform LDS.128 broadcasts.  Per pixel and cube: 6 FFMA/FADD
+// class instructions + 2 FMNMX3 + 1 FSETP; per pixel and sphere: 1 FADD + 1 FFMA + 1 FSETP.  The
+// nearest-hit update (and the sphere's sqrt) sits behind a per-thread branch that is only taken
+// when one of the thread's PX rays actually hits the primitive.
+//
+// Compiled with -fmad=false: every FMA is an explicit fmaf() from raycast_math.h so the scalar
+// emulator in tests/emu reproduces the kernel bit for bit.
+#include "raycast_kernels.cuh"
+
+namespace rtb {
+
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+// 1-D TMA bulk copy global -> shared, completion signalled on the mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(addr), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+
+template <int PX>
+struct PixelState {
+    float u[PX];
+    float best[PX];
+    int id[PX];
+};
+
+// All cubes of one staged chunk against this thread's PX pixels.
+template <int PX>
+__device__ __forceinline__ void cubes_chunk(const float4* __restrict__ rec, int count, int first_id, float v,
+                                            PixelState<PX>& st) {
+#pragma unroll 2
+    for (int c = 0; c < count; ++c) {
+        const float4 r0 = rec[3 * c + 0], r1 = rec[3 * c + 1], r2 = rec[3 * c + 2];
+        const RtbSlab s0 = {r0.x, r0.y, r0.z, r0.w}, s1 = {r1.x, r1.y, r1.z, r1.w}, s2 = {r2.x, r2.y, r2.z, r2.w};
+        const float b0 = rtb_slab_base(s0, v), b1 = rtb_slab_base(s1, v), b2 = rtb_slab_base(s2, v);
+        float tn[PX], tf[PX];
+        bool any = false;
+#pragma unroll
+        for (int p = 0; p < PX; ++p) {
+            const float n0 = rtb_slab_near(s0, b0, st.u[p]);
+            const float n1 = rtb_slab_near(s1, b1, st.u[p]);
+            const float n2 = rtb_slab_near(s2, b2, st.u[p]);
+            const float f0 = n0 + s0.width, f1 = n1 + s1.width, f2 = n2 + s2.width;
+            tn[p] = fmaxf(fmaxf(n0, n1), n2);  // FMNMX3
+            tf[p] = fminf(fminf(f0, f1), f2);  // FMNMX3
+            any |= (tn[p] <= tf[p]);
+        }
+        if (any) {
+#pragma unroll
+            for (int p = 0; p < PX; ++p) rtb_cube_update(tn[p], tf[p], first_id + c, st.best[p], st.id[p]);
+        }
+    }
+}
+
+template <int PX>
+__device__ __forceinline__ void spheres_chunk(const float4* __restrict__ rec, int count, int first_id, float v,
+                                              const RtbCam& cam, PixelState<PX>& st) {
+#pragma unroll 4
+    for (int s = 0; s < count; ++s) {
+        const float4 r = rec[s];
+        const RtbSphere sp = {r.x, r.y, r.z, r.w};
+        const float radv = rtb_sphere_radv(sp, v);
+        float rad[PX];
+        bool any = false;
+#pragma unroll
+        for (int p = 0; p < PX; ++p) {
+            rad[p] = rtb_sphere_rad(sp, radv, st.u[p]);
+            any |= (rad[p] >= 0.0f);
+        }
+        if (any) {
+            const float wv = cam.tau_v * v;
+#pragma unroll
+            for (int p = 0; p < PX; ++p) {
+                const float wpix = fmaf(cam.tau_u, st.u[p], wv);
+                rtb_sphere_update(sp, rad[p], wpix, first_id + s, st.best[p], st.id[p]);
+            }
+        }
+    }
+}
+
+template <int PX, int WARPS_X, int WARPS_Y>
+__global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y)
+raycast_grid_kernel(const GridParams p) {
+    constexpr int kThreads = 32 * WARPS_X * WARPS_Y;
+    constexpr int kTileW = WARPS_X * 8 * PX;
+    constexpr int kTileH = WARPS_Y * 4;
+    __shared__ __align__(128) float4 stage[2][kChunkRecords];
+    __shared__ __align__(8) uint64_t full_bar[2];
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int wx = warp % WARPS_X, wy = warp / WARPS_X;
+    const int lx = lane & 7, ly = lane >> 3;
+    const int x0 = blockIdx.x * kTileW + (wx * 8 + lx) * PX;
+    const int lrow = blockIdx.y * kTileH + wy * 4 + ly;  // row in the packed (local) output
+    // interleaved row bands: local band lb -> global band lb*world + rank
+    const int lb = lrow / p.band_rows;
+    const int gy = (lb * p.band_world + p.band_rank) * p.band_rows + (lrow - lb * p.band_rows);
+
+    const int n_cube_chunks = (p.n_cubes + kCubesPerChunk - 1) / kCubesPerChunk;
+    const int n_sph_chunks = (p.n_spheres + kSpheresPerChunk - 1) / kSpheresPerChunk;
+    const int n_chunks = n_cube_chunks + n_sph_chunks;
+
+    auto issue = [&](int k) {  // called by thread 0 only
+        const int b = k & 1;
+        const void* src;
+        uint32_t bytes;
+        if (k < n_cube_chunks) {
+            const int first = k * kCubesPerChunk;
+            const int cnt = min(kCubesPerChunk, p.n_cubes - first);
+            src = p.cube_rec + 3 * (size_t)first;
+            bytes = (uint32_t)cnt * 48u;
+        } else {
+            const int first = (k - n_cube_chunks) * kSpheresPerChunk;
+            const int cnt = min(kSpheresPerChunk, p.n_spheres - first);
+            src = p.sph_rec + first;
+            bytes = (uint32_t)cnt * 16u;
+        }
+        mbar_arrive_expect_tx(&full_bar[b], bytes);
+        bulk_g2s(&stage[b][0], src, bytes, &full_bar[b]);
+    };
+
+    if (tid == 0) {
+        mbar_init(&full_bar[0], 1);
+        mbar_init(&full_bar[1], 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        if (n_chunks > 0) issue(0);
+        if (n_chunks > 1) issue(1);
+    }
+
+    PixelState<PX> st;
+    const float fy = (float)gy;
+    const float v = rtb_cam_v(p.cam, fy);
+#pragma unroll
+    for (int q = 0; q < PX; ++q) {
+        st.u[q] = rtb_cam_u(p.cam, (float)(x0 + q), fy);
+        st.best[q] = RTB_MISS_T;
+        st.id[q] = -1;
+    }
+
+    for (int k = 0; k < n_chunks; ++k) {
+        const int b = k & 1;
+        mbar_wait(&full_bar[b], (uint32_t)((k >> 1) & 1));
+        if (k < n_cube_chunks) {
+            const int first = k * kCubesPerChunk;
+            cubes_chunk<PX>(&stage[b][0], min(kCubesPerChunk, p.n_cubes - first), first, v, st);
+        } else {
+            const int first = (k - n_cube_chunks) * kSpheresPerChunk;
+            spheres_chunk<PX>(&stage[b][0], min(kSpheresPerChunk, p.n_spheres - first), p.n_cubes + first, v,
+                              p.cam, st);
+        }
+        if (k + 2 < n_chunks) {
+            __syncthreads();  // every warp is done reading stage[b] before TMA refills it
+            if (tid == 0) issue(k + 2);
+        }
+    }
+
+    // ---- nearest-hit shading + stores -------------------------------------------------------
+    if (lrow >= p.local_rows || gy >= p.height || x0 >= p.width) return;
+    uint32_t rgba8[PX];
+    int32_t rgba[PX][4];
+#pragma unroll
+    for (int q = 0; q < PX; ++q) {
+        float cr = 0.f, cg = 0.f, cb = 0.f;
+        if (st.best[q] == RTB_MISS_T) st.id[q] = -1;
+        if (st.id[q] >= 0) {
+            const float4 col = (st.id[q] < p.n_cubes) ? __ldg(p.cube_col + st.id[q])
+                                                      : __ldg(p.sph_col + (st.id[q] - p.n_cubes));
+            cr = col.x; cg = col.y; cb = col.z;
+        }
+        rtb_shade(st.best[q], cr, cg, cb, rgba[q]);
+        rgba8[q] = rtb_pack_rgba8(rgba[q]);
+    }
+    const size_t row_off = (size_t)lrow * p.width;
+    const bool full = p.vec_ok && (x0 + PX <= p.width);
+    if (full) {
+        if (p.out_rgba8) {
+#pragma unroll
+            for (int q = 0; q < PX; q += 4)
+                *reinterpret_cast<uint4*>(p.out_rgba8 + row_off + x0 + q) =
+                    make_uint4(rgba8[q], rgba8[q + 1], rgba8[q + 2], rgba8[q + 3]);
+        }
+        if (p.out_id) {
+#pragma unroll
+            for (int q = 0; q < PX; q += 4)
+                *reinterpret_cast<int4*>(p.out_id + row_off + x0 + q) =
+                    make_int4(st.id[q], st.id[q + 1], st.id[q + 2], st.id[q + 3]);
+        }
+        if (p.out_i32) {
+#pragma unroll
+            for (int q = 0; q < PX; ++q)
+                p.out_i32[row_off + x0 + q] = make_int4(rgba[q][0], rgba[q][1], rgba[q][2], rgba[q][3]);
+        }
+    } else {
+#pragma unroll
+        for (int q = 0; q < PX; ++q) {
+            if (x0 + q < p.width) {
+                if (p.out_rgba8) p.out_rgba8[row_off + x0 + q] = rgba8[q];
+                if (p.out_id) p.out_id[row_off + x0 + q] = st.id[q];
+                if (p.out_i32) {
+                    int32_t* o = reinterpret_cast<int32_t*>(p.out_i32) + 4 * (row_off + x0 + q);
+                    o[0] = rgba[q][0]; o[1] = rgba[q][1]; o[2] = rgba[q][2]; o[3] = rgba[q][3];
+                }
+            }
+        }
+    }
+}
+
+}  // namespace
+
+// ---- explicit-origin kernel (rtb_render_rays) --------------------------------------------------
+// Argument-for-argument the OpenCL kernel's rayOrigins[] + rayDir form (rayTracer.cl:111-120).
+// One thread per ray; world-space slab records; spheres use the reference's float formula in
+// the reference's operation order (bit-identical to MainState::intersectSphere).
+namespace {
+
+__global__ void __launch_bounds__(256) raycast_rays_kernel(const RaysParams p) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n_rays) return;
+    const float4 o = __ldg(p.origins + i);
+    float best = RTB_MISS_T;
+    int id = -1;
+    for (int c = 0; c < p.n_cubes; ++c) {
+        const float4 r0 = __ldg(p.cube_rec + 4 * c + 0), r1 = __ldg(p.cube_rec + 4 * c + 1),
+                     r2 = __ldg(p.cube_rec + 4 * c + 2), w = __ldg(p.cube_rec + 4 * c + 3);
+        const float n0 = fmaf(r0.x, o.x, fmaf(r0.y, o.y, fmaf(r0.z, o.z, r0.w)));
+        const float n1 = fmaf(r1.x, o.x, fmaf(r1.y, o.y, fmaf(r1.z, o.z, r1.w)));
+        const float n2 = fmaf(r2.x, o.x, fmaf(r2.y, o.y, fmaf(r2.z, o.z, r2.w)));
+        const float tn = fmaxf(fmaxf(n0, n1), n2);
+        const float tf = fminf(fminf(n0 + w.x, n1 + w.y), n2 + w.z);
+        rtb_cube_update(tn, tf, c, best, id);
+    }
+    const float o4[4] = {o.x, o.y, o.z, o.w};
+    for (int s = 0; s < p.n_spheres; ++s) {
+        const float4 c4 = __ldg(p.sph_rec + 2 * s), q = __ldg(p.sph_rec + 2 * s + 1);
+        const float cc[4] = {c4.x, c4.y, c4.z, c4.w};
+        const float t0 = rtb_sphere_t_reference(o4, p.dir, q.x, cc);
+        if (t0 != 0.0f && t0 < best) { best = t0; id = p.n_cubes + s; }
+    }
+    float cr = 0.f, cg = 0.f, cb = 0.f;
+    if (best == RTB_MISS_T) id = -1;
+    if (id >= 0) {
+        const float4 col = (id < p.n_cubes) ? __ldg(p.cube_col + id) : __ldg(p.sph_col + (id - p.n_cubes));
+        cr = col.x; cg = col.y; cb = col.z;
+    }
+    int32_t rgba[4];
+    rtb_shade(best, cr, cg, cb, rgba);
+    if (p.out_rgba8) p.out_rgba8[i] = rtb_pack_rgba8(rgba);
+    if (p.out_id) p.out_id[i] = id;
+    if (p.out_i32) p.out_i32[i] = make_int4(rgba[0], rgba[1], rgba[2], rgba[3]);
+}
+
+template <int PX, int WX, int WY>
+GridLaunchShape shape_of(int width, int local_rows) {
+    GridLaunchShape s;
+    s.px = PX;
+    s.block = dim3(32 * WX * WY);
+    const int tw = WX * 8 * PX, th = WY * 4;
+    s.grid = dim3((width + tw - 1) / tw, (local_rows + th - 1) / th);
+    s.smem = 0;
+    return s;
+}
+
+}  // namespace
+
+GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
+    GridLaunchShape big = shape_of<8, 2, 4>(width, local_rows);
+    if ((long long)big.grid.x * big.grid.y >= 2LL * sm_count) return big;
+    return shape_of<4, 2, 2>(width, local_rows);
+}
+
+cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) {
+    const GridLaunchShape s = grid_launch_shape(p.width, p.local_rows, sm_count);
+    if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
+    if (s.px == 8)
+        raycast_grid_kernel<8, 2, 4><<<s.grid, s.block, 0, stream>>>(p);
+    else
+        raycast_grid_kernel<4, 2, 2><<<s.grid, s.block, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rays(const RaysParams& p, cudaStream_t stream) {
+    if (p.n_rays == 0) return cudaSuccess;
+    const unsigned blocks = (unsigned)((p.n_rays + 255) / 256);
+    raycast_rays_kernel<<<blocks, 256, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t configure_kernels() { return cudaSuccess; }
+
+}  // namespace rtb

@@ -1,0 +1,58 @@
+// raycast_kernels.cuh -- launch interface between the C ABI (rtb_api.cu) and the sm_100a kernels.
+#ifndef RTB_RAYCAST_KERNELS_CUH_
+#define RTB_RAYCAST_KERNELS_CUH_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "raycast_math.h"
+
+namespace rtb {
+
+// Records per staged shared-memory chunk (16 B each): 768 records = 12 KB = 256 cubes or 768 spheres.
+constexpr int kChunkRecords = 768;
+constexpr int kCubesPerChunk = kChunkRecords / 3;
+constexpr int kSpheresPerChunk = kChunkRecords;
+
+struct GridParams {
+    int width, height;                      // full frame
+    int band_rows, band_rank, band_world;   // interleaved row bands (band_world == 1: whole frame)
+    int local_rows;                         // rows this launch renders = rows of the packed outputs
+    int n_cubes, n_spheres;
+    const float4* cube_rec;                 // 3 RtbSlab per cube
+    const float4* sph_rec;                  // 1 RtbSphere per sphere
+    const float4* cube_col;                 // (r,g,b,255)
+    const float4* sph_col;
+    uint32_t* out_rgba8;                    // nullable, local_rows*width
+    int32_t* out_id;                        // nullable
+    int4* out_i32;                          // nullable
+    int vec_ok;                             // outputs 16-byte aligned and width % 4 == 0
+    RtbCam cam;
+};
+
+// Explicit-origin ("rays") form: world-space records, one thread per ray.
+struct RaysParams {
+    size_t n_rays;
+    const float4* origins;                  // n_rays
+    float dir[4];
+    int n_cubes, n_spheres;
+    const float4* cube_rec;                 // 4 float4 per cube: 3 x (nx,ny,nz,alpha) + (w0,w1,w2,0)
+    const float4* sph_rec;                  // 2 float4 per sphere: centre(4) + (r2, 0,0,0)
+    const float4* cube_col;
+    const float4* sph_col;
+    uint32_t* out_rgba8;
+    int32_t* out_id;
+    int4* out_i32;
+};
+
+// Tile geometry of the grid kernel variant chosen for a frame.
+struct GridLaunchShape { int px; dim3 grid, block; size_t smem; };
+
+GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count);
+cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream);
+cudaError_t launch_rays(const RaysParams& p, cudaStream_t stream);
+cudaError_t configure_kernels();  // one-time cudaFuncSetAttribute calls
+
+}  // namespace rtb
+
+#endif

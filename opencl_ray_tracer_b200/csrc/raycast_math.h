@@ -1,0 +1,116 @@
+// raycast_math.h -- per-pixel arithmetic of the B200 ray-cast path, shared verbatim between the
+// CUDA kernels (raycast_kernels.cu) and the test-only scalar emulator (tests/emu/).  Everything
+// here is written with explicit fmaf() and is compiled with FMA contraction OFF on both sides
+// (nvcc -fmad=false, g++ -ffp-contract=off), with IEEE divide and sqrt, so the emulator and the
+// kernel produce bit-identical pixels.
+//
+// Formulation.  All rays of a frame are parallel (one shared rayDir,
+// RayTrace/states/MainState.cpp:37-39) and their origins form an affine pixel grid
+// (:41-50), so every per-primitive quantity the reference evaluates per ray is a polynomial in
+// the pixel coordinates.  The host (scene_pack.cpp) changes variables to camera coordinates
+//   u = l11*x + l12*y,  v = l22*y
+// in which
+//   sphere i (MainState.cpp:300-327):  r^2 - d^2 = rho_i - (uc_i-u)^2 - (vc_i-v)^2,
+//                                      tca = tau0_i - (tau_u*u + tau_v*v)
+//   cube c   (MainState.cpp:347-377):  min over its 12 triangles of the line parameter t
+//                                      = max_k near_k,  hit iff max_k near_k <= min_k far_k,
+//                                      near_k = alpha_k + beta_k*u + gamma_k*v, far_k = near_k + w_k
+//                                      (slab test on the parallelepiped spanned by the cube's
+//                                      vertices; edges inclusive, t may be negative, as in
+//                                      intersectTri which has no t>0 rejection).
+#ifndef RTB_RAYCAST_MATH_H_
+#define RTB_RAYCAST_MATH_H_
+
+#include <math.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define RTB_HD __host__ __device__ __forceinline__
+#else
+#define RTB_HD inline
+#endif
+
+#define RTB_MISS_T 300000.0f  // `closest` sentinel, MainState.cpp:345
+
+// Camera constants for one frame (8 floats).
+struct RtbCam {
+    float l11, l12, l22;  // u = l11*x + l12*y, v = l22*y
+    float tau_u, tau_v;   // ray-origin offset along rayDir: wpix = tau_u*u + tau_v*v
+    float pad0, pad1, pad2;
+};
+
+// One cube = 3 slab records; one sphere = 1 record.  16 bytes each (one LDS.128).
+struct RtbSlab { float alpha, beta, gamma, width; };
+struct RtbSphere { float uc, vc, rho, tau0; };
+
+RTB_HD float rtb_cam_u(const RtbCam& c, float x, float y) { return fmaf(c.l11, x, c.l12 * y); }
+RTB_HD float rtb_cam_v(const RtbCam& c, float y) { return c.l22 * y; }
+
+// slab: base = alpha + gamma*v (shared by all pixels of a row), near = base + beta*u
+RTB_HD float rtb_slab_base(const RtbSlab& s, float v) { return fmaf(s.gamma, v, s.alpha); }
+RTB_HD float rtb_slab_near(const RtbSlab& s, float base, float u) { return fmaf(s.beta, u, base); }
+
+// sphere: radv = rho - (vc-v)^2 (shared by a row), rad = radv - (uc-u)^2 = r^2 - d^2
+RTB_HD float rtb_sphere_radv(const RtbSphere& s, float v) {
+    const float dv = s.vc - v;
+    return fmaf(-dv, dv, s.rho);
+}
+RTB_HD float rtb_sphere_rad(const RtbSphere& s, float radv, float u) {
+    const float du = s.uc - u;
+    return fmaf(-du, du, radv);
+}
+
+// Nearest-hit update for one cube on one pixel: strict '<' so the lowest index wins ties
+// (MainState.cpp:370-374); the slab bounds are inclusive like the reference's u,v tests (:282-291).
+RTB_HD void rtb_cube_update(float tn, float tf, int id, float& best, int& best_id) {
+    if (tn <= tf && tn < best) { best = tn; best_id = id; }
+}
+
+// Sphere update, MainState.cpp:300-327 and :382-393: needs rad >= 0 (d^2 <= r^2), tca >= 0,
+// t0 != 0 (0.0f is the reference's miss value), t0 < closest.  t0 < 0 (origin inside) is kept.
+RTB_HD void rtb_sphere_update(const RtbSphere& s, float rad, float wpix, int id, float& best,
+                              int& best_id) {
+    if (rad >= 0.0f) {
+        const float tca = s.tau0 - wpix;
+        if (tca >= 0.0f) {
+            const float t0 = tca - sqrtf(rad);
+            if (t0 != 0.0f && t0 < best) { best = t0; best_id = id; }
+        }
+    }
+}
+
+// The reference's float sphere test in the reference's operation order (MainState.cpp:300-327,
+// glm::dot order (x+y)+(z+w), glm/detail/func_geometric.inl:75-82); 0.0f = miss.  Used by the
+// explicit-origin kernel, where no per-frame precompute is possible.  Needs contraction OFF.
+RTB_HD float rtb_sphere_t_reference(const float o[4], const float d[4], float radius, const float c[4]) {
+    const float lx = c[0] - o[0], ly = c[1] - o[1], lz = c[2] - o[2], lw = c[3] - o[3];
+    const float tca = (lx * d[0] + ly * d[1]) + (lz * d[2] + lw * d[3]);
+    if (tca < 0.0f) return 0.0f;
+    const float d2 = ((lx * lx + ly * ly) + (lz * lz + lw * lw)) - tca * tca;
+    const float r2 = radius * radius;
+    if (d2 > r2) return 0.0f;
+    return tca - sqrtf(r2 - d2);
+}
+
+// Depth-fog shade + (int) truncation, MainState.cpp:397-407, misc/Utility.cpp:109-116,
+// MainState.cpp:952-955.  Same operation order as the reference; no contraction.
+RTB_HD void rtb_shade(float closest, float cr, float cg, float cb, int32_t out[4]) {
+    if (closest == RTB_MISS_T) {
+        out[0] = 0; out[1] = 0; out[2] = 0; out[3] = 255;
+        return;
+    }
+    const float norm = (closest - 0.0f) / (180.0f - 0.0f);
+    const float k = 255.0f - (norm * 255.0f);
+    out[0] = (int32_t)(k * cr);
+    out[1] = (int32_t)(k * cg);
+    out[2] = (int32_t)(k * cb);
+    out[3] = 255;
+}
+
+// (uint8_t) narrowing of MainState.cpp:1023-1037, packed little-endian R,G,B,A.
+RTB_HD uint32_t rtb_pack_rgba8(const int32_t c[4]) {
+    return ((uint32_t)c[0] & 0xFFu) | (((uint32_t)c[1] & 0xFFu) << 8) |
+           (((uint32_t)c[2] & 0xFFu) << 16) | (((uint32_t)c[3] & 0xFFu) << 24);
+}
+
+#endif  // RTB_RAYCAST_MATH_H_

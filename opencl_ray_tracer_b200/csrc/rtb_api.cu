@@ -1,0 +1,553 @@
+// rtb_api.cu -- implementation of the C ABI declared in include/rtb.h.
+//
+// Host-side replacement for MainState::openCLInit / executeRayTracerOpenCL
+// (RayTrace/states/MainState.cpp:1181-1326, :641-934): device pick, resident scene buffers,
+// per-frame camera-space pack (scene_pack.cpp), kernel launch (raycast_kernels.cu), read-back.
+// There is NO CPU path in this library.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/rtb.h"
+#include "raycast_kernels.cuh"
+#include "scene_pack.h"
+
+using namespace rtb;
+
+struct EventPair { cudaEvent_t a, b; };
+
+struct rtb_ctx {
+    int device = 0;
+    int sm_count = 0;
+    int clock_khz = 0;
+    char name[128] = {0};
+    cudaStream_t stream = nullptr;
+    std::string last_error;
+
+    // scene (host copies, reference layout) + recovered boxes
+    bool have_scene = false;
+    int ns = 0, nc = 0;
+    std::vector<float> sph_o, sph_r;
+    std::vector<Box> boxes;
+    std::vector<float> cube_v;  // kept for rtb_render_rays-free re-validation/debug
+
+    // device buffers
+    float4* d_cube_col = nullptr;
+    float4* d_sph_col = nullptr;
+    float4* d_rec = nullptr;       // per-frame packed records (cubes then spheres), grow-only
+    size_t d_rec_cap = 0;          // in float4
+    float4* h_rec = nullptr;       // pinned staging for the records
+    size_t h_rec_cap = 0;
+    void* d_out[3] = {nullptr, nullptr, nullptr};  // rgba8, id, i32 frame buffers, grow-only
+    size_t d_out_cap[3] = {0, 0, 0};
+    float4* d_origins = nullptr;   // rays path
+    size_t d_origins_cap = 0;
+
+    // timing / accounting
+    cudaEvent_t ev_total0 = nullptr, ev_total1 = nullptr;
+    cudaEvent_t ev_rec = nullptr;  // last upload out of the pinned record staging area
+    std::vector<EventPair> ev_free, ev_pending;
+    double kernel_ms_sum = 0.0;
+    int kernel_ms_n = 0;
+    unsigned long long launches = 0;
+};
+
+namespace {
+
+int fail(rtb_ctx* ctx, int status, const std::string& msg) {
+    if (ctx) ctx->last_error = msg;
+    return status;
+}
+
+#define RTB_CUDA(ctx, call)                                                                   \
+    do {                                                                                      \
+        cudaError_t e__ = (call);                                                             \
+        if (e__ != cudaSuccess) {                                                             \
+            const int st__ = (e__ == cudaErrorMemoryAllocation) ? RTB_ERR_OUT_OF_MEMORY : RTB_ERR_CUDA; \
+            return fail(ctx, st__, std::string(#call) + ": " + cudaGetErrorString(e__));      \
+        }                                                                                     \
+    } while (0)
+
+int ensure_device(rtb_ctx* ctx, void** p, size_t* cap, size_t need_bytes) {
+    if (*cap >= need_bytes) return RTB_OK;
+    if (*p) RTB_CUDA(ctx, cudaFree(*p));
+    *p = nullptr;
+    *cap = 0;
+    RTB_CUDA(ctx, cudaMalloc(p, need_bytes));
+    *cap = need_bytes;
+    return RTB_OK;
+}
+
+int ensure_records(rtb_ctx* ctx, size_t n_float4) {
+    if (n_float4 == 0) n_float4 = 1;
+    if (ctx->d_rec_cap < n_float4) {
+        if (ctx->d_rec) RTB_CUDA(ctx, cudaFree(ctx->d_rec));
+        ctx->d_rec = nullptr;
+        RTB_CUDA(ctx, cudaMalloc(&ctx->d_rec, n_float4 * sizeof(float4)));
+        ctx->d_rec_cap = n_float4;
+    }
+    if (ctx->h_rec_cap < n_float4) {
+        if (ctx->h_rec) RTB_CUDA(ctx, cudaFreeHost(ctx->h_rec));
+        ctx->h_rec = nullptr;
+        RTB_CUDA(ctx, cudaMallocHost(&ctx->h_rec, n_float4 * sizeof(float4)));
+        ctx->h_rec_cap = n_float4;
+    }
+    return RTB_OK;
+}
+
+// Event pairs for per-launch kernel timing on whatever stream the launch goes to.
+int take_events(rtb_ctx* ctx, EventPair* out) {
+    if (ctx->ev_free.empty()) {
+        EventPair e;
+        RTB_CUDA(ctx, cudaEventCreate(&e.a));
+        RTB_CUDA(ctx, cudaEventCreate(&e.b));
+        ctx->ev_free.push_back(e);
+    }
+    *out = ctx->ev_free.back();
+    ctx->ev_free.pop_back();
+    return RTB_OK;
+}
+
+int resolve_pending(rtb_ctx* ctx) {
+    for (const EventPair& e : ctx->ev_pending) {
+        RTB_CUDA(ctx, cudaEventSynchronize(e.b));
+        float ms = 0.f;
+        RTB_CUDA(ctx, cudaEventElapsedTime(&ms, e.a, e.b));
+        ctx->kernel_ms_sum += ms;
+        ctx->kernel_ms_n += 1;
+        ctx->ev_free.push_back(e);
+    }
+    ctx->ev_pending.clear();
+    return RTB_OK;
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+}  // namespace
+
+extern "C" {
+
+const char* rtb_version(void) { return "rtb 0.1 (sm_100a)"; }
+
+const char* rtb_error_string(int status) {
+    switch (status) {
+        case RTB_OK: return "RTB_OK";
+        case RTB_ERR_INVALID_ARG: return "RTB_ERR_INVALID_ARG";
+        case RTB_ERR_NO_DEVICE: return "RTB_ERR_NO_DEVICE";
+        case RTB_ERR_CUDA: return "RTB_ERR_CUDA";
+        case RTB_ERR_NO_SCENE: return "RTB_ERR_NO_SCENE";
+        case RTB_ERR_NOT_A_BOX: return "RTB_ERR_NOT_A_BOX";
+        case RTB_ERR_CAMERA: return "RTB_ERR_CAMERA";
+        case RTB_ERR_OUT_OF_MEMORY: return "RTB_ERR_OUT_OF_MEMORY";
+        case RTB_ERR_UNSUPPORTED: return "RTB_ERR_UNSUPPORTED";
+        default: return "RTB_ERR_UNKNOWN";
+    }
+}
+
+const char* rtb_last_error_message(const rtb_ctx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
+
+int rtb_init(rtb_ctx** out, int n_devices, const int* device_ids) {
+    if (!out) return RTB_ERR_INVALID_ARG;
+    *out = nullptr;
+    if (n_devices < 1) return RTB_ERR_INVALID_ARG;
+    if (n_devices > 1) return RTB_ERR_UNSUPPORTED;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) return RTB_ERR_NO_DEVICE;
+    const int dev = device_ids ? device_ids[0] : 0;
+    if (dev < 0 || dev >= count) return RTB_ERR_NO_DEVICE;
+    if (cudaSetDevice(dev) != cudaSuccess) return RTB_ERR_NO_DEVICE;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return RTB_ERR_CUDA;
+    if (prop.major < 10) return RTB_ERR_NO_DEVICE;  // sm_100a binary only
+    rtb_ctx* ctx = new (std::nothrow) rtb_ctx();
+    if (!ctx) return RTB_ERR_OUT_OF_MEMORY;
+    ctx->device = dev;
+    ctx->sm_count = prop.multiProcessorCount;
+    cudaDeviceGetAttribute(&ctx->clock_khz, cudaDevAttrClockRate, dev);
+    std::snprintf(ctx->name, sizeof ctx->name, "%s", prop.name);
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&ctx->ev_total0) != cudaSuccess || cudaEventCreate(&ctx->ev_total1) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_rec, cudaEventDisableTiming) != cudaSuccess ||
+        configure_kernels() != cudaSuccess) {
+        rtb_shutdown(ctx);
+        return RTB_ERR_CUDA;
+    }
+    *out = ctx;
+    return RTB_OK;
+}
+
+void rtb_shutdown(rtb_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (const EventPair& e : ctx->ev_pending) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    for (const EventPair& e : ctx->ev_free) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    if (ctx->ev_total0) cudaEventDestroy(ctx->ev_total0);
+    if (ctx->ev_total1) cudaEventDestroy(ctx->ev_total1);
+    if (ctx->ev_rec) cudaEventDestroy(ctx->ev_rec);
+    cudaFree(ctx->d_cube_col);
+    cudaFree(ctx->d_sph_col);
+    cudaFree(ctx->d_rec);
+    if (ctx->h_rec) cudaFreeHost(ctx->h_rec);
+    for (int i = 0; i < 3; ++i) cudaFree(ctx->d_out[i]);
+    cudaFree(ctx->d_origins);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int rtb_set_scene(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins, const float* sphereRadius,
+                  const float* sphereColours, int numCubes, const float* cubeVertices,
+                  const float* cubeColours) {
+    if (!ctx) return RTB_ERR_INVALID_ARG;
+    if (numSpheres < 0 || numCubes < 0) return fail(ctx, RTB_ERR_INVALID_ARG, "negative primitive count");
+    if (numSpheres > 0 && (!sphereOrigins || !sphereRadius || !sphereColours))
+        return fail(ctx, RTB_ERR_INVALID_ARG, "null sphere array");
+    if (numCubes > 0 && (!cubeVertices || !cubeColours)) return fail(ctx, RTB_ERR_INVALID_ARG, "null cube array");
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    std::vector<Box> boxes((size_t)numCubes);
+    for (int c = 0; c < numCubes; ++c) {
+        if (!box_from_vertices(cubeVertices + (size_t)c * 144, &boxes[c])) {
+            char buf[160];
+            std::snprintf(buf, sizeof buf,
+                          "cube %d: its 36 vertices are not an affine image of the Cube.cpp vertex list", c);
+            return fail(ctx, RTB_ERR_NOT_A_BOX, buf);
+        }
+    }
+    ctx->have_scene = false;
+    RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->d_cube_col);
+    cudaFree(ctx->d_sph_col);
+    ctx->d_cube_col = ctx->d_sph_col = nullptr;
+    RTB_CUDA(ctx, cudaMalloc(&ctx->d_cube_col, sizeof(float4) * (size_t)(numCubes > 0 ? numCubes : 1)));
+    RTB_CUDA(ctx, cudaMalloc(&ctx->d_sph_col, sizeof(float4) * (size_t)(numSpheres > 0 ? numSpheres : 1)));
+    if (numCubes > 0)
+        RTB_CUDA(ctx, cudaMemcpy(ctx->d_cube_col, cubeColours, sizeof(float4) * (size_t)numCubes,
+                                 cudaMemcpyHostToDevice));
+    if (numSpheres > 0)
+        RTB_CUDA(ctx, cudaMemcpy(ctx->d_sph_col, sphereColours, sizeof(float4) * (size_t)numSpheres,
+                                 cudaMemcpyHostToDevice));
+    ctx->ns = numSpheres;
+    ctx->nc = numCubes;
+    ctx->boxes.swap(boxes);
+    ctx->sph_o.assign(sphereOrigins, sphereOrigins + 4 * (size_t)numSpheres);
+    ctx->sph_r.assign(sphereRadius, sphereRadius + (size_t)numSpheres);
+    const int rc = ensure_records(ctx, 4 * (size_t)numCubes + 2 * (size_t)numSpheres);
+    if (rc != RTB_OK) return rc;
+    ctx->have_scene = true;
+    return RTB_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+// Packs one frame's records (3 per cube, then 1 per sphere) into dst (host).
+void pack_frame(const rtb_ctx* ctx, const CameraFrame& cf, float4* dst) {
+    RtbSlab* slabs = reinterpret_cast<RtbSlab*>(dst);
+    for (int c = 0; c < ctx->nc; ++c) pack_box(cf, ctx->boxes[c], slabs + 3 * (size_t)c);
+    RtbSphere* sph = reinterpret_cast<RtbSphere*>(dst + 3 * (size_t)ctx->nc);
+    for (int s = 0; s < ctx->ns; ++s) pack_sphere(cf, &ctx->sph_o[4 * (size_t)s], ctx->sph_r[s], sph + s);
+}
+
+size_t frame_records(const rtb_ctx* ctx) { return 3 * (size_t)ctx->nc + (size_t)ctx->ns; }
+
+// Enqueues one grid-kernel launch (with its timing event pair) on `stream`.
+int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width, int height, int band_rows,
+                 int band_rank, int band_world, int local_rows, void* d_rgba8, void* d_id, void* d_i32,
+                 cudaStream_t stream) {
+    GridParams p;
+    p.width = width; p.height = height;
+    p.band_rows = band_rows; p.band_rank = band_rank; p.band_world = band_world;
+    p.local_rows = local_rows;
+    p.n_cubes = ctx->nc; p.n_spheres = ctx->ns;
+    p.cube_rec = d_rec;
+    p.sph_rec = d_rec + 3 * (size_t)ctx->nc;
+    p.cube_col = ctx->d_cube_col;
+    p.sph_col = ctx->d_sph_col;
+    p.out_rgba8 = static_cast<uint32_t*>(d_rgba8);
+    p.out_id = static_cast<int32_t*>(d_id);
+    p.out_i32 = static_cast<int4*>(d_i32);
+    p.vec_ok = (width % 4 == 0) && aligned16(d_rgba8) && aligned16(d_id) && aligned16(d_i32);
+    p.cam = cam;
+    EventPair ev;
+    const int rc = take_events(ctx, &ev);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaEventRecord(ev.a, stream));
+    RTB_CUDA(ctx, launch_grid(p, ctx->sm_count, stream));
+    RTB_CUDA(ctx, cudaEventRecord(ev.b, stream));
+    ctx->ev_pending.push_back(ev);
+    ctx->launches += 1;
+    if (ctx->ev_pending.size() > 1024) return resolve_pending(ctx);
+    return RTB_OK;
+}
+
+int check_frame_args(rtb_ctx* ctx, int width, int height, const float* o0, const float* du, const float* dv,
+                     const float* dir) {
+    if (!ctx) return RTB_ERR_INVALID_ARG;
+    if (width <= 0 || height <= 0 || !o0 || !du || !dv || !dir)
+        return fail(ctx, RTB_ERR_INVALID_ARG, "bad frame size or null camera vector");
+    if ((long long)width * height > (1LL << 31) - 1) return fail(ctx, RTB_ERR_INVALID_ARG, "frame too large");
+    if (!ctx->have_scene) return fail(ctx, RTB_ERR_NO_SCENE, "rtb_set_scene has not been called");
+    return RTB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtb_band_local_rows(int height, int band_rows, int band_rank, int band_world) {
+    if (height <= 0 || band_rows <= 0 || band_world <= 0 || band_rank < 0 || band_rank >= band_world) return 0;
+    const int n_bands = (height + band_rows - 1) / band_rows;
+    int rows = 0;
+    for (int b = band_rank; b < n_bands; b += band_world) {
+        const int y0 = b * band_rows;
+        rows += (height - y0 < band_rows) ? (height - y0) : band_rows;
+    }
+    return rows;
+}
+
+int rtb_render_bands_device(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+                            const float dV[4], const float rayDir[4], int band_rows, int band_rank,
+                            int band_world, void* d_rgba8, void* d_prim_id, void* d_rgba_i32,
+                            void* cuda_stream) {
+    int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
+    if (rc != RTB_OK) return rc;
+    if (band_rows <= 0 || band_rows % 4 != 0 || band_world <= 0 || band_rank < 0 || band_rank >= band_world)
+        return fail(ctx, RTB_ERR_INVALID_ARG, "band_rows must be a positive multiple of 4; 0 <= rank < world");
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    CameraFrame cf;
+    if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
+        return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
+    cudaStream_t stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->stream;
+    // the pinned staging area is reused: the previous frame's upload must have left it
+    RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
+    pack_frame(ctx, cf, ctx->h_rec);
+    const size_t nrec = frame_records(ctx);
+    if (nrec)
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, nrec * sizeof(float4), cudaMemcpyHostToDevice,
+                                      stream));
+    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_rec, stream));
+    const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
+    rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, band_rows, band_rank, band_world, local_rows,
+                      d_rgba8, d_prim_id, d_rgba_i32, stream);
+    if (rc != RTB_OK) return rc;
+    if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
+    return RTB_OK;
+}
+
+int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+               const float dV[4], const float rayDir[4], uint8_t* rgba8_out, int32_t* prim_id_out,
+               int32_t* rgba_i32_out, float* kernel_ms, float* total_ms) {
+    int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    CameraFrame cf;
+    if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
+        return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
+    const size_t n = (size_t)width * height;
+    const size_t bytes[3] = {4 * n, 4 * n, 16 * n};
+    void* host[3] = {rgba8_out, prim_id_out, rgba_i32_out};
+    for (int i = 0; i < 3; ++i)
+        if (host[i]) {
+            rc = ensure_device(ctx, &ctx->d_out[i], &ctx->d_out_cap[i], bytes[i]);
+            if (rc != RTB_OK) return rc;
+        }
+    rc = resolve_pending(ctx);
+    if (rc != RTB_OK) return rc;
+    const double k_sum0 = ctx->kernel_ms_sum;
+    cudaStream_t st = ctx->stream;
+    RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
+    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total0, st));
+    pack_frame(ctx, cf, ctx->h_rec);
+    const size_t nrec = frame_records(ctx);
+    if (nrec)
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, nrec * sizeof(float4), cudaMemcpyHostToDevice, st));
+    rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, 4, 0, 1, height, host[0] ? ctx->d_out[0] : nullptr,
+                      host[1] ? ctx->d_out[1] : nullptr, host[2] ? ctx->d_out[2] : nullptr, st);
+    if (rc != RTB_OK) return rc;
+    for (int i = 0; i < 3; ++i)
+        if (host[i]) RTB_CUDA(ctx, cudaMemcpyAsync(host[i], ctx->d_out[i], bytes[i], cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total1, st));
+    RTB_CUDA(ctx, cudaStreamSynchronize(st));
+    rc = resolve_pending(ctx);
+    if (rc != RTB_OK) return rc;
+    if (kernel_ms) *kernel_ms = (float)(ctx->kernel_ms_sum - k_sum0);
+    if (total_ms) RTB_CUDA(ctx, cudaEventElapsedTime(total_ms, ctx->ev_total0, ctx->ev_total1));
+    return RTB_OK;
+}
+
+int rtb_render_rays(rtb_ctx* ctx, size_t n_rays, const float* rayOrigins, const float rayDir[4],
+                    uint8_t* rgba8_out, int32_t* prim_id_out, int32_t* rgba_i32_out, float* kernel_ms,
+                    float* total_ms) {
+    if (!ctx) return RTB_ERR_INVALID_ARG;
+    if (!rayDir || (n_rays > 0 && !rayOrigins)) return fail(ctx, RTB_ERR_INVALID_ARG, "null ray array");
+    if (!ctx->have_scene) return fail(ctx, RTB_ERR_NO_SCENE, "rtb_set_scene has not been called");
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    const double dir3[3] = {rayDir[0], rayDir[1], rayDir[2]};
+    if (!(dir3[0] * dir3[0] + dir3[1] * dir3[1] + dir3[2] * dir3[2] > 0.0))
+        return fail(ctx, RTB_ERR_CAMERA, "rayDir.xyz is zero");
+    const size_t bytes[3] = {4 * n_rays, 4 * n_rays, 16 * n_rays};
+    void* host[3] = {rgba8_out, prim_id_out, rgba_i32_out};
+    int rc;
+    for (int i = 0; i < 3; ++i)
+        if (host[i] && n_rays) {
+            rc = ensure_device(ctx, &ctx->d_out[i], &ctx->d_out_cap[i], bytes[i]);
+            if (rc != RTB_OK) return rc;
+        }
+    void* dorig = ctx->d_origins;
+    rc = ensure_device(ctx, &dorig, &ctx->d_origins_cap, 16 * (n_rays ? n_rays : 1));
+    ctx->d_origins = static_cast<float4*>(dorig);
+    if (rc != RTB_OK) return rc;
+    cudaStream_t st = ctx->stream;
+    RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
+    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total0, st));
+    // world-space records: 4 float4 per cube, then 2 per sphere (centre, radius)
+    float* h = reinterpret_cast<float*>(ctx->h_rec);
+    for (int c = 0; c < ctx->nc; ++c) pack_box_world(dir3, ctx->boxes[c], h + 16 * (size_t)c);
+    float* hs = h + 16 * (size_t)ctx->nc;
+    for (int s = 0; s < ctx->ns; ++s) {
+        std::memcpy(hs + 8 * (size_t)s, &ctx->sph_o[4 * (size_t)s], 16);
+        hs[8 * (size_t)s + 4] = ctx->sph_r[s];
+        hs[8 * (size_t)s + 5] = hs[8 * (size_t)s + 6] = hs[8 * (size_t)s + 7] = 0.f;
+    }
+    const size_t nrec = 4 * (size_t)ctx->nc + 2 * (size_t)ctx->ns;
+    if (nrec)
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, nrec * sizeof(float4), cudaMemcpyHostToDevice, st));
+    if (n_rays)
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_origins, rayOrigins, 16 * n_rays, cudaMemcpyHostToDevice, st));
+    RaysParams p;
+    p.n_rays = n_rays;
+    p.origins = ctx->d_origins;
+    for (int k = 0; k < 4; ++k) p.dir[k] = rayDir[k];
+    p.n_cubes = ctx->nc; p.n_spheres = ctx->ns;
+    p.cube_rec = ctx->d_rec;
+    p.sph_rec = ctx->d_rec + 4 * (size_t)ctx->nc;
+    p.cube_col = ctx->d_cube_col;
+    p.sph_col = ctx->d_sph_col;
+    p.out_rgba8 = host[0] ? static_cast<uint32_t*>(ctx->d_out[0]) : nullptr;
+    p.out_id = host[1] ? static_cast<int32_t*>(ctx->d_out[1]) : nullptr;
+    p.out_i32 = host[2] ? static_cast<int4*>(ctx->d_out[2]) : nullptr;
+    EventPair ev;
+    rc = take_events(ctx, &ev);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaEventRecord(ev.a, st));
+    RTB_CUDA(ctx, launch_rays(p, st));
+    RTB_CUDA(ctx, cudaEventRecord(ev.b, st));
+    ctx->launches += (n_rays ? 1 : 0);
+    for (int i = 0; i < 3; ++i)
+        if (host[i] && n_rays)
+            RTB_CUDA(ctx, cudaMemcpyAsync(host[i], ctx->d_out[i], bytes[i], cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total1, st));
+    RTB_CUDA(ctx, cudaStreamSynchronize(st));
+    float kms = 0.f;
+    RTB_CUDA(ctx, cudaEventElapsedTime(&kms, ev.a, ev.b));
+    ctx->ev_free.push_back(ev);
+    if (kernel_ms) *kernel_ms = kms;
+    if (total_ms) RTB_CUDA(ctx, cudaEventElapsedTime(total_ms, ctx->ev_total0, ctx->ev_total1));
+    return RTB_OK;
+}
+
+int rtb_render_sequence_device(rtb_ctx* ctx, int width, int height, int n_frames, const float* cameras,
+                               void* d_rgba8, float* kernel_ms_total) {
+    if (!ctx) return RTB_ERR_INVALID_ARG;
+    if (n_frames < 0 || (n_frames > 0 && (!cameras || !d_rgba8)))
+        return fail(ctx, RTB_ERR_INVALID_ARG, "null cameras / output");
+    if (n_frames == 0) { if (kernel_ms_total) *kernel_ms_total = 0.f; return RTB_OK; }
+    int rc = check_frame_args(ctx, width, height, cameras, cameras + 4, cameras + 8, cameras + 12);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t nrec = frame_records(ctx);
+    const size_t stride = (nrec + 7) & ~(size_t)7;  // keep each frame's records 128-byte aligned
+    RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
+    rc = ensure_records(ctx, stride * (size_t)n_frames + 8);
+    if (rc != RTB_OK) return rc;
+    std::vector<RtbCam> cams((size_t)n_frames);
+    for (int f = 0; f < n_frames; ++f) {
+        const float* c = cameras + 16 * (size_t)f;
+        CameraFrame cf;
+        if (!camera_prepare(c, c + 4, c + 8, c + 12, &cf)) {
+            char buf[96];
+            std::snprintf(buf, sizeof buf, "degenerate camera in frame %d", f);
+            return fail(ctx, RTB_ERR_CAMERA, buf);
+        }
+        pack_frame(ctx, cf, ctx->h_rec + stride * (size_t)f);
+        cams[f] = cf.cam;
+    }
+    rc = resolve_pending(ctx);
+    if (rc != RTB_OK) return rc;
+    const double k0 = ctx->kernel_ms_sum;
+    cudaStream_t st = ctx->stream;
+    RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, stride * (size_t)n_frames * sizeof(float4),
+                                  cudaMemcpyHostToDevice, st));
+    const size_t frame_bytes = 4 * (size_t)width * height;
+    for (int f = 0; f < n_frames; ++f) {
+        rc = enqueue_grid(ctx, cams[f], ctx->d_rec + stride * (size_t)f, width, height, 4, 0, 1, height,
+                          static_cast<uint8_t*>(d_rgba8) + frame_bytes * (size_t)f, nullptr, nullptr, st);
+        if (rc != RTB_OK) return rc;
+    }
+    RTB_CUDA(ctx, cudaStreamSynchronize(st));
+    rc = resolve_pending(ctx);
+    if (rc != RTB_OK) return rc;
+    if (kernel_ms_total) *kernel_ms_total = (float)(ctx->kernel_ms_sum - k0);
+    return RTB_OK;
+}
+
+int rtb_host_alloc(void** out, size_t bytes) {
+    if (!out) return RTB_ERR_INVALID_ARG;
+    *out = nullptr;
+    const cudaError_t e = cudaMallocHost(out, bytes ? bytes : 1);
+    if (e == cudaErrorMemoryAllocation) return RTB_ERR_OUT_OF_MEMORY;
+    return e == cudaSuccess ? RTB_OK : RTB_ERR_CUDA;
+}
+
+void rtb_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int rtb_device_info(const rtb_ctx* ctx, int* sm_count, int* sm_clock_khz, char* name, size_t name_cap) {
+    if (!ctx) return RTB_ERR_INVALID_ARG;
+    if (sm_count) *sm_count = ctx->sm_count;
+    if (sm_clock_khz) *sm_clock_khz = ctx->clock_khz;
+    if (name && name_cap) std::snprintf(name, name_cap, "%s", ctx->name);
+    return RTB_OK;
+}
+
+unsigned long long rtb_launch_count(const rtb_ctx* ctx) { return ctx ? ctx->launches : 0ull; }
+
+float rtb_kernel_ms_avg(rtb_ctx* ctx, int reset, int* n_launches) {
+    if (!ctx) return 0.f;
+    cudaSetDevice(ctx->device);
+    resolve_pending(ctx);
+    const int n = ctx->kernel_ms_n;
+    const float avg = n ? (float)(ctx->kernel_ms_sum / n) : 0.f;
+    if (n_launches) *n_launches = n;
+    if (reset) { ctx->kernel_ms_sum = 0.0; ctx->kernel_ms_n = 0; }
+    return avg;
+}
+
+int rtb_debug_pack(int numSpheres, const float* sphereOrigins, const float* sphereRadius, int numCubes,
+                   const float* cubeVertices, const float origin0[4], const float dU[4], const float dV[4],
+                   const float rayDir[4], float* cube_rec, float* sphere_rec, float* cam, int* bad_cube_index) {
+    if (numSpheres < 0 || numCubes < 0 || !origin0 || !dU || !dV || !rayDir) return RTB_ERR_INVALID_ARG;
+    if (bad_cube_index) *bad_cube_index = -1;
+    CameraFrame cf;
+    if (!camera_prepare(origin0, dU, dV, rayDir, &cf)) return RTB_ERR_CAMERA;
+    for (int c = 0; c < numCubes; ++c) {
+        Box b;
+        if (!box_from_vertices(cubeVertices + 144 * (size_t)c, &b)) {
+            if (bad_cube_index) *bad_cube_index = c;
+            return RTB_ERR_NOT_A_BOX;
+        }
+        if (cube_rec) pack_box(cf, b, reinterpret_cast<RtbSlab*>(cube_rec) + 3 * (size_t)c);
+    }
+    if (sphere_rec)
+        for (int s = 0; s < numSpheres; ++s)
+            pack_sphere(cf, sphereOrigins + 4 * (size_t)s, sphereRadius[s],
+                        reinterpret_cast<RtbSphere*>(sphere_rec) + s);
+    if (cam) std::memcpy(cam, &cf.cam, sizeof(RtbCam));
+    return RTB_OK;
+}
+
+}  // extern "C"

@@ -78,6 +78,11 @@ class PortOracle:
         L.orc_fnv1a64.restype = C.c_uint64
         L.orc_fnv1a64_words.argtypes = [C.POINTER(C.c_int32), C.c_size_t]
         L.orc_fnv1a64_words.restype = C.c_uint64
+        L.orc_intersect_sphere.argtypes = [fp, fp, C.c_float, fp]
+        L.orc_intersect_sphere.restype = C.c_float
+        dp = C.POINTER(C.c_double)
+        L.orc_intersect_tri.argtypes = [dp] * 6
+        L.orc_intersect_tri.restype = C.c_int
         L.orc_pixel_origin.argtypes = [C.c_int, C.c_int, fp, fp, fp, fp]
 
     def max_threads(self):
@@ -126,6 +131,23 @@ def _fnv_words(self, rgba_i32):
 
 
 PortOracle.fnv1a64_words = _fnv_words
+
+
+def _port_intersect_sphere(self, o4, d4, radius, c4):
+    o, d, c = _f32(o4), _f32(d4), _f32(c4)
+    return float(self.lib.orc_intersect_sphere(_fp(o), _fp(d), float(radius), _fp(c)))
+
+
+def _port_intersect_tri(self, o, d, v0, v1, v2):
+    arrs = [np.ascontiguousarray(a, np.float64) for a in (o, d, v0, v1, v2)]
+    t = np.zeros(1, np.float64)
+    dp = C.POINTER(C.c_double)
+    hit = self.lib.orc_intersect_tri(*[a.ctypes.data_as(dp) for a in arrs], t.ctypes.data_as(dp))
+    return hit, float(t[0])
+
+
+PortOracle.intersect_sphere = _port_intersect_sphere
+PortOracle.intersect_tri = _port_intersect_tri
 
 
 def narrow_u8(rgba_i32):

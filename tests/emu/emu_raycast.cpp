@@ -1,0 +1,54 @@
+// emu_raycast.cpp -- TEST INFRASTRUCTURE.  Scalar CPU walk-through of raycast_grid_kernel's
+// arithmetic (opencl_ray_tracer_b200/csrc/raycast_kernels.cu), built from the SAME header
+// (raycast_math.h) with contraction off, so it reproduces the kernel bit for bit.  It lets the
+// CPU test-suite check the host packer + kernel formulation against the oracle without a GPU.
+// It is not linked into, nor reachable from, the product library.
+#include <cstdint>
+#include <cstddef>
+
+#include "../../opencl_ray_tracer_b200/csrc/raycast_math.h"
+
+extern "C" int emu_render_grid(int width, int height, const float* cam8, int nc, const float* cube_rec,
+                               int ns, const float* sph_rec, const float* cube_col, const float* sph_col,
+                               int32_t* rgba_i32, int32_t* prim_id, float* closest) {
+    const RtbCam cam = {cam8[0], cam8[1], cam8[2], cam8[3], cam8[4], 0.f, 0.f, 0.f};
+    const RtbSlab* slabs = reinterpret_cast<const RtbSlab*>(cube_rec);
+    const RtbSphere* sph = reinterpret_cast<const RtbSphere*>(sph_rec);
+#pragma omp parallel for schedule(dynamic, 4)
+    for (int y = 0; y < height; ++y) {
+        const float fy = (float)y;
+        const float v = rtb_cam_v(cam, fy);
+        for (int x = 0; x < width; ++x) {
+            const float u = rtb_cam_u(cam, (float)x, fy);
+            float best = RTB_MISS_T;
+            int id = -1;
+            for (int c = 0; c < nc; ++c) {
+                const RtbSlab &s0 = slabs[3 * c], &s1 = slabs[3 * c + 1], &s2 = slabs[3 * c + 2];
+                const float n0 = rtb_slab_near(s0, rtb_slab_base(s0, v), u);
+                const float n1 = rtb_slab_near(s1, rtb_slab_base(s1, v), u);
+                const float n2 = rtb_slab_near(s2, rtb_slab_base(s2, v), u);
+                const float f0 = n0 + s0.width, f1 = n1 + s1.width, f2 = n2 + s2.width;
+                const float tn = fmaxf(fmaxf(n0, n1), n2);
+                const float tf = fminf(fminf(f0, f1), f2);
+                rtb_cube_update(tn, tf, c, best, id);
+            }
+            const float wv = cam.tau_v * v;
+            for (int s = 0; s < ns; ++s) {
+                const float rad = rtb_sphere_rad(sph[s], rtb_sphere_radv(sph[s], v), u);
+                const float wpix = fmaf(cam.tau_u, u, wv);
+                rtb_sphere_update(sph[s], rad, wpix, nc + s, best, id);
+            }
+            if (best == RTB_MISS_T) id = -1;
+            float cr = 0.f, cg = 0.f, cb = 0.f;
+            if (id >= 0) {
+                const float* col = (id < nc) ? cube_col + 4 * id : sph_col + 4 * (id - nc);
+                cr = col[0]; cg = col[1]; cb = col[2];
+            }
+            const size_t i = (size_t)y * width + x;
+            rtb_shade(best, cr, cg, cb, rgba_i32 + 4 * i);
+            if (prim_id) prim_id[i] = id;
+            if (closest) closest[i] = best;
+        }
+    }
+    return 0;
+}
