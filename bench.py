@@ -1,0 +1,439 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark of the ray-cast path (BASELINE.json metric: Mrays/s and
+ray-primitive tests/s on synthetic scenes; % of FP32 peak; the CPU path timed beside it).
+
+  python bench.py --gpus N --steps K --warmup W            our arm (sm_100a kernels through the C ABI)
+  python bench.py --impl reference --gpus N --steps K ...  the reference's CPU path on the host cores
+
+One "step" = one frame of the workload.  With N > 1 (one process per GPU, torchrun) the frame is
+sharded as interleaved 16-row bands (strong scaling: the frame is fixed), the bands are gathered into
+rank 0's frame buffer over NCCL and de-interleaved by one copy kernel.  Prints ONE JSON line on
+rank 0.  Nothing here reads /root/reference.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# BASELINE.json configs: name -> (width, height, spheres, cubes, seed)
+WORKLOADS = {
+    "c2": (1920, 1080, 64, 64, 2),
+    "c3": (3840, 2160, 512, 512, 3),       # the roofline point: 4K x 1024 primitives
+    "c4": (7680, 4320, 2048, 2048, 4),
+}
+BAND_ROWS = 16
+
+# FP32 operations the shipped kernel executes per ray-primitive test (FMA = 2):
+#   cube  : 3 FFMA (near_k = beta_k*u + base_k) + 3 FADD (far_k = near_k + w_k)            =  9 flop
+#   sphere: 1 FADD (du = uc - u) + 1 FFMA (rad = radv - du*du)                             =  3 flop
+# plus per thread-row (amortised over the PX = 8 pixels a thread owns):
+#   cube  : 3 FFMA (base_k = gamma_k*v + alpha_k) = 6 flop / 8;  sphere: FADD + FFMA = 3 flop / 8
+FLOP_PER_CUBE_TEST = 9.0 + 6.0 / 8.0
+FLOP_PER_SPHERE_TEST = 3.0 + 3.0 / 8.0
+
+
+def workload_name(key):
+    w, h, ns, nc, seed = WORKLOADS[key]
+    return "%s: %dx%d, %d spheres + %d cubes, createScene3 recipe, seed %d, reference camera" % (key, w, h, ns, nc, seed)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        return json.load(open(p)), "measured (MEASURED_PEAKS.json)"
+    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag = index, [], set(), False
+        self.max_mhz = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+            nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake",
+        }
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def result(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def fp32_probe_tflops():
+    """Empirical FP32 peak: profiles/microbench/fp32_issue_probe (packed-FFMA2 chains), TFLOP/s."""
+    import subprocess
+    exe = os.path.join(ROOT, "profiles", "microbench", "fp32_issue_probe")
+    if not os.path.isfile(exe):
+        return None
+    try:
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout
+        sms = 148
+        for line in out.splitlines():
+            j = json.loads(line)
+            if "sms" in j:
+                sms = j["sms"]
+            if j.get("mix") == "8xFFMA2":
+                fmas = 16.0 * 4096 * 1024 * sms  # per launch: 16 FMA x ITERS x threads/SM x SMs
+                return 2.0 * fmas / (j["ms"] * 1e-3) / 1e12
+    except Exception:
+        return None
+    return None
+
+
+def cpu_baseline_port(scene, w, h, target_seconds):
+    """The oracle port (hoisted copies, OpenMP over rows, bit-identical to the reference's CPU path)
+    on all host cores, on a bounded sample of rows of the SAME frame."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle.oracle import PortOracle, Scene
+    port = PortOracle()
+    sc = Scene(*scene.as_tuple())
+    cores = port.max_threads()
+    probe_rows = max(cores, 8)
+    step = max(1, h // probe_rows)
+    t0 = time.perf_counter()
+    port.render(sc, w, h, rows=(0, h, step))
+    dt = time.perf_counter() - t0
+    n_probe = len(range(0, h, step))
+    rows = int(min(h, max(n_probe, n_probe * target_seconds / max(dt, 1e-6))))
+    step = max(1, h // rows)
+    t0 = time.perf_counter()
+    port.render(sc, w, h, rows=(0, h, step))
+    dt = time.perf_counter() - t0
+    n_rows = len(range(0, h, step))
+    return {"value": n_rows * w / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "port",
+            "sample": "rows 0,%d,... (%d of %d rows) of the same %dx%d frame, %.1f s" % (step, n_rows, h, w, h, dt),
+            "tests_per_s": n_rows * w * (scene.ns + scene.nc) / dt}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from opencl_ray_tracer_b200 import bands, capi, host_scene as hs
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and rank == 0:
+        print("warning: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world), file=sys.stderr)
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    w, h, ns, nc, seed = WORKLOADS[args.workload]
+    scene = hs.random_scene(w, h, ns, nc, seed)
+    if world > 1:
+        # the scene lives on rank 0's host: broadcast the flattened arrays over NCCL (north_star)
+        arrays = []
+        for a in scene.as_tuple():
+            g = torch.from_numpy(np.ascontiguousarray(a) if rank == 0 else np.zeros_like(a)).cuda()
+            dist.broadcast(g, 0)
+            arrays.append(g.cpu().numpy())
+        scene = hs.SceneArrays(*arrays, label=scene.label)
+    ctx = capi.Context(local_rank)                # raises if librtb.so / the device is missing
+    ctx.set_scene(*scene.as_tuple())
+    cam = capi.REFERENCE_CAMERA
+    n_px = w * h
+    rows_of = [ctx.band_local_rows(h, BAND_ROWS, r, world) for r in range(world)]
+    my_rows = rows_of[rank]
+    stream = torch.cuda.Stream()          # everything below (kernels, NCCL, events) runs on this stream
+    torch.cuda.set_stream(stream)
+    sptr = stream.cuda_stream
+
+    if world == 1:
+        d_frame = torch.empty((h, w, 4), dtype=torch.uint8, device="cuda")
+        d_packed = d_frame
+        my_slice = d_frame
+    else:
+        if rank == 0:
+            d_packed = torch.empty((h, w, 4), dtype=torch.uint8, device="cuda")   # rank-major packed rows
+            d_frame = torch.empty((h, w, 4), dtype=torch.uint8, device="cuda")
+            my_slice = d_packed[:my_rows]
+        else:
+            d_packed = d_frame = None
+            my_slice = torch.empty((max(my_rows, 1), w, 4), dtype=torch.uint8, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+    h_frame = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
+
+    def gather_and_assemble():
+        if world == 1:
+            return 0
+        bands.gather_packed(dist, my_slice, d_packed, rows_of, rank, world)
+        if rank == 0:
+            ctx.assemble_bands_device(w, h, BAND_ROWS, world, 4, d_packed.data_ptr(), d_frame.data_ptr(), sptr)
+            return 1
+        return 0
+
+    def device_step():
+        ctx.render_bands_device(w, h, cam, BAND_ROWS, rank, world, d_rgba8=my_slice.data_ptr(), stream=sptr)
+        return 1 + gather_and_assemble()
+
+    def e2e_step():
+        # what a caller of the C ABI does per frame with HOST data: scene arrays in, frame out
+        ctx.set_scene(*scene.as_tuple())
+        if world == 1:
+            ctx.render(w, h, cam, want=("rgba8",), out={"rgba8": h_np})
+            return 1
+        ctx.render_bands_device(w, h, cam, BAND_ROWS, rank, world, d_rgba8=my_slice.data_ptr(), stream=sptr)
+        n = 1 + gather_and_assemble()
+        if rank == 0:
+            h_frame.copy_(d_frame, non_blocking=True)
+        stream.synchronize()
+        return n
+
+    h_np = h_frame.numpy() if rank == 0 else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (value) -------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        device_step()
+    barrier()
+    ctx.kernel_ms_avg(reset=True)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches = 0
+    barrier()
+    wall0 = time.perf_counter()
+    for a, b in ev:
+        flush.zero_()                      # L2 flush between timed iterations (not timed)
+        a.record(stream)
+        launches += device_step()
+        b.record(stream)
+    barrier()
+    wall = time.perf_counter() - wall0
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    k_avg_ms, k_n = ctx.kernel_ms_avg(reset=True)
+    sampler.stop_flag = True
+    sampler.join()
+    t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms = float(t.item())
+    ms_per_step = dev_ms / args.steps
+
+    # ---- end-to-end timing through the C ABI with host buffers (e2e) ---------------------------
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    h2d0, d2h0 = ctx.transfer_bytes()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    h2d1, d2h1 = ctx.transfer_bytes()
+    t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    d2h_per_step = (d2h1 - d2h0) / args.steps + (4 * n_px if (world > 1 and rank == 0) else 0)
+    h2d_per_step = (h2d1 - h2d0) / args.steps
+    return dict(rank=rank, world=world, w=w, h=h, ns=ns, nc=nc, seed=seed, scene=scene, ctx=ctx,
+                ms_per_step=ms_per_step, wall_ms_per_step=wall * 1e3 / args.steps, k_avg_ms=k_avg_ms, k_n=k_n,
+                launches=launches, clocks=sampler.result(), e2e_s=e2e_s, h2d=h2d_per_step, d2h=d2h_per_step,
+                my_rows=my_rows)
+
+
+# ---- reference arm -------------------------------------------------------------------------------
+_REF = {}
+
+
+def _ref_worker_init(sph_o, sph_r, sph_c, cube_c, recipes, kind):
+    from oracle.oracle import PortOracle, RefOracle, Scene
+    if kind == "reference":
+        ref = RefOracle()
+        ref.clear_scene()
+        for o, r, c in zip(sph_o, sph_r, sph_c):
+            ref.add_sphere(o, r, c)
+        for c, q in zip(cube_c, recipes):  # same calls as createScene3's loop body, MainState.cpp:618-638
+            ref.add_cube_ops(c, [("scale", (q[0],) * 3), ("rotate", (0, 0, q[1])), ("rotate", (0, q[2], 0)),
+                                 ("rotate", (q[3], 0, 0)), ("translate", (q[4], q[5], q[6]))])
+        _REF["ref"] = ref
+    else:
+        _REF["port"] = PortOracle()
+
+
+def _ref_worker_rows(job):
+    w, h, segs, scene_tuple = job
+    d = np.array([0, 0, -1, -1], np.float32)
+    n = 0
+    for (y, x0, x1) in segs:
+        o = np.zeros((x1 - x0, 4), np.float32)
+        o[:, 0], o[:, 1], o[:, 3] = np.arange(x0, x1, dtype=np.float32), float(y), 1.0
+        if "ref" in _REF:
+            _REF["ref"].render(o, d)   # the reference's own executeRayTracerCPU loop body + collide
+        else:
+            from oracle.oracle import Scene
+            sc = Scene(*scene_tuple)
+            _REF["port"].render(sc, x1 - x0, 1, ray_origins=o, ray_dir=d, faithful=True, threads=1)
+        n += x1 - x0
+    return n
+
+
+def run_reference(args):
+    """The reference's CPU implementation of the path on this box's host cores: the per-ray code is
+    the reference's own (oracle/_ref: MainState::collide / intersectTri / intersectSphere compiled
+    from its sources) when that library was built, else the faithful mode of the oracle port.  The
+    reference is single-threaded; to use every host core the rays of the sample are spread over one
+    worker process per core, each running the unmodified per-ray loop.  Each step is a bounded
+    sample (row segments spread over the frame) sized so that the whole run takes about 90 s."""
+    import multiprocessing as mp
+    from opencl_ray_tracer_b200 import host_scene as hs
+    from oracle.oracle import ref_available
+    w, h, ns, nc, seed = WORKLOADS[args.workload]
+    scene = hs.random_scene(w, h, ns, nc, seed)
+    kind = "reference" if (ref_available() and scene.cube_recipes is not None) else "port"
+    cores = os.cpu_count() or 1
+    init = (scene.sph_o, scene.sph_r, scene.sph_c, scene.cube_c, scene.cube_recipes, kind)
+    ctxm = mp.get_context("fork")
+    with ctxm.Pool(cores, initializer=_ref_worker_init, initargs=init) as pool:
+        def step(k, seg_len):
+            ys = [int((i + 0.5) * h / cores + 7 * k) % h for i in range(cores)]   # one row per worker, spread
+            x0 = (k * seg_len) % max(1, w - seg_len + 1)
+            jobs = [(w, h, [(ys[i], x0, x0 + seg_len)], scene.as_tuple() if kind == "port" else None)
+                    for i in range(cores)]
+            t0 = time.perf_counter()
+            rays = sum(pool.map(_ref_worker_rows, jobs))
+            return rays, time.perf_counter() - t0
+        probe_len = min(w, 256)
+        _, s = step(0, probe_len)                       # untimed probe: rays/s per worker
+        rate = probe_len / max(s, 1e-6)
+        budget = 90.0 / max(1, args.steps + args.warmup)
+        seg_len = int(max(64, min(w, rate * budget)))
+        for k in range(args.warmup):
+            step(k, seg_len)
+        tot_rays, tot_s = 0, 0.0
+        for k in range(args.steps):
+            r, s = step(args.warmup + k, seg_len)
+            tot_rays += r
+            tot_s += s
+    mrays = tot_rays / tot_s / 1e6
+    sample = "%d row segments of %d rays per step (one per worker process, rows spread over the frame), %d steps, of the same %dx%d frame" % (
+        cores, seg_len, args.steps, w, h)
+    line = {
+        "impl": "reference", "metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_s * 1e3 / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32 (f64 triangle test)",
+        "data": "synthetic",
+        "config": {"workload": workload_name(args.workload)},
+        "tests_per_s": mrays * 1e6 * (ns + nc),
+        "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    if args.impl == "reference":
+        if rank == 0:
+            run_reference(args)
+        return
+    r = run_ours(args)
+    import torch.distributed as dist
+    if r["rank"] == 0:
+        peaks, peaks_src = load_peaks()
+        w, h, ns, nc = r["w"], r["h"], r["ns"], r["nc"]
+        n_px = w * h
+        s_step = r["ms_per_step"] * 1e-3
+        mrays = n_px / s_step / 1e6
+        info = r["ctx"].device_info()
+        sms = info["sm_count"]
+        sm_max = (r["clocks"]["sm_max_mhz"] or peaks.get("sm_max_mhz", 1965.0))
+        peak_nominal = sms * 128 * 2 * sm_max * 1e6 / 1e12          # TFLOP/s at the max SM clock
+        probe = fp32_probe_tflops()
+        # dominant kernel = the ray-cast grid kernel; this rank's launch covers my_rows rows
+        flops_per_launch = r["my_rows"] * w * (nc * FLOP_PER_CUBE_TEST + ns * FLOP_PER_SPHERE_TEST)
+        k_s = r["k_avg_ms"] * 1e-3
+        achieved = flops_per_launch / k_s / 1e12 if k_s > 0 else 0.0
+        peak = probe if probe else peak_nominal
+        line = {
+            "metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": r["world"], "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args.workload),
+                       "parallelism": "interleaved %d-row bands over %d GPU(s)%s" % (
+                           BAND_ROWS, r["world"], ", NCCL gather to rank 0 + de-interleave kernel" if r["world"] > 1 else ""),
+                       "l2": "256 MiB buffer written between timed iterations (L2 flush); per-step CUDA events"},
+            "tests_per_s": mrays * 1e6 * (ns + nc),
+            "wall_ms_per_step_incl_flush": r["wall_ms_per_step"],
+            "clocks": r["clocks"],
+            "e2e": {"value": n_px * args.steps / r["e2e_s"] / 1e6, "unit": "Mrays/s",
+                    "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                    "ms_per_step": r["e2e_s"] * 1e3 / args.steps,
+                    "what": "rtb_set_scene + rtb_render into pinned host memory (N=1) / bands + NCCL gather + D2H (N>1)"},
+            "gpu_launches": r["launches"],
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                         "frac": achieved / peak if peak else None, "traffic": None,
+                         "kernel": "raycast_grid_kernel", "kernel_ms": r["k_avg_ms"], "kernel_launches_timed": r["k_n"],
+                         "flop_per_cube_test": FLOP_PER_CUBE_TEST, "flop_per_sphere_test": FLOP_PER_SPHERE_TEST,
+                         "peak_source": ("fp32_issue_probe (packed FFMA2 chains) run on this GPU just now" if probe
+                                         else "nominal SMs x 128 lanes x 2 x max SM clock"),
+                         "peak_nominal_tflops": peak_nominal,
+                         "frac_of_nominal": achieved / peak_nominal,
+                         "framebuffer_write_gbs": r["my_rows"] * w * 4 / k_s / 1e9 if k_s > 0 else None,
+                         "hbm_peak_gbs": peaks.get("hbm_gbs"), "hbm_peak_source": peaks_src},
+        }
+        if r["world"] == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_port(r["scene"], w, h, args.cpu_seconds)
+        print(json.dumps(line))
+    if r["world"] > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -107,6 +107,14 @@ int rtb_render_bands_device(rtb_ctx* ctx, int width, int height, const float ori
 /* Number of local rows rank `band_rank` owns for a frame of `height` rows. */
 int rtb_band_local_rows(int height, int band_rows, int band_rank, int band_world);
 
+/* Multi-GPU gather epilogue.  After the ranks' packed band buffers have been gathered back to back
+ * (rank 0's rows, then rank 1's, ...; rank r contributes rtb_band_local_rows(height, band_rows, r,
+ * band_world) rows) into d_packed, this copies every row to its place in the final frame d_frame.
+ * elem_bytes = 4 (rgba8 / prim_id) or 16 (rgba_i32).  Stream semantics as above.  (The reference has
+ * no counterpart: it is single-device.) */
+int rtb_assemble_bands_device(rtb_ctx* ctx, int width, int height, int band_rows, int band_world,
+                              int elem_bytes, const void* d_packed, void* d_frame, void* cuda_stream);
+
 /* n_frames frames of the same scene with per-frame cameras (cameras = n_frames x 16 floats:
  * origin0, dU, dV, rayDir), kept on the device: d_rgba8 receives n_frames packed frames
  * (4*width*height bytes each).  Used for the orbit sequence (BASELINE.json config 5). */
@@ -121,6 +129,8 @@ void rtb_host_free(void* p);
 int rtb_device_info(const rtb_ctx* ctx, int* sm_count, int* sm_clock_khz, char* name, size_t name_cap);
 /* Kernel launches issued by this context so far (ray-cast + helper kernels). */
 unsigned long long rtb_launch_count(const rtb_ctx* ctx);
+/* Bytes this context has copied host->device / device->host so far (scene, records, frames). */
+void rtb_transfer_bytes(const rtb_ctx* ctx, unsigned long long* h2d, unsigned long long* d2h);
 /* Average device time (ms) of the ray-cast kernel launches since the last call with reset != 0;
  * measured with CUDA events on the launching stream.  n_launches (nullable) receives the count. */
 float rtb_kernel_ms_avg(rtb_ctx* ctx, int reset, int* n_launches);

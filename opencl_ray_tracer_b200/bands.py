@@ -1,0 +1,51 @@
+"""Interleaved row-band sharding of one frame over the ranks of a torch.distributed job (one
+process per GPU) -- host-side bookkeeping and the gather to rank 0.  (New: the reference is
+single-device)
+
+Band b = rows [b*band_rows, (b+1)*band_rows) belongs to rank b % world.  Rank r renders its bands
+into a PACKED buffer (local row = (b // world)*band_rows + (y - b*band_rows)); rank 0 receives every
+rank's packed rows back to back ("rank-major packed" buffer) and librtb's
+rtb_assemble_bands_device de-interleaves them into the final frame.  The same arithmetic lives in
+rtb_band_local_rows / raycast_grid_kernel / assemble_bands_kernel (csrc/).
+"""
+import numpy as np
+
+
+def local_rows(height, band_rows, rank, world):
+    """Rows rank `rank` owns (mirror of rtb_band_local_rows)."""
+    n_bands = (height + band_rows - 1) // band_rows
+    return sum(min(band_rows, height - b * band_rows) for b in range(rank, n_bands, world))
+
+
+def global_rows_of_rank(height, band_rows, rank, world):
+    """Global row index of each packed local row of `rank`, in packed order."""
+    n_bands = (height + band_rows - 1) // band_rows
+    out = []
+    for b in range(rank, n_bands, world):
+        out.extend(range(b * band_rows, min(height, (b + 1) * band_rows)))
+    return np.asarray(out, dtype=np.int64)
+
+
+def packed_to_frame_rows(height, band_rows, world):
+    """For the rank-major packed buffer: frame_row[i] of packed row i (a permutation of 0..height-1)."""
+    return np.concatenate([global_rows_of_rank(height, band_rows, r, world) for r in range(world)])
+
+
+def gather_packed(dist, my_slice, packed, rows_of, rank, world):
+    """Gathers every rank's packed rows into rank 0's `packed` tensor (rank 0's own rows are expected
+    to be rendered in place at packed[:rows_of[0]]).  Works for CUDA tensors over NCCL and CPU
+    tensors over gloo.  Grouped point-to-point: ranks own different row counts (ragged)."""
+    if world == 1:
+        return
+    ops = []
+    if rank == 0:
+        off = rows_of[0]
+        for r in range(1, world):
+            if rows_of[r]:
+                ops.append(dist.P2POp(dist.irecv, packed[off:off + rows_of[r]], r))
+            off += rows_of[r]
+    elif rows_of[rank]:
+        ops.append(dist.P2POp(dist.isend, my_slice[:rows_of[rank]], 0))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()

@@ -25,6 +25,7 @@ EXPORTED_SYMBOLS = [
     "rtb_render", "rtb_render_rays", "rtb_render_bands_device", "rtb_band_local_rows",
     "rtb_render_sequence_device", "rtb_host_alloc", "rtb_host_free", "rtb_device_info",
     "rtb_launch_count", "rtb_kernel_ms_avg", "rtb_debug_pack", "rtb_version",
+    "rtb_assemble_bands_device", "rtb_transfer_bytes",
 ]
 
 
@@ -62,6 +63,9 @@ def load_library(path=None):
     lib.rtb_render_bands_device.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, C.c_int,
                                             C.c_int, vp, vp, vp, vp]
     lib.rtb_band_local_rows.argtypes = [C.c_int] * 4
+    lib.rtb_assemble_bands_device.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp]
+    lib.rtb_transfer_bytes.argtypes = [vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]
+    lib.rtb_transfer_bytes.restype = None
     lib.rtb_render_sequence_device.argtypes = [vp, C.c_int, C.c_int, C.c_int, fp, vp, fp]
     lib.rtb_host_alloc.argtypes = [C.POINTER(vp), C.c_size_t]
     lib.rtb_host_free.argtypes = [vp]
@@ -216,6 +220,16 @@ class Context:
             self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d), band_rows, rank, world,
             C.c_void_p(d_rgba8 or None), C.c_void_p(d_prim_id or None), C.c_void_p(d_rgba_i32 or None),
             C.c_void_p(stream or None)))
+
+    def assemble_bands_device(self, width, height, band_rows, world, elem_bytes, d_packed, d_frame, stream=0):
+        self._check(self.lib.rtb_assemble_bands_device(self._h, width, height, band_rows, world, elem_bytes,
+                                                       C.c_void_p(d_packed), C.c_void_p(d_frame),
+                                                       C.c_void_p(stream or None)))
+
+    def transfer_bytes(self):
+        a, b = C.c_ulonglong(), C.c_ulonglong()
+        self.lib.rtb_transfer_bytes(self._h, C.byref(a), C.byref(b))
+        return a.value, b.value
 
     def render_sequence_device(self, width, height, cameras, d_rgba8):
         cams = _f32(cameras).reshape(-1, 16)

@@ -328,6 +328,37 @@ cudaError_t launch_rays(const RaysParams& p, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
+// ---- band de-interleave (multi-GPU gather epilogue) --------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) assemble_bands_kernel(const AssembleParams p) {
+    const int y = blockIdx.y;
+    const int b = y / p.band_rows;
+    const int r = b % p.band_world;
+    const int lrow = (b / p.band_world) * p.band_rows + (y - b * p.band_rows);
+    const uint8_t* s = p.src + (size_t)(p.row_off[r] + lrow) * p.row_bytes;
+    uint8_t* d = p.dst + (size_t)y * p.row_bytes;
+    const bool vec = ((p.row_bytes & 15) == 0) && ((reinterpret_cast<uintptr_t>(p.src) & 15) == 0) &&
+                     ((reinterpret_cast<uintptr_t>(p.dst) & 15) == 0);
+    if (vec) {
+        const size_t n = p.row_bytes >> 4;
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+            reinterpret_cast<uint4*>(d)[i] = __ldg(reinterpret_cast<const uint4*>(s) + i);
+    } else {
+        const size_t n = p.row_bytes >> 2;  // elements are 4 or 16 bytes: rows are whole words
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+            reinterpret_cast<uint32_t*>(d)[i] = __ldg(reinterpret_cast<const uint32_t*>(s) + i);
+    }
+}
+}  // namespace
+
+cudaError_t launch_assemble(const AssembleParams& p, cudaStream_t stream) {
+    if (p.height <= 0 || p.row_bytes == 0) return cudaSuccess;
+    const unsigned per_row = (unsigned)((p.row_bytes / 16 + 255) / 256);
+    dim3 grid(per_row < 1 ? 1 : (per_row > 8 ? 8 : per_row), (unsigned)p.height);
+    assemble_bands_kernel<<<grid, 256, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t configure_kernels() { return cudaSuccess; }
 
 }  // namespace rtb

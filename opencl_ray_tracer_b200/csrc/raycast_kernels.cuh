@@ -45,6 +45,18 @@ struct RaysParams {
     int4* out_i32;
 };
 
+// De-interleave of gathered row bands (multi-GPU): `src` holds rank 0's packed rows, then rank 1's,
+// ...; row_off[r] = first packed row of rank r.  dst = the final frame.  row_bytes = width * element size.
+constexpr int kMaxBandWorld = 64;
+struct AssembleParams {
+    int height, band_rows, band_world;
+    size_t row_bytes;
+    const uint8_t* src;
+    uint8_t* dst;
+    int row_off[kMaxBandWorld];
+};
+cudaError_t launch_assemble(const AssembleParams& p, cudaStream_t stream);
+
 // Tile geometry of the grid kernel variant chosen for a frame.
 struct GridLaunchShape { int px; dim3 grid, block; size_t smem; };
 

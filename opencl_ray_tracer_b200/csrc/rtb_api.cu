@@ -43,6 +43,11 @@ struct rtb_ctx {
     size_t h_rec_cap = 0;
     void* d_out[3] = {nullptr, nullptr, nullptr};  // rgba8, id, i32 frame buffers, grow-only
     size_t d_out_cap[3] = {0, 0, 0};
+    size_t d_col_cap[2] = {0, 0};  // cube / sphere colour capacity in float4
+    // which camera the records in d_rec were packed for (skip pack + upload when unchanged)
+    bool packed_valid = false;
+    float packed_cam[16] = {0};
+    unsigned long long h2d_bytes = 0, d2h_bytes = 0;  // bytes this context copied over PCIe
     float4* d_origins = nullptr;   // rays path
     size_t d_origins_cap = 0;
 
@@ -217,18 +222,30 @@ int rtb_set_scene(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins, cons
         }
     }
     ctx->have_scene = false;
+    ctx->packed_valid = false;
     RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    cudaFree(ctx->d_cube_col);
-    cudaFree(ctx->d_sph_col);
-    ctx->d_cube_col = ctx->d_sph_col = nullptr;
-    RTB_CUDA(ctx, cudaMalloc(&ctx->d_cube_col, sizeof(float4) * (size_t)(numCubes > 0 ? numCubes : 1)));
-    RTB_CUDA(ctx, cudaMalloc(&ctx->d_sph_col, sizeof(float4) * (size_t)(numSpheres > 0 ? numSpheres : 1)));
+    {
+        void* p = ctx->d_cube_col;
+        size_t cap = ctx->d_col_cap[0] * sizeof(float4);
+        int rc0 = ensure_device(ctx, &p, &cap, sizeof(float4) * (size_t)(numCubes > 0 ? numCubes : 1));
+        ctx->d_cube_col = static_cast<float4*>(p);
+        ctx->d_col_cap[0] = cap / sizeof(float4);
+        if (rc0 != RTB_OK) return rc0;
+        p = ctx->d_sph_col;
+        cap = ctx->d_col_cap[1] * sizeof(float4);
+        rc0 = ensure_device(ctx, &p, &cap, sizeof(float4) * (size_t)(numSpheres > 0 ? numSpheres : 1));
+        ctx->d_sph_col = static_cast<float4*>(p);
+        ctx->d_col_cap[1] = cap / sizeof(float4);
+        if (rc0 != RTB_OK) return rc0;
+    }
     if (numCubes > 0)
-        RTB_CUDA(ctx, cudaMemcpy(ctx->d_cube_col, cubeColours, sizeof(float4) * (size_t)numCubes,
-                                 cudaMemcpyHostToDevice));
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_cube_col, cubeColours, sizeof(float4) * (size_t)numCubes,
+                                      cudaMemcpyHostToDevice, ctx->stream));
     if (numSpheres > 0)
-        RTB_CUDA(ctx, cudaMemcpy(ctx->d_sph_col, sphereColours, sizeof(float4) * (size_t)numSpheres,
-                                 cudaMemcpyHostToDevice));
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_sph_col, sphereColours, sizeof(float4) * (size_t)numSpheres,
+                                      cudaMemcpyHostToDevice, ctx->stream));
+    RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the caller may free its arrays on return
+    ctx->h2d_bytes += sizeof(float4) * ((size_t)numCubes + (size_t)numSpheres);
     ctx->ns = numSpheres;
     ctx->nc = numCubes;
     ctx->boxes.swap(boxes);
@@ -253,6 +270,28 @@ void pack_frame(const rtb_ctx* ctx, const CameraFrame& cf, float4* dst) {
 }
 
 size_t frame_records(const rtb_ctx* ctx) { return 3 * (size_t)ctx->nc + (size_t)ctx->ns; }
+
+// Packs this frame's records and enqueues their upload, unless d_rec already holds the records of
+// exactly this camera (same 16 floats, same scene).
+int upload_frame_records(rtb_ctx* ctx, const CameraFrame& cf, const float* o0, const float* du, const float* dv,
+                         const float* dir, cudaStream_t stream) {
+    float cam16[16];
+    std::memcpy(cam16, o0, 16); std::memcpy(cam16 + 4, du, 16);
+    std::memcpy(cam16 + 8, dv, 16); std::memcpy(cam16 + 12, dir, 16);
+    if (ctx->packed_valid && std::memcmp(cam16, ctx->packed_cam, sizeof cam16) == 0) return RTB_OK;
+    // the pinned staging area is reused: the previous upload must have left it
+    RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
+    pack_frame(ctx, cf, ctx->h_rec);
+    const size_t nrec = frame_records(ctx);
+    if (nrec)
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, nrec * sizeof(float4), cudaMemcpyHostToDevice,
+                                      stream));
+    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_rec, stream));
+    ctx->h2d_bytes += nrec * sizeof(float4);
+    std::memcpy(ctx->packed_cam, cam16, sizeof cam16);
+    ctx->packed_valid = true;
+    return RTB_OK;
+}
 
 // Enqueues one grid-kernel launch (with its timing event pair) on `stream`.
 int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width, int height, int band_rows,
@@ -322,18 +361,36 @@ int rtb_render_bands_device(rtb_ctx* ctx, int width, int height, const float ori
     if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
         return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
     cudaStream_t stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->stream;
-    // the pinned staging area is reused: the previous frame's upload must have left it
-    RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
-    pack_frame(ctx, cf, ctx->h_rec);
-    const size_t nrec = frame_records(ctx);
-    if (nrec)
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, nrec * sizeof(float4), cudaMemcpyHostToDevice,
-                                      stream));
-    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_rec, stream));
+    rc = upload_frame_records(ctx, cf, origin0, dU, dV, rayDir, stream);
+    if (rc != RTB_OK) return rc;
     const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
     rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, band_rows, band_rank, band_world, local_rows,
                       d_rgba8, d_prim_id, d_rgba_i32, stream);
     if (rc != RTB_OK) return rc;
+    if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
+    return RTB_OK;
+}
+
+int rtb_assemble_bands_device(rtb_ctx* ctx, int width, int height, int band_rows, int band_world,
+                               int elem_bytes, const void* d_packed, void* d_frame, void* cuda_stream) {
+    if (!ctx) return RTB_ERR_INVALID_ARG;
+    if (width <= 0 || height <= 0 || band_rows <= 0 || band_world <= 0 || band_world > kMaxBandWorld ||
+        (elem_bytes != 4 && elem_bytes != 16) || !d_packed || !d_frame)
+        return fail(ctx, RTB_ERR_INVALID_ARG, "bad assemble arguments (elem_bytes is 4 or 16; world <= 64)");
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    AssembleParams p;
+    p.height = height; p.band_rows = band_rows; p.band_world = band_world;
+    p.row_bytes = (size_t)width * (size_t)elem_bytes;
+    p.src = static_cast<const uint8_t*>(d_packed);
+    p.dst = static_cast<uint8_t*>(d_frame);
+    int off = 0;
+    for (int r = 0; r < kMaxBandWorld; ++r) {
+        p.row_off[r] = off;
+        if (r < band_world) off += rtb_band_local_rows(height, band_rows, r, band_world);
+    }
+    cudaStream_t stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->stream;
+    RTB_CUDA(ctx, launch_assemble(p, stream));
+    ctx->launches += 1;
     if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
     return RTB_OK;
 }
@@ -359,17 +416,17 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
     if (rc != RTB_OK) return rc;
     const double k_sum0 = ctx->kernel_ms_sum;
     cudaStream_t st = ctx->stream;
-    RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total0, st));
-    pack_frame(ctx, cf, ctx->h_rec);
-    const size_t nrec = frame_records(ctx);
-    if (nrec)
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, nrec * sizeof(float4), cudaMemcpyHostToDevice, st));
+    rc = upload_frame_records(ctx, cf, origin0, dU, dV, rayDir, st);
+    if (rc != RTB_OK) return rc;
     rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, 4, 0, 1, height, host[0] ? ctx->d_out[0] : nullptr,
                       host[1] ? ctx->d_out[1] : nullptr, host[2] ? ctx->d_out[2] : nullptr, st);
     if (rc != RTB_OK) return rc;
     for (int i = 0; i < 3; ++i)
-        if (host[i]) RTB_CUDA(ctx, cudaMemcpyAsync(host[i], ctx->d_out[i], bytes[i], cudaMemcpyDeviceToHost, st));
+        if (host[i]) {
+            RTB_CUDA(ctx, cudaMemcpyAsync(host[i], ctx->d_out[i], bytes[i], cudaMemcpyDeviceToHost, st));
+            ctx->d2h_bytes += bytes[i];
+        }
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total1, st));
     RTB_CUDA(ctx, cudaStreamSynchronize(st));
     rc = resolve_pending(ctx);
@@ -405,6 +462,7 @@ int rtb_render_rays(rtb_ctx* ctx, size_t n_rays, const float* rayOrigins, const 
     RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total0, st));
     // world-space records: 4 float4 per cube, then 2 per sphere (centre, radius)
+    ctx->packed_valid = false;
     float* h = reinterpret_cast<float*>(ctx->h_rec);
     for (int c = 0; c < ctx->nc; ++c) pack_box_world(dir3, ctx->boxes[c], h + 16 * (size_t)c);
     float* hs = h + 16 * (size_t)ctx->nc;
@@ -464,6 +522,7 @@ int rtb_render_sequence_device(rtb_ctx* ctx, int width, int height, int n_frames
     RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
     rc = ensure_records(ctx, stride * (size_t)n_frames + 8);
+    ctx->packed_valid = false;
     if (rc != RTB_OK) return rc;
     std::vector<RtbCam> cams((size_t)n_frames);
     for (int f = 0; f < n_frames; ++f) {
@@ -515,6 +574,11 @@ int rtb_device_info(const rtb_ctx* ctx, int* sm_count, int* sm_clock_khz, char* 
 }
 
 unsigned long long rtb_launch_count(const rtb_ctx* ctx) { return ctx ? ctx->launches : 0ull; }
+
+void rtb_transfer_bytes(const rtb_ctx* ctx, unsigned long long* h2d, unsigned long long* d2h) {
+    if (h2d) *h2d = ctx ? ctx->h2d_bytes : 0ull;
+    if (d2h) *d2h = ctx ? ctx->d2h_bytes : 0ull;
+}
 
 float rtb_kernel_ms_avg(rtb_ctx* ctx, int reset, int* n_launches) {
     if (!ctx) return 0.f;

@@ -42,6 +42,7 @@ void Scene::clear() {
     sphereRadius.clear();
     sphereColours.clear();
     cubes.clear();
+    cubeRecipes.clear();
 }
 
 void Scene::createScene1() {  // MainState.cpp:419-462
@@ -95,14 +96,18 @@ void Scene::randomCubes(Random& rng, int n, float xmax, float ymax) {  // MainSt
         Cube cube(randomColour(rng));
         const float s = rng.getFloat(5.0f, 30.0f);
         cube.scale({s, s, s});
-        cube.rotate({0.0f, 0.0f, convertAngleToRadian(rng.getFloat(0.0f, 359.0f))});
-        cube.rotate({0.0f, convertAngleToRadian(rng.getFloat(0.0f, 359.0f)), 0.0f});
-        cube.rotate({convertAngleToRadian(rng.getFloat(0.0f, 359.0f)), 0.0f, 0.0f});
+        const float rz = convertAngleToRadian(rng.getFloat(0.0f, 359.0f));
+        cube.rotate({0.0f, 0.0f, rz});
+        const float ry = convertAngleToRadian(rng.getFloat(0.0f, 359.0f));
+        cube.rotate({0.0f, ry, 0.0f});
+        const float rx = convertAngleToRadian(rng.getFloat(0.0f, 359.0f));
+        cube.rotate({rx, 0.0f, 0.0f});
         const float x = rng.getFloat(0.0f, xmax);
         const float y = rng.getFloat(0.0f, ymax);
         const float z = -rng.getFloat(30.0f, 100.0f);
         cube.translate({x, y, z});
         cubes.push_back(cube);
+        cubeRecipes.insert(cubeRecipes.end(), {s, rz, ry, rx, x, y, z});
     }
 }
 

@@ -21,6 +21,10 @@ struct Scene {
     std::vector<float> sphereRadius;
     std::vector<Vec4> sphereColours;
     std::vector<Cube> cubes;
+    // For cubes made by randomCubes(): the 8 draws behind each cube (scale, rz, ry, rx in radians,
+    // tx, ty, tz -- the arguments of its scale / rotate x3 / translate calls), so that a checker
+    // can rebuild the same cube with the reference's own Cube class.  Empty for scenes 1 and 2.
+    std::vector<float> cubeRecipes;
 
     void clear();
     void createScene1();                 // deterministic

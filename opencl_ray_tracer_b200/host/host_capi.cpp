@@ -12,7 +12,7 @@ using namespace rtbh;
 extern "C" {
 
 struct rtbh_scene {
-    std::vector<float> so, sr, sc, cv, cc;
+    std::vector<float> so, sr, sc, cv, cc, recipes;
 };
 
 // kind 1,2,3 = the reference's createScene1/2/3 (seed feeds the PCG stream of 2 and 3);
@@ -26,6 +26,7 @@ rtbh_scene* rtbh_scene_create(int kind, unsigned long long seed, int width, int 
     else return nullptr;
     rtbh_scene* h = new rtbh_scene();
     s.flatten(&h->so, &h->sr, &h->sc, &h->cv, &h->cc);
+    h->recipes = s.cubeRecipes;
     return h;
 }
 
@@ -40,6 +41,13 @@ void rtbh_scene_export(const rtbh_scene* h, float* so, float* sr, float* sc, flo
     if (!h->sc.empty()) std::memcpy(sc, h->sc.data(), h->sc.size() * 4);
     if (!h->cv.empty()) std::memcpy(cv, h->cv.data(), h->cv.size() * 4);
     if (!h->cc.empty()) std::memcpy(cc, h->cc.data(), h->cc.size() * 4);
+}
+
+// 7 floats per cube (scale, rz, ry, rx [radians], tx, ty, tz) for randomly generated cubes; returns
+// the number of cubes that have a recipe (0 for scenes 1 and 2).  out may be NULL to query.
+int rtbh_scene_export_recipes(const rtbh_scene* h, float* out) {
+    if (out && !h->recipes.empty()) std::memcpy(out, h->recipes.data(), h->recipes.size() * 4);
+    return (int)(h->recipes.size() / 7);
 }
 
 void rtbh_scene_free(rtbh_scene* h) { delete h; }

@@ -24,6 +24,7 @@ def load_host_library():
     lib.rtbh_scene_create.restype = C.c_void_p
     lib.rtbh_scene_counts.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.rtbh_scene_export.argtypes = [C.c_void_p, fp, fp, fp, fp, fp]
+    lib.rtbh_scene_export_recipes.argtypes = [C.c_void_p, fp]
     lib.rtbh_scene_free.argtypes = [C.c_void_p]
     lib.rtbh_cube_build.argtypes = [fp, C.c_int, C.POINTER(C.c_int), fp, fp]
     lib.rtbh_convert_angle_to_radian.argtypes = [C.c_float]
@@ -46,6 +47,7 @@ class SceneArrays:
         self.sph_o, self.sph_r, self.sph_c = sph_o, sph_r, sph_c
         self.cube_v, self.cube_c = cube_v, cube_c
         self.label = label
+        self.cube_recipes = None  # [nc, 7] (scale, rz, ry, rx, tx, ty, tz) for generated cubes
 
     @property
     def ns(self):
@@ -71,9 +73,15 @@ def _build(kind, seed, width, height, ns, nc, label):
         so, sr, sc = np.zeros((ns_, 4), np.float32), np.zeros(ns_, np.float32), np.zeros((ns_, 4), np.float32)
         cv, cc = np.zeros((nc_, 36, 4), np.float32), np.zeros((nc_, 4), np.float32)
         lib.rtbh_scene_export(h, _fp(so), _fp(sr), _fp(sc), _fp(cv), _fp(cc))
+        nrec = lib.rtbh_scene_export_recipes(h, None)
+        rec = np.zeros((nrec, 7), np.float32)
+        if nrec:
+            lib.rtbh_scene_export_recipes(h, _fp(rec))
     finally:
         lib.rtbh_scene_free(h)
-    return SceneArrays(so, sr, sc, cv, cc, label)
+    out = SceneArrays(so, sr, sc, cv, cc, label)
+    out.cube_recipes = rec if nrec == nc_ else None
+    return out
 
 
 def reference_scene(which, seed=1):
