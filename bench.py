@@ -30,13 +30,22 @@ WORKLOADS = {
 }
 BAND_ROWS = 16
 
-# FP32 operations the shipped kernel executes per ray-primitive test (FMA = 2):
-#   cube  : 3 FFMA (near_k = beta_k*u + base_k) + 3 FADD (far_k = near_k + w_k)            =  9 flop
-#   sphere: 1 FADD (du = uc - u) + 1 FFMA (rad = radv - du*du)                             =  3 flop
-# plus per thread-row (amortised over the PX = 8 pixels a thread owns):
-#   cube  : 3 FFMA (base_k = gamma_k*v + alpha_k) = 6 flop / 8;  sphere: FADD + FFMA = 3 flop / 8
-FLOP_PER_CUBE_TEST = 9.0 + 6.0 / 8.0
-FLOP_PER_SPHERE_TEST = 3.0 + 3.0 / 8.0
+# FP32 operations the shipped kernel executes per ray-primitive test (FMA = 2).  Cubes and
+# spheres go through the same dense loop: the primitive's conic footprint bound q(u,v) is evaluated on
+# every ray with 2 FFMA (q = (A*u + B)*u + C) = 4 flop; per thread and primitive 3 FFMA of row terms
+# (B, C) = 6 flop amortised over the PX rays a thread owns (PX = 16 at the roofline point).  The
+# reference-exact slab / sphere arithmetic runs only on rays inside a bound (a few per mille of the
+# tests) and is NOT counted.  Bit-pattern ANDs, votes, compares count 0.
+FLOP_PER_TEST_RAY = 4.0
+FLOP_PER_TEST_ROW = 6.0
+
+
+def grid_px(width, rows, sms):
+    """Rays per thread of the kernel variant grid_launch_shape() picks (raycast_kernels.cu)."""
+    for px, tw, th in ((16, 256, 16), (8, 128, 16)):
+        if -(-width // tw) * -(-rows // th) >= 2 * sms:
+            return px
+    return 4
 
 
 def workload_name(key):
@@ -396,7 +405,9 @@ def main():
         peak_nominal = sms * 128 * 2 * sm_max * 1e6 / 1e12          # TFLOP/s at the max SM clock
         probe = fp32_probe_tflops()
         # dominant kernel = the ray-cast grid kernel; this rank's launch covers my_rows rows
-        flops_per_launch = r["my_rows"] * w * (nc * FLOP_PER_CUBE_TEST + ns * FLOP_PER_SPHERE_TEST)
+        px = grid_px(w, r["my_rows"], sms)
+        flop_per_test = FLOP_PER_TEST_RAY + FLOP_PER_TEST_ROW / px
+        flops_per_launch = r["my_rows"] * w * (nc + ns) * flop_per_test
         k_s = r["k_avg_ms"] * 1e-3
         achieved = flops_per_launch / k_s / 1e12 if k_s > 0 else 0.0
         peak = probe if probe else peak_nominal
@@ -419,7 +430,7 @@ def main():
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                          "frac": achieved / peak if peak else None, "traffic": None,
                          "kernel": "raycast_grid_kernel", "kernel_ms": r["k_avg_ms"], "kernel_launches_timed": r["k_n"],
-                         "flop_per_cube_test": FLOP_PER_CUBE_TEST, "flop_per_sphere_test": FLOP_PER_SPHERE_TEST,
+                         "flop_per_test": flop_per_test, "rays_per_thread": px,
                          "peak_source": ("fp32_issue_probe (packed FFMA2 chains) run on this GPU just now" if probe
                                          else "nominal SMs x 128 lanes x 2 x max SM clock"),
                          "peak_nominal_tflops": peak_nominal,

@@ -143,6 +143,15 @@ int rtb_debug_pack(int numSpheres, const float* sphereOrigins, const float* sphe
                    const float dU[4], const float dV[4], const float rayDir[4], float* cube_rec,
                    float* sphere_rec, float* cam, int* bad_cube_index);
 
+/* Debug/test entry: the conservative conic bound records (8 floats per primitive, cubes then
+ * spheres; raycast_math.h RtbBound) the grid kernel's dense loop evaluates for a width x height
+ * frame of this camera.  Host only.  Replaces nothing in the reference: the bound is an internal
+ * accelerator of the rayTracer.cl:140-184 loops and never changes a pixel. */
+int rtb_debug_pack_bounds(int numSpheres, const float* sphereOrigins, const float* sphereRadius,
+                          int numCubes, const float* cubeVertices, int width, int height,
+                          const float origin0[4], const float dU[4], const float dV[4],
+                          const float rayDir[4], float* bound_rec);
+
 const char* rtb_version(void);
 
 #ifdef __cplusplus

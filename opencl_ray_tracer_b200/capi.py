@@ -24,7 +24,7 @@ EXPORTED_SYMBOLS = [
     "rtb_init", "rtb_shutdown", "rtb_error_string", "rtb_last_error_message", "rtb_set_scene",
     "rtb_render", "rtb_render_rays", "rtb_render_bands_device", "rtb_band_local_rows",
     "rtb_render_sequence_device", "rtb_host_alloc", "rtb_host_free", "rtb_device_info",
-    "rtb_launch_count", "rtb_kernel_ms_avg", "rtb_debug_pack", "rtb_version",
+    "rtb_launch_count", "rtb_kernel_ms_avg", "rtb_debug_pack", "rtb_debug_pack_bounds", "rtb_version",
     "rtb_assemble_bands_device", "rtb_transfer_bytes",
 ]
 
@@ -77,6 +77,7 @@ def load_library(path=None):
     lib.rtb_kernel_ms_avg.restype = C.c_float
     lib.rtb_debug_pack.argtypes = [C.c_int, fp, fp, C.c_int, fp, fp, fp, fp, fp, fp, fp, fp,
                                    C.POINTER(C.c_int)]
+    lib.rtb_debug_pack_bounds.argtypes = [C.c_int, fp, fp, C.c_int, fp, C.c_int, C.c_int, fp, fp, fp, fp, fp]
     lib.rtb_version.restype = C.c_char_p
     if path is None:
         _lib = lib
@@ -119,6 +120,20 @@ def debug_pack(sph_o, sph_r, cube_v, camera=REFERENCE_CAMERA):
     if rc != RTB_OK:
         raise RtbError(rc, "cube %d" % bad.value if bad.value >= 0 else "")
     return cube_rec, sph_rec, cam
+
+
+def debug_pack_bounds(sph_o, sph_r, cube_v, width, height, camera=REFERENCE_CAMERA):
+    """Host-side packer only: the conic bound records [nc+ns, 8] of a width x height frame."""
+    lib = load_library()
+    sph_o, sph_r, cube_v = _f32(sph_o).reshape(-1, 4), _f32(sph_r).reshape(-1), _f32(cube_v).reshape(-1, 36, 4)
+    ns, nc = len(sph_r), len(cube_v)
+    rec = np.zeros((nc + ns, 8), np.float32)
+    o0, du, dv, d = [_f32(v) for v in camera]
+    rc = lib.rtb_debug_pack_bounds(ns, _fp(sph_o), _fp(sph_r), nc, _fp(cube_v), int(width), int(height),
+                                   _fp(o0), _fp(du), _fp(dv), _fp(d), _fp(rec))
+    if rc != RTB_OK:
+        raise RtbError(rc)
+    return rec
 
 
 class Context:

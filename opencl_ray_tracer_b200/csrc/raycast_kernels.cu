@@ -63,56 +63,73 @@ struct PixelState {
     int id[PX];
 };
 
-// All cubes of one staged chunk against this thread's PX pixels.
+// Reference-exact nearest-hit update of primitive `prim` on this thread's PX rays (the arithmetic
+// of raycast_math.h that tests/emu replays).  Reached only from the rare "some ray of this warp
+// is inside the primitive's conic bound" branch, so its records come straight from global/L2.
 template <int PX>
-__device__ __forceinline__ void cubes_chunk(const float4* __restrict__ rec, int count, int first_id, float v,
-                                            PixelState<PX>& st) {
-#pragma unroll 2
-    for (int c = 0; c < count; ++c) {
-        const float4 r0 = rec[3 * c + 0], r1 = rec[3 * c + 1], r2 = rec[3 * c + 2];
+__device__ __forceinline__ void exact_update(const GridParams& p, int prim, float v, PixelState<PX>& st) {
+    if (prim < p.n_cubes) {
+        const float4 r0 = __ldg(p.cube_rec + 3 * (size_t)prim + 0), r1 = __ldg(p.cube_rec + 3 * (size_t)prim + 1),
+                     r2 = __ldg(p.cube_rec + 3 * (size_t)prim + 2);
         const RtbSlab s0 = {r0.x, r0.y, r0.z, r0.w}, s1 = {r1.x, r1.y, r1.z, r1.w}, s2 = {r2.x, r2.y, r2.z, r2.w};
         const float b0 = rtb_slab_base(s0, v), b1 = rtb_slab_base(s1, v), b2 = rtb_slab_base(s2, v);
-        float tn[PX], tf[PX];
-        bool any = false;
 #pragma unroll
-        for (int p = 0; p < PX; ++p) {
-            const float n0 = rtb_slab_near(s0, b0, st.u[p]);
-            const float n1 = rtb_slab_near(s1, b1, st.u[p]);
-            const float n2 = rtb_slab_near(s2, b2, st.u[p]);
+        for (int q = 0; q < PX; ++q) {
+            const float n0 = rtb_slab_near(s0, b0, st.u[q]);
+            const float n1 = rtb_slab_near(s1, b1, st.u[q]);
+            const float n2 = rtb_slab_near(s2, b2, st.u[q]);
             const float f0 = n0 + s0.width, f1 = n1 + s1.width, f2 = n2 + s2.width;
-            tn[p] = fmaxf(fmaxf(n0, n1), n2);  // FMNMX3
-            tf[p] = fminf(fminf(f0, f1), f2);  // FMNMX3
-            any |= (tn[p] <= tf[p]);
+            const float tn = fmaxf(fmaxf(n0, n1), n2);
+            const float tf = fminf(fminf(f0, f1), f2);
+            rtb_cube_update(tn, tf, prim, st.best[q], st.id[q]);
         }
-        if (any) {
+    } else if (prim < p.n_cubes + p.n_spheres) {
+        const float4 r = __ldg(p.sph_rec + (size_t)(prim - p.n_cubes));
+        const RtbSphere sp = {r.x, r.y, r.z, r.w};
+        const float radv = rtb_sphere_radv(sp, v);
+        const float wv = p.cam.tau_v * v;
 #pragma unroll
-            for (int p = 0; p < PX; ++p) rtb_cube_update(tn[p], tf[p], first_id + c, st.best[p], st.id[p]);
+        for (int q = 0; q < PX; ++q) {
+            const float rad = rtb_sphere_rad(sp, radv, st.u[q]);
+            const float wpix = fmaf(p.cam.tau_u, st.u[q], wv);
+            rtb_sphere_update(sp, rad, wpix, prim, st.best[q], st.id[q]);
         }
     }
 }
 
-template <int PX>
-__device__ __forceinline__ void spheres_chunk(const float4* __restrict__ rec, int count, int first_id, float v,
-                                              const RtbCam& cam, PixelState<PX>& st) {
-#pragma unroll 4
-    for (int s = 0; s < count; ++s) {
-        const float4 r = rec[s];
-        const RtbSphere sp = {r.x, r.y, r.z, r.w};
-        const float radv = rtb_sphere_radv(sp, v);
-        float rad[PX];
-        bool any = false;
+// The dense test: G primitives of a staged chunk against this thread's PX rays.  Per ray and
+// primitive 2 FFMA (conic bound q) + half a LOP3 (AND of the IEEE patterns: bit 30 survives only
+// if every ray has q >= 2); per thread and primitive 1 LDS.128 + 1 LDS.64 + 3 FFMA (row terms);
+// one warp vote per G primitives.
+template <int PX, int G>
+__device__ __forceinline__ void bound_group(const GridParams& p, const float4* __restrict__ rec, int first_prim,
+                                            float v, PixelState<PX>& st) {
+    uint32_t acc[G];
 #pragma unroll
-        for (int p = 0; p < PX; ++p) {
-            rad[p] = rtb_sphere_rad(sp, radv, st.u[p]);
-            any |= (rad[p] >= 0.0f);
+    for (int g = 0; g < G; ++g) {
+        const float4 r0 = rec[2 * g];                                            // A, m_uv, m_u, m_vv
+        const float2 r1 = *reinterpret_cast<const float2*>(rec + 2 * g + 1);      // m_v, m_0
+        const RtbBound b = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, 0.f, 0.f};
+        const float rowB = rtb_bound_row_b(b, v), rowC = rtb_bound_row_c(b, v);
+        uint32_t a = 0xFFFFFFFFu;
+#pragma unroll
+        for (int q = 0; q < PX; q += 2) {
+            const float q0 = rtb_bound_q(b.A, rowB, rowC, st.u[q]);
+            const float q1 = rtb_bound_q(b.A, rowB, rowC, st.u[q + 1]);
+            a &= __float_as_uint(q0) & __float_as_uint(q1);
         }
-        if (any) {
-            const float wv = cam.tau_v * v;
+        acc[g] = a;
+    }
+    uint32_t all = acc[0];
 #pragma unroll
-            for (int p = 0; p < PX; ++p) {
-                const float wpix = fmaf(cam.tau_u, st.u[p], wv);
-                rtb_sphere_update(sp, rad[p], wpix, first_id + s, st.best[p], st.id[p]);
-            }
+    for (int g = 1; g < G; ++g) all &= acc[g];
+    if (__any_sync(0xFFFFFFFFu, (all & RTB_BOUND_FAIL_BIT) == 0u)) {
+#pragma unroll 1
+        for (int g = 0; g < G; ++g) {
+            uint32_t a = acc[0];
+#pragma unroll
+            for (int h = 1; h < G; ++h) a = (g == h) ? acc[h] : a;
+            if (__any_sync(0xFFFFFFFFu, (a & RTB_BOUND_FAIL_BIT) == 0u)) exact_update<PX>(p, first_prim + g, v, st);
         }
     }
 }
@@ -123,8 +140,10 @@ raycast_grid_kernel(const GridParams p) {
     constexpr int kThreads = 32 * WARPS_X * WARPS_Y;
     constexpr int kTileW = WARPS_X * 8 * PX;
     constexpr int kTileH = WARPS_Y * 4;
-    __shared__ __align__(128) float4 stage[2][kChunkRecords];
+    constexpr int G = kBoundGroup;
+    __shared__ __align__(128) float4 stage[2][2 * kChunkPrims];
     __shared__ __align__(8) uint64_t full_bar[2];
+    (void)kThreads;
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -136,27 +155,17 @@ raycast_grid_kernel(const GridParams p) {
     const int lb = lrow / p.band_rows;
     const int gy = (lb * p.band_world + p.band_rank) * p.band_rows + (lrow - lb * p.band_rows);
 
-    const int n_cube_chunks = (p.n_cubes + kCubesPerChunk - 1) / kCubesPerChunk;
-    const int n_sph_chunks = (p.n_spheres + kSpheresPerChunk - 1) / kSpheresPerChunk;
-    const int n_chunks = n_cube_chunks + n_sph_chunks;
+    // bound records: one per primitive (cubes, then spheres), padded by the host to a multiple of G
+    const int n_bound = p.n_bound;
+    const int n_chunks = (n_bound + kChunkPrims - 1) / kChunkPrims;
 
     auto issue = [&](int k) {  // called by thread 0 only
         const int b = k & 1;
-        const void* src;
-        uint32_t bytes;
-        if (k < n_cube_chunks) {
-            const int first = k * kCubesPerChunk;
-            const int cnt = min(kCubesPerChunk, p.n_cubes - first);
-            src = p.cube_rec + 3 * (size_t)first;
-            bytes = (uint32_t)cnt * 48u;
-        } else {
-            const int first = (k - n_cube_chunks) * kSpheresPerChunk;
-            const int cnt = min(kSpheresPerChunk, p.n_spheres - first);
-            src = p.sph_rec + first;
-            bytes = (uint32_t)cnt * 16u;
-        }
+        const int first = k * kChunkPrims;
+        const int cnt = min(kChunkPrims, n_bound - first);
+        const uint32_t bytes = (uint32_t)cnt * 32u;
         mbar_arrive_expect_tx(&full_bar[b], bytes);
-        bulk_g2s(&stage[b][0], src, bytes, &full_bar[b]);
+        bulk_g2s(&stage[b][0], p.bound_rec + 2 * (size_t)first, bytes, &full_bar[b]);
     };
 
     if (tid == 0) {
@@ -183,14 +192,10 @@ raycast_grid_kernel(const GridParams p) {
     for (int k = 0; k < n_chunks; ++k) {
         const int b = k & 1;
         mbar_wait(&full_bar[b], (uint32_t)((k >> 1) & 1));
-        if (k < n_cube_chunks) {
-            const int first = k * kCubesPerChunk;
-            cubes_chunk<PX>(&stage[b][0], min(kCubesPerChunk, p.n_cubes - first), first, v, st);
-        } else {
-            const int first = (k - n_cube_chunks) * kSpheresPerChunk;
-            spheres_chunk<PX>(&stage[b][0], min(kSpheresPerChunk, p.n_spheres - first), p.n_cubes + first, v,
-                              p.cam, st);
-        }
+        const int first = k * kChunkPrims;
+        const int cnt = min(kChunkPrims, n_bound - first);
+#pragma unroll 1
+        for (int j = 0; j < cnt; j += G) bound_group<PX, G>(p, &stage[b][2 * j], first + j, v, st);
         if (k + 2 < n_chunks) {
             __syncthreads();  // every warp is done reading stage[b] before TMA refills it
             if (tid == 0) issue(k + 2);
@@ -306,15 +311,19 @@ GridLaunchShape shape_of(int width, int local_rows) {
 }  // namespace
 
 GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
-    GridLaunchShape big = shape_of<8, 2, 4>(width, local_rows);
+    GridLaunchShape big = shape_of<16, 2, 4>(width, local_rows);
     if ((long long)big.grid.x * big.grid.y >= 2LL * sm_count) return big;
+    GridLaunchShape mid = shape_of<8, 2, 4>(width, local_rows);
+    if ((long long)mid.grid.x * mid.grid.y >= 2LL * sm_count) return mid;
     return shape_of<4, 2, 2>(width, local_rows);
 }
 
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) {
     const GridLaunchShape s = grid_launch_shape(p.width, p.local_rows, sm_count);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
-    if (s.px == 8)
+    if (s.px == 16)
+        raycast_grid_kernel<16, 2, 4><<<s.grid, s.block, 0, stream>>>(p);
+    else if (s.px == 8)
         raycast_grid_kernel<8, 2, 4><<<s.grid, s.block, 0, stream>>>(p);
     else
         raycast_grid_kernel<4, 2, 2><<<s.grid, s.block, 0, stream>>>(p);

@@ -9,10 +9,10 @@
 
 namespace rtb {
 
-// Records per staged shared-memory chunk (16 B each): 768 records = 12 KB = 256 cubes or 768 spheres.
-constexpr int kChunkRecords = 768;
-constexpr int kCubesPerChunk = kChunkRecords / 3;
-constexpr int kSpheresPerChunk = kChunkRecords;
+// Bound records (RtbBound, 32 B) per staged shared-memory chunk: 512 primitives = 16 KB per stage.
+constexpr int kChunkPrims = 512;
+// Primitives per warp vote in the dense loop; the host pads the bound list to a multiple of it.
+constexpr int kBoundGroup = 4;
 
 struct GridParams {
     int width, height;                      // full frame
@@ -21,6 +21,8 @@ struct GridParams {
     int n_cubes, n_spheres;
     const float4* cube_rec;                 // 3 RtbSlab per cube
     const float4* sph_rec;                  // 1 RtbSphere per sphere
+    const float4* bound_rec;                // 2 float4 (RtbBound) per primitive: cubes, spheres, padding
+    int n_bound;                            // n_cubes + n_spheres rounded up to kBoundGroup
     const float4* cube_col;                 // (r,g,b,255)
     const float4* sph_col;
     uint32_t* out_rgba8;                    // nullable, local_rows*width

@@ -47,6 +47,7 @@ struct rtb_ctx {
     // which camera the records in d_rec were packed for (skip pack + upload when unchanged)
     bool packed_valid = false;
     float packed_cam[16] = {0};
+    int packed_w = 0, packed_h = 0;
     unsigned long long h2d_bytes = 0, d2h_bytes = 0;  // bytes this context copied over PCIe
     float4* d_origins = nullptr;   // rays path
     size_t d_origins_cap = 0;
@@ -251,7 +252,7 @@ int rtb_set_scene(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins, cons
     ctx->boxes.swap(boxes);
     ctx->sph_o.assign(sphereOrigins, sphereOrigins + 4 * (size_t)numSpheres);
     ctx->sph_r.assign(sphereRadius, sphereRadius + (size_t)numSpheres);
-    const int rc = ensure_records(ctx, 4 * (size_t)numCubes + 2 * (size_t)numSpheres);
+    const int rc = ensure_records(ctx, 6 * (size_t)numCubes + 4 * (size_t)numSpheres + 32);
     if (rc != RTB_OK) return rc;
     ctx->have_scene = true;
     return RTB_OK;
@@ -261,27 +262,45 @@ int rtb_set_scene(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins, cons
 
 namespace {
 
-// Packs one frame's records (3 per cube, then 1 per sphere) into dst (host).
-void pack_frame(const rtb_ctx* ctx, const CameraFrame& cf, float4* dst) {
+// One frame's records in d_rec / h_rec (float4 units):
+//   [0, 3nc)            RtbSlab x3 per cube      (reference-exact path, read through L2)
+//   [3nc, 3nc+ns)       RtbSphere per sphere
+//   [bound_offset, +2*n_bound)  RtbBound per primitive (cubes, spheres, "never" padding up to a
+//                       multiple of kBoundGroup): the list the grid kernel stages with TMA
+size_t exact_records(const rtb_ctx* ctx) { return 3 * (size_t)ctx->nc + (size_t)ctx->ns; }
+size_t bound_offset(const rtb_ctx* ctx) { return (exact_records(ctx) + 7) & ~(size_t)7; }  // 128-byte aligned
+int bound_count(const rtb_ctx* ctx) {
+    return (int)(((size_t)ctx->nc + (size_t)ctx->ns + kBoundGroup - 1) / kBoundGroup * kBoundGroup);
+}
+size_t frame_records(const rtb_ctx* ctx) { return bound_offset(ctx) + 2 * (size_t)bound_count(ctx); }
+
+void pack_frame(const rtb_ctx* ctx, const CameraFrame& cf, int width, int height, float4* dst) {
     RtbSlab* slabs = reinterpret_cast<RtbSlab*>(dst);
     for (int c = 0; c < ctx->nc; ++c) pack_box(cf, ctx->boxes[c], slabs + 3 * (size_t)c);
     RtbSphere* sph = reinterpret_cast<RtbSphere*>(dst + 3 * (size_t)ctx->nc);
     for (int s = 0; s < ctx->ns; ++s) pack_sphere(cf, &ctx->sph_o[4 * (size_t)s], ctx->sph_r[s], sph + s);
+    for (size_t i = exact_records(ctx); i < bound_offset(ctx); ++i) dst[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const FrameExtent fe = frame_extent(cf, width, height);
+    RtbBound* bnd = reinterpret_cast<RtbBound*>(dst + bound_offset(ctx));
+    for (int c = 0; c < ctx->nc; ++c) pack_bound_box(fe, slabs + 3 * (size_t)c, bnd + c);
+    for (int s = 0; s < ctx->ns; ++s) pack_bound_sphere(fe, sph[s], bnd + ctx->nc + s);
+    const RtbBound never = {0.f, 0.f, 0.f, 0.f, 0.f, 4.f, 0.f, 0.f};
+    for (int i = ctx->nc + ctx->ns; i < bound_count(ctx); ++i) bnd[i] = never;
 }
-
-size_t frame_records(const rtb_ctx* ctx) { return 3 * (size_t)ctx->nc + (size_t)ctx->ns; }
 
 // Packs this frame's records and enqueues their upload, unless d_rec already holds the records of
 // exactly this camera (same 16 floats, same scene).
-int upload_frame_records(rtb_ctx* ctx, const CameraFrame& cf, const float* o0, const float* du, const float* dv,
-                         const float* dir, cudaStream_t stream) {
+int upload_frame_records(rtb_ctx* ctx, const CameraFrame& cf, int width, int height, const float* o0,
+                         const float* du, const float* dv, const float* dir, cudaStream_t stream) {
     float cam16[16];
     std::memcpy(cam16, o0, 16); std::memcpy(cam16 + 4, du, 16);
     std::memcpy(cam16 + 8, dv, 16); std::memcpy(cam16 + 12, dir, 16);
-    if (ctx->packed_valid && std::memcmp(cam16, ctx->packed_cam, sizeof cam16) == 0) return RTB_OK;
+    if (ctx->packed_valid && ctx->packed_w == width && ctx->packed_h == height &&
+        std::memcmp(cam16, ctx->packed_cam, sizeof cam16) == 0)
+        return RTB_OK;
     // the pinned staging area is reused: the previous upload must have left it
     RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
-    pack_frame(ctx, cf, ctx->h_rec);
+    pack_frame(ctx, cf, width, height, ctx->h_rec);
     const size_t nrec = frame_records(ctx);
     if (nrec)
         RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, nrec * sizeof(float4), cudaMemcpyHostToDevice,
@@ -289,6 +308,7 @@ int upload_frame_records(rtb_ctx* ctx, const CameraFrame& cf, const float* o0, c
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_rec, stream));
     ctx->h2d_bytes += nrec * sizeof(float4);
     std::memcpy(ctx->packed_cam, cam16, sizeof cam16);
+    ctx->packed_w = width; ctx->packed_h = height;
     ctx->packed_valid = true;
     return RTB_OK;
 }
@@ -304,6 +324,8 @@ int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width
     p.n_cubes = ctx->nc; p.n_spheres = ctx->ns;
     p.cube_rec = d_rec;
     p.sph_rec = d_rec + 3 * (size_t)ctx->nc;
+    p.bound_rec = d_rec + bound_offset(ctx);
+    p.n_bound = bound_count(ctx);
     p.cube_col = ctx->d_cube_col;
     p.sph_col = ctx->d_sph_col;
     p.out_rgba8 = static_cast<uint32_t*>(d_rgba8);
@@ -361,7 +383,7 @@ int rtb_render_bands_device(rtb_ctx* ctx, int width, int height, const float ori
     if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
         return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
     cudaStream_t stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->stream;
-    rc = upload_frame_records(ctx, cf, origin0, dU, dV, rayDir, stream);
+    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, stream);
     if (rc != RTB_OK) return rc;
     const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
     rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, band_rows, band_rank, band_world, local_rows,
@@ -417,7 +439,7 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
     const double k_sum0 = ctx->kernel_ms_sum;
     cudaStream_t st = ctx->stream;
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total0, st));
-    rc = upload_frame_records(ctx, cf, origin0, dU, dV, rayDir, st);
+    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, st);
     if (rc != RTB_OK) return rc;
     rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, 4, 0, 1, height, host[0] ? ctx->d_out[0] : nullptr,
                       host[1] ? ctx->d_out[1] : nullptr, host[2] ? ctx->d_out[2] : nullptr, st);
@@ -533,7 +555,7 @@ int rtb_render_sequence_device(rtb_ctx* ctx, int width, int height, int n_frames
             std::snprintf(buf, sizeof buf, "degenerate camera in frame %d", f);
             return fail(ctx, RTB_ERR_CAMERA, buf);
         }
-        pack_frame(ctx, cf, ctx->h_rec + stride * (size_t)f);
+        pack_frame(ctx, cf, width, height, ctx->h_rec + stride * (size_t)f);
         cams[f] = cf.cam;
     }
     rc = resolve_pending(ctx);
@@ -611,6 +633,30 @@ int rtb_debug_pack(int numSpheres, const float* sphereOrigins, const float* sphe
             pack_sphere(cf, sphereOrigins + 4 * (size_t)s, sphereRadius[s],
                         reinterpret_cast<RtbSphere*>(sphere_rec) + s);
     if (cam) std::memcpy(cam, &cf.cam, sizeof(RtbCam));
+    return RTB_OK;
+}
+
+int rtb_debug_pack_bounds(int numSpheres, const float* sphereOrigins, const float* sphereRadius, int numCubes,
+                          const float* cubeVertices, int width, int height, const float origin0[4],
+                          const float dU[4], const float dV[4], const float rayDir[4], float* bound_rec) {
+    if (numSpheres < 0 || numCubes < 0 || width <= 0 || height <= 0 || !origin0 || !dU || !dV || !rayDir || !bound_rec)
+        return RTB_ERR_INVALID_ARG;
+    CameraFrame cf;
+    if (!camera_prepare(origin0, dU, dV, rayDir, &cf)) return RTB_ERR_CAMERA;
+    const FrameExtent fe = frame_extent(cf, width, height);
+    RtbBound* out = reinterpret_cast<RtbBound*>(bound_rec);
+    for (int c = 0; c < numCubes; ++c) {
+        Box b;
+        if (!box_from_vertices(cubeVertices + 144 * (size_t)c, &b)) return RTB_ERR_NOT_A_BOX;
+        RtbSlab slabs[3];
+        pack_box(cf, b, slabs);
+        pack_bound_box(fe, slabs, out + c);
+    }
+    for (int s = 0; s < numSpheres; ++s) {
+        RtbSphere sp;
+        pack_sphere(cf, sphereOrigins + 4 * (size_t)s, sphereRadius[s], &sp);
+        pack_bound_sphere(fe, sp, out + numCubes + s);
+    }
     return RTB_OK;
 }
 

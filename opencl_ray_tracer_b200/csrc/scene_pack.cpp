@@ -177,6 +177,151 @@ void pack_box(const CameraFrame& cf, const Box& box, RtbSlab out[3]) {
     }
 }
 
+// ---- conservative conic bounds -------------------------------------------------------------
+FrameExtent frame_extent(const CameraFrame& cf, int width, int height) {
+    // the kernel's own float constants: u = l11*x + l12*y, v = l22*y
+    const double l11 = cf.cam.l11, l12 = cf.cam.l12, l22 = cf.cam.l22;
+    const double xs[2] = {0.0, (double)(width > 0 ? width - 1 : 0)};
+    const double ys[2] = {0.0, (double)(height > 0 ? height - 1 : 0)};
+    FrameExtent fe;
+    fe.umin = fe.vmin = 1e300;
+    fe.umax = fe.vmax = -1e300;
+    for (int i = 0; i < 2; ++i)
+        for (int j = 0; j < 2; ++j) {
+            const double u = l11 * xs[i] + l12 * ys[j], v = l22 * ys[j];
+            fe.umin = std::fmin(fe.umin, u); fe.umax = std::fmax(fe.umax, u);
+            fe.vmin = std::fmin(fe.vmin, v); fe.vmax = std::fmax(fe.vmax, v);
+        }
+    fe.pitch = std::fmin(std::fabs(l11), std::fabs(l22));
+    const double grow = fe.pitch + 1e-5 * (std::fabs(fe.umin) + std::fabs(fe.umax) + std::fabs(fe.vmin) +
+                                           std::fabs(fe.vmax));
+    fe.umin -= grow; fe.umax += grow; fe.vmin -= grow; fe.vmax += grow;
+    fe.uabs = std::fmax(std::fabs(fe.umin), std::fabs(fe.umax));
+    fe.vabs = std::fmax(std::fabs(fe.vmin), std::fabs(fe.vmax));
+    return fe;
+}
+
+namespace {
+
+struct P2 { double u, v; };
+
+const RtbBound kBoundAlways = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // q = 0: every ray passes
+const RtbBound kBoundNever = {0.f, 0.f, 0.f, 0.f, 0.f, 4.f, 0.f, 0.f};   // q = 4: no ray passes
+
+// Keeps the part of the convex polygon `poly` (n vertices) with hu*u + hv*v + hc <= 0.
+int clip_halfplane(const P2* poly, int n, double hu, double hv, double hc, P2* out) {
+    int m = 0;
+    for (int i = 0; i < n; ++i) {
+        const P2 a = poly[i], b = poly[(i + 1) % n];
+        const double fa = hu * a.u + hv * a.v + hc, fb = hu * b.u + hv * b.v + hc;
+        if (fa <= 0.0) out[m++] = a;
+        if ((fa <= 0.0) != (fb <= 0.0)) {
+            const double t = fa / (fa - fb);
+            out[m++] = {a.u + t * (b.u - a.u), a.v + t * (b.v - a.v)};
+        }
+    }
+    return m;
+}
+
+// Ellipse  a*(u-cu)^2 + 2b*(u-cu)(v-cv) + d*(v-cv)^2 <= 1  ->  RtbBound scaled so that the fp32
+// Horner evaluation of any point inside stays below 2 (evaluation error bound errq).
+void emit_conic(const FrameExtent& fe, double cu, double cv, double a, double b, double d, RtbBound* out) {
+    const double A = a, muv = 2.0 * b, mu = -2.0 * (a * cu + b * cv), mvv = d, mv = -2.0 * (b * cu + d * cv),
+                 m0 = a * cu * cu + 2.0 * b * cu * cv + d * cv * cv;
+    const double U = fe.uabs, V = fe.vabs;
+    const double mag = std::fabs(A) * U * U + std::fabs(muv) * U * V + std::fabs(mu) * U + std::fabs(mvv) * V * V +
+                       std::fabs(mv) * V + std::fabs(m0);
+    const double errq = mag / 2097152.0;  // 2^-21: 6 coefficient roundings + 5 fma roundings, x(8/11) spare
+    const double s = 2.0 * (1.0 - 1.0 / 1024.0) / (1.0 + errq);
+    const RtbBound r = {(float)(s * A), (float)(s * muv), (float)(s * mu), (float)(s * mvv),
+                        (float)(s * mv), (float)(s * m0), 0.f, 0.f};
+    const bool ok = std::isfinite(r.A) && std::isfinite(r.m_uv) && std::isfinite(r.m_u) && std::isfinite(r.m_vv) &&
+                    std::isfinite(r.m_v) && std::isfinite(r.m_0) && std::isfinite(mag);
+    *out = ok ? r : kBoundAlways;
+}
+
+}  // namespace
+
+void pack_bound_box(const FrameExtent& fe, const RtbSlab slabs[3], RtbBound* out) {
+    double al[3], be[3], ga[3], wi[3], E[3];
+    for (int k = 0; k < 3; ++k) {
+        al[k] = slabs[k].alpha; be[k] = slabs[k].beta; ga[k] = slabs[k].gamma; wi[k] = slabs[k].width;
+        if (!std::isfinite(al[k]) || !std::isfinite(be[k]) || !std::isfinite(ga[k]) || !std::isfinite(wi[k])) {
+            *out = kBoundAlways;
+            return;
+        }
+        // fp32 error of near_k / far_k as the kernel computes them (2 fma + 1 add), doubled
+        E[k] = (std::fabs(al[k]) + std::fabs(be[k]) * fe.uabs + std::fabs(ga[k]) * fe.vabs + std::fabs(wi[k])) /
+               4194304.0;
+    }
+    // A hit needs near_i <= far_j for every pair: three strips in (u,v); clip the frame box by them.
+    P2 bufa[16], bufb[16];
+    P2* poly = bufa;
+    P2* next = bufb;
+    int n = 4;
+    poly[0] = {fe.umin, fe.vmin}; poly[1] = {fe.umax, fe.vmin};
+    poly[2] = {fe.umax, fe.vmax}; poly[3] = {fe.umin, fe.vmax};
+    for (int i = 0; i < 3 && n > 0; ++i)
+        for (int j = 0; j < 3 && n > 0; ++j) {
+            if (i == j) continue;
+            double hu = be[i] - be[j], hv = ga[i] - ga[j], hc = al[i] - al[j] - wi[j] - (E[i] + E[j]);
+            const double m = std::fmax(std::fabs(hu), std::fabs(hv));
+            if (!(m * (fe.uabs + fe.vabs) > 1e-9 * std::fabs(hc)) || m == 0.0) {
+                if (hc > 0.0) n = 0;  // constant and violated: the cube is never hit
+                continue;
+            }
+            hu /= m; hv /= m; hc /= m;
+            n = clip_halfplane(poly, n, hu, hv, hc, next);
+            P2* t = poly; poly = next; next = t;
+        }
+    if (n <= 0) {
+        *out = kBoundNever;
+        return;
+    }
+    double cu = 0.0, cv = 0.0;
+    for (int i = 0; i < n; ++i) { cu += poly[i].u; cv += poly[i].v; }
+    cu /= n; cv /= n;
+    // four symmetric helper points keep the fit non-degenerate (a clipped sliver, a single vertex)
+    const double r0 = 0.05 * fe.pitch;
+    poly[n] = {cu + r0, cv}; poly[n + 1] = {cu - r0, cv}; poly[n + 2] = {cu, cv + r0}; poly[n + 3] = {cu, cv - r0};
+    const int nt = n + 4;
+    double suu = 0.0, suv = 0.0, svv = 0.0;
+    for (int i = 0; i < nt; ++i) {
+        const double x = poly[i].u - cu, y = poly[i].v - cv;
+        suu += x * x; suv += x * y; svv += y * y;
+    }
+    suu /= nt; suv /= nt; svv /= nt;
+    const double det = suu * svv - suv * suv;
+    if (!(det > 0.0) || !std::isfinite(det)) {
+        *out = kBoundAlways;
+        return;
+    }
+    const double iuu = svv / det, iuv = -suv / det, ivv = suu / det;
+    double T = 0.0;
+    for (int i = 0; i < nt; ++i) {
+        const double x = poly[i].u - cu, y = poly[i].v - cv;
+        T = std::fmax(T, iuu * x * x + 2.0 * iuv * x * y + ivv * y * y);
+    }
+    T *= 1.0 + 1e-6;
+    emit_conic(fe, cu, cv, iuu / T, iuv / T, ivv / T, out);
+}
+
+void pack_bound_sphere(const FrameExtent& fe, const RtbSphere& sph, RtbBound* out) {
+    const double rho = sph.rho, uc = sph.uc, vc = sph.vc;
+    if (!std::isfinite(rho) || !std::isfinite(uc) || !std::isfinite(vc)) {
+        *out = kBoundAlways;
+        return;
+    }
+    if (rho < 0.0) {  // rtb_sphere_rad is then negative on every ray (two monotone roundings)
+        *out = kBoundNever;
+        return;
+    }
+    // rad >= 0 in fp32  =>  (uc-u)^2 + (vc-v)^2 <= rho*(1 + 3*2^-24 + ...)
+    const double r0 = 0.05 * fe.pitch;
+    const double T = rho * (1.0 + 1.0 / 1048576.0) + r0 * r0;
+    emit_conic(fe, uc, vc, 1.0 / T, 0.0, 1.0 / T, out);
+}
+
 void pack_box_world(const double dir3[3], const Box& box, float out[16]) {
     if (box.degenerate) {
         const float miss[16] = {0, 0, 0, 1e30f, 0, 0, 0, -1e30f, 0, 0, 0, -1e30f, 0, 0, 0, 0};

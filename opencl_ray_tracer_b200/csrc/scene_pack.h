@@ -40,6 +40,20 @@ bool camera_prepare(const float o0[4], const float du[4], const float dv[4], con
 void pack_sphere(const CameraFrame& cf, const float centre[4], float radius, RtbSphere* out);
 void pack_box(const CameraFrame& cf, const Box& box, RtbSlab out[3]);
 
+// Extent of a frame's ray grid in camera coordinates (pixels x in [0,W-1], y in [0,H-1]).
+struct FrameExtent {
+    double umin, umax, vmin, vmax;  // bounding box of the (u,v) image of the pixel grid
+    double uabs, vabs;              // max |u|, max |v| over the grid
+    double pitch;                   // min(l11, l22): (u,v) length of one pixel step
+};
+FrameExtent frame_extent(const CameraFrame& cf, int width, int height);
+
+// Conservative conic bounds (RtbBound, raycast_math.h) of the footprints that the float records
+// `slabs` / `sph` produce in the kernel's fp32 arithmetic: every pixel of the frame on which
+// rtb_cube_update / rtb_sphere_update can fire evaluates to q < 2 in fp32.
+void pack_bound_box(const FrameExtent& fe, const RtbSlab slabs[3], RtbBound* out);
+void pack_bound_sphere(const FrameExtent& fe, const RtbSphere& sph, RtbBound* out);
+
 // World-space records for the explicit-origin kernel: out[k] = (nx, ny, nz, alpha) with
 // near_k(O) = alpha + n.O for k = 0..2, out[3] = (w0, w1, w2, 0).  dir3 = rayDir.xyz.
 void pack_box_world(const double dir3[3], const Box& box, float out[16]);

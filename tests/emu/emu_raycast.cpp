@@ -52,3 +52,50 @@ extern "C" int emu_render_grid(int width, int height, const float* cam8, int nc,
     }
     return 0;
 }
+
+// Conservativeness of the conic bounds (RtbBound): walks every pixel x primitive exactly like the
+// kernel's dense loop and counts (a) pixels where the reference-exact update could fire
+// (footprint: slab interval non-empty / sphere rad >= 0) although the bound says "fail" --
+// must be 0 -- and (b) how many tests pass the bound vs how many are in the footprint
+// (selectivity, informational).  out[0] = violations, out[1] = bound passes, out[2] = footprint
+// tests, out[3] = total tests.
+extern "C" int emu_check_bounds(int width, int height, const float* cam8, int nc, const float* cube_rec, int ns,
+                                const float* sph_rec, const float* bound_rec, long long* out) {
+    const RtbCam cam = {cam8[0], cam8[1], cam8[2], cam8[3], cam8[4], 0.f, 0.f, 0.f};
+    const RtbSlab* slabs = reinterpret_cast<const RtbSlab*>(cube_rec);
+    const RtbSphere* sph = reinterpret_cast<const RtbSphere*>(sph_rec);
+    const RtbBound* bnd = reinterpret_cast<const RtbBound*>(bound_rec);
+    long long viol = 0, pass = 0, foot = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : viol, pass, foot)
+    for (int y = 0; y < height; ++y) {
+        const float fy = (float)y;
+        const float v = rtb_cam_v(cam, fy);
+        for (int x = 0; x < width; ++x) {
+            const float u = rtb_cam_u(cam, (float)x, fy);
+            for (int i = 0; i < nc + ns; ++i) {
+                const RtbBound& b = bnd[i];
+                const float q = rtb_bound_q(b.A, rtb_bound_row_b(b, v), rtb_bound_row_c(b, v), u);
+                uint32_t bits;
+                __builtin_memcpy(&bits, &q, 4);
+                const bool bound_pass = (bits & RTB_BOUND_FAIL_BIT) == 0u;
+                bool in_foot;
+                if (i < nc) {
+                    const RtbSlab &s0 = slabs[3 * i], &s1 = slabs[3 * i + 1], &s2 = slabs[3 * i + 2];
+                    const float n0 = rtb_slab_near(s0, rtb_slab_base(s0, v), u);
+                    const float n1 = rtb_slab_near(s1, rtb_slab_base(s1, v), u);
+                    const float n2 = rtb_slab_near(s2, rtb_slab_base(s2, v), u);
+                    const float f0 = n0 + s0.width, f1 = n1 + s1.width, f2 = n2 + s2.width;
+                    in_foot = fmaxf(fmaxf(n0, n1), n2) <= fminf(fminf(f0, f1), f2);
+                } else {
+                    const RtbSphere& s = sph[i - nc];
+                    in_foot = rtb_sphere_rad(s, rtb_sphere_radv(s, v), u) >= 0.0f;
+                }
+                pass += bound_pass;
+                foot += in_foot;
+                viol += (in_foot && !bound_pass);
+            }
+        }
+    }
+    out[0] = viol; out[1] = pass; out[2] = foot; out[3] = (long long)width * height * (nc + ns);
+    return 0;
+}

@@ -106,3 +106,14 @@ class Emulator:
         self.lib.emu_render_grid(w, h, fp(cam), scene.nc, fp(cr), scene.ns, fp(sr), fp(cc), fp(sc),
                                  ip(rgba), ip(pid), fp(tt))
         return rgba, pid, tt
+
+    def check_bounds(self, scene, w, h, camera=None):
+        """Walks the kernel's dense loop: returns dict(violations, bound_pass, footprint, total)."""
+        from opencl_ray_tracer_b200 import capi
+        camera = camera or capi.REFERENCE_CAMERA
+        cr, sr, cam = capi.debug_pack(scene.sph_o, scene.sph_r, scene.cube_v, camera)
+        bnd = capi.debug_pack_bounds(scene.sph_o, scene.sph_r, scene.cube_v, w, h, camera)
+        fp = lambda a: np.ascontiguousarray(a, np.float32).ctypes.data_as(C.POINTER(C.c_float))
+        out = (C.c_longlong * 4)()
+        self.lib.emu_check_bounds(w, h, fp(cam), scene.nc, fp(cr), scene.ns, fp(sr), fp(bnd), out)
+        return {"violations": out[0], "bound_pass": out[1], "footprint": out[2], "total": out[3]}

@@ -1,0 +1,66 @@
+"""The grid kernel's dense loop evaluates one conservative conic bound per (ray, primitive) and
+only rays that pass reach the reference-exact slab / sphere arithmetic.  The bound must therefore
+NEVER reject a ray on which that arithmetic could fire (else a pixel would change).  Checked here
+on the CPU by walking the kernel's fp32 arithmetic (tests/emu, same header as the kernel) over
+every pixel x primitive of several frames; the GPU tests additionally require kernel == emulator
+bit for bit, where the emulator does not use the bound at all."""
+import os
+
+import numpy as np
+import pytest
+
+from parity import GOLDEN, kat_names, load_npz_scene, to_oracle_scene
+
+
+def _check(emu, sc, w, h, cam=None, min_selectivity=None):
+    r = emu.check_bounds(sc, w, h, cam)
+    assert r["violations"] == 0, r
+    assert r["bound_pass"] >= r["footprint"]
+    if min_selectivity is not None and r["bound_pass"]:
+        assert r["footprint"] / r["bound_pass"] >= min_selectivity, r
+    return r
+
+
+def test_scene1(emu):
+    sc = load_npz_scene(np.load(os.path.join(GOLDEN, "scene1.npz")))
+    _check(emu, sc, 640, 480, min_selectivity=0.5)
+
+
+@pytest.mark.parametrize("name", kat_names())
+def test_known_answer_cases(emu, name):
+    z = np.load(os.path.join(GOLDEN, "kats.npz"))
+    _check(emu, load_npz_scene(z, name + "/"), 64, 48)
+
+
+@pytest.mark.parametrize("w,h,ns,nc,seed", [(640, 480, 100, 100, 7), (333, 201, 40, 3, 11), (512, 256, 0, 64, 5),
+                                            (1920, 1080, 16, 16, 2)])
+def test_random_scenes(emu, built_libs, w, h, ns, nc, seed):
+    from opencl_ray_tracer_b200 import host_scene as hs
+    r = _check(emu, to_oracle_scene(hs.random_scene(w, h, ns, nc, seed)), w, h, min_selectivity=0.5)
+    assert r["bound_pass"] < 0.05 * r["total"]  # the bound actually culls
+
+
+@pytest.mark.parametrize("k", [1, 17, 45, 90, 119])
+def test_orbit_cameras(emu, built_libs, k):
+    from opencl_ray_tracer_b200 import host_scene as hs
+    sc = to_oracle_scene(hs.random_scene(480, 360, 48, 48, 9))
+    _check(emu, sc, 480, 360, hs.orbit_camera(480, 360, k), min_selectivity=0.3)
+
+
+def test_tiny_huge_and_offscreen_primitives(emu, built_libs):
+    """Sub-pixel, frame-filling and off-screen primitives; far-from-origin coordinates."""
+    from opencl_ray_tracer_b200 import host_scene as hs
+    rng = np.random.default_rng(5)
+    base = hs.random_scene(256, 192, 24, 24, 3)
+    sc = to_oracle_scene(base)
+    scale = np.array([1e-3, 0.02, 0.3, 1.0, 8.0, 40.0])
+    sph_r = sc.sph_r * scale[rng.integers(0, len(scale), len(sc.sph_r))]
+    cube_v = sc.cube_v.reshape(-1, 36, 4).copy()
+    for c in range(len(cube_v)):
+        ctr = cube_v[c, :, :3].mean(0)
+        cube_v[c, :, :3] = ctr + (cube_v[c, :, :3] - ctr) * scale[rng.integers(0, len(scale))]
+        if c % 5 == 0:
+            cube_v[c, :, 0] += 1000.0  # off screen
+    from oracle.oracle import Scene
+    sc2 = Scene(sc.sph_o, sph_r.astype(np.float32), sc.sph_c, cube_v, sc.cube_c)
+    _check(emu, sc2, 256, 192)
