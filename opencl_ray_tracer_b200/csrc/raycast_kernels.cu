@@ -56,11 +56,34 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     } while (!done);
 }
 
+// Packed FP32 pairs (sm_100 FFMA2): one 64-bit register pair = two rays' values.
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ void unpack2u(uint64_t v, uint32_t& lo, uint32_t& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {  // two IEEE fmaf
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
 template <int PX>
 struct PixelState {
-    float u[PX];
+    uint64_t u2[PX / 2];  // camera u of rays (2j, 2j+1), packed for FFMA2
     float best[PX];
     int id[PX];
+    __device__ __forceinline__ float u(int q) const {
+        float lo, hi;
+        unpack2(u2[q >> 1], lo, hi);
+        return (q & 1) ? hi : lo;
+    }
 };
 
 // Reference-exact nearest-hit update of primitive `prim` on this thread's PX rays (the arithmetic
@@ -75,9 +98,9 @@ __device__ __forceinline__ void exact_update(const GridParams& p, int prim, floa
         const float b0 = rtb_slab_base(s0, v), b1 = rtb_slab_base(s1, v), b2 = rtb_slab_base(s2, v);
 #pragma unroll
         for (int q = 0; q < PX; ++q) {
-            const float n0 = rtb_slab_near(s0, b0, st.u[q]);
-            const float n1 = rtb_slab_near(s1, b1, st.u[q]);
-            const float n2 = rtb_slab_near(s2, b2, st.u[q]);
+            const float n0 = rtb_slab_near(s0, b0, st.u(q));
+            const float n1 = rtb_slab_near(s1, b1, st.u(q));
+            const float n2 = rtb_slab_near(s2, b2, st.u(q));
             const float f0 = n0 + s0.width, f1 = n1 + s1.width, f2 = n2 + s2.width;
             const float tn = fmaxf(fmaxf(n0, n1), n2);
             const float tf = fminf(fminf(f0, f1), f2);
@@ -90,8 +113,8 @@ __device__ __forceinline__ void exact_update(const GridParams& p, int prim, floa
         const float wv = p.cam.tau_v * v;
 #pragma unroll
         for (int q = 0; q < PX; ++q) {
-            const float rad = rtb_sphere_rad(sp, radv, st.u[q]);
-            const float wpix = fmaf(p.cam.tau_u, st.u[q], wv);
+            const float rad = rtb_sphere_rad(sp, radv, st.u(q));
+            const float wpix = fmaf(p.cam.tau_u, st.u(q), wv);
             rtb_sphere_update(sp, rad, wpix, prim, st.best[q], st.id[q]);
         }
     }
@@ -111,12 +134,16 @@ __device__ __forceinline__ void bound_group(const GridParams& p, const float4* _
         const float2 r1 = *reinterpret_cast<const float2*>(rec + 2 * g + 1);      // m_v, m_0
         const RtbBound b = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, 0.f, 0.f};
         const float rowB = rtb_bound_row_b(b, v), rowC = rtb_bound_row_c(b, v);
+        // q = (A*u + B)*u + C on two rays per FFMA2 (same two roundings per ray as rtb_bound_q)
+        const uint64_t A2 = pack2(b.A, b.A), B2 = pack2(rowB, rowB), C2 = pack2(rowC, rowC);
         uint32_t a = 0xFFFFFFFFu;
 #pragma unroll
-        for (int q = 0; q < PX; q += 2) {
-            const float q0 = rtb_bound_q(b.A, rowB, rowC, st.u[q]);
-            const float q1 = rtb_bound_q(b.A, rowB, rowC, st.u[q + 1]);
-            a &= __float_as_uint(q0) & __float_as_uint(q1);
+        for (int j = 0; j < PX / 2; ++j) {
+            const uint64_t t2 = ffma2(st.u2[j], A2, B2);
+            const uint64_t q2 = ffma2(st.u2[j], t2, C2);
+            uint32_t q0, q1;
+            unpack2u(q2, q0, q1);
+            a &= q0 & q1;
         }
         acc[g] = a;
     }
@@ -183,10 +210,10 @@ raycast_grid_kernel(const GridParams p) {
     const float fy = (float)gy;
     const float v = rtb_cam_v(p.cam, fy);
 #pragma unroll
-    for (int q = 0; q < PX; ++q) {
-        st.u[q] = rtb_cam_u(p.cam, (float)(x0 + q), fy);
-        st.best[q] = RTB_MISS_T;
-        st.id[q] = -1;
+    for (int q = 0; q < PX; q += 2) {
+        st.u2[q >> 1] = pack2(rtb_cam_u(p.cam, (float)(x0 + q), fy), rtb_cam_u(p.cam, (float)(x0 + q + 1), fy));
+        st.best[q] = st.best[q + 1] = RTB_MISS_T;
+        st.id[q] = st.id[q + 1] = -1;
     }
 
     for (int k = 0; k < n_chunks; ++k) {
