@@ -32,17 +32,18 @@ BAND_ROWS = 16
 
 # FP32 operations the shipped kernel executes per ray-primitive test (FMA = 2).  Cubes and
 # spheres go through the same dense loop: the primitive's conic footprint bound q(u,v) is evaluated on
-# every ray with 2 FFMA (q = (A*u + B)*u + C) = 4 flop; per thread and primitive 3 FFMA of row terms
-# (B, C) = 6 flop amortised over the PX rays a thread owns (PX = 16 at the roofline point).  The
+# every ray with 2 FMA (w = sA*u + rowW; q = w*w + rowC; issued as FFMA2 on ray pairs) = 4 flop; per thread
+# and primitive the row terms (1 FFMA + 1 FADD + 2 FMUL) = 5 flop amortised over the PX rays a thread owns
+# (PX = 16 at the roofline point).  The
 # reference-exact slab / sphere arithmetic runs only on rays inside a bound (a few per mille of the
 # tests) and is NOT counted.  Bit-pattern ANDs, votes, compares count 0.
 FLOP_PER_TEST_RAY = 4.0
-FLOP_PER_TEST_ROW = 6.0
+FLOP_PER_TEST_ROW = 5.0
 
 
 def grid_px(width, rows, sms):
     """Rays per thread of the kernel variant grid_launch_shape() picks (raycast_kernels.cu)."""
-    for px, tw, th in ((16, 256, 16), (8, 128, 16)):
+    for px, tw, th in ((16, 256, 8), (8, 128, 16)):
         if -(-width // tw) * -(-rows // th) >= 2 * sms:
             return px
     return 4

@@ -17,6 +17,8 @@
 // emulator in tests/emu reproduces the kernel bit for bit.
 #include "raycast_kernels.cuh"
 
+#include <cstdlib>
+
 namespace rtb {
 
 namespace {
@@ -121,8 +123,9 @@ __device__ __forceinline__ void exact_update(const GridParams& p, int prim, floa
 }
 
 // The dense test: G primitives of a staged chunk against this thread's PX rays.  Per ray and
-// primitive 2 FFMA (conic bound q) + half a LOP3 (AND of the IEEE patterns: bit 30 survives only
-// if every ray has q >= 2); per thread and primitive 1 LDS.128 + 1 LDS.64 + 3 FFMA (row terms);
+// primitive 2 FMA as one FFMA2 per ray pair and stage (conic bound q) + half a LOP3 (AND of the
+// IEEE patterns: bit 30 survives only if every ray has q >= 2); per thread and primitive
+// 1 LDS.128 + 1 LDS.32 + 4 FP32 ops (row terms);
 // one warp vote per G primitives.
 template <int PX, int G>
 __device__ __forceinline__ void bound_group(const GridParams& p, const float4* __restrict__ rec, int first_prim,
@@ -130,17 +133,17 @@ __device__ __forceinline__ void bound_group(const GridParams& p, const float4* _
     uint32_t acc[G];
 #pragma unroll
     for (int g = 0; g < G; ++g) {
-        const float4 r0 = rec[2 * g];                                            // A, m_uv, m_u, m_vv
-        const float2 r1 = *reinterpret_cast<const float2*>(rec + 2 * g + 1);      // m_v, m_0
-        const RtbBound b = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, 0.f, 0.f};
-        const float rowB = rtb_bound_row_b(b, v), rowC = rtb_bound_row_c(b, v);
-        // q = (A*u + B)*u + C on two rays per FFMA2 (same two roundings per ray as rtb_bound_q)
-        const uint64_t A2 = pack2(b.A, b.A), B2 = pack2(rowB, rowB), C2 = pack2(rowC, rowC);
+        const float4 r0 = rec[2 * g];                                 // sA, k1, k0, e
+        const float r1 = *reinterpret_cast<const float*>(rec + 2 * g + 1);  // cv
+        const RtbBound b = {r0.x, r0.y, r0.z, r0.w, r1, 0.f, 0.f, 0.f};
+        const float rowW = rtb_bound_row_w(b, v), rowC = rtb_bound_row_c(b, v);
+        // w = sA*u + rowW; q = w*w + rowC on two rays per FFMA2 (same roundings per ray as rtb_bound_q)
+        const uint64_t S2 = pack2(b.sA, b.sA), W2 = pack2(rowW, rowW), C2 = pack2(rowC, rowC);
         uint32_t a = 0xFFFFFFFFu;
 #pragma unroll
         for (int j = 0; j < PX / 2; ++j) {
-            const uint64_t t2 = ffma2(st.u2[j], A2, B2);
-            const uint64_t q2 = ffma2(st.u2[j], t2, C2);
+            const uint64_t w2 = ffma2(st.u2[j], S2, W2);
+            const uint64_t q2 = ffma2(w2, w2, C2);
             uint32_t q0, q1;
             unpack2u(q2, q0, q1);
             a &= q0 & q1;
@@ -161,13 +164,13 @@ __device__ __forceinline__ void bound_group(const GridParams& p, const float4* _
     }
 }
 
-template <int PX, int WARPS_X, int WARPS_Y>
-__global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y)
+template <int PX, int WARPS_X, int WARPS_Y, int G = kBoundGroup, int MIN_CTAS = (PX >= 16 ? 3 : 4)>
+__global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y, MIN_CTAS)
 raycast_grid_kernel(const GridParams p) {
     constexpr int kThreads = 32 * WARPS_X * WARPS_Y;
     constexpr int kTileW = WARPS_X * 8 * PX;
     constexpr int kTileH = WARPS_Y * 4;
-    constexpr int G = kBoundGroup;
+    static_assert(kBoundGroup % G == 0, "the host pads the bound list to kBoundGroup");
     __shared__ __align__(128) float4 stage[2][2 * kChunkPrims];
     __shared__ __align__(8) uint64_t full_bar[2];
     (void)kThreads;
@@ -338,18 +341,43 @@ GridLaunchShape shape_of(int width, int local_rows) {
 }  // namespace
 
 GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
-    GridLaunchShape big = shape_of<16, 2, 4>(width, local_rows);
+    GridLaunchShape big = shape_of<16, 2, 2>(width, local_rows);
     if ((long long)big.grid.x * big.grid.y >= 2LL * sm_count) return big;
     GridLaunchShape mid = shape_of<8, 2, 4>(width, local_rows);
     if ((long long)mid.grid.x * mid.grid.y >= 2LL * sm_count) return mid;
     return shape_of<4, 2, 2>(width, local_rows);
 }
 
+// Experiment hook (profiles/): RTB_GRID_VARIANT=n picks another tiling of the same kernel.
+template <int PX, int WX, int WY, int G, int MINB>
+cudaError_t launch_variant(const GridParams& p, cudaStream_t stream) {
+    const GridLaunchShape s = shape_of<PX, WX, WY>(p.width, p.local_rows);
+    if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
+    raycast_grid_kernel<PX, WX, WY, G, MINB><<<s.grid, s.block, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) {
+    static const int variant = [] {
+        const char* e = std::getenv("RTB_GRID_VARIANT");
+        return e ? std::atoi(e) : 0;
+    }();
+    switch (variant) {
+        case 1: return launch_variant<16, 2, 4, 2, 3>(p, stream);
+        case 2: return launch_variant<16, 2, 4, 4, 2>(p, stream);
+        case 3: return launch_variant<32, 2, 4, 4, 1>(p, stream);
+        case 4: return launch_variant<32, 2, 4, 2, 2>(p, stream);
+        case 5: return launch_variant<16, 2, 4, 4, 3>(p, stream);
+        case 6: return launch_variant<16, 1, 4, 4, 6>(p, stream);
+        case 7: return launch_variant<8, 2, 4, 4, 4>(p, stream);
+        case 8: return launch_variant<16, 2, 4, 1, 3>(p, stream);
+        case 9: return launch_variant<16, 2, 4, 4, 1>(p, stream);
+        default: break;
+    }
     const GridLaunchShape s = grid_launch_shape(p.width, p.local_rows, sm_count);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
     if (s.px == 16)
-        raycast_grid_kernel<16, 2, 4><<<s.grid, s.block, 0, stream>>>(p);
+        raycast_grid_kernel<16, 2, 2, kBoundGroup, 4><<<s.grid, s.block, 0, stream>>>(p);
     else if (s.px == 8)
         raycast_grid_kernel<8, 2, 4><<<s.grid, s.block, 0, stream>>>(p);
     else

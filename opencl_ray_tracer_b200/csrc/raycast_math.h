@@ -94,21 +94,29 @@ RTB_HD float rtb_sphere_t_reference(const float o[4], const float d[4], float ra
 
 // ---- conservative screen-space bound (the dense per-ray test of the grid kernel) -------------
 // Every primitive's footprint under the frame's parallel projection is convex (a cube projects
-// to a hexagon, a sphere to a disc), so the host encloses it in one conic
-//   q(u,v) = A*u^2 + m_uv*u*v + m_u*u + m_vv*v^2 + m_v*v + m_0,   footprint  =>  q < 2
-// (scaled so that fp32 evaluation error cannot push a footprint pixel to q >= 2; scene_pack.cpp).
-// Per ray and primitive the kernel evaluates q with 2 FFMA; "q >= 2 or NaN" is bit 30 of the
-// IEEE pattern, so a thread ANDs the patterns of its rays and tests one bit per primitive.  Only
-// rays that pass reach the reference-exact slab / sphere arithmetic above, therefore the bound
-// never changes a pixel: results are those of rtb_cube_update / rtb_sphere_update alone.
-struct RtbBound { float A, m_uv, m_u, m_vv, m_v, m_0, pad0, pad1; };  // 32 B = LDS.128 + LDS.64
+// to a hexagon, a sphere to a disc), so the host encloses it in one ellipse, written with the
+// square completed in u:
+//   q(u,v) = w^2 + e*(v - cv)^2,   w = sA*u + (k1*v + k0),      footprint  =>  q < 2
+// (scaled so that fp32 evaluation error cannot push a footprint ray to q >= 2; scene_pack.cpp).
+// Per ray and primitive the kernel evaluates q with 2 FFMA (w, then w*w + rowC); "q >= 2 or NaN"
+// is bit 30 of the IEEE pattern, so a thread ANDs the patterns of its rays and tests one bit per
+// primitive.  Only rays that pass reach the reference-exact slab / sphere arithmetic above,
+// therefore the bound never changes a pixel: results are those of rtb_cube_update /
+// rtb_sphere_update alone.
+struct RtbBound { float sA, k1, k0, e, cv, pad0, pad1, pad2; };  // 32 B: LDS.128 + LDS.32
 
 #define RTB_BOUND_FAIL_BIT 0x40000000u  // set <=> |q| >= 2 (or Inf/NaN)
 
-// per row: B = m_uv*v + m_u, C = (m_vv*v + m_v)*v + m_0;  per ray: q = (A*u + B)*u + C
-RTB_HD float rtb_bound_row_b(const RtbBound& b, float v) { return fmaf(b.m_uv, v, b.m_u); }
-RTB_HD float rtb_bound_row_c(const RtbBound& b, float v) { return fmaf(fmaf(b.m_vv, v, b.m_v), v, b.m_0); }
-RTB_HD float rtb_bound_q(float A, float rowB, float rowC, float u) { return fmaf(fmaf(A, u, rowB), u, rowC); }
+// per row: rowW = k1*v + k0, rowC = (e*(v-cv))*(v-cv);  per ray: w = sA*u + rowW, q = w*w + rowC
+RTB_HD float rtb_bound_row_w(const RtbBound& b, float v) { return fmaf(b.k1, v, b.k0); }
+RTB_HD float rtb_bound_row_c(const RtbBound& b, float v) {
+    const float dv = v - b.cv;
+    return (b.e * dv) * dv;
+}
+RTB_HD float rtb_bound_q(float sA, float rowW, float rowC, float u) {
+    const float w = fmaf(u, sA, rowW);
+    return fmaf(w, w, rowC);
+}
 
 // Depth-fog shade + (int) truncation, MainState.cpp:397-407, misc/Utility.cpp:109-116,
 // MainState.cpp:952-955.  Same operation order as the reference; no contraction.

@@ -25,6 +25,8 @@ struct rtb_ctx {
     int clock_khz = 0;
     char name[128] = {0};
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;  // device->host copies of finished row chunks (rtb_render)
+    cudaEvent_t ev_chunk[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::string last_error;
 
     // scene (host copies, reference layout) + recovered boxes
@@ -174,7 +176,10 @@ int rtb_init(rtb_ctx** out, int n_devices, const int* device_ids) {
     ctx->sm_count = prop.multiProcessorCount;
     cudaDeviceGetAttribute(&ctx->clock_khz, cudaDevAttrClockRate, dev);
     std::snprintf(ctx->name, sizeof ctx->name, "%s", prop.name);
-    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+    bool chunk_ok = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; i < 8 && chunk_ok; ++i)
+        chunk_ok = cudaEventCreateWithFlags(&ctx->ev_chunk[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!chunk_ok || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&ctx->ev_total0) != cudaSuccess || cudaEventCreate(&ctx->ev_total1) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_rec, cudaEventDisableTiming) != cudaSuccess ||
         configure_kernels() != cudaSuccess) {
@@ -200,6 +205,9 @@ void rtb_shutdown(rtb_ctx* ctx) {
     if (ctx->h_rec) cudaFreeHost(ctx->h_rec);
     for (int i = 0; i < 3; ++i) cudaFree(ctx->d_out[i]);
     cudaFree(ctx->d_origins);
+    for (int i = 0; i < 8; ++i)
+        if (ctx->ev_chunk[i]) cudaEventDestroy(ctx->ev_chunk[i]);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -284,7 +292,7 @@ void pack_frame(const rtb_ctx* ctx, const CameraFrame& cf, int width, int height
     RtbBound* bnd = reinterpret_cast<RtbBound*>(dst + bound_offset(ctx));
     for (int c = 0; c < ctx->nc; ++c) pack_bound_box(fe, slabs + 3 * (size_t)c, bnd + c);
     for (int s = 0; s < ctx->ns; ++s) pack_bound_sphere(fe, sph[s], bnd + ctx->nc + s);
-    const RtbBound never = {0.f, 0.f, 0.f, 0.f, 0.f, 4.f, 0.f, 0.f};
+    const RtbBound never = {0.f, 0.f, 2.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // w = 2, q = 4
     for (int i = ctx->nc + ctx->ns; i < bound_count(ctx); ++i) bnd[i] = never;
 }
 
@@ -441,15 +449,37 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total0, st));
     rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, st);
     if (rc != RTB_OK) return rc;
-    rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, 4, 0, 1, height, host[0] ? ctx->d_out[0] : nullptr,
-                      host[1] ? ctx->d_out[1] : nullptr, host[2] ? ctx->d_out[2] : nullptr, st);
-    if (rc != RTB_OK) return rc;
-    for (int i = 0; i < 3; ++i)
-        if (host[i]) {
-            RTB_CUDA(ctx, cudaMemcpyAsync(host[i], ctx->d_out[i], bytes[i], cudaMemcpyDeviceToHost, st));
-            ctx->d2h_bytes += bytes[i];
+    // The frame is rendered as up to 4 chunks of whole rows; chunk k travels to the host on
+    // copy_stream while chunk k+1 is still being rendered (the reference's OpenCL path does one
+    // blocking clEnqueueMapBuffer after the kernel, MainState.cpp:876-886).
+    const bool any_host = host[0] || host[1] || host[2];
+    int n_chunks = (any_host && height >= 256) ? 4 : 1;
+    int chunk_rows = ((height + n_chunks - 1) / n_chunks + 7) & ~7;
+    n_chunks = (height + chunk_rows - 1) / chunk_rows;
+    const size_t elem[3] = {4, 4, 16};
+    cudaStream_t cs = (n_chunks > 1) ? ctx->copy_stream : st;
+    for (int k = 0; k < n_chunks; ++k) {
+        const int y0 = k * chunk_rows;
+        const int rows = (height - y0 < chunk_rows) ? (height - y0) : chunk_rows;
+        void* d[3];
+        for (int i = 0; i < 3; ++i)
+            d[i] = host[i] ? static_cast<uint8_t*>(ctx->d_out[i]) + elem[i] * (size_t)y0 * width : nullptr;
+        rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, chunk_rows, k, n_chunks, rows, d[0], d[1], d[2], st);
+        if (rc != RTB_OK) return rc;
+        if (n_chunks > 1) {
+            RTB_CUDA(ctx, cudaEventRecord(ctx->ev_chunk[k], st));
+            RTB_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_chunk[k], 0));
         }
-    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total1, st));
+        for (int i = 0; i < 3; ++i)
+            if (host[i]) {
+                const size_t nb = elem[i] * (size_t)rows * width;
+                RTB_CUDA(ctx, cudaMemcpyAsync(static_cast<uint8_t*>(host[i]) + elem[i] * (size_t)y0 * width, d[i], nb,
+                                              cudaMemcpyDeviceToHost, cs));
+                ctx->d2h_bytes += nb;
+            }
+    }
+    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total1, cs));
+    RTB_CUDA(ctx, cudaStreamSynchronize(cs));
     RTB_CUDA(ctx, cudaStreamSynchronize(st));
     rc = resolve_pending(ctx);
     if (rc != RTB_OK) return rc;

@@ -206,7 +206,7 @@ namespace {
 struct P2 { double u, v; };
 
 const RtbBound kBoundAlways = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // q = 0: every ray passes
-const RtbBound kBoundNever = {0.f, 0.f, 0.f, 0.f, 0.f, 4.f, 0.f, 0.f};   // q = 4: no ray passes
+const RtbBound kBoundNever = {0.f, 0.f, 2.f, 0.f, 0.f, 0.f, 0.f, 0.f};   // w = 2, q = 4: no ray passes
 
 // Keeps the part of the convex polygon `poly` (n vertices) with hu*u + hv*v + hc <= 0.
 int clip_halfplane(const P2* poly, int n, double hu, double hv, double hc, P2* out) {
@@ -223,21 +223,39 @@ int clip_halfplane(const P2* poly, int n, double hu, double hv, double hc, P2* o
     return m;
 }
 
-// Ellipse  a*(u-cu)^2 + 2b*(u-cu)(v-cv) + d*(v-cv)^2 <= 1  ->  RtbBound scaled so that the fp32
-// Horner evaluation of any point inside stays below 2 (evaluation error bound errq).
+// Ellipse  a*(u-cu)^2 + 2b*(u-cu)(v-cv) + d*(v-cv)^2 <= 1  ->  RtbBound.  Completing the square,
+//   Q = a*[(u-cu) + (b/a)(v-cv)]^2 + (d - b^2/a)*(v-cv)^2,
+// and q = s*Q with the largest s for which the fp32 evaluation (rtb_bound_q) of any point with
+// Q <= 1 stays below 2 (error budget below).
 void emit_conic(const FrameExtent& fe, double cu, double cv, double a, double b, double d, RtbBound* out) {
-    const double A = a, muv = 2.0 * b, mu = -2.0 * (a * cu + b * cv), mvv = d, mv = -2.0 * (b * cu + d * cv),
-                 m0 = a * cu * cu + 2.0 * b * cu * cv + d * cv * cv;
+    if (!(a > 0.0) || !std::isfinite(a) || !std::isfinite(b) || !std::isfinite(d) || !std::isfinite(cu) ||
+        !std::isfinite(cv)) {
+        *out = kBoundAlways;
+        return;
+    }
+    const double k = b / a;
+    const double e0 = std::fmax(d - b * b / a, 0.0);
     const double U = fe.uabs, V = fe.vabs;
-    const double mag = std::fabs(A) * U * U + std::fabs(muv) * U * V + std::fabs(mu) * U + std::fabs(mvv) * V * V +
-                       std::fabs(mv) * V + std::fabs(m0);
-    const double errq = mag / 2097152.0;  // 2^-21: 6 coefficient roundings + 5 fma roundings, x(8/11) spare
-    const double s = 2.0 * (1.0 - 1.0 / 1024.0) / (1.0 + errq);
-    const RtbBound r = {(float)(s * A), (float)(s * muv), (float)(s * mu), (float)(s * mvv),
-                        (float)(s * mv), (float)(s * m0), 0.f, 0.f};
-    const bool ok = std::isfinite(r.A) && std::isfinite(r.m_uv) && std::isfinite(r.m_u) && std::isfinite(r.m_vv) &&
-                    std::isfinite(r.m_v) && std::isfinite(r.m_0) && std::isfinite(mag);
-    *out = ok ? r : kBoundAlways;
+    const double eps22 = 1.0 / 4194304.0;
+    double s = 2.0 * (1.0 - 1.0 / 512.0);
+    for (int it = 0; it < 400; ++it, s *= 0.9) {
+        const double sA = std::sqrt(s * a), k1 = sA * k, k0 = -sA * (cu + k * cv), e = s * e0;
+        // |w_fp32 - w| <= ew: roundings of sA, k1, k0 (double -> float) and of the two fma
+        const double ew = eps22 * (sA * U + std::fabs(k1) * V + std::fabs(k0));
+        // |rowC_fp32 - rowC| <= ec: rounding of cv inside dv (rowC <= 2 there, so e*|dv| <= sqrt(2e)),
+        // plus three relative roundings of the products
+        const double ec = eps22 * (std::sqrt(2.0 * e) * (std::fabs(cv) + V) + 2.0);
+        const double wmax = std::sqrt(s) + ew;
+        const double worst = s * (1.0 + 1.0 / 1048576.0) + 2.0 * wmax * ew + ew * ew + ec;
+        if (worst < 2.0 * (1.0 - 1.0 / 4096.0)) {
+            const RtbBound r = {(float)sA, (float)k1, (float)k0, (float)e, (float)cv, 0.f, 0.f, 0.f};
+            const bool ok = std::isfinite(r.sA) && std::isfinite(r.k1) && std::isfinite(r.k0) &&
+                            std::isfinite(r.e) && std::isfinite(r.cv);
+            *out = ok ? r : kBoundAlways;
+            return;
+        }
+    }
+    *out = kBoundAlways;
 }
 
 }  // namespace

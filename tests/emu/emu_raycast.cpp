@@ -74,7 +74,7 @@ extern "C" int emu_check_bounds(int width, int height, const float* cam8, int nc
             const float u = rtb_cam_u(cam, (float)x, fy);
             for (int i = 0; i < nc + ns; ++i) {
                 const RtbBound& b = bnd[i];
-                const float q = rtb_bound_q(b.A, rtb_bound_row_b(b, v), rtb_bound_row_c(b, v), u);
+                const float q = rtb_bound_q(b.sA, rtb_bound_row_w(b, v), rtb_bound_row_c(b, v), u);
                 uint32_t bits;
                 __builtin_memcpy(&bits, &q, 4);
                 const bool bound_pass = (bits & RTB_BOUND_FAIL_BIT) == 0u;
