@@ -63,6 +63,7 @@ def parse_args():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-peer", action="store_true", help="N > 1: NCCL gather instead of peer-memory stores")
     return ap.parse_args()
 
 
@@ -211,6 +212,15 @@ def run_ours(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     h_frame = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
 
+    # N > 1: every rank's kernel stores its bands straight into rank 0's frame over NVLink (CUDA IPC
+    # mapping); falls back to the NCCL gather + de-interleave kernel if IPC is refused.
+    peer = None
+    if world > 1 and not args.no_peer:
+        peer = bands.PeerFrame(dist, ctx, w, h, rank, world)
+        if not peer.ok:
+            peer = None
+    peer_frame = peer.as_tensor() if (peer and rank == 0) else None
+
     def gather_and_assemble():
         if world == 1:
             return 0
@@ -221,6 +231,10 @@ def run_ours(args):
         return 0
 
     def device_step():
+        if peer:
+            peer.render(cam, BAND_ROWS, sptr)
+            peer.fence()                   # 4-byte all-reduce on this stream: every rank's stores have landed
+            return 1
         ctx.render_bands_device(w, h, cam, BAND_ROWS, rank, world, d_rgba8=my_slice.data_ptr(), stream=sptr)
         return 1 + gather_and_assemble()
 
@@ -230,10 +244,15 @@ def run_ours(args):
         if world == 1:
             ctx.render(w, h, cam, want=("rgba8",), out={"rgba8": h_np})
             return 1
-        ctx.render_bands_device(w, h, cam, BAND_ROWS, rank, world, d_rgba8=my_slice.data_ptr(), stream=sptr)
-        n = 1 + gather_and_assemble()
+        if peer:
+            peer.render(cam, BAND_ROWS, sptr)
+            peer.fence()
+            n = 1
+        else:
+            ctx.render_bands_device(w, h, cam, BAND_ROWS, rank, world, d_rgba8=my_slice.data_ptr(), stream=sptr)
+            n = 1 + gather_and_assemble()
         if rank == 0:
-            h_frame.copy_(d_frame, non_blocking=True)
+            h_frame.copy_(peer_frame if peer else d_frame, non_blocking=True)
         stream.synchronize()
         return n
 
@@ -291,7 +310,7 @@ def run_ours(args):
     h2d_per_step = (h2d1 - h2d0) / args.steps
     return dict(rank=rank, world=world, w=w, h=h, ns=ns, nc=nc, seed=seed, scene=scene, ctx=ctx,
                 ms_per_step=ms_per_step, wall_ms_per_step=wall * 1e3 / args.steps, k_avg_ms=k_avg_ms, k_n=k_n,
-                launches=launches, clocks=sampler.result(), e2e_s=e2e_s, h2d=h2d_per_step, d2h=d2h_per_step,
+                launches=launches, clocks=sampler.result(), peer=bool(peer), e2e_s=e2e_s, h2d=h2d_per_step, d2h=d2h_per_step,
                 my_rows=my_rows)
 
 
@@ -418,7 +437,10 @@ def main():
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(args.workload),
                        "parallelism": "interleaved %d-row bands over %d GPU(s)%s" % (
-                           BAND_ROWS, r["world"], ", NCCL gather to rank 0 + de-interleave kernel" if r["world"] > 1 else ""),
+                           BAND_ROWS, r["world"],
+                           "" if r["world"] == 1 else
+                           (", kernels store into rank 0's frame over NVLink peer memory + 4-byte NCCL all-reduce as the fence"
+                            if r["peer"] else ", NCCL gather to rank 0 + de-interleave kernel")),
                        "l2": "256 MiB buffer written between timed iterations (L2 flush); per-step CUDA events"},
             "tests_per_s": mrays * 1e6 * (ns + nc),
             "wall_ms_per_step_incl_flush": r["wall_ms_per_step"],
@@ -426,7 +448,10 @@ def main():
             "e2e": {"value": n_px * args.steps / r["e2e_s"] / 1e6, "unit": "Mrays/s",
                     "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                     "ms_per_step": r["e2e_s"] * 1e3 / args.steps,
-                    "what": "rtb_set_scene + rtb_render into pinned host memory (N=1) / bands + NCCL gather + D2H (N>1)"},
+                    "what": ("rtb_set_scene + rtb_render (row chunks pipelined with their D2H copies) into pinned host memory"
+                             if r["world"] == 1 else
+                             "rtb_set_scene + band kernels into rank 0's frame (%s) + D2H to pinned host memory"
+                             % ("NVLink peer stores + fence" if r["peer"] else "NCCL gather + de-interleave"))},
             "gpu_launches": r["launches"],
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                          "frac": achieved / peak if peak else None, "traffic": None,

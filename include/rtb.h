@@ -107,6 +107,23 @@ int rtb_render_bands_device(rtb_ctx* ctx, int width, int height, const float ori
 /* Number of local rows rank `band_rank` owns for a frame of `height` rows. */
 int rtb_band_local_rows(int height, int band_rows, int band_rank, int band_world);
 
+/* Row-band render of this rank's bands straight into a WHOLE rgba8 frame (row = frame row).
+ * d_frame_rgba8 may be this GPU's memory or another GPU's frame mapped with rtb_peer_frame_open:
+ * the kernel's 128-bit framebuffer stores then travel over NVLink / NVSwitch and no gather or
+ * de-interleave pass is needed (the caller orders "all ranks done" with one tiny collective).
+ * New (the reference is single-device); replaces the per-render clEnqueueMapBuffer read-back of
+ * MainState.cpp:876-886 for the multi-GPU frame. */
+int rtb_render_bands_frame(rtb_ctx* ctx, int width, int height, const float origin0[4],
+                           const float dU[4], const float dV[4], const float rayDir[4], int band_rows,
+                           int band_rank, int band_world, void* d_frame_rgba8, void* cuda_stream);
+
+/* A device frame buffer other processes (one per GPU) can map: create on the owning rank (returns
+ * the device pointer and a 64-byte CUDA IPC handle to hand to the peers, e.g. with a broadcast),
+ * open on the peers, close on both (owner != 0 frees the allocation). */
+int rtb_peer_frame_create(rtb_ctx* ctx, size_t bytes, void** d_ptr, unsigned char handle_out[64]);
+int rtb_peer_frame_open(rtb_ctx* ctx, const unsigned char handle[64], void** d_ptr);
+int rtb_peer_frame_close(rtb_ctx* ctx, void* d_ptr, int owner);
+
 /* Multi-GPU gather epilogue.  After the ranks' packed band buffers have been gathered back to back
  * (rank 0's rows, then rank 1's, ...; rank r contributes rtb_band_local_rows(height, band_rows, r,
  * band_world) rows) into d_packed, this copies every row to its place in the final frame d_frame.

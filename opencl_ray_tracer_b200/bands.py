@@ -49,3 +49,65 @@ def gather_packed(dist, my_slice, packed, rows_of, rank, world):
     if ops:
         for req in dist.batch_isend_irecv(ops):
             req.wait()
+
+
+class PeerFrame:
+    """Rank 0's whole rgba8 frame, mapped into every rank (CUDA IPC through librtb), so that each
+    rank's grid kernel stores its row bands straight into it over NVLink / NVSwitch: no gather, no
+    de-interleave pass.  `dist` is torch.distributed (NCCL in production, gloo in the tests) and is
+    used for the 64-byte handle broadcast and for the per-frame "every rank has finished" token."""
+
+    def __init__(self, dist, ctx, width, height, rank, world, device=None):
+        import torch
+        self.dist, self.ctx, self.rank, self.world = dist, ctx, rank, world
+        self.width, self.height = width, height
+        self.nbytes = 4 * width * height
+        self.ptr, self.owner = None, rank == 0
+        dev = device if device is not None else ("cuda" if dist.get_backend() == "nccl" else "cpu")
+        ok, hb = 1, torch.zeros(64, dtype=torch.uint8)
+        if rank == 0:
+            try:
+                self.ptr, handle = ctx.peer_frame_create(self.nbytes)
+                hb = torch.tensor(list(handle), dtype=torch.uint8)
+            except Exception:
+                ok = 0
+        hb = hb.to(dev)
+        dist.broadcast(hb, 0)
+        if rank != 0:
+            try:
+                self.ptr = ctx.peer_frame_open(bytes(hb.cpu().numpy().tobytes()))
+            except Exception:
+                ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32).to(dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        self.ok = bool(int(flag.item()))
+        self.token = torch.zeros(1, dtype=torch.int32).to(dev)
+        if not self.ok:
+            self.close()
+
+    def render(self, camera, band_rows, stream=0):
+        """This rank's bands into the shared frame, then the completion token (stream ordered on
+        NCCL; the caller synchronises before a gloo token)."""
+        self.ctx.render_bands_frame(self.width, self.height, camera, band_rows, self.rank, self.world,
+                                    self.ptr, stream)
+
+    def fence(self):
+        self.dist.all_reduce(self.token)
+
+    def as_tensor(self):
+        """torch uint8 view [H, W, 4] of the frame (rank 0)."""
+        import torch
+
+        class _Raw:
+            pass
+        raw = _Raw()
+        raw.__cuda_array_interface__ = {"shape": (self.height, self.width, 4), "typestr": "|u1",
+                                        "data": (int(self.ptr), False), "version": 3, "strides": None}
+        return torch.as_tensor(raw, device="cuda")
+
+    def close(self):
+        if self.ptr:
+            try:
+                self.ctx.peer_frame_close(self.ptr, self.owner)
+            finally:
+                self.ptr = None

@@ -25,7 +25,8 @@ EXPORTED_SYMBOLS = [
     "rtb_render", "rtb_render_rays", "rtb_render_bands_device", "rtb_band_local_rows",
     "rtb_render_sequence_device", "rtb_host_alloc", "rtb_host_free", "rtb_device_info",
     "rtb_launch_count", "rtb_kernel_ms_avg", "rtb_debug_pack", "rtb_debug_pack_bounds", "rtb_version",
-    "rtb_assemble_bands_device", "rtb_transfer_bytes",
+    "rtb_assemble_bands_device", "rtb_transfer_bytes", "rtb_render_bands_frame", "rtb_peer_frame_create",
+    "rtb_peer_frame_open", "rtb_peer_frame_close",
 ]
 
 
@@ -63,6 +64,10 @@ def load_library(path=None):
     lib.rtb_render_bands_device.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, C.c_int,
                                             C.c_int, vp, vp, vp, vp]
     lib.rtb_band_local_rows.argtypes = [C.c_int] * 4
+    lib.rtb_render_bands_frame.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, C.c_int, C.c_int, vp, vp]
+    lib.rtb_peer_frame_create.argtypes = [vp, C.c_size_t, C.POINTER(vp), C.POINTER(C.c_ubyte)]
+    lib.rtb_peer_frame_open.argtypes = [vp, C.POINTER(C.c_ubyte), C.POINTER(vp)]
+    lib.rtb_peer_frame_close.argtypes = [vp, vp, C.c_int]
     lib.rtb_assemble_bands_device.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp]
     lib.rtb_transfer_bytes.argtypes = [vp, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]
     lib.rtb_transfer_bytes.restype = None
@@ -235,6 +240,29 @@ class Context:
             self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d), band_rows, rank, world,
             C.c_void_p(d_rgba8 or None), C.c_void_p(d_prim_id or None), C.c_void_p(d_rgba_i32 or None),
             C.c_void_p(stream or None)))
+
+    def render_bands_frame(self, width, height, camera, band_rows, rank, world, d_frame_rgba8, stream=0):
+        """This rank's bands written straight into a whole frame (own or peer-mapped memory)."""
+        o0, du, dv, d = [_f32(v) for v in camera]
+        self._check(self.lib.rtb_render_bands_frame(
+            self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d), band_rows, rank, world,
+            C.c_void_p(d_frame_rgba8), C.c_void_p(stream or None)))
+
+    def peer_frame_create(self, nbytes):
+        """-> (device pointer, 64-byte IPC handle as bytes)."""
+        p = C.c_void_p()
+        h = (C.c_ubyte * 64)()
+        self._check(self.lib.rtb_peer_frame_create(self._h, C.c_size_t(nbytes), C.byref(p), h))
+        return p.value, bytes(h)
+
+    def peer_frame_open(self, handle):
+        p = C.c_void_p()
+        h = (C.c_ubyte * 64).from_buffer_copy(handle)
+        self._check(self.lib.rtb_peer_frame_open(self._h, h, C.byref(p)))
+        return p.value
+
+    def peer_frame_close(self, ptr, owner):
+        self._check(self.lib.rtb_peer_frame_close(self._h, C.c_void_p(ptr), int(bool(owner))))
 
     def assemble_bands_device(self, width, height, band_rows, world, elem_bytes, d_packed, d_frame, stream=0):
         self._check(self.lib.rtb_assemble_bands_device(self._h, width, height, band_rows, world, elem_bytes,

@@ -248,7 +248,8 @@ raycast_grid_kernel(const GridParams p) {
         rtb_shade(st.best[q], cr, cg, cb, rgba[q]);
         rgba8[q] = rtb_pack_rgba8(rgba[q]);
     }
-    const size_t row_off = (size_t)lrow * p.width;
+    // packed band buffer (row = local row) or a whole frame -- e.g. rank 0's, mapped over NVLink
+    const size_t row_off = (size_t)(p.out_global_rows ? gy : lrow) * p.width;
     const bool full = p.vec_ok && (x0 + PX <= p.width);
     if (full) {
         if (p.out_rgba8) {

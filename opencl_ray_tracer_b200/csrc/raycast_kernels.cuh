@@ -18,6 +18,7 @@ struct GridParams {
     int width, height;                      // full frame
     int band_rows, band_rank, band_world;   // interleaved row bands (band_world == 1: whole frame)
     int local_rows;                         // rows this launch renders = rows of the packed outputs
+    int out_global_rows;                    // 1: outputs are whole frames (possibly peer memory), row = frame row
     int n_cubes, n_spheres;
     const float4* cube_rec;                 // 3 RtbSlab per cube
     const float4* sph_rec;                  // 1 RtbSphere per sphere

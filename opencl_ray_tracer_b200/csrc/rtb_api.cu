@@ -324,8 +324,9 @@ int upload_frame_records(rtb_ctx* ctx, const CameraFrame& cf, int width, int hei
 // Enqueues one grid-kernel launch (with its timing event pair) on `stream`.
 int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width, int height, int band_rows,
                  int band_rank, int band_world, int local_rows, void* d_rgba8, void* d_id, void* d_i32,
-                 cudaStream_t stream) {
+                 cudaStream_t stream, int out_global_rows = 0) {
     GridParams p;
+    p.out_global_rows = out_global_rows;
     p.width = width; p.height = height;
     p.band_rows = band_rows; p.band_rank = band_rank; p.band_world = band_world;
     p.local_rows = local_rows;
@@ -398,6 +399,64 @@ int rtb_render_bands_device(rtb_ctx* ctx, int width, int height, const float ori
                       d_rgba8, d_prim_id, d_rgba_i32, stream);
     if (rc != RTB_OK) return rc;
     if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
+    return RTB_OK;
+}
+
+int rtb_render_bands_frame(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+                           const float dV[4], const float rayDir[4], int band_rows, int band_rank,
+                           int band_world, void* d_frame_rgba8, void* cuda_stream) {
+    int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
+    if (rc != RTB_OK) return rc;
+    if (band_rows <= 0 || band_rows % 4 != 0 || band_world <= 0 || band_rank < 0 || band_rank >= band_world ||
+        !d_frame_rgba8)
+        return fail(ctx, RTB_ERR_INVALID_ARG, "band_rows must be a positive multiple of 4; 0 <= rank < world");
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    CameraFrame cf;
+    if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
+        return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
+    cudaStream_t stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->stream;
+    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, stream);
+    if (rc != RTB_OK) return rc;
+    const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
+    rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, band_rows, band_rank, band_world, local_rows,
+                      d_frame_rgba8, nullptr, nullptr, stream, 1);
+    if (rc != RTB_OK) return rc;
+    if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
+    return RTB_OK;
+}
+
+int rtb_peer_frame_create(rtb_ctx* ctx, size_t bytes, void** d_ptr, unsigned char handle_out[64]) {
+    if (!ctx || !d_ptr || !handle_out || bytes == 0) return RTB_ERR_INVALID_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "rtb.h promises a 64-byte handle");
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    *d_ptr = nullptr;
+    RTB_CUDA(ctx, cudaMalloc(d_ptr, bytes));  // a whole allocation: IPC handles name allocations
+    cudaIpcMemHandle_t h;
+    const cudaError_t e = cudaIpcGetMemHandle(&h, *d_ptr);
+    if (e != cudaSuccess) {
+        cudaFree(*d_ptr);
+        *d_ptr = nullptr;
+        return fail(ctx, RTB_ERR_CUDA, std::string("cudaIpcGetMemHandle: ") + cudaGetErrorString(e));
+    }
+    std::memcpy(handle_out, &h, 64);
+    return RTB_OK;
+}
+
+int rtb_peer_frame_open(rtb_ctx* ctx, const unsigned char handle[64], void** d_ptr) {
+    if (!ctx || !d_ptr || !handle) return RTB_ERR_INVALID_ARG;
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, 64);
+    *d_ptr = nullptr;
+    RTB_CUDA(ctx, cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return RTB_OK;
+}
+
+int rtb_peer_frame_close(rtb_ctx* ctx, void* d_ptr, int owner) {
+    if (!ctx || !d_ptr) return RTB_ERR_INVALID_ARG;
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (owner) RTB_CUDA(ctx, cudaFree(d_ptr));
+    else RTB_CUDA(ctx, cudaIpcCloseMemHandle(d_ptr));
     return RTB_OK;
 }
 
