@@ -41,14 +41,6 @@ FLOP_PER_TEST_RAY = 4.0
 FLOP_PER_TEST_ROW = 5.0
 
 
-def grid_px(width, rows, sms):
-    """Rays per thread of the kernel variant grid_launch_shape() picks (raycast_kernels.cu)."""
-    for px, tw, th in ((16, 256, 8), (8, 128, 16)):
-        if -(-width // tw) * -(-rows // th) >= 2 * sms:
-            return px
-    return 4
-
-
 def workload_name(key):
     w, h, ns, nc, seed = WORKLOADS[key]
     return "%s: %dx%d, %d spheres + %d cubes, createScene3 recipe, seed %d, reference camera" % (key, w, h, ns, nc, seed)
@@ -412,6 +404,7 @@ def main():
             run_reference(args)
         return
     r = run_ours(args)
+    from opencl_ray_tracer_b200 import capi as capi_mod
     import torch.distributed as dist
     if r["rank"] == 0:
         peaks, peaks_src = load_peaks()
@@ -425,7 +418,7 @@ def main():
         peak_nominal = sms * 128 * 2 * sm_max * 1e6 / 1e12          # TFLOP/s at the max SM clock
         probe = fp32_probe_tflops()
         # dominant kernel = the ray-cast grid kernel; this rank's launch covers my_rows rows
-        px = grid_px(w, r["my_rows"], sms)
+        px = capi_mod.debug_grid_shape(w, r["my_rows"], sms)[0]
         flop_per_test = FLOP_PER_TEST_RAY + FLOP_PER_TEST_ROW / px
         flops_per_launch = r["my_rows"] * w * (nc + ns) * flop_per_test
         k_s = r["k_avg_ms"] * 1e-3

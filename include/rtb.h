@@ -169,6 +169,10 @@ int rtb_debug_pack_bounds(int numSpheres, const float* sphereOrigins, const floa
                           const float origin0[4], const float dU[4], const float dV[4],
                           const float rayDir[4], float* bound_rec);
 
+/* Debug/test entry: the tiling the grid kernel uses for a width x rows launch on a GPU with
+ * sm_count SMs: out = {rays per thread, tile width, tile height, CTAs}.  Host only. */
+int rtb_debug_grid_shape(int width, int rows, int sm_count, int out[4]);
+
 const char* rtb_version(void);
 
 #ifdef __cplusplus

@@ -24,7 +24,7 @@ EXPORTED_SYMBOLS = [
     "rtb_init", "rtb_shutdown", "rtb_error_string", "rtb_last_error_message", "rtb_set_scene",
     "rtb_render", "rtb_render_rays", "rtb_render_bands_device", "rtb_band_local_rows",
     "rtb_render_sequence_device", "rtb_host_alloc", "rtb_host_free", "rtb_device_info",
-    "rtb_launch_count", "rtb_kernel_ms_avg", "rtb_debug_pack", "rtb_debug_pack_bounds", "rtb_version",
+    "rtb_launch_count", "rtb_kernel_ms_avg", "rtb_debug_pack", "rtb_debug_pack_bounds", "rtb_debug_grid_shape", "rtb_version",
     "rtb_assemble_bands_device", "rtb_transfer_bytes", "rtb_render_bands_frame", "rtb_peer_frame_create",
     "rtb_peer_frame_open", "rtb_peer_frame_close",
 ]
@@ -125,6 +125,15 @@ def debug_pack(sph_o, sph_r, cube_v, camera=REFERENCE_CAMERA):
     if rc != RTB_OK:
         raise RtbError(rc, "cube %d" % bad.value if bad.value >= 0 else "")
     return cube_rec, sph_rec, cam
+
+
+def debug_grid_shape(width, rows, sm_count):
+    """-> (rays per thread, tile width, tile height, CTAs) of the grid kernel for this launch."""
+    out = (C.c_int * 4)()
+    rc = load_library().rtb_debug_grid_shape(int(width), int(rows), int(sm_count), out)
+    if rc != RTB_OK:
+        raise RtbError(rc)
+    return tuple(out)
 
 
 def debug_pack_bounds(sph_o, sph_r, cube_v, width, height, camera=REFERENCE_CAMERA):

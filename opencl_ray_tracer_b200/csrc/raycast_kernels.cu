@@ -17,6 +17,7 @@
 // emulator in tests/emu reproduces the kernel bit for bit.
 #include "raycast_kernels.cuh"
 
+#include <cmath>
 #include <cstdlib>
 
 namespace rtb {
@@ -164,10 +165,14 @@ __device__ __forceinline__ void bound_group(const GridParams& p, const float4* _
     }
 }
 
-template <int PX, int WARPS_X, int WARPS_Y, int G = kBoundGroup, int MIN_CTAS = (PX >= 16 ? 3 : 4)>
-__global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y, MIN_CTAS)
+// S > 1: S warps share one pixel tile and split the primitive list between them (groups of G,
+// round robin); their nearest hits are merged through shared memory before shading.  Used when a
+// launch has too few pixel tiles to load every scheduler evenly (the per-GPU share of a frame on 8
+// GPUs): the 4 warps of a CTA then sit on the 4 schedulers of an SM with equal work.
+template <int PX, int WARPS_X, int WARPS_Y, int G = kBoundGroup, int MIN_CTAS = (PX >= 16 ? 3 : 4), int S = 1>
+__global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y * S, MIN_CTAS)
 raycast_grid_kernel(const GridParams p) {
-    constexpr int kThreads = 32 * WARPS_X * WARPS_Y;
+    constexpr int kThreads = 32 * WARPS_X * WARPS_Y * S;
     constexpr int kTileW = WARPS_X * 8 * PX;
     constexpr int kTileH = WARPS_Y * 4;
     static_assert(kBoundGroup % G == 0, "the host pads the bound list to kBoundGroup");
@@ -177,7 +182,8 @@ raycast_grid_kernel(const GridParams p) {
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
-    const int wx = warp % WARPS_X, wy = warp / WARPS_X;
+    const int split = warp % S, tile_warp = warp / S;  // the S warps of a tile are neighbours
+    const int wx = tile_warp % WARPS_X, wy = tile_warp / WARPS_X;
     const int lx = lane & 7, ly = lane >> 3;
     const int x0 = blockIdx.x * kTileW + (wx * 8 + lx) * PX;
     const int lrow = blockIdx.y * kTileH + wy * 4 + ly;  // row in the packed (local) output
@@ -225,10 +231,38 @@ raycast_grid_kernel(const GridParams p) {
         const int first = k * kChunkPrims;
         const int cnt = min(kChunkPrims, n_bound - first);
 #pragma unroll 1
-        for (int j = 0; j < cnt; j += G) bound_group<PX, G>(p, &stage[b][2 * j], first + j, v, st);
+        for (int j = split * G; j < cnt; j += S * G) bound_group<PX, G>(p, &stage[b][2 * j], first + j, v, st);
         if (k + 2 < n_chunks) {
             __syncthreads();  // every warp is done reading stage[b] before TMA refills it
             if (tid == 0) issue(k + 2);
+        }
+    }
+
+    // ---- merge of the primitive splits (S > 1) -----------------------------------------------
+    if constexpr (S > 1) {
+        __shared__ float m_best[WARPS_X * WARPS_Y * (S > 1 ? S - 1 : 1)][PX][32];
+        __shared__ int m_id[WARPS_X * WARPS_Y * (S > 1 ? S - 1 : 1)][PX][32];
+        if (split > 0) {
+#pragma unroll
+            for (int q = 0; q < PX; ++q) {
+                m_best[tile_warp * (S - 1) + split - 1][q][lane] = st.best[q];
+                m_id[tile_warp * (S - 1) + split - 1][q][lane] = st.id[q];
+            }
+        }
+        __syncthreads();
+        if (split > 0) return;
+#pragma unroll
+        for (int o = 0; o < S - 1; ++o) {
+#pragma unroll
+            for (int q = 0; q < PX; ++q) {
+                const float ob = m_best[tile_warp * (S - 1) + o][q][lane];
+                const int oi = m_id[tile_warp * (S - 1) + o][q][lane];
+                // same winner as one ascending pass: nearest t, ties to the lowest primitive index
+                if (ob < st.best[q] || (ob == st.best[q] && oi >= 0 && (st.id[q] < 0 || oi < st.id[q]))) {
+                    st.best[q] = ob;
+                    st.id[q] = oi;
+                }
+            }
         }
     }
 
@@ -331,7 +365,7 @@ __global__ void __launch_bounds__(256) raycast_rays_kernel(const RaysParams p) {
 template <int PX, int WX, int WY>
 GridLaunchShape shape_of(int width, int local_rows) {
     GridLaunchShape s;
-    s.px = PX;
+    s.px = PX; s.wx = WX; s.wy = WY; s.split = 1;
     s.block = dim3(32 * WX * WY);
     const int tw = WX * 8 * PX, th = WY * 4;
     s.grid = dim3((width + tw - 1) / tw, (local_rows + th - 1) / th);
@@ -341,20 +375,50 @@ GridLaunchShape shape_of(int width, int local_rows) {
 
 }  // namespace
 
+// Production tilings of the grid kernel: rays per thread, pixel-tile warps per CTA (x, y), warps
+// per pixel tile (primitive split), and the measured cost per ray-primitive test relative to the
+// first (profiles/r01_variant_sweeps.txt).
+struct Tiling { int px, wx, wy, split; double cost; };
+static const Tiling kTilings[] = {
+    {16, 2, 2, 1, 1.00},  // 256 x 8 pixels, 4 warps
+    {16, 2, 1, 2, 1.00},  // 256 x 4 pixels, 4 warps, two per tile: short band sets (8-GPU frames)
+    {8, 2, 2, 1, 1.10},   // 128 x 8 pixels
+    {4, 2, 2, 1, 1.35},   //  64 x 8 pixels: small frames
+};
+
+// The CTA scheduler spreads a grid evenly over the SMs and a CTA's warps over the 4 schedulers of
+// its SM; a launch lasts about (warps on the fullest scheduler) x (work per warp):
+//   ceil(CTAs / SMs * warps per CTA / 4) * (32 * px / split) * cost.   Pick the tiling minimising it.
 GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
-    GridLaunchShape big = shape_of<16, 2, 2>(width, local_rows);
-    if ((long long)big.grid.x * big.grid.y >= 2LL * sm_count) return big;
-    GridLaunchShape mid = shape_of<8, 2, 4>(width, local_rows);
-    if ((long long)mid.grid.x * mid.grid.y >= 2LL * sm_count) return mid;
-    return shape_of<4, 2, 2>(width, local_rows);
+    GridLaunchShape best;
+    double best_t = 0.0;
+    if (sm_count <= 0) sm_count = 1;
+    for (int i = 0; i < (int)(sizeof kTilings / sizeof kTilings[0]); ++i) {
+        const Tiling& t = kTilings[i];
+        const int tw = t.wx * 8 * t.px, th = t.wy * 4;
+        GridLaunchShape s;
+        s.px = t.px; s.wx = t.wx; s.wy = t.wy; s.split = t.split;
+        s.block = dim3(32 * t.wx * t.wy * t.split);
+        s.grid = dim3((width + tw - 1) / tw, (local_rows + th - 1) / th);
+        s.smem = 0;
+        const double ctas = (double)s.grid.x * s.grid.y;
+        const double warps_per_sched = std::ceil(ctas / sm_count * (t.wx * t.wy * t.split) / 4.0 - 1e-9);
+        const double est = warps_per_sched * (32.0 * t.px / t.split) * t.cost;
+        if (i == 0 || est < best_t * 0.97) {  // 3 % hysteresis in favour of the earlier entry
+            best = s;
+            best_t = est;
+        }
+    }
+    return best;
 }
 
 // Experiment hook (profiles/): RTB_GRID_VARIANT=n picks another tiling of the same kernel.
-template <int PX, int WX, int WY, int G, int MINB>
+template <int PX, int WX, int WY, int G, int MINB, int S = 1>
 cudaError_t launch_variant(const GridParams& p, cudaStream_t stream) {
-    const GridLaunchShape s = shape_of<PX, WX, WY>(p.width, p.local_rows);
+    GridLaunchShape s = shape_of<PX, WX, WY>(p.width, p.local_rows);
+    s.block = dim3(32 * WX * WY * S);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
-    raycast_grid_kernel<PX, WX, WY, G, MINB><<<s.grid, s.block, 0, stream>>>(p);
+    raycast_grid_kernel<PX, WX, WY, G, MINB, S><<<s.grid, s.block, 0, stream>>>(p);
     return cudaGetLastError();
 }
 
@@ -366,23 +430,24 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) 
     switch (variant) {
         case 1: return launch_variant<16, 2, 4, 2, 3>(p, stream);
         case 2: return launch_variant<16, 2, 4, 4, 2>(p, stream);
-        case 3: return launch_variant<32, 2, 4, 4, 1>(p, stream);
-        case 4: return launch_variant<32, 2, 4, 2, 2>(p, stream);
         case 5: return launch_variant<16, 2, 4, 4, 3>(p, stream);
-        case 6: return launch_variant<16, 1, 4, 4, 6>(p, stream);
-        case 7: return launch_variant<8, 2, 4, 4, 4>(p, stream);
+        case 6: return launch_variant<8, 2, 2, 4, 8>(p, stream);
+        case 7: return launch_variant<16, 2, 1, 4, 4, 2>(p, stream);
+        case 3: return launch_variant<16, 1, 1, 4, 4, 4>(p, stream);
         case 8: return launch_variant<16, 2, 4, 1, 3>(p, stream);
-        case 9: return launch_variant<16, 2, 4, 4, 1>(p, stream);
+        case 9: return launch_variant<4, 2, 2, 4, 8>(p, stream);
         default: break;
     }
     const GridLaunchShape s = grid_launch_shape(p.width, p.local_rows, sm_count);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
-    if (s.px == 16)
+    if (s.px == 16 && s.wy == 2)
         raycast_grid_kernel<16, 2, 2, kBoundGroup, 4><<<s.grid, s.block, 0, stream>>>(p);
+    else if (s.px == 16)
+        raycast_grid_kernel<16, 2, 1, kBoundGroup, 4, 2><<<s.grid, s.block, 0, stream>>>(p);
     else if (s.px == 8)
-        raycast_grid_kernel<8, 2, 4><<<s.grid, s.block, 0, stream>>>(p);
+        raycast_grid_kernel<8, 2, 2, kBoundGroup, 8><<<s.grid, s.block, 0, stream>>>(p);
     else
-        raycast_grid_kernel<4, 2, 2><<<s.grid, s.block, 0, stream>>>(p);
+        raycast_grid_kernel<4, 2, 2, kBoundGroup, 8><<<s.grid, s.block, 0, stream>>>(p);
     return cudaGetLastError();
 }
 

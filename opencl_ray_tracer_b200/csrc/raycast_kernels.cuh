@@ -61,7 +61,7 @@ struct AssembleParams {
 cudaError_t launch_assemble(const AssembleParams& p, cudaStream_t stream);
 
 // Tile geometry of the grid kernel variant chosen for a frame.
-struct GridLaunchShape { int px; dim3 grid, block; size_t smem; };
+struct GridLaunchShape { int px, wx, wy, split; dim3 grid, block; size_t smem; };
 
 GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count);
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream);

@@ -749,4 +749,14 @@ int rtb_debug_pack_bounds(int numSpheres, const float* sphereOrigins, const floa
     return RTB_OK;
 }
 
+int rtb_debug_grid_shape(int width, int rows, int sm_count, int out[4]) {
+    if (width <= 0 || rows <= 0 || sm_count <= 0 || !out) return RTB_ERR_INVALID_ARG;
+    const GridLaunchShape s = grid_launch_shape(width, rows, sm_count);
+    out[0] = s.px;
+    out[1] = s.wx * 8 * s.px;
+    out[2] = s.wy * 4;
+    out[3] = (int)(s.grid.x * s.grid.y);
+    return RTB_OK;
+}
+
 }  // extern "C"
