@@ -32,11 +32,11 @@ BAND_ROWS = 16
 
 # FP32 operations the shipped kernel executes per ray-primitive test (FMA = 2).  Cubes and
 # spheres go through the same dense loop: the primitive's conic footprint bound q(u,v) is evaluated on
-# every ray with 2 FMA (w = sA*u + rowW; q = w*w + rowC; issued as FFMA2 on ray pairs) = 4 flop; per thread
-# and primitive the row terms (1 FFMA + 1 FADD + 2 FMUL) = 5 flop amortised over the PX rays a thread owns
-# (PX = 16 at the roofline point).  The
-# reference-exact slab / sphere arithmetic runs only on rays inside a bound (a few per mille of the
-# tests) and is NOT counted.  Bit-pattern ANDs, votes, compares count 0.
+# every ray with 2 FMA (w = sA*u + rowW; q = w*w + rowC; issued as FFMA2 on ray pairs) = 4 flop.  The row
+# terms (1 FFMA + 1 FADD + 2 FMUL = 5 flop) are computed once per primitive and CTA pixel row into the
+# shared-memory row table, i.e. amortised over the width of a CTA's pixel tile (256 rays at the roofline
+# point: +0.02 flop per test).  The reference-exact slab / sphere arithmetic runs only on rays inside a
+# bound (a few per mille of the tests) and is NOT counted.  Bit-pattern ANDs, votes, compares count 0.
 FLOP_PER_TEST_RAY = 4.0
 FLOP_PER_TEST_ROW = 5.0
 
@@ -418,8 +418,8 @@ def main():
         peak_nominal = sms * 128 * 2 * sm_max * 1e6 / 1e12          # TFLOP/s at the max SM clock
         probe = fp32_probe_tflops()
         # dominant kernel = the ray-cast grid kernel; this rank's launch covers my_rows rows
-        px = capi_mod.debug_grid_shape(w, r["my_rows"], sms)[0]
-        flop_per_test = FLOP_PER_TEST_RAY + FLOP_PER_TEST_ROW / px
+        px, tile_w = capi_mod.debug_grid_shape(w, r["my_rows"], sms)[:2]
+        flop_per_test = FLOP_PER_TEST_RAY + FLOP_PER_TEST_ROW / tile_w
         flops_per_launch = r["my_rows"] * w * (nc + ns) * flop_per_test
         k_s = r["k_avg_ms"] * 1e-3
         achieved = flops_per_launch / k_s / 1e12 if k_s > 0 else 0.0
@@ -441,7 +441,8 @@ def main():
             "e2e": {"value": n_px * args.steps / r["e2e_s"] / 1e6, "unit": "Mrays/s",
                     "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                     "ms_per_step": r["e2e_s"] * 1e3 / args.steps,
-                    "what": ("rtb_set_scene + rtb_render (row chunks pipelined with their D2H copies) into pinned host memory"
+                    "what": ("rtb_set_scene (scene arrays H2D, boxes recovered on the device) + rtb_render (device record pack, ONE grid "
+                             "launch, finished row chunks copied to pinned host memory while it runs)"
                              if r["world"] == 1 else
                              "rtb_set_scene + band kernels into rank 0's frame (%s) + D2H to pinned host memory"
                              % ("NVLink peer stores + fence" if r["peer"] else "NCCL gather + de-interleave"))},

@@ -72,8 +72,10 @@ const char* rtb_error_string(int status);
 const char* rtb_last_error_message(const rtb_ctx* ctx);
 
 /* Replaces the 6 clCreateBuffer + clEnqueueWriteBuffer pairs for the scene
- * (MainState.cpp:677-839) and the clSetKernelArg calls 1-7 (:747-753).  The scene stays resident
- * on the device until the next rtb_set_scene.  Arrays are copied; the caller may free them. */
+ * (MainState.cpp:677-839) and the clSetKernelArg calls 1-7 (:747-753).  The arrays are copied to
+ * the device as they are (the caller may free them on return) and stay resident until the next
+ * rtb_set_scene; a device kernel recovers each cube's box from its 36 vertices and the call fails
+ * with RTB_ERR_NOT_A_BOX (lowest offending index in rtb_last_error_message) if one is not a box. */
 int rtb_set_scene(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins,
                   const float* sphereRadius, const float* sphereColours, int numCubes,
                   const float* cubeVertices, const float* cubeColours);
@@ -168,6 +170,14 @@ int rtb_debug_pack_bounds(int numSpheres, const float* sphereOrigins, const floa
                           int numCubes, const float* cubeVertices, int width, int height,
                           const float origin0[4], const float dU[4], const float dV[4],
                           const float rayDir[4], float* bound_rec);
+
+/* Debug/test entry: packs the records of one frame ON THE DEVICE (the per-frame path of rtb_render*)
+ * and copies them out: 4 floats per record in the layout of rtb_debug_pack (3 per cube, 1 per sphere)
+ * followed, from float index *bound_offset_floats, by 8 floats per bound.  With out == NULL only the
+ * sizes are returned.  Must equal the host packer's records bit for bit. */
+int rtb_debug_device_records(rtb_ctx* ctx, int width, int height, const float origin0[4],
+                             const float dU[4], const float dV[4], const float rayDir[4], float* out,
+                             size_t out_cap_floats, size_t* n_floats, size_t* bound_offset_floats);
 
 /* Debug/test entry: the tiling the grid kernel uses for a width x rows launch on a GPU with
  * sm_count SMs: out = {rays per thread, tile width, tile height, CTAs}.  Host only. */

@@ -26,7 +26,7 @@ EXPORTED_SYMBOLS = [
     "rtb_render_sequence_device", "rtb_host_alloc", "rtb_host_free", "rtb_device_info",
     "rtb_launch_count", "rtb_kernel_ms_avg", "rtb_debug_pack", "rtb_debug_pack_bounds", "rtb_debug_grid_shape", "rtb_version",
     "rtb_assemble_bands_device", "rtb_transfer_bytes", "rtb_render_bands_frame", "rtb_peer_frame_create",
-    "rtb_peer_frame_open", "rtb_peer_frame_close",
+    "rtb_peer_frame_open", "rtb_peer_frame_close", "rtb_debug_device_records",
 ]
 
 
@@ -83,6 +83,8 @@ def load_library(path=None):
     lib.rtb_debug_pack.argtypes = [C.c_int, fp, fp, C.c_int, fp, fp, fp, fp, fp, fp, fp, fp,
                                    C.POINTER(C.c_int)]
     lib.rtb_debug_pack_bounds.argtypes = [C.c_int, fp, fp, C.c_int, fp, C.c_int, C.c_int, fp, fp, fp, fp, fp]
+    lib.rtb_debug_device_records.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, fp, C.c_size_t,
+                                             C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
     lib.rtb_version.restype = C.c_char_p
     if path is None:
         _lib = lib
@@ -289,6 +291,20 @@ class Context:
         self._check(self.lib.rtb_render_sequence_device(self._h, width, height, len(cams), _fp(cams),
                                                         C.c_void_p(d_rgba8), C.byref(kms)))
         return kms.value
+
+    def debug_device_records(self, width, height, camera=REFERENCE_CAMERA):
+        """The frame records as the DEVICE pack kernel writes them:
+        (cube_rec[nc,3,4], sphere_rec[ns,4], bound_rec[n_bound,8])."""
+        o0, du, dv, d = [_f32(v) for v in camera]
+        n, off = C.c_size_t(), C.c_size_t()
+        self._check(self.lib.rtb_debug_device_records(self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d),
+                                                      None, 0, C.byref(n), C.byref(off)))
+        buf = np.zeros(n.value, np.float32)
+        self._check(self.lib.rtb_debug_device_records(self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d),
+                                                      _fp(buf), buf.size, C.byref(n), C.byref(off)))
+        nc, ns = self.nc, self.ns
+        return (buf[:12 * nc].reshape(nc, 3, 4).copy(), buf[12 * nc:12 * nc + 4 * ns].reshape(ns, 4).copy(),
+                buf[off.value:].reshape(-1, 8).copy())
 
     def launch_count(self):
         return int(self.lib.rtb_launch_count(self._h))

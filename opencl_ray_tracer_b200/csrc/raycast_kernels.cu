@@ -5,13 +5,14 @@
 // MainState::executeRayTracerCPU -> collide (RayTrace/states/MainState.cpp:936-956, :330-408).
 //
 // Mapping: one warp = an 8x4 lane tile, each lane owns PX horizontally adjacent
-// pixels (one primary ray each), so a warp covers (8*PX) x 4 pixels and a lane's PX RGBA8 results
-// leave as 128-bit stores.  The packed primitive records (16 B each) are staged global->shared
-// in 12 KB chunks with 1-D TMA bulk copies (cp.async.bulk + mbarrier complete_tx), double
-// buffered, and read back as warp-uniform LDS.128 broadcasts.  Per pixel and cube: 6 FFMA/FADD
-// class instructions + 2 FMNMX3 + 1 FSETP; per pixel and sphere: 1 FADD + 1 FFMA + 1 FSETP.  The
-// nearest-hit update (and the sphere's sqrt) sits behind a per-thread branch that is only taken
-// when one of the thread's PX rays actually hits the primitive.
+// pixels (one primary ray each, held as PX/2 packed FP32 pairs), so a warp covers (8*PX) x 4 pixels
+// and a lane's PX RGBA8 results leave as 128-bit stores.  The conic bound records (32 B per
+// primitive) are staged global->shared in chunks with 1-D TMA bulk copies (cp.async.bulk + mbarrier
+// complete_tx), double buffered; per chunk the CTA turns them into a row table
+// (primitive, CTA row) -> (sA, rowW, rowC) that the dense loop reads with one LDS.128 per thread and
+// primitive.  Per ray pair and primitive: 2 FFMA2 (w = sA*u + rowW; q = w*w + rowC) + 1 LOP3 (AND
+// of the IEEE patterns; bit 30 = "q >= 2").  One warp vote per 4 primitives; the reference-exact
+// slab / sphere update (raycast_math.h) runs only behind it.
 //
 // Compiled with -fmad=false: every FMA is an explicit fmaf() from raycast_math.h so the scalar
 // emulator in tests/emu reproduces the kernel bit for bit.
@@ -165,109 +166,46 @@ __device__ __forceinline__ void bound_group(const GridParams& p, const float4* _
     }
 }
 
-// S > 1: S warps share one pixel tile and split the primitive list between them (groups of G,
-// round robin); their nearest hits are merged through shared memory before shading.  Used when a
-// launch has too few pixel tiles to load every scheduler evenly (the per-GPU share of a frame on 8
-// GPUs): the 4 warps of a CTA then sit on the 4 schedulers of an SM with equal work.
-template <int PX, int WARPS_X, int WARPS_Y, int G = kBoundGroup, int MIN_CTAS = (PX >= 16 ? 3 : 4), int S = 1>
-__global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y * S, MIN_CTAS)
-raycast_grid_kernel(const GridParams p) {
-    constexpr int kThreads = 32 * WARPS_X * WARPS_Y * S;
-    constexpr int kTileW = WARPS_X * 8 * PX;
-    constexpr int kTileH = WARPS_Y * 4;
-    static_assert(kBoundGroup % G == 0, "the host pads the bound list to kBoundGroup");
-    __shared__ __align__(128) float4 stage[2][2 * kChunkPrims];
-    __shared__ __align__(8) uint64_t full_bar[2];
-    (void)kThreads;
-
-    const int tid = threadIdx.x;
-    const int warp = tid >> 5, lane = tid & 31;
-    const int split = warp % S, tile_warp = warp / S;  // the S warps of a tile are neighbours
-    const int wx = tile_warp % WARPS_X, wy = tile_warp / WARPS_X;
-    const int lx = lane & 7, ly = lane >> 3;
-    const int x0 = blockIdx.x * kTileW + (wx * 8 + lx) * PX;
-    const int lrow = blockIdx.y * kTileH + wy * 4 + ly;  // row in the packed (local) output
-    // interleaved row bands: local band lb -> global band lb*world + rank
-    const int lb = lrow / p.band_rows;
-    const int gy = (lb * p.band_world + p.band_rank) * p.band_rows + (lrow - lb * p.band_rows);
-
-    // bound records: one per primitive (cubes, then spheres), padded by the host to a multiple of G
-    const int n_bound = p.n_bound;
-    const int n_chunks = (n_bound + kChunkPrims - 1) / kChunkPrims;
-
-    auto issue = [&](int k) {  // called by thread 0 only
-        const int b = k & 1;
-        const int first = k * kChunkPrims;
-        const int cnt = min(kChunkPrims, n_bound - first);
-        const uint32_t bytes = (uint32_t)cnt * 32u;
-        mbar_arrive_expect_tx(&full_bar[b], bytes);
-        bulk_g2s(&stage[b][0], p.bound_rec + 2 * (size_t)first, bytes, &full_bar[b]);
-    };
-
-    if (tid == 0) {
-        mbar_init(&full_bar[0], 1);
-        mbar_init(&full_bar[1], 1);
-        fence_mbar_init();
-    }
-    __syncthreads();
-    if (tid == 0) {
-        if (n_chunks > 0) issue(0);
-        if (n_chunks > 1) issue(1);
-    }
-
-    PixelState<PX> st;
-    const float fy = (float)gy;
-    const float v = rtb_cam_v(p.cam, fy);
+// Same dense test with the per-row terms taken from the CTA's row table (built once per chunk by
+// all threads, see the kernel): ONE LDS.128 (sA, rowW, rowC, -) per thread and primitive and no
+// scalar FP32 work in the loop -- 16 FFMA2 + 8 LOP3 + 1 LDS for the 16 rays of a thread.
+// `tab` points at this thread's row of the first primitive; consecutive primitives are ROWS apart.
+template <int PX, int G, int ROWS>
+__device__ __forceinline__ void bound_group_tab(const GridParams& p, const float4* __restrict__ tab, int first_prim,
+                                                float v, PixelState<PX>& st) {
+    uint32_t acc[G];
 #pragma unroll
-    for (int q = 0; q < PX; q += 2) {
-        st.u2[q >> 1] = pack2(rtb_cam_u(p.cam, (float)(x0 + q), fy), rtb_cam_u(p.cam, (float)(x0 + q + 1), fy));
-        st.best[q] = st.best[q + 1] = RTB_MISS_T;
-        st.id[q] = st.id[q + 1] = -1;
+    for (int g = 0; g < G; ++g) {
+        const float4 t = tab[g * ROWS];
+        const uint64_t S2 = pack2(t.x, t.x), W2 = pack2(t.y, t.y), C2 = pack2(t.z, t.z);
+        uint32_t a = 0xFFFFFFFFu;
+#pragma unroll
+        for (int j = 0; j < PX / 2; ++j) {
+            const uint64_t w2 = ffma2(st.u2[j], S2, W2);
+            const uint64_t q2 = ffma2(w2, w2, C2);
+            uint32_t q0, q1;
+            unpack2u(q2, q0, q1);
+            a &= q0 & q1;
+        }
+        acc[g] = a;
     }
-
-    for (int k = 0; k < n_chunks; ++k) {
-        const int b = k & 1;
-        mbar_wait(&full_bar[b], (uint32_t)((k >> 1) & 1));
-        const int first = k * kChunkPrims;
-        const int cnt = min(kChunkPrims, n_bound - first);
+    uint32_t all = acc[0];
+#pragma unroll
+    for (int g = 1; g < G; ++g) all &= acc[g];
+    if (__any_sync(0xFFFFFFFFu, (all & RTB_BOUND_FAIL_BIT) == 0u)) {
 #pragma unroll 1
-        for (int j = split * G; j < cnt; j += S * G) bound_group<PX, G>(p, &stage[b][2 * j], first + j, v, st);
-        if (k + 2 < n_chunks) {
-            __syncthreads();  // every warp is done reading stage[b] before TMA refills it
-            if (tid == 0) issue(k + 2);
+        for (int g = 0; g < G; ++g) {
+            uint32_t a = acc[0];
+#pragma unroll
+            for (int h = 1; h < G; ++h) a = (g == h) ? acc[h] : a;
+            if (__any_sync(0xFFFFFFFFu, (a & RTB_BOUND_FAIL_BIT) == 0u)) exact_update<PX>(p, first_prim + g, v, st);
         }
     }
+}
 
-    // ---- merge of the primitive splits (S > 1) -----------------------------------------------
-    if constexpr (S > 1) {
-        __shared__ float m_best[WARPS_X * WARPS_Y * (S > 1 ? S - 1 : 1)][PX][32];
-        __shared__ int m_id[WARPS_X * WARPS_Y * (S > 1 ? S - 1 : 1)][PX][32];
-        if (split > 0) {
-#pragma unroll
-            for (int q = 0; q < PX; ++q) {
-                m_best[tile_warp * (S - 1) + split - 1][q][lane] = st.best[q];
-                m_id[tile_warp * (S - 1) + split - 1][q][lane] = st.id[q];
-            }
-        }
-        __syncthreads();
-        if (split > 0) return;
-#pragma unroll
-        for (int o = 0; o < S - 1; ++o) {
-#pragma unroll
-            for (int q = 0; q < PX; ++q) {
-                const float ob = m_best[tile_warp * (S - 1) + o][q][lane];
-                const int oi = m_id[tile_warp * (S - 1) + o][q][lane];
-                // same winner as one ascending pass: nearest t, ties to the lowest primitive index
-                if (ob < st.best[q] || (ob == st.best[q] && oi >= 0 && (st.id[q] < 0 || oi < st.id[q]))) {
-                    st.best[q] = ob;
-                    st.id[q] = oi;
-                }
-            }
-        }
-    }
-
-    // ---- nearest-hit shading + stores -------------------------------------------------------
-    if (lrow >= p.local_rows || gy >= p.height || x0 >= p.width) return;
+// Nearest-hit shading (rtb_shade) + 128-bit coalesced stores of one thread's PX pixels.
+template <int PX>
+__device__ __forceinline__ void shade_and_store(const GridParams& p, PixelState<PX>& st, int x0, int lrow, int gy) {
     uint32_t rgba8[PX];
     int32_t rgba[PX][4];
 #pragma unroll
@@ -313,6 +251,172 @@ raycast_grid_kernel(const GridParams p) {
                     int32_t* o = reinterpret_cast<int32_t*>(p.out_i32) + 4 * (row_off + x0 + q);
                     o[0] = rgba[q][0]; o[1] = rgba[q][1]; o[2] = rgba[q][2]; o[3] = rgba[q][3];
                 }
+            }
+        }
+    }
+}
+
+// S > 1: S warps share one pixel tile and split the primitive list between them (groups of G,
+// round robin); their nearest hits are merged through shared memory before shading.  Used when a
+// launch has too few pixel tiles to load every scheduler evenly (the per-GPU share of a frame on 8
+// GPUs): the 4 warps of a CTA then sit on the 4 schedulers of an SM with equal work.
+//
+// TAB: the row terms of the bound (rowW, rowC: 4 FP32 ops per thread and primitive when every
+// thread computes them for itself) come from a shared-memory table built once per chunk and CTA:
+// entry (primitive, CTA row) = (sA, rowW, rowC, -), kTileH rows x kTabPrims primitives x 16 B per
+// stage.  The values are those of rtb_bound_row_w / rtb_bound_row_c, computed once per row
+// instead of once per thread (16 threads of a CTA share a row).
+template <int PX, int WARPS_X, int WARPS_Y, int G = kBoundGroup, int MIN_CTAS = (PX >= 16 ? 3 : 4), int S = 1,
+          bool TAB = false>
+__global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y * S, MIN_CTAS)
+raycast_grid_kernel(const GridParams p) {
+    constexpr int kThreads = 32 * WARPS_X * WARPS_Y * S;
+    constexpr int kTileW = WARPS_X * 8 * PX;
+    constexpr int kTileH = WARPS_Y * 4;
+    constexpr int kChunk = TAB ? kTabPrims : kChunkPrims;   // primitives per staged chunk
+    static_assert(kBoundGroup % G == 0, "the host pads the bound list to kBoundGroup");
+    static_assert(!TAB || (kThreads % kTileH == 0 && kTileH <= 8), "row table: a thread always builds the same row");
+    __shared__ __align__(128) float4 stage[2][2 * kChunk];
+    __shared__ __align__(16) float4 rowtab[TAB ? 2 : 1][TAB ? kTabPrims * kTileH : 1];
+    __shared__ __align__(8) uint64_t full_bar[2];
+    (void)kThreads;
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int split = warp % S, tile_warp = warp / S;  // the S warps of a tile are neighbours
+    const int wx = tile_warp % WARPS_X, wy = tile_warp / WARPS_X;
+    const int lx = lane & 7, ly = lane >> 3;
+    const int x0 = blockIdx.x * kTileW + (wx * 8 + lx) * PX;
+    const int lrow = blockIdx.y * kTileH + wy * 4 + ly;  // row in the packed (local) output
+    // interleaved row bands: local band lb -> global band lb*world + rank
+    const int lb = lrow / p.band_rows;
+    const int gy = (lb * p.band_world + p.band_rank) * p.band_rows + (lrow - lb * p.band_rows);
+
+    // bound records: one per primitive (cubes, then spheres), padded by the host to a multiple of G
+    const int n_bound = p.n_bound;
+    const int n_chunks = (n_bound + kChunk - 1) / kChunk;
+
+    auto issue = [&](int k) {  // called by thread 0 only
+        const int b = k & 1;
+        const int first = k * kChunk;
+        const int cnt = min(kChunk, n_bound - first);
+        const uint32_t bytes = (uint32_t)cnt * 32u;
+        mbar_arrive_expect_tx(&full_bar[b], bytes);
+        bulk_g2s(&stage[b][0], p.bound_rec + 2 * (size_t)first, bytes, &full_bar[b]);
+    };
+
+    if (tid == 0) {
+        mbar_init(&full_bar[0], 1);
+        mbar_init(&full_bar[1], 1);
+        fence_mbar_init();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        if (n_chunks > 0) issue(0);
+        if (n_chunks > 1) issue(1);
+    }
+
+    PixelState<PX> st;
+    const float fy = (float)gy;
+    const float v = rtb_cam_v(p.cam, fy);
+#pragma unroll
+    for (int q = 0; q < PX; q += 2) {
+        st.u2[q >> 1] = pack2(rtb_cam_u(p.cam, (float)(x0 + q), fy), rtb_cam_u(p.cam, (float)(x0 + q + 1), fy));
+        st.best[q] = st.best[q + 1] = RTB_MISS_T;
+        st.id[q] = st.id[q + 1] = -1;
+    }
+
+    // row-table build: thread t always fills CTA row t % kTileH (kThreads is a multiple of kTileH)
+    float tab_v = 0.f;
+    if constexpr (TAB) {
+        const int trow = blockIdx.y * kTileH + (tid % kTileH);
+        const int tlb = trow / p.band_rows;
+        const int tgy = (tlb * p.band_world + p.band_rank) * p.band_rows + (trow - tlb * p.band_rows);
+        tab_v = rtb_cam_v(p.cam, (float)tgy);
+    }
+
+    for (int k = 0; k < n_chunks; ++k) {
+        const int b = k & 1;
+        mbar_wait(&full_bar[b], (uint32_t)((k >> 1) & 1));
+        const int first = k * kChunk;
+        const int cnt = min(kChunk, n_bound - first);
+        if constexpr (TAB) {
+            for (int i = tid; i < cnt * kTileH; i += kThreads) {
+                const int prim = i / kTileH;
+                const float4 r0 = stage[b][2 * prim];
+                const float r1 = *reinterpret_cast<const float*>(&stage[b][2 * prim + 1]);
+                const RtbBound bd = {r0.x, r0.y, r0.z, r0.w, r1, 0.f, 0.f, 0.f};
+                rowtab[b][i] = make_float4(bd.sA, rtb_bound_row_w(bd, tab_v), rtb_bound_row_c(bd, tab_v), 0.f);
+            }
+            // table b is complete; stage[b] has been consumed and may be refilled.  Table b is next
+            // rebuilt two chunks on, behind the barrier of chunk k+1, which a warp only reaches
+            // after its dense loop over table b.
+            __syncthreads();
+            if (tid == 0 && k + 2 < n_chunks) issue(k + 2);
+            const float4* tab = &rowtab[b][wy * 4 + ly];
+#pragma unroll 1
+            for (int j = split * G; j < cnt; j += S * G)
+                bound_group_tab<PX, G, kTileH>(p, tab + j * kTileH, first + j, v, st);
+        } else {
+#pragma unroll 1
+            for (int j = split * G; j < cnt; j += S * G) bound_group<PX, G>(p, &stage[b][2 * j], first + j, v, st);
+            if (k + 2 < n_chunks) {
+                __syncthreads();  // every warp is done reading stage[b] before TMA refills it
+                if (tid == 0) issue(k + 2);
+            }
+        }
+    }
+
+    // ---- merge of the primitive splits (S > 1) -----------------------------------------------
+    const bool owner = (split == 0);  // the warp of a tile that shades and stores
+    if constexpr (S > 1) {
+        __shared__ float m_best[WARPS_X * WARPS_Y * (S > 1 ? S - 1 : 1)][PX][32];
+        __shared__ int m_id[WARPS_X * WARPS_Y * (S > 1 ? S - 1 : 1)][PX][32];
+        if (split > 0) {
+#pragma unroll
+            for (int q = 0; q < PX; ++q) {
+                m_best[tile_warp * (S - 1) + split - 1][q][lane] = st.best[q];
+                m_id[tile_warp * (S - 1) + split - 1][q][lane] = st.id[q];
+            }
+        }
+        __syncthreads();
+        if (owner) {
+#pragma unroll
+            for (int o = 0; o < S - 1; ++o) {
+#pragma unroll
+                for (int q = 0; q < PX; ++q) {
+                    const float ob = m_best[tile_warp * (S - 1) + o][q][lane];
+                    const int oi = m_id[tile_warp * (S - 1) + o][q][lane];
+                    // same winner as one ascending pass: nearest t, ties to the lowest primitive index
+                    if (ob < st.best[q] || (ob == st.best[q] && oi >= 0 && (st.id[q] < 0 || oi < st.id[q]))) {
+                        st.best[q] = ob;
+                        st.id[q] = oi;
+                    }
+                }
+            }
+        }
+    }
+
+    // ---- nearest-hit shading + stores -------------------------------------------------------
+    if (owner && lrow < p.local_rows && gy < p.height && x0 < p.width) shade_and_store<PX>(p, st, x0, lrow, gy);
+
+    // ---- progress: lets the host start copying finished row chunks while the launch still runs --
+    // The launch's rows are cut into chunks of p.progress_rows rows; the last CTA of a chunk to
+    // finish publishes p.progress_epoch in the chunk's flag word, on which the copy stream waits
+    // (cuStreamWaitValue32, rtb_render).  Counter reset by that same CTA: one launch at a time.
+    if (p.progress != nullptr) {
+        __syncthreads();  // every store of this CTA is ordered before thread 0's fence
+        if (tid == 0) {
+            __threadfence_system();
+            const int row0 = blockIdx.y * kTileH;
+            const int chunk = row0 / p.progress_rows;
+            const int c0 = chunk * p.progress_rows;
+            const int c1 = min(c0 + p.progress_rows, p.local_rows);
+            const unsigned expected = gridDim.x * (unsigned)((c1 - c0 + kTileH - 1) / kTileH);
+            if (atomicAdd(&p.progress[chunk], 1u) + 1u == expected) {
+                p.progress[chunk] = 0u;
+                __threadfence_system();
+                *reinterpret_cast<volatile unsigned*>(&p.progress[kMaxProgressChunks + chunk]) = p.progress_epoch;
             }
         }
     }
@@ -413,12 +517,12 @@ GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
 }
 
 // Experiment hook (profiles/): RTB_GRID_VARIANT=n picks another tiling of the same kernel.
-template <int PX, int WX, int WY, int G, int MINB, int S = 1>
+template <int PX, int WX, int WY, int G, int MINB, int S = 1, bool TAB = false>
 cudaError_t launch_variant(const GridParams& p, cudaStream_t stream) {
     GridLaunchShape s = shape_of<PX, WX, WY>(p.width, p.local_rows);
     s.block = dim3(32 * WX * WY * S);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
-    raycast_grid_kernel<PX, WX, WY, G, MINB, S><<<s.grid, s.block, 0, stream>>>(p);
+    raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB><<<s.grid, s.block, 0, stream>>>(p);
     return cudaGetLastError();
 }
 
@@ -428,26 +532,27 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) 
         return e ? std::atoi(e) : 0;
     }();
     switch (variant) {
-        case 1: return launch_variant<16, 2, 4, 2, 3>(p, stream);
-        case 2: return launch_variant<16, 2, 4, 4, 2>(p, stream);
-        case 5: return launch_variant<16, 2, 4, 4, 3>(p, stream);
+        case 1: return launch_variant<16, 2, 2, 4, 4>(p, stream);            // row terms per thread (round-1 v2 kernel)
+        case 2: return launch_variant<16, 2, 4, 4, 3>(p, stream);            // 256 x 16 tile, per-thread row terms
         case 6: return launch_variant<8, 2, 2, 4, 8>(p, stream);
         case 7: return launch_variant<16, 2, 1, 4, 4, 2>(p, stream);
-        case 3: return launch_variant<16, 1, 1, 4, 4, 4>(p, stream);
-        case 8: return launch_variant<16, 2, 4, 1, 3>(p, stream);
         case 9: return launch_variant<4, 2, 2, 4, 8>(p, stream);
+        case 10: return launch_variant<16, 2, 2, 4, 4, 1, true>(p, stream);  // row table (production at C3)
+        case 11: return launch_variant<16, 2, 2, 4, 3, 1, true>(p, stream);
+        case 13: return launch_variant<16, 2, 2, 2, 4, 1, true>(p, stream);
+        case 15: return launch_variant<8, 2, 2, 4, 8, 1, true>(p, stream);
         default: break;
     }
     const GridLaunchShape s = grid_launch_shape(p.width, p.local_rows, sm_count);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
     if (s.px == 16 && s.wy == 2)
-        raycast_grid_kernel<16, 2, 2, kBoundGroup, 4><<<s.grid, s.block, 0, stream>>>(p);
+        raycast_grid_kernel<16, 2, 2, kBoundGroup, 4, 1, true><<<s.grid, s.block, 0, stream>>>(p);
     else if (s.px == 16)
-        raycast_grid_kernel<16, 2, 1, kBoundGroup, 4, 2><<<s.grid, s.block, 0, stream>>>(p);
+        raycast_grid_kernel<16, 2, 1, kBoundGroup, 4, 2, true><<<s.grid, s.block, 0, stream>>>(p);
     else if (s.px == 8)
-        raycast_grid_kernel<8, 2, 2, kBoundGroup, 8><<<s.grid, s.block, 0, stream>>>(p);
+        raycast_grid_kernel<8, 2, 2, kBoundGroup, 8, 1, true><<<s.grid, s.block, 0, stream>>>(p);
     else
-        raycast_grid_kernel<4, 2, 2, kBoundGroup, 8><<<s.grid, s.block, 0, stream>>>(p);
+        raycast_grid_kernel<4, 2, 2, kBoundGroup, 8, 1, true><<<s.grid, s.block, 0, stream>>>(p);
     return cudaGetLastError();
 }
 

@@ -11,6 +11,10 @@ namespace rtb {
 
 // Bound records (RtbBound, 32 B) per staged shared-memory chunk: 512 primitives = 16 KB per stage.
 constexpr int kChunkPrims = 512;
+// Row-table kernels: primitives per staged chunk (4 KB of bound records -> 16 B x rows x 128 table).
+constexpr int kTabPrims = 128;
+// Row chunks a launch can report as finished while it is still running (rtb_render's pipelined copies).
+constexpr int kMaxProgressChunks = 32;
 // Primitives per warp vote in the dense loop; the host pads the bound list to a multiple of it.
 constexpr int kBoundGroup = 4;
 
@@ -30,6 +34,11 @@ struct GridParams {
     int32_t* out_id;                        // nullable
     int4* out_i32;                          // nullable
     int vec_ok;                             // outputs 16-byte aligned and width % 4 == 0
+    // Progress words (nullable): [0, kMaxProgressChunks) CTA counters, [kMaxProgressChunks, 2x) flags.
+    // Chunk c = local rows [c*progress_rows, (c+1)*progress_rows); progress_rows is a multiple of 16.
+    unsigned int* progress;
+    int progress_rows;
+    unsigned int progress_epoch;
     RtbCam cam;
 };
 

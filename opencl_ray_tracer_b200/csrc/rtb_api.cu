@@ -2,11 +2,14 @@
 //
 // Host-side replacement for MainState::openCLInit / executeRayTracerOpenCL
 // (RayTrace/states/MainState.cpp:1181-1326, :641-934): device pick, resident scene buffers,
-// per-frame camera-space pack (scene_pack.cpp), kernel launch (raycast_kernels.cu), read-back.
+// per-frame camera-space pack ON the device (scene_pack_device.cu), kernel launch
+// (raycast_kernels.cu), read-back.
 // There is NO CPU path in this library.
+#include <cuda.h>  // types of the driver entry point fetched below; libcuda is NOT linked
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -14,6 +17,7 @@
 #include "../../include/rtb.h"
 #include "raycast_kernels.cuh"
 #include "scene_pack.h"
+#include "scene_pack_device.cuh"
 
 using namespace rtb;
 
@@ -27,21 +31,34 @@ struct rtb_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;  // device->host copies of finished row chunks (rtb_render)
     cudaEvent_t ev_chunk[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    // In-launch progress (rtb_render): the grid kernel publishes finished row chunks in d_progress and
+    // copy_stream waits on the flag words with cuStreamWaitValue32 (fetched through the runtime).
+    unsigned int* d_progress = nullptr;  // 2 * kMaxProgressChunks words
+    unsigned int progress_epoch = 0;
+    CUresult (*stream_wait_value32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int) = nullptr;
     std::string last_error;
 
-    // scene (host copies, reference layout) + recovered boxes
+    // scene: resident on the device in the reference's layout + the boxes recovered from the cubes
     bool have_scene = false;
     int ns = 0, nc = 0;
+    float* d_cube_v = nullptr;     // 144 floats per cube (rayTracer.cl cubeVertices)
+    float4* d_sph_o = nullptr;
+    float* d_sph_r = nullptr;
+    Box* d_boxes = nullptr;
+    size_t d_scene_cap[4] = {0, 0, 0, 0};  // bytes: cube_v, sph_o, sph_r, boxes
+    int* d_bad = nullptr;          // lowest index of a cube that is not a box (boxes_from_vertices_kernel)
+    int* h_bad = nullptr;          // pinned
+    // host mirror of boxes / spheres, downloaded on demand (rtb_render_rays packs on the host)
+    bool host_scene_valid = false;
     std::vector<float> sph_o, sph_r;
     std::vector<Box> boxes;
-    std::vector<float> cube_v;  // kept for rtb_render_rays-free re-validation/debug
 
     // device buffers
     float4* d_cube_col = nullptr;
     float4* d_sph_col = nullptr;
     float4* d_rec = nullptr;       // per-frame packed records (cubes then spheres), grow-only
     size_t d_rec_cap = 0;          // in float4
-    float4* h_rec = nullptr;       // pinned staging for the records
+    float4* h_rec = nullptr;       // pinned staging for host-packed records (rtb_render_rays only)
     size_t h_rec_cap = 0;
     void* d_out[3] = {nullptr, nullptr, nullptr};  // rgba8, id, i32 frame buffers, grow-only
     size_t d_out_cap[3] = {0, 0, 0};
@@ -89,7 +106,7 @@ int ensure_device(rtb_ctx* ctx, void** p, size_t* cap, size_t need_bytes) {
     return RTB_OK;
 }
 
-int ensure_records(rtb_ctx* ctx, size_t n_float4) {
+int ensure_records(rtb_ctx* ctx, size_t n_float4, bool host_staging = false) {
     if (n_float4 == 0) n_float4 = 1;
     if (ctx->d_rec_cap < n_float4) {
         if (ctx->d_rec) RTB_CUDA(ctx, cudaFree(ctx->d_rec));
@@ -97,7 +114,7 @@ int ensure_records(rtb_ctx* ctx, size_t n_float4) {
         RTB_CUDA(ctx, cudaMalloc(&ctx->d_rec, n_float4 * sizeof(float4)));
         ctx->d_rec_cap = n_float4;
     }
-    if (ctx->h_rec_cap < n_float4) {
+    if (host_staging && ctx->h_rec_cap < n_float4) {
         if (ctx->h_rec) RTB_CUDA(ctx, cudaFreeHost(ctx->h_rec));
         ctx->h_rec = nullptr;
         RTB_CUDA(ctx, cudaMallocHost(&ctx->h_rec, n_float4 * sizeof(float4)));
@@ -182,9 +199,23 @@ int rtb_init(rtb_ctx** out, int n_devices, const int* device_ids) {
     if (!chunk_ok || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreate(&ctx->ev_total0) != cudaSuccess || cudaEventCreate(&ctx->ev_total1) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_rec, cudaEventDisableTiming) != cudaSuccess ||
-        configure_kernels() != cudaSuccess) {
+        cudaMalloc(&ctx->d_bad, sizeof(int)) != cudaSuccess ||
+        cudaMalloc(&ctx->d_progress, 2 * kMaxProgressChunks * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMemset(ctx->d_progress, 0, 2 * kMaxProgressChunks * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMallocHost(&ctx->h_bad, sizeof(int)) != cudaSuccess || configure_kernels() != cudaSuccess) {
         rtb_shutdown(ctx);
         return RTB_ERR_CUDA;
+    }
+    {   // optional: without it rtb_render falls back to one launch per row chunk
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        const char* off = std::getenv("RTB_NO_STREAM_WAIT");
+        if (!(off && off[0] == '1') &&
+            cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &qr) == cudaSuccess &&
+            qr == cudaDriverEntryPointSuccess && fn)
+            ctx->stream_wait_value32 = reinterpret_cast<CUresult (*)(CUstream, CUdeviceptr, cuuint32_t, unsigned int)>(fn);
+        else
+            (void)cudaGetLastError();
     }
     *out = ctx;
     return RTB_OK;
@@ -202,6 +233,13 @@ void rtb_shutdown(rtb_ctx* ctx) {
     cudaFree(ctx->d_cube_col);
     cudaFree(ctx->d_sph_col);
     cudaFree(ctx->d_rec);
+    cudaFree(ctx->d_cube_v);
+    cudaFree(ctx->d_sph_o);
+    cudaFree(ctx->d_sph_r);
+    cudaFree(ctx->d_boxes);
+    cudaFree(ctx->d_bad);
+    cudaFree(ctx->d_progress);
+    if (ctx->h_bad) cudaFreeHost(ctx->h_bad);
     if (ctx->h_rec) cudaFreeHost(ctx->h_rec);
     for (int i = 0; i < 3; ++i) cudaFree(ctx->d_out[i]);
     cudaFree(ctx->d_origins);
@@ -221,46 +259,58 @@ int rtb_set_scene(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins, cons
         return fail(ctx, RTB_ERR_INVALID_ARG, "null sphere array");
     if (numCubes > 0 && (!cubeVertices || !cubeColours)) return fail(ctx, RTB_ERR_INVALID_ARG, "null cube array");
     RTB_CUDA(ctx, cudaSetDevice(ctx->device));
-    std::vector<Box> boxes((size_t)numCubes);
-    for (int c = 0; c < numCubes; ++c) {
-        if (!box_from_vertices(cubeVertices + (size_t)c * 144, &boxes[c])) {
-            char buf[160];
-            std::snprintf(buf, sizeof buf,
-                          "cube %d: its 36 vertices are not an affine image of the Cube.cpp vertex list", c);
-            return fail(ctx, RTB_ERR_NOT_A_BOX, buf);
-        }
-    }
     ctx->have_scene = false;
     ctx->packed_valid = false;
-    RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->host_scene_valid = false;
+    cudaStream_t st = ctx->stream;
+    RTB_CUDA(ctx, cudaStreamSynchronize(st));
+    const size_t nc = (size_t)numCubes, ns = (size_t)numSpheres;
     {
-        void* p = ctx->d_cube_col;
-        size_t cap = ctx->d_col_cap[0] * sizeof(float4);
-        int rc0 = ensure_device(ctx, &p, &cap, sizeof(float4) * (size_t)(numCubes > 0 ? numCubes : 1));
-        ctx->d_cube_col = static_cast<float4*>(p);
-        ctx->d_col_cap[0] = cap / sizeof(float4);
-        if (rc0 != RTB_OK) return rc0;
-        p = ctx->d_sph_col;
-        cap = ctx->d_col_cap[1] * sizeof(float4);
-        rc0 = ensure_device(ctx, &p, &cap, sizeof(float4) * (size_t)(numSpheres > 0 ? numSpheres : 1));
-        ctx->d_sph_col = static_cast<float4*>(p);
-        ctx->d_col_cap[1] = cap / sizeof(float4);
+        void* p[6] = {ctx->d_cube_v, ctx->d_sph_o, ctx->d_sph_r, ctx->d_boxes, ctx->d_cube_col, ctx->d_sph_col};
+        size_t cap[6] = {ctx->d_scene_cap[0], ctx->d_scene_cap[1], ctx->d_scene_cap[2], ctx->d_scene_cap[3],
+                         ctx->d_col_cap[0] * sizeof(float4), ctx->d_col_cap[1] * sizeof(float4)};
+        const size_t need[6] = {144 * sizeof(float) * (nc ? nc : 1), sizeof(float4) * (ns ? ns : 1),
+                                sizeof(float) * (ns ? ns : 1), sizeof(Box) * (nc ? nc : 1),
+                                sizeof(float4) * (nc ? nc : 1), sizeof(float4) * (ns ? ns : 1)};
+        int rc0 = RTB_OK;
+        for (int k = 0; k < 6 && rc0 == RTB_OK; ++k) rc0 = ensure_device(ctx, &p[k], &cap[k], need[k]);
+        ctx->d_cube_v = static_cast<float*>(p[0]);
+        ctx->d_sph_o = static_cast<float4*>(p[1]);
+        ctx->d_sph_r = static_cast<float*>(p[2]);
+        ctx->d_boxes = static_cast<Box*>(p[3]);
+        ctx->d_cube_col = static_cast<float4*>(p[4]);
+        ctx->d_sph_col = static_cast<float4*>(p[5]);
+        for (int k = 0; k < 4; ++k) ctx->d_scene_cap[k] = cap[k];
+        ctx->d_col_cap[0] = cap[4] / sizeof(float4);
+        ctx->d_col_cap[1] = cap[5] / sizeof(float4);
         if (rc0 != RTB_OK) return rc0;
     }
-    if (numCubes > 0)
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_cube_col, cubeColours, sizeof(float4) * (size_t)numCubes,
-                                      cudaMemcpyHostToDevice, ctx->stream));
-    if (numSpheres > 0)
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_sph_col, sphereColours, sizeof(float4) * (size_t)numSpheres,
-                                      cudaMemcpyHostToDevice, ctx->stream));
-    RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the caller may free its arrays on return
-    ctx->h2d_bytes += sizeof(float4) * ((size_t)numCubes + (size_t)numSpheres);
+    // The scene goes to the device exactly as the reference lays it out (the 6 arrays of
+    // MainState.cpp:677-839); the boxes are recovered from the vertices there.
+    if (nc) {
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_cube_v, cubeVertices, 144 * sizeof(float) * nc, cudaMemcpyHostToDevice, st));
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_cube_col, cubeColours, sizeof(float4) * nc, cudaMemcpyHostToDevice, st));
+    }
+    if (ns) {
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_sph_o, sphereOrigins, sizeof(float4) * ns, cudaMemcpyHostToDevice, st));
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_sph_r, sphereRadius, sizeof(float) * ns, cudaMemcpyHostToDevice, st));
+        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_sph_col, sphereColours, sizeof(float4) * ns, cudaMemcpyHostToDevice, st));
+    }
+    RTB_CUDA(ctx, launch_boxes_from_vertices(ctx->d_cube_v, numCubes, ctx->d_boxes, ctx->d_bad, st));
+    if (nc) ctx->launches += 1;
+    RTB_CUDA(ctx, cudaMemcpyAsync(ctx->h_bad, ctx->d_bad, sizeof(int), cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(ctx, cudaStreamSynchronize(st));  // the caller may free its arrays on return
+    ctx->h2d_bytes += (144 * sizeof(float) + sizeof(float4)) * nc + (2 * sizeof(float4) + sizeof(float)) * ns;
+    ctx->d2h_bytes += sizeof(int);
+    if (nc && *ctx->h_bad != kNoBadCube) {
+        char buf[160];
+        std::snprintf(buf, sizeof buf, "cube %d: its 36 vertices are not an affine image of the Cube.cpp vertex list",
+                      *ctx->h_bad);
+        return fail(ctx, RTB_ERR_NOT_A_BOX, buf);
+    }
     ctx->ns = numSpheres;
     ctx->nc = numCubes;
-    ctx->boxes.swap(boxes);
-    ctx->sph_o.assign(sphereOrigins, sphereOrigins + 4 * (size_t)numSpheres);
-    ctx->sph_r.assign(sphereRadius, sphereRadius + (size_t)numSpheres);
-    const int rc = ensure_records(ctx, 6 * (size_t)numCubes + 4 * (size_t)numSpheres + 32);
+    const int rc = ensure_records(ctx, 6 * nc + 4 * ns + 32);
     if (rc != RTB_OK) return rc;
     ctx->have_scene = true;
     return RTB_OK;
@@ -282,22 +332,22 @@ int bound_count(const rtb_ctx* ctx) {
 }
 size_t frame_records(const rtb_ctx* ctx) { return bound_offset(ctx) + 2 * (size_t)bound_count(ctx); }
 
-void pack_frame(const rtb_ctx* ctx, const CameraFrame& cf, int width, int height, float4* dst) {
-    RtbSlab* slabs = reinterpret_cast<RtbSlab*>(dst);
-    for (int c = 0; c < ctx->nc; ++c) pack_box(cf, ctx->boxes[c], slabs + 3 * (size_t)c);
-    RtbSphere* sph = reinterpret_cast<RtbSphere*>(dst + 3 * (size_t)ctx->nc);
-    for (int s = 0; s < ctx->ns; ++s) pack_sphere(cf, &ctx->sph_o[4 * (size_t)s], ctx->sph_r[s], sph + s);
-    for (size_t i = exact_records(ctx); i < bound_offset(ctx); ++i) dst[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    const FrameExtent fe = frame_extent(cf, width, height);
-    RtbBound* bnd = reinterpret_cast<RtbBound*>(dst + bound_offset(ctx));
-    for (int c = 0; c < ctx->nc; ++c) pack_bound_box(fe, slabs + 3 * (size_t)c, bnd + c);
-    for (int s = 0; s < ctx->ns; ++s) pack_bound_sphere(fe, sph[s], bnd + ctx->nc + s);
-    const RtbBound never = {0.f, 0.f, 2.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // w = 2, q = 4
-    for (int i = ctx->nc + ctx->ns; i < bound_count(ctx); ++i) bnd[i] = never;
+// Enqueues the device pack of one frame's records into `dst` (scene_pack_device.cu).
+int enqueue_pack(rtb_ctx* ctx, const CameraFrame& cf, int width, int height, float4* dst, cudaStream_t stream) {
+    PackFrameParams pp;
+    pp.cf = cf;
+    pp.fe = frame_extent(cf, width, height);
+    pp.nc = ctx->nc; pp.ns = ctx->ns; pp.n_bound = bound_count(ctx);
+    pp.boxes = ctx->d_boxes; pp.sph_o = ctx->d_sph_o; pp.sph_r = ctx->d_sph_r;
+    pp.rec = dst;
+    pp.bound_off = bound_offset(ctx);
+    RTB_CUDA(ctx, launch_pack_frame(pp, stream));
+    ctx->launches += 1;
+    return RTB_OK;
 }
 
-// Packs this frame's records and enqueues their upload, unless d_rec already holds the records of
-// exactly this camera (same 16 floats, same scene).
+// Packs this frame's records on the device, unless d_rec already holds the records of exactly this
+// camera (same 16 floats, same frame size, same scene).
 int upload_frame_records(rtb_ctx* ctx, const CameraFrame& cf, int width, int height, const float* o0,
                          const float* du, const float* dv, const float* dir, cudaStream_t stream) {
     float cam16[16];
@@ -306,27 +356,40 @@ int upload_frame_records(rtb_ctx* ctx, const CameraFrame& cf, int width, int hei
     if (ctx->packed_valid && ctx->packed_w == width && ctx->packed_h == height &&
         std::memcmp(cam16, ctx->packed_cam, sizeof cam16) == 0)
         return RTB_OK;
-    // the pinned staging area is reused: the previous upload must have left it
-    RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
-    pack_frame(ctx, cf, width, height, ctx->h_rec);
-    const size_t nrec = frame_records(ctx);
-    if (nrec)
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, nrec * sizeof(float4), cudaMemcpyHostToDevice,
-                                      stream));
-    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_rec, stream));
-    ctx->h2d_bytes += nrec * sizeof(float4);
+    const int rc = enqueue_pack(ctx, cf, width, height, ctx->d_rec, stream);
+    if (rc != RTB_OK) return rc;
     std::memcpy(ctx->packed_cam, cam16, sizeof cam16);
     ctx->packed_w = width; ctx->packed_h = height;
     ctx->packed_valid = true;
     return RTB_OK;
 }
 
+// Host mirror of the device scene (boxes, sphere centres / radii) for the host-packed rays path.
+int ensure_host_scene(rtb_ctx* ctx) {
+    if (ctx->host_scene_valid) return RTB_OK;
+    ctx->boxes.resize((size_t)ctx->nc);
+    ctx->sph_o.resize(4 * (size_t)ctx->ns);
+    ctx->sph_r.resize((size_t)ctx->ns);
+    if (ctx->nc)
+        RTB_CUDA(ctx, cudaMemcpy(ctx->boxes.data(), ctx->d_boxes, sizeof(Box) * (size_t)ctx->nc, cudaMemcpyDeviceToHost));
+    if (ctx->ns) {
+        RTB_CUDA(ctx, cudaMemcpy(ctx->sph_o.data(), ctx->d_sph_o, sizeof(float4) * (size_t)ctx->ns, cudaMemcpyDeviceToHost));
+        RTB_CUDA(ctx, cudaMemcpy(ctx->sph_r.data(), ctx->d_sph_r, sizeof(float) * (size_t)ctx->ns, cudaMemcpyDeviceToHost));
+    }
+    ctx->d2h_bytes += sizeof(Box) * (size_t)ctx->nc + (sizeof(float4) + sizeof(float)) * (size_t)ctx->ns;
+    ctx->host_scene_valid = true;
+    return RTB_OK;
+}
+
 // Enqueues one grid-kernel launch (with its timing event pair) on `stream`.
 int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width, int height, int band_rows,
                  int band_rank, int band_world, int local_rows, void* d_rgba8, void* d_id, void* d_i32,
-                 cudaStream_t stream, int out_global_rows = 0) {
+                 cudaStream_t stream, int out_global_rows = 0, int progress_rows = 0) {
     GridParams p;
     p.out_global_rows = out_global_rows;
+    p.progress = progress_rows > 0 ? ctx->d_progress : nullptr;
+    p.progress_rows = progress_rows > 0 ? progress_rows : 1;
+    p.progress_epoch = ctx->progress_epoch;
     p.width = width; p.height = height;
     p.band_rows = band_rows; p.band_rank = band_rank; p.band_world = band_world;
     p.local_rows = local_rows;
@@ -508,34 +571,72 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total0, st));
     rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, st);
     if (rc != RTB_OK) return rc;
-    // The frame is rendered as up to 4 chunks of whole rows; chunk k travels to the host on
-    // copy_stream while chunk k+1 is still being rendered (the reference's OpenCL path does one
-    // blocking clEnqueueMapBuffer after the kernel, MainState.cpp:876-886).
     const bool any_host = host[0] || host[1] || host[2];
-    int n_chunks = (any_host && height >= 256) ? 4 : 1;
-    int chunk_rows = ((height + n_chunks - 1) / n_chunks + 7) & ~7;
-    n_chunks = (height + chunk_rows - 1) / chunk_rows;
     const size_t elem[3] = {4, 4, 16};
-    cudaStream_t cs = (n_chunks > 1) ? ctx->copy_stream : st;
-    for (int k = 0; k < n_chunks; ++k) {
-        const int y0 = k * chunk_rows;
-        const int rows = (height - y0 < chunk_rows) ? (height - y0) : chunk_rows;
-        void* d[3];
-        for (int i = 0; i < 3; ++i)
-            d[i] = host[i] ? static_cast<uint8_t*>(ctx->d_out[i]) + elem[i] * (size_t)y0 * width : nullptr;
-        rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, chunk_rows, k, n_chunks, rows, d[0], d[1], d[2], st);
+    size_t row_bytes = 0;
+    for (int i = 0; i < 3; ++i)
+        if (host[i]) row_bytes += elem[i] * (size_t)width;
+    cudaStream_t cs = st;
+    if (any_host && ctx->stream_wait_value32 && height >= 64) {
+        // ONE launch for the whole frame; the kernel publishes finished row chunks (about 2 MB of
+        // output each, at most kMaxProgressChunks) and copy_stream copies chunk k to the host as soon
+        // as its flag shows this frame's epoch, while later rows are still being rendered.  (The
+        // reference's OpenCL path does one blocking clEnqueueMapBuffer after the kernel,
+        // MainState.cpp:876-886.)
+        size_t want = (row_bytes * (size_t)height + (2u << 20) - 1) / (2u << 20);
+        if (want < 1) want = 1;
+        if (want > (size_t)kMaxProgressChunks) want = kMaxProgressChunks;
+        int chunk_rows = (int)(((size_t)height + want - 1) / want);
+        chunk_rows = (chunk_rows + 15) & ~15;
+        const int n_chunks = (height + chunk_rows - 1) / chunk_rows;
+        cs = ctx->copy_stream;
+        ctx->progress_epoch += 1;
+        if (ctx->progress_epoch == 0) ctx->progress_epoch = 1;
+        rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, 16, 0, 1, height, host[0] ? ctx->d_out[0] : nullptr,
+                          host[1] ? ctx->d_out[1] : nullptr, host[2] ? ctx->d_out[2] : nullptr, st, 0, chunk_rows);
         if (rc != RTB_OK) return rc;
-        if (n_chunks > 1) {
-            RTB_CUDA(ctx, cudaEventRecord(ctx->ev_chunk[k], st));
-            RTB_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_chunk[k], 0));
+        for (int k = 0; k < n_chunks; ++k) {
+            const int y0 = k * chunk_rows;
+            const int rows = (height - y0 < chunk_rows) ? (height - y0) : chunk_rows;
+            const CUdeviceptr flag = reinterpret_cast<CUdeviceptr>(ctx->d_progress + kMaxProgressChunks + k);
+            if (ctx->stream_wait_value32(cs, flag, ctx->progress_epoch, CU_STREAM_WAIT_VALUE_EQ) != CUDA_SUCCESS)
+                return fail(ctx, RTB_ERR_CUDA, "cuStreamWaitValue32 failed");
+            for (int i = 0; i < 3; ++i)
+                if (host[i]) {
+                    const size_t off = elem[i] * (size_t)y0 * width, nb = elem[i] * (size_t)rows * width;
+                    RTB_CUDA(ctx, cudaMemcpyAsync(static_cast<uint8_t*>(host[i]) + off,
+                                                  static_cast<uint8_t*>(ctx->d_out[i]) + off, nb,
+                                                  cudaMemcpyDeviceToHost, cs));
+                    ctx->d2h_bytes += nb;
+                }
         }
-        for (int i = 0; i < 3; ++i)
-            if (host[i]) {
-                const size_t nb = elem[i] * (size_t)rows * width;
-                RTB_CUDA(ctx, cudaMemcpyAsync(static_cast<uint8_t*>(host[i]) + elem[i] * (size_t)y0 * width, d[i], nb,
-                                              cudaMemcpyDeviceToHost, cs));
-                ctx->d2h_bytes += nb;
+    } else {
+        // Fallback without stream memory operations: up to 4 launches of whole-row chunks, chunk k
+        // travelling to the host on copy_stream while chunk k+1 is rendered.
+        int n_chunks = (any_host && height >= 256) ? 4 : 1;
+        int chunk_rows = ((height + n_chunks - 1) / n_chunks + 7) & ~7;
+        n_chunks = (height + chunk_rows - 1) / chunk_rows;
+        cs = (n_chunks > 1) ? ctx->copy_stream : st;
+        for (int k = 0; k < n_chunks; ++k) {
+            const int y0 = k * chunk_rows;
+            const int rows = (height - y0 < chunk_rows) ? (height - y0) : chunk_rows;
+            void* d[3];
+            for (int i = 0; i < 3; ++i)
+                d[i] = host[i] ? static_cast<uint8_t*>(ctx->d_out[i]) + elem[i] * (size_t)y0 * width : nullptr;
+            rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, chunk_rows, k, n_chunks, rows, d[0], d[1], d[2], st);
+            if (rc != RTB_OK) return rc;
+            if (n_chunks > 1) {
+                RTB_CUDA(ctx, cudaEventRecord(ctx->ev_chunk[k], st));
+                RTB_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev_chunk[k], 0));
             }
+            for (int i = 0; i < 3; ++i)
+                if (host[i]) {
+                    const size_t nb = elem[i] * (size_t)rows * width;
+                    RTB_CUDA(ctx, cudaMemcpyAsync(static_cast<uint8_t*>(host[i]) + elem[i] * (size_t)y0 * width, d[i], nb,
+                                                  cudaMemcpyDeviceToHost, cs));
+                    ctx->d2h_bytes += nb;
+                }
+        }
     }
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total1, cs));
     RTB_CUDA(ctx, cudaStreamSynchronize(cs));
@@ -570,6 +671,10 @@ int rtb_render_rays(rtb_ctx* ctx, size_t n_rays, const float* rayOrigins, const 
     ctx->d_origins = static_cast<float4*>(dorig);
     if (rc != RTB_OK) return rc;
     cudaStream_t st = ctx->stream;
+    rc = ensure_host_scene(ctx);
+    if (rc != RTB_OK) return rc;
+    rc = ensure_records(ctx, 4 * (size_t)ctx->nc + 2 * (size_t)ctx->ns + 8, true);
+    if (rc != RTB_OK) return rc;
     RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total0, st));
     // world-space records: 4 float4 per cube, then 2 per sphere (centre, radius)
@@ -585,8 +690,10 @@ int rtb_render_rays(rtb_ctx* ctx, size_t n_rays, const float* rayOrigins, const 
     const size_t nrec = 4 * (size_t)ctx->nc + 2 * (size_t)ctx->ns;
     if (nrec)
         RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, nrec * sizeof(float4), cudaMemcpyHostToDevice, st));
+    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_rec, st));
     if (n_rays)
         RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_origins, rayOrigins, 16 * n_rays, cudaMemcpyHostToDevice, st));
+    ctx->h2d_bytes += nrec * sizeof(float4) + 16 * n_rays;
     RaysParams p;
     p.n_rays = n_rays;
     p.origins = ctx->d_origins;
@@ -628,34 +735,26 @@ int rtb_render_sequence_device(rtb_ctx* ctx, int width, int height, int n_frames
     int rc = check_frame_args(ctx, width, height, cameras, cameras + 4, cameras + 8, cameras + 12);
     if (rc != RTB_OK) return rc;
     RTB_CUDA(ctx, cudaSetDevice(ctx->device));
-    const size_t nrec = frame_records(ctx);
-    const size_t stride = (nrec + 7) & ~(size_t)7;  // keep each frame's records 128-byte aligned
-    RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
-    rc = ensure_records(ctx, stride * (size_t)n_frames + 8);
-    ctx->packed_valid = false;
+    cudaStream_t st = ctx->stream;
+    RTB_CUDA(ctx, cudaStreamSynchronize(st));
+    ctx->packed_valid = false;  // d_rec is re-packed per frame below (pack kernel, same stream)
+    rc = resolve_pending(ctx);
     if (rc != RTB_OK) return rc;
-    std::vector<RtbCam> cams((size_t)n_frames);
+    const double k0 = ctx->kernel_ms_sum;
+    const size_t frame_bytes = 4 * (size_t)width * height;
     for (int f = 0; f < n_frames; ++f) {
         const float* c = cameras + 16 * (size_t)f;
         CameraFrame cf;
         if (!camera_prepare(c, c + 4, c + 8, c + 12, &cf)) {
             char buf[96];
             std::snprintf(buf, sizeof buf, "degenerate camera in frame %d", f);
+            cudaStreamSynchronize(st);
             return fail(ctx, RTB_ERR_CAMERA, buf);
         }
-        pack_frame(ctx, cf, width, height, ctx->h_rec + stride * (size_t)f);
-        cams[f] = cf.cam;
-    }
-    rc = resolve_pending(ctx);
-    if (rc != RTB_OK) return rc;
-    const double k0 = ctx->kernel_ms_sum;
-    cudaStream_t st = ctx->stream;
-    RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, stride * (size_t)n_frames * sizeof(float4),
-                                  cudaMemcpyHostToDevice, st));
-    const size_t frame_bytes = 4 * (size_t)width * height;
-    for (int f = 0; f < n_frames; ++f) {
-        rc = enqueue_grid(ctx, cams[f], ctx->d_rec + stride * (size_t)f, width, height, 4, 0, 1, height,
+        float4* rec = ctx->d_rec;
+        rc = enqueue_pack(ctx, cf, width, height, rec, st);
+        if (rc != RTB_OK) return rc;
+        rc = enqueue_grid(ctx, cf.cam, rec, width, height, 4, 0, 1, height,
                           static_cast<uint8_t*>(d_rgba8) + frame_bytes * (size_t)f, nullptr, nullptr, st);
         if (rc != RTB_OK) return rc;
     }
@@ -746,6 +845,27 @@ int rtb_debug_pack_bounds(int numSpheres, const float* sphereOrigins, const floa
         pack_sphere(cf, sphereOrigins + 4 * (size_t)s, sphereRadius[s], &sp);
         pack_bound_sphere(fe, sp, out + numCubes + s);
     }
+    return RTB_OK;
+}
+
+int rtb_debug_device_records(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+                             const float dV[4], const float rayDir[4], float* out, size_t out_cap_floats,
+                             size_t* n_floats, size_t* bound_offset_floats) {
+    int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    CameraFrame cf;
+    if (!camera_prepare(origin0, dU, dV, rayDir, &cf)) return fail(ctx, RTB_ERR_CAMERA, "degenerate camera");
+    const size_t n = 4 * frame_records(ctx);
+    if (n_floats) *n_floats = n;
+    if (bound_offset_floats) *bound_offset_floats = 4 * bound_offset(ctx);
+    if (!out) return RTB_OK;
+    if (out_cap_floats < n) return fail(ctx, RTB_ERR_INVALID_ARG, "record buffer too small");
+    ctx->packed_valid = false;
+    rc = enqueue_pack(ctx, cf, width, height, ctx->d_rec, ctx->stream);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaMemcpyAsync(out, ctx->d_rec, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return RTB_OK;
 }
 

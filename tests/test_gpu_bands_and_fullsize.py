@@ -64,7 +64,7 @@ def test_sequence_equals_single_frames(gpu_ctx):
     torch.cuda.synchronize()
     n0 = gpu_ctx.launch_count()
     kms = gpu_ctx.render_sequence_device(w, h, flat, out.data_ptr())
-    assert gpu_ctx.launch_count() - n0 == nf and kms > 0
+    assert gpu_ctx.launch_count() - n0 == 2 * nf and kms > 0      # per frame: device pack kernel + grid kernel
     seq = out.cpu().numpy()
     for k in range(nf):
         single = gpu_ctx.render(w, h, camera=cams[k], want=("rgba8",))["rgba8"]
@@ -94,6 +94,25 @@ def test_full_size_rows_vs_oracle_and_band_property(gpu_ctx, port, w, h, ns, nc,
     assert np.array_equal(f8, g["rgba8"]) and np.array_equal(fid, g["prim_id"])
 
 
+def test_pipelined_render_equals_chunked_fallback(gpu_ctx, monkeypatch):
+    """rtb_render's single-launch path (in-launch progress flags + cuStreamWaitValue32 on the copy
+    stream) against the multi-launch fallback used when stream memory operations are unavailable."""
+    from opencl_ray_tracer_b200 import capi, host_scene as hs
+    w, h = 1920, 1080
+    s = hs.random_scene(w, h, 64, 64, 2)
+    _set(gpu_ctx, s)
+    a = gpu_ctx.render(w, h)
+    a2 = gpu_ctx.render(w, h)                          # flags carry a new epoch every frame
+    monkeypatch.setenv("RTB_NO_STREAM_WAIT", "1")
+    with capi.Context(0) as ctx2:
+        _set(ctx2, s)
+        n0 = ctx2.launch_count()
+        b = ctx2.render(w, h)
+        assert ctx2.launch_count() - n0 == 1 + 4       # pack + 4 row-chunk launches
+    for k in ("rgba8", "prim_id", "rgba_i32"):
+        assert np.array_equal(a[k], b[k]) and np.array_equal(a2[k], b[k]), k
+
+
 def test_kernel_timer_and_launch_counter(gpu_ctx):
     from opencl_ray_tracer_b200 import host_scene as hs
     s = hs.random_scene(640, 480, 16, 16, 2)
@@ -103,10 +122,11 @@ def test_kernel_timer_and_launch_counter(gpu_ctx):
     for _ in range(3):
         gpu_ctx.render(640, 480, want=("rgba8",))
     avg, n = gpu_ctx.kernel_ms_avg()
-    # rtb_render pipelines a frame as up to 4 row chunks (one launch each) with their D2H copies
-    assert n in (3, 12) and avg > 0 and gpu_ctx.launch_count() - n0 == n
+    # rtb_render = ONE grid launch per frame (finished row chunks are copied out while it runs); the
+    # record pack kernel runs once, the two other frames find their camera's records resident
+    assert n == 3 and avg > 0 and gpu_ctx.launch_count() - n0 == 4
     n1 = gpu_ctx.launch_count()
-    gpu_ctx.render(64, 48, want=("rgba8",))           # small frames stay a single launch
-    assert gpu_ctx.launch_count() - n1 == 1
+    gpu_ctx.render(64, 48, want=("rgba8",))           # new frame size: pack + grid
+    assert gpu_ctx.launch_count() - n1 == 2
     info = gpu_ctx.device_info()
     assert info["sm_count"] >= 100 and "B200" in info["name"].upper() or info["sm_count"] > 0
