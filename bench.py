@@ -110,6 +110,18 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(s)}
 
 
+def ncu_traffic_bytes(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, from the
+    committed ncu --set full capture (profiles/r01_ncu_traffic.json); None for other workloads."""
+    try:
+        j = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))
+        if j.get("workload") == workload:
+            return j["dram_bytes_read"] + j["dram_bytes_write"]
+    except Exception:
+        pass
+    return None
+
+
 def fp32_probe_tflops():
     """Empirical FP32 peak: profiles/microbench/fp32_issue_probe (packed-FFMA2 chains), TFLOP/s."""
     import subprocess
@@ -212,6 +224,8 @@ def run_ours(args):
         if not peer.ok:
             peer = None
     peer_frame = peer.as_tensor() if (peer and rank == 0) else None
+    # N > 1, end to end: one frame in shared host memory; every rank's GPU delivers its own bands into it
+    shared = bands.SharedHostFrame(dist, w, h, rank, world) if world > 1 else None
 
     def gather_and_assemble():
         if world == 1:
@@ -236,19 +250,13 @@ def run_ours(args):
         if world == 1:
             ctx.render(w, h, cam, want=("rgba8",), out={"rgba8": h_np})
             return 1
-        if peer:
-            peer.render(cam, BAND_ROWS, sptr)
-            peer.fence()
-            n = 1
-        else:
-            ctx.render_bands_device(w, h, cam, BAND_ROWS, rank, world, d_rgba8=my_slice.data_ptr(), stream=sptr)
-            n = 1 + gather_and_assemble()
-        if rank == 0:
-            h_frame.copy_(peer_frame if peer else d_frame, non_blocking=True)
+        shared.render(ctx, cam, BAND_ROWS)     # blocking: this rank's bands are in the shared host frame
+        peer.fence() if peer else dist.all_reduce(token)   # 4-byte all-reduce: every rank has delivered
         stream.synchronize()
-        return n
+        return 1
 
     h_np = h_frame.numpy() if rank == 0 else None
+    token = torch.zeros(1, dtype=torch.int32, device="cuda")
 
     def barrier():
         if world > 1:
@@ -298,8 +306,13 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_s = float(t.item())
-    d2h_per_step = (d2h1 - d2h0) / args.steps + (4 * n_px if (world > 1 and rank == 0) else 0)
-    h2d_per_step = (h2d1 - h2d0) / args.steps
+    # bytes this rank moved; summed over the ranks below (every rank uploads the scene, each downloads its bands)
+    tb = torch.tensor([float(h2d1 - h2d0), float(d2h1 - d2h0)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tb)
+    h2d_per_step, d2h_per_step = float(tb[0].item()) / args.steps, float(tb[1].item()) / args.steps
+    if shared is not None:
+        shared.close()
     return dict(rank=rank, world=world, w=w, h=h, ns=ns, nc=nc, seed=seed, scene=scene, ctx=ctx,
                 ms_per_step=ms_per_step, wall_ms_per_step=wall * 1e3 / args.steps, k_avg_ms=k_avg_ms, k_n=k_n,
                 launches=launches, clocks=sampler.result(), peer=bool(peer), e2e_s=e2e_s, h2d=h2d_per_step, d2h=d2h_per_step,
@@ -444,11 +457,13 @@ def main():
                     "what": ("rtb_set_scene (scene arrays H2D, boxes recovered on the device) + rtb_render (device record pack, ONE grid "
                              "launch, finished row chunks copied to pinned host memory while it runs)"
                              if r["world"] == 1 else
-                             "rtb_set_scene + band kernels into rank 0's frame (%s) + D2H to pinned host memory"
-                             % ("NVLink peer stores + fence" if r["peer"] else "NCCL gather + de-interleave"))},
+                             "rtb_set_scene on every rank + rtb_render_bands_host: each GPU copies its own bands (finished chunks while its "
+                             "launch runs) over its own PCIe link into ONE frame in shared, page-locked host memory; 4-byte all-reduce as the barrier")},
             "gpu_launches": r["launches"],
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak if peak else None, "traffic": None,
+                         "frac": achieved / peak if peak else None,
+                         "traffic": ncu_traffic_bytes(args.workload) if r["world"] == 1 else None,
+                         "traffic_unit": "bytes of DRAM traffic per launch (ncu capture in profiles/, not this run)",
                          "kernel": "raycast_grid_kernel", "kernel_ms": r["k_avg_ms"], "kernel_launches_timed": r["k_n"],
                          "flop_per_test": flop_per_test, "rays_per_thread": px,
                          "peak_source": ("fp32_issue_probe (packed FFMA2 chains) run on this GPU just now" if probe

@@ -119,6 +119,22 @@ int rtb_render_bands_frame(rtb_ctx* ctx, int width, int height, const float orig
                            const float dU[4], const float dV[4], const float rayDir[4], int band_rows,
                            int band_rank, int band_world, void* d_frame_rgba8, void* cuda_stream);
 
+/* Row-band render of this rank's bands straight into a WHOLE rgba8 frame in HOST memory (row = frame
+ * row): the multi-GPU counterpart of rtb_render.  With the frame in memory shared by the ranks'
+ * processes (e.g. POSIX shared memory, pinned in each with rtb_host_register) every GPU delivers its
+ * bands over its own PCIe link, in parallel, and finished chunks of bands leave while the launch is
+ * still running.  Blocking; the caller orders "all ranks done" (a barrier).  band_world = 1 is a
+ * whole-frame render.  kernel_ms nullable.  Replaces the clEnqueueMapBuffer read-back of
+ * MainState.cpp:876-886 for the multi-GPU frame. */
+int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+                          const float dV[4], const float rayDir[4], int band_rows, int band_rank,
+                          int band_world, uint8_t* host_frame_rgba8, float* kernel_ms);
+
+/* Page-locks caller-owned host memory (e.g. a shared-memory frame) for direct DMA; undo with
+ * rtb_host_unregister before freeing it.  Optional: pageable buffers work, only slower. */
+int rtb_host_register(void* p, size_t bytes);
+int rtb_host_unregister(void* p);
+
 /* A device frame buffer other processes (one per GPU) can map: create on the owning rank (returns
  * the device pointer and a 64-byte CUDA IPC handle to hand to the peers, e.g. with a broadcast),
  * open on the peers, close on both (owner != 0 frees the allocation). */

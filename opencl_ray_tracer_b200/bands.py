@@ -111,3 +111,51 @@ class PeerFrame:
                 self.ctx.peer_frame_close(self.ptr, self.owner)
             finally:
                 self.ptr = None
+
+
+class SharedHostFrame:
+    """One rgba8 frame in POSIX shared memory, mapped by every rank's process and page-locked in each
+    (rtb_host_register), so that rtb_render_bands_host lets every GPU deliver its row bands over its
+    OWN PCIe link straight into the frame rank 0 reads: the device-to-host leg of a multi-GPU frame
+    scales with the number of GPUs and needs no gather.  `dist` carries the segment's name."""
+
+    def __init__(self, dist, width, height, rank, world, register=True):
+        from multiprocessing import shared_memory
+        self.rank, self.world, self.width, self.height = rank, world, width, height
+        nbytes = 4 * width * height
+        names = [None]
+        if rank == 0:
+            self.shm = shared_memory.SharedMemory(create=True, size=nbytes)
+            names = [self.shm.name]
+        if world > 1:
+            dist.broadcast_object_list(names, 0)
+        if rank != 0:
+            self.shm = shared_memory.SharedMemory(name=names[0])
+            try:  # the creator unlinks; attached processes must not (Python < 3.13 tracks them too)
+                from multiprocessing import resource_tracker
+                resource_tracker.unregister(self.shm._name, "shared_memory")
+            except Exception:
+                pass
+        self.frame = np.frombuffer(self.shm.buf, dtype=np.uint8, count=nbytes).reshape(height, width, 4)
+        self.registered = False
+        if register:
+            from . import capi
+            capi.host_register(self.frame)
+            self.registered = True
+
+    def render(self, ctx, camera, band_rows):
+        """This rank's bands into the shared frame (blocking); returns the kernel's device ms."""
+        return ctx.render_bands_host(self.width, self.height, camera, band_rows, self.rank, self.world, self.frame)
+
+    def close(self):
+        if self.registered:
+            from . import capi
+            capi.host_unregister(self.frame)
+            self.registered = False
+        self.frame = None
+        try:
+            self.shm.close()
+            if self.rank == 0:
+                self.shm.unlink()
+        except Exception:
+            pass

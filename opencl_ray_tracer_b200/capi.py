@@ -26,7 +26,8 @@ EXPORTED_SYMBOLS = [
     "rtb_render_sequence_device", "rtb_host_alloc", "rtb_host_free", "rtb_device_info",
     "rtb_launch_count", "rtb_kernel_ms_avg", "rtb_debug_pack", "rtb_debug_pack_bounds", "rtb_debug_grid_shape", "rtb_version",
     "rtb_assemble_bands_device", "rtb_transfer_bytes", "rtb_render_bands_frame", "rtb_peer_frame_create",
-    "rtb_peer_frame_open", "rtb_peer_frame_close", "rtb_debug_device_records",
+    "rtb_peer_frame_open", "rtb_peer_frame_close", "rtb_debug_device_records", "rtb_render_bands_host",
+    "rtb_host_register", "rtb_host_unregister",
 ]
 
 
@@ -65,6 +66,9 @@ def load_library(path=None):
                                             C.c_int, vp, vp, vp, vp]
     lib.rtb_band_local_rows.argtypes = [C.c_int] * 4
     lib.rtb_render_bands_frame.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, C.c_int, C.c_int, vp, vp]
+    lib.rtb_render_bands_host.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, C.c_int, C.c_int, vp, fp]
+    lib.rtb_host_register.argtypes = [vp, C.c_size_t]
+    lib.rtb_host_unregister.argtypes = [vp]
     lib.rtb_peer_frame_create.argtypes = [vp, C.c_size_t, C.POINTER(vp), C.POINTER(C.c_ubyte)]
     lib.rtb_peer_frame_open.argtypes = [vp, C.POINTER(C.c_ubyte), C.POINTER(vp)]
     lib.rtb_peer_frame_close.argtypes = [vp, vp, C.c_int]
@@ -259,6 +263,16 @@ class Context:
             self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d), band_rows, rank, world,
             C.c_void_p(d_frame_rgba8), C.c_void_p(stream or None)))
 
+    def render_bands_host(self, width, height, camera, band_rows, rank, world, host_frame):
+        """This rank's bands into a whole HOST frame (numpy uint8 [H, W, 4], e.g. over shared memory);
+        blocking.  Returns the grid kernel's device time in ms."""
+        o0, du, dv, d = [_f32(v) for v in camera]
+        kms = C.c_float()
+        self._check(self.lib.rtb_render_bands_host(
+            self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d), band_rows, rank, world,
+            C.c_void_p(host_frame.ctypes.data), C.byref(kms)))
+        return kms.value
+
     def peer_frame_create(self, nbytes):
         """-> (device pointer, 64-byte IPC handle as bytes)."""
         p = C.c_void_p()
@@ -326,6 +340,17 @@ def host_alloc(nbytes):
     arr = np.frombuffer(buf, dtype=np.uint8)
     arr_ptr = p.value
     return arr, arr_ptr
+
+
+def host_register(arr):
+    """Page-locks a caller-owned numpy buffer (shared memory, ...) for direct DMA."""
+    rc = load_library().rtb_host_register(C.c_void_p(arr.ctypes.data), C.c_size_t(arr.nbytes))
+    if rc != RTB_OK:
+        raise RtbError(rc, "rtb_host_register")
+
+
+def host_unregister(arr):
+    load_library().rtb_host_unregister(C.c_void_p(arr.ctypes.data))
 
 
 def host_free(ptr):

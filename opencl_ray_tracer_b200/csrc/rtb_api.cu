@@ -648,6 +648,94 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
     return RTB_OK;
 }
 
+int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+                          const float dV[4], const float rayDir[4], int band_rows, int band_rank, int band_world,
+                          uint8_t* host_frame_rgba8, float* kernel_ms) {
+    int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
+    if (rc != RTB_OK) return rc;
+    if (band_rows <= 0 || band_rows % 4 != 0 || band_world <= 0 || band_rank < 0 || band_rank >= band_world ||
+        !host_frame_rgba8)
+        return fail(ctx, RTB_ERR_INVALID_ARG, "band_rows must be a positive multiple of 4; 0 <= rank < world");
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    CameraFrame cf;
+    if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
+        return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
+    const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
+    const size_t row_bytes = 4 * (size_t)width;
+    rc = ensure_device(ctx, &ctx->d_out[0], &ctx->d_out_cap[0], row_bytes * (size_t)(local_rows > 0 ? local_rows : 1));
+    if (rc != RTB_OK) return rc;
+    rc = resolve_pending(ctx);
+    if (rc != RTB_OK) return rc;
+    const double k_sum0 = ctx->kernel_ms_sum;
+    cudaStream_t st = ctx->stream;
+    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, st);
+    if (rc != RTB_OK) return rc;
+    if (local_rows > 0) {
+        // chunk = whole bands (and a multiple of 16 rows, the progress granularity): about 2 MB each
+        int unit = band_rows;
+        while (unit % 16 != 0) unit *= 2;
+        size_t want = (row_bytes * (size_t)local_rows + (2u << 20) - 1) / (2u << 20);
+        if (want < 1) want = 1;
+        if (want > (size_t)kMaxProgressChunks) want = kMaxProgressChunks;
+        int chunk_rows = (int)(((size_t)local_rows + want - 1) / want);
+        chunk_rows = (chunk_rows + unit - 1) / unit * unit;
+        const int n_chunks = (local_rows + chunk_rows - 1) / chunk_rows;
+        const bool flags = ctx->stream_wait_value32 != nullptr;
+        cudaStream_t cs = flags ? ctx->copy_stream : st;
+        if (flags) {
+            ctx->progress_epoch += 1;
+            if (ctx->progress_epoch == 0) ctx->progress_epoch = 1;
+        }
+        rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, band_rows, band_rank, band_world, local_rows,
+                          ctx->d_out[0], nullptr, nullptr, st, 0, flags ? chunk_rows : 0);
+        if (rc != RTB_OK) return rc;
+        const size_t band_bytes = row_bytes * (size_t)band_rows;
+        for (int k = 0; k < n_chunks; ++k) {
+            const int l0 = k * chunk_rows;
+            const int rows = (local_rows - l0 < chunk_rows) ? (local_rows - l0) : chunk_rows;
+            if (flags) {
+                const CUdeviceptr flag = reinterpret_cast<CUdeviceptr>(ctx->d_progress + kMaxProgressChunks + k);
+                if (ctx->stream_wait_value32(cs, flag, ctx->progress_epoch, CU_STREAM_WAIT_VALUE_EQ) != CUDA_SUCCESS)
+                    return fail(ctx, RTB_ERR_CUDA, "cuStreamWaitValue32 failed");
+            }
+            // local rows [l0, l0+rows) = whole bands lb0.. (the frame's last band may be short): one strided
+            // copy moves them to their frame rows (band lb -> frame band lb*world + rank)
+            const int lb0 = l0 / band_rows;
+            const int full = rows / band_rows, tail = rows - full * band_rows;
+            const uint8_t* src = static_cast<const uint8_t*>(ctx->d_out[0]) + row_bytes * (size_t)l0;
+            uint8_t* dst = host_frame_rgba8 + band_bytes * ((size_t)lb0 * band_world + band_rank);
+            if (full > 0)
+                RTB_CUDA(ctx, cudaMemcpy2DAsync(dst, band_bytes * (size_t)band_world, src, band_bytes, band_bytes,
+                                                (size_t)full, cudaMemcpyDeviceToHost, cs));
+            if (tail > 0)
+                RTB_CUDA(ctx, cudaMemcpyAsync(dst + band_bytes * (size_t)band_world * full, src + band_bytes * full,
+                                              row_bytes * (size_t)tail, cudaMemcpyDeviceToHost, cs));
+            ctx->d2h_bytes += row_bytes * (size_t)rows;
+        }
+        RTB_CUDA(ctx, cudaStreamSynchronize(cs));
+    }
+    RTB_CUDA(ctx, cudaStreamSynchronize(st));
+    rc = resolve_pending(ctx);
+    if (rc != RTB_OK) return rc;
+    if (kernel_ms) *kernel_ms = (float)(ctx->kernel_ms_sum - k_sum0);
+    return RTB_OK;
+}
+
+int rtb_host_register(void* p, size_t bytes) {
+    if (!p || bytes == 0) return RTB_ERR_INVALID_ARG;
+    const cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+    if (e == cudaErrorMemoryAllocation) return RTB_ERR_OUT_OF_MEMORY;
+    if (e != cudaSuccess) (void)cudaGetLastError();
+    return e == cudaSuccess ? RTB_OK : RTB_ERR_CUDA;
+}
+
+int rtb_host_unregister(void* p) {
+    if (!p) return RTB_ERR_INVALID_ARG;
+    const cudaError_t e = cudaHostUnregister(p);
+    if (e != cudaSuccess) (void)cudaGetLastError();
+    return e == cudaSuccess ? RTB_OK : RTB_ERR_CUDA;
+}
+
 int rtb_render_rays(rtb_ctx* ctx, size_t n_rays, const float* rayOrigins, const float rayDir[4],
                     uint8_t* rgba8_out, int32_t* prim_id_out, int32_t* rgba_i32_out, float* kernel_ms,
                     float* total_ms) {

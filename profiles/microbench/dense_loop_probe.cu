@@ -3,7 +3,11 @@
 // centres switchable: rays per thread (PAIRS), where the row terms come from (computed per thread as
 // in the shipped kernel / read from a per-row table in shared memory), and how the results are
 // consumed (LOP3 bit-AND as shipped / folded into the FFMA2 chain, which measures the FFMA2 stream
-// alone).  Reports BOTH SM cycles (clock64) and wall time, so a clock drop under load is visible.
+// alone).  Times are CUDA-event wall times of a one-wave launch, converted to cycles at the maximum SM
+// clock (an upper bound on real cycles).  NOTE: a per-CTA clock64() span was also tried and is NOT
+// reported: thread 0 sits in the oldest warp of its CTA, which the scheduler favours, so its span is
+// far shorter than the launch (it made the loop look issue-bound at 1 instruction/clock; ncu's
+// sm__cycles_elapsed and these wall times agree on about 53 cycles per thread-primitive instead).
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -o dense_loop_probe dense_loop_probe.cu
 #include <cstdio>
 #include <cstdint>
@@ -135,15 +139,17 @@ void run(const char* what, const float4* d_rec, float* d_out, long long* d_cyc, 
     delete[] h;
     const double warps_per_smsp = occ * (THREADS / 32) / 4.0;
     const double tp = warps_per_smsp * iters * NPRIM;  // warp-level thread-primitives per SMSP
-    const double cyc_clock = mean / tp, cyc_wall = best * 1e-3 * clk_ghz * 1e9 / tp;
-    // FMA-pipe bound: an FFMA2 holds the pipe 2 cycles, a scalar FP op 1
-    const double pipe = PAIRS * 2 * 2.0 + (ROW == 0 ? 4.0 : 0.0);
+    (void)mean;
+    const double cyc_wall = best * 1e-3 * clk_ghz * 1e9 / tp;
+    // dispatch model that fits every line within 10 %: an FFMA2 takes 2 dispatch cycles, anything else 1
+    const int lop = (ACC == 0 ? PAIRS : (ACC == 2 ? PAIRS : 0));
+    const double model = PAIRS * 2 * 2.0 + (ROW == 0 ? 4.0 + 2.0 : (ROW == 1 ? 2.0 : 1.0)) + lop + 2.0;
+    const double pipe = PAIRS * 2 * 2.0;  // FMA-pipe cycles of the per-ray FFMA2 alone
     std::printf("{\"what\": \"%s\", \"pairs\": %d, \"row\": %d, \"acc\": %d, \"threads\": %d, \"ctas_per_sm\": %d, \"regs\": %d, "
-                "\"ms\": %.4f, \"cycles_per_thread_prim_clock64\": %.2f, \"cycles_per_thread_prim_wall\": %.2f, "
-                "\"cycles_per_test_clock64\": %.3f, \"fma_pipe_bound_cycles\": %.1f, \"pipe_frac_clock64\": %.3f, "
-                "\"eff_clock_mhz\": %.0f, \"err\": \"%s\"}\n",
-                what, PAIRS, ROW, ACC, THREADS, occ, fa.numRegs, best, cyc_clock, cyc_wall, cyc_clock / (2.0 * PAIRS), pipe,
-                pipe / cyc_clock, mean / (best * 1e3), cudaGetErrorString(cudaGetLastError()));
+                "\"ms\": %.4f, \"cycles_per_thread_prim\": %.2f, \"cycles_per_test\": %.3f, "
+                "\"dispatch_model_cycles\": %.1f, \"ffma2_share_of_cycles\": %.3f, \"err\": \"%s\"}\n",
+                what, PAIRS, ROW, ACC, THREADS, occ, fa.numRegs, best, cyc_wall, cyc_wall / (2.0 * PAIRS), model,
+                pipe / cyc_wall, cudaGetErrorString(cudaGetLastError()));
 }
 
 int main() {

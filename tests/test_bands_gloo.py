@@ -66,3 +66,42 @@ def test_gather_over_gloo(world, h, band_rows):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert ok
+
+
+def _shared_worker(rank, world, port, h, w, band_rows, q):
+    import torch.distributed as dist
+    from opencl_ray_tracer_b200 import bands
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # no device here: the segment is created / attached / unlinked, not page-locked
+        shf = bands.SharedHostFrame(dist, w, h, rank, world, register=False)
+        want = (np.arange(h * w * 4, dtype=np.int64).reshape(h, w, 4) % 251).astype(np.uint8)
+        mine = bands.global_rows_of_rank(h, band_rows, rank, world)
+        shf.frame[mine] = want[mine]                      # what rtb_render_bands_host delivers for this rank
+        dist.barrier()
+        if rank == 0:
+            q.put(bool(np.array_equal(shf.frame, want)))
+        dist.barrier()
+        shf.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,h,band_rows", [(2, 203, 16), (3, 100, 4)])
+def test_shared_host_frame_over_gloo(world, h, band_rows):
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_shared_worker, args=(r, world, port, h, 37, band_rows, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    ok = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert ok

@@ -62,3 +62,51 @@ def test_bands_written_into_rank0_frame_over_ipc(built_libs, world, w, h, band_r
     if res == "ipc-unavailable":
         pytest.skip("CUDA IPC is not available in this container")
     assert res is True
+
+
+def _host_worker(rank, world, port, w, h, band_rows, q):
+    import torch.distributed as dist
+    from opencl_ray_tracer_b200 import bands, capi, host_scene as hs
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        ctx = capi.Context(0)
+        s = hs.random_scene(w, h, 40, 40, 31)
+        ctx.set_scene(*s.as_tuple())
+        shf = bands.SharedHostFrame(dist, w, h, rank, world)
+        if rank == 0:
+            shf.frame[:] = 7
+        dist.barrier()
+        for _ in range(2):                      # twice: the progress flags carry a new epoch per frame
+            kms = shf.render(ctx, capi.REFERENCE_CAMERA, band_rows)
+            assert kms > 0
+        dist.barrier()                          # every rank's bands are in the shared frame
+        if rank == 0:
+            whole = ctx.render(w, h, want=("rgba8",))["rgba8"]
+            q.put(bool(np.array_equal(shf.frame, whole)))
+        dist.barrier()
+        shf.close()
+        ctx.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,w,h,band_rows", [(2, 1920, 1080, 16), (3, 333, 203, 4), (1, 640, 480, 16)])
+def test_bands_delivered_into_shared_host_frame(built_libs, world, w, h, band_rows):
+    """rtb_render_bands_host: every rank copies its bands (finished chunks first, while its launch is
+    still running) into ONE frame in shared host memory; the frame equals the whole-frame render."""
+    import torch.multiprocessing as mp
+    sk = socket.socket()
+    sk.bind(("127.0.0.1", 0))
+    port = sk.getsockname()[1]
+    sk.close()
+    mctx = mp.get_context("spawn")
+    q = mctx.Queue()
+    procs = [mctx.Process(target=_host_worker, args=(r, world, port, w, h, band_rows, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert res is True
