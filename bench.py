@@ -355,6 +355,35 @@ def _ref_worker_rows(job):
     return n
 
 
+def _time_opencl_kernel_on_host(scene, w, h, target_seconds=8.0):
+    """The reference's OTHER path, timed beside its CPU path: the kernel source rayTracer.cl compiled
+    as C++ (oracle/_ref/libraytracer_cl_ref.so; there is no OpenCL ICD on this box), one call per work
+    item, OpenMP over the work items on all host cores, on a bounded sample of rows of the same frame."""
+    from oracle.oracle import ClRefOracle, Scene, cl_ref_available
+    if not cl_ref_available():
+        return None
+    cl = ClRefOracle()
+    sc = Scene(*scene.as_tuple())
+    d = np.array([0, 0, -1, -1], np.float32)
+
+    def rows(ys):
+        o = np.zeros((len(ys), w, 4), np.float32)
+        o[..., 0] = np.arange(w, dtype=np.float32)[None, :]
+        o[..., 1] = np.asarray(ys, np.float32)[:, None]
+        o[..., 3] = 1.0
+        t0 = time.perf_counter()
+        cl.render(sc, o.reshape(-1, 4), d)
+        return time.perf_counter() - t0
+    probe = list(range(0, h, max(1, h // 8)))[:8]
+    dt = rows(probe)
+    n = int(max(len(probe), min(h, len(probe) * target_seconds / max(dt, 1e-6))))
+    ys = list(range(0, h, max(1, h // n)))[:n]
+    dt = rows(ys)
+    return {"value": len(ys) * w / dt / 1e6, "unit": "Mrays/s", "cores": os.cpu_count() or 1,
+            "kind": "reference: rayTracer.cl compiled as C++ for the host (OpenCL ICD unavailable on this box)",
+            "sample": "%d of %d rows of the same %dx%d frame, %.1f s" % (len(ys), h, w, h, dt)}
+
+
 def run_reference(args):
     """The reference's CPU implementation of the path on this box's host cores: the per-ray code is
     the reference's own (oracle/_ref: MainState::collide / intersectTri / intersectSphere compiled
@@ -392,6 +421,7 @@ def run_reference(args):
             r, s = step(args.warmup + k, seg_len)
             tot_rays += r
             tot_s += s
+    opencl_path = _time_opencl_kernel_on_host(scene, w, h)
     mrays = tot_rays / tot_s / 1e6
     sample = "%d row segments of %d rays per step (one per worker process, rows spread over the frame), %d steps, of the same %dx%d frame" % (
         cores, seg_len, args.steps, w, h)
@@ -406,6 +436,8 @@ def run_reference(args):
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if opencl_path:
+        line["opencl_path_on_host"] = opencl_path
     print(json.dumps(line))
 
 

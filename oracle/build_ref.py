@@ -128,7 +128,39 @@ def build(force=False, quiet=True):
     return OUT_SO
 
 
+OUT_CL_SO = os.path.join(OUT_DIR, "libraytracer_cl_ref.so")
+CL_SRC = os.path.join(RT, "resources", "shaders", "rayTracer.cl")
+
+
+def build_cl(force=False, quiet=True):
+    """oracle/_ref/libraytracer_cl_ref.so: the reference's OpenCL kernel source compiled as C++ for
+    the host cores (cl_shim.h + cl_ref_driver.cpp).  The kernel text is read where it lies; the scratch
+    copy differs only in the vector-literal syntax `(float4)(...)` -> `make_float4(...)`."""
+    if not os.path.isfile(CL_SRC):
+        return None
+    deps = [CL_SRC, os.path.join(HERE, "cl_shim.h"), os.path.join(HERE, "cl_ref_driver.cpp"), os.path.abspath(__file__)]
+    if (not force and os.path.isfile(OUT_CL_SO)
+            and all(os.path.getmtime(OUT_CL_SO) >= os.path.getmtime(d) for d in deps)):
+        return OUT_CL_SO
+    text = open(CL_SRC, encoding="utf-8", errors="replace").read()
+    n_lit = len(re.findall(r"\(float4\)\s*\(", text))
+    text = re.sub(r"\(float4\)\s*\(", "make_float4(", text)
+    os.makedirs(OUT_DIR, exist_ok=True)
+    with tempfile.TemporaryDirectory(prefix="rtb_ref_cl_build_") as tmp:
+        with open(os.path.join(tmp, "raytracer_cl.inc"), "w") as f:
+            f.write(text)
+        cmd = ["g++", "-std=c++14", "-O2", "-ffp-contract=off", "-fopenmp", "-fPIC", "-w", "-shared", "-I", HERE, "-I", tmp,
+               os.path.join(HERE, "cl_ref_driver.cpp"), "-o", OUT_CL_SO]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("reference OpenCL-kernel build failed: %s\n%s" % (" ".join(cmd), r.stderr))
+    if not quiet:
+        print("built", OUT_CL_SO, "(%d vector literals rewritten)" % n_lit)
+    return OUT_CL_SO
+
+
 if __name__ == "__main__":
+    build_cl(force="--force" in sys.argv, quiet=False)
     so = build(force="--force" in sys.argv, quiet=False)
     if so is None:
         print("reference sources not present at %s; nothing built" % REF)

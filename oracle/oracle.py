@@ -4,6 +4,8 @@
 * `RefOracle`   : oracle/_ref/libraycast_ref.so, the reference's own function bodies compiled by
                   oracle/build_ref.py (only buildable where /root/reference exists; the built .so
                   travels to the GPU box).
+* `ClRefOracle` : oracle/_ref/libraytracer_cl_ref.so, the reference's OpenCL kernel source compiled as
+                  C++ for the host (same recipe); `PortOracle.render(path="opencl")` is its restatement.
 
 Only tests/, __graft_entry__.smoke()/build() and bench.py's cpu_baseline / --impl reference legs
 may import this module.  Nothing under opencl_ray_tracer_b200/ does.
@@ -90,9 +92,11 @@ class PortOracle:
 
     def render(self, scene, width, height, o0=DEFAULT_O0, du=DEFAULT_DU, dv=DEFAULT_DV,
                ray_dir=DEFAULT_DIR, ray_origins=None, rows=None, faithful=False, threads=0,
-               want_t=False):
+               want_t=False, path="cpu"):
         """Returns (rgba_i32[H,W,4], prim_id[H,W], closest[H,W] or None).
-        rows = (begin, end, step) renders a subset; untouched rows hold -2 in prim_id."""
+        rows = (begin, end, step) renders a subset; untouched rows hold -2 in prim_id.
+        path = "cpu" (MainState::executeRayTracerCPU, double triangle test) or "opencl" (the kernel
+        rayTracer.cl: float triangle test, OpenCL dot())."""
         n = width * height
         rgba = np.zeros((height, width, 4), np.int32)
         pid = np.full((height, width), -2, np.int32)
@@ -107,7 +111,7 @@ class PortOracle:
             scene.ns, _fp(scene.sph_o), _fp(scene.sph_r), _fp(scene.sph_c),
             scene.nc, _fp(scene.cube_v), _fp(scene.cube_c),
             rgba.ctypes.data_as(C.POINTER(C.c_int32)), pid.ctypes.data_as(C.POINTER(C.c_int32)),
-            _fp(tt), 1 if faithful else 0, threads)
+            _fp(tt), 2 if path == "opencl" else (1 if faithful else 0), threads)
         if rc != 0:
             raise RuntimeError("orc_render failed: %d" % rc)
         return rgba, pid, tt
@@ -157,6 +161,38 @@ def narrow_u8(rgba_i32):
 
 def ref_available():
     return os.path.isfile(REF_SO)
+
+
+CL_REF_SO = os.path.join(HERE, "_ref", "libraytracer_cl_ref.so")
+
+
+def cl_ref_available():
+    return os.path.isfile(CL_REF_SO)
+
+
+class ClRefOracle:
+    """The reference's OpenCL kernel source (rayTracer.cl) compiled as C++ for the host cores
+    (oracle/cl_shim.h, oracle/build_ref.py build_cl): its own arithmetic, one call per work item."""
+
+    def __init__(self):
+        if not cl_ref_available():
+            raise RuntimeError("oracle/_ref/libraytracer_cl_ref.so missing (python oracle/build_ref.py)")
+        self.lib = C.CDLL(CL_REF_SO)
+        fp = C.POINTER(C.c_float)
+        self.lib.cl_ref_run.argtypes = [C.c_size_t, C.POINTER(C.c_int32), C.c_int, fp, fp, fp, C.c_int, fp, fp, fp, fp,
+                                        C.c_int]
+
+    def render(self, scene, origins, ray_dir, threads=0):
+        """origins [n,4] (the kernel's rayOrigins argument) -> int32 [n,4] (its `output`)."""
+        o = _f32(origins).reshape(-1, 4)
+        d = _f32(ray_dir)
+        out = np.zeros((len(o), 4), np.int32)
+        rc = self.lib.cl_ref_run(len(o), out.ctypes.data_as(C.POINTER(C.c_int32)), scene.ns, _fp(scene.sph_o),
+                                 _fp(scene.sph_r), _fp(scene.sph_c), scene.nc, _fp(scene.cube_v), _fp(scene.cube_c),
+                                 _fp(o), _fp(d), threads)
+        if rc != 0:
+            raise RuntimeError("cl_ref_run failed")
+        return out
 
 
 class RefOracle:

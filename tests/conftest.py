@@ -35,6 +35,20 @@ def ref():
 
 
 @pytest.fixture(scope="session")
+def cl_ref():
+    """The reference's OpenCL kernel source compiled as C++ for the host; present only where oracle/_ref was built."""
+    from oracle import build_ref
+    from oracle.oracle import ClRefOracle, cl_ref_available
+    try:
+        build_ref.build_cl()
+    except Exception as e:  # pragma: no cover
+        pytest.skip("oracle/_ref (OpenCL kernel) could not be built: %s" % e)
+    if not cl_ref_available():
+        pytest.skip("oracle/_ref/libraytracer_cl_ref.so not present (reference sources absent)")
+    return ClRefOracle()
+
+
+@pytest.fixture(scope="session")
 def built_libs():
     """Makes sure librtb.so / librtb_host.so exist (cross-compiles without a GPU)."""
     import subprocess

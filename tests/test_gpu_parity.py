@@ -117,3 +117,20 @@ def test_explicit_ray_origins_entry_point(gpu_ctx, port):
     assert np.array_equal(g2["rgba_i32"], g["rgba_i32"][idx]) and np.array_equal(g2["prim_id"], g["prim_id"][idx])
     g0 = gpu_ctx.render_rays(np.zeros((0, 4), np.float32), d)
     assert g0["prim_id"].size == 0
+
+
+@pytest.mark.parametrize("w,h,ns,nc,seed", [(640, 480, 0, 0, 0), (640, 480, 100, 100, 7), (1920, 1080, 64, 64, 2)])
+def test_parity_with_the_opencl_path(gpu_ctx, port, w, h, ns, nc, seed):
+    """Second parity target: the reference's OpenCL kernel (float triangle test),
+    through the port's path="opencl" restatement, which tests/test_oracle_cl_variant.py pins to the
+    kernel's own compiled source.  Same bar as against the CPU path."""
+    from opencl_ray_tracer_b200 import host_scene as hs
+    if ns + nc == 0:
+        sc = load_npz_scene(np.load(os.path.join(GOLDEN, "scene1.npz")))
+    else:
+        sc = to_oracle_scene(hs.random_scene(w, h, ns, nc, seed))
+    _set(gpu_ctx, sc)
+    g = gpu_ctx.render(w, h)
+    o = port.render(sc, w, h, path="opencl")
+    rep = parity_report(o[0], o[1], g["rgba_i32"], g["prim_id"])
+    assert_parity(rep)
