@@ -28,6 +28,7 @@ WORKLOADS = {
     "c3": (3840, 2160, 512, 512, 3),       # the roofline point: 4K x 1024 primitives
     "c4": (7680, 4320, 2048, 2048, 4),
 }
+SEQUENCE = {"c5": ("c3", 120, 3)}           # BASELINE config 5: 120-frame orbit (3 degrees per frame) of C3's scene
 BAND_ROWS = 16
 
 # FP32 operations the shipped kernel executes per ray-primitive test (FMA = 2).  Cubes and
@@ -52,7 +53,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS) + sorted(SEQUENCE))
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-peer", action="store_true", help="N > 1: NCCL gather instead of peer-memory stores")
@@ -319,6 +320,135 @@ def run_ours(args):
                 my_rows=my_rows)
 
 
+def run_sequence(args):
+    """BASELINE config 5: the 120-frame orbiting-camera sequence at C3's size.  One step = the whole
+    sequence, frames device-resident (N = 1: rtb_render_sequence_device; N > 1: every frame sharded as
+    row bands, every rank's kernels storing into rank 0's sequence buffer over NVLink, ONE fence at the
+    end).  e2e = every frame delivered into a pinned / shared host frame (rtb_render, rtb_render_bands_host)."""
+    import torch
+    import torch.distributed as dist
+    from opencl_ray_tracer_b200 import bands, capi, host_scene as hs
+    rank, world, local_rank = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    base, n_frames, deg = SEQUENCE[args.workload]
+    w, h, ns, nc, seed = WORKLOADS[base]
+    scene = hs.random_scene(w, h, ns, nc, seed)
+    ctx = capi.Context(local_rank)
+    ctx.set_scene(*scene.as_tuple())
+    cams = [hs.orbit_camera(w, h, k) for k in range(n_frames)]
+    flat = np.stack([np.concatenate(c) for c in cams])
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    sptr = stream.cuda_stream
+    peer = bands.PeerFrame(dist, ctx, w, h, rank, world, n_frames=n_frames) if world > 1 else None
+    if peer is not None and not peer.ok:
+        raise RuntimeError("CUDA IPC unavailable: the sequence bench needs the peer frame buffer")
+    d_out = torch.empty((n_frames, h, w, 4), dtype=torch.uint8, device="cuda") if world == 1 else None
+    shared = bands.SharedHostFrame(dist, w, h, rank, world) if world > 1 else None
+    h_frame = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory().numpy() if world == 1 else None
+    token = torch.zeros(1, dtype=torch.int32, device="cuda")
+
+    def device_step():
+        if world == 1:
+            ctx.render_sequence_device(w, h, flat, d_out.data_ptr())     # blocking
+            return
+        for f in range(n_frames):
+            peer.render(cams[f], BAND_ROWS, sptr, frame=f)
+        peer.fence()
+        stream.synchronize()
+
+    def e2e_step():
+        for f in range(n_frames):
+            if world == 1:
+                ctx.render(w, h, cams[f], want=("rgba8",), out={"rgba8": h_frame})
+            else:
+                shared.render(ctx, cams[f], BAND_ROWS)
+        if world > 1:
+            dist.all_reduce(token)
+            stream.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            fn()
+        barrier()
+        t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    steps = max(1, args.steps)
+    for _ in range(max(1, min(args.warmup, 3))):
+        device_step()
+    ctx.kernel_ms_avg(reset=True)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    dev_s = timed(device_step, steps)
+    sampler.stop_flag = True
+    sampler.join()
+    k_avg_ms, k_n = ctx.kernel_ms_avg(reset=True)
+    e2e_step()
+    e2e_steps = max(1, steps // 4)
+    h2d0, d2h0 = ctx.transfer_bytes()
+    e2e_s = timed(e2e_step, e2e_steps)
+    h2d1, d2h1 = ctx.transfer_bytes()
+    tb = torch.tensor([float(h2d1 - h2d0), float(d2h1 - d2h0)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tb)
+    if rank == 0:
+        n_px = w * h
+        s_step = dev_s / steps
+        sms = ctx.device_info()["sm_count"]
+        my_rows = ctx.band_local_rows(h, BAND_ROWS, 0, world)
+        px, tile_w = capi.debug_grid_shape(w, my_rows, sms)[:2]
+        flop_per_test = FLOP_PER_TEST_RAY + FLOP_PER_TEST_ROW / tile_w
+        probe = fp32_probe_tflops()
+        peak_nominal = sms * 128 * 2 * (sampler.result()["sm_max_mhz"] or 1965.0) * 1e6 / 1e12
+        achieved = my_rows * w * (ns + nc) * flop_per_test / (k_avg_ms * 1e-3) / 1e12 if k_avg_ms > 0 else 0.0
+        peak = probe if probe else peak_nominal
+        line = {
+            "metric": "Mrays/s", "value": n_frames * n_px / s_step / 1e6, "unit": "Mrays/s", "n_gpus": world,
+            "steps": steps, "warmup": max(1, min(args.warmup, 3)), "ms_per_step": s_step * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "c5: %d-frame orbit (%d degrees per frame about the scene centre) of %s" % (
+                           n_frames, deg, workload_name(base)),
+                       "parallelism": "every frame as interleaved %d-row bands over %d GPU(s)%s" % (
+                           BAND_ROWS, world, "" if world == 1 else ", kernels store into rank 0's sequence buffer over NVLink peer memory, one fence per sequence"),
+                       "l2": "each step writes %d frames = %.1f GB of output (larger than L2); a step is timed as a whole (wall clock around blocking calls, max over ranks)" % (
+                           n_frames, n_frames * 4 * n_px / 1e9)},
+            "frames_per_s": n_frames / s_step, "ms_per_frame": s_step * 1e3 / n_frames,
+            "tests_per_s": n_frames * n_px * (ns + nc) / s_step,
+            "clocks": sampler.result(),
+            "e2e": {"value": n_frames * n_px * e2e_steps / e2e_s / 1e6, "unit": "Mrays/s",
+                    "frames_per_s": n_frames * e2e_steps / e2e_s,
+                    "h2d_bytes_per_step": float(tb[0].item()) / e2e_steps, "d2h_bytes_per_step": float(tb[1].item()) / e2e_steps,
+                    "ms_per_step": e2e_s * 1e3 / e2e_steps,
+                    "what": "every frame rendered and delivered into a pinned (N = 1) / shared page-locked (N > 1) host frame; the scene stays resident, the step's input is the camera sequence"},
+            "gpu_launches": 2 * n_frames * steps,
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
+                         "traffic": None, "kernel": "raycast_grid_kernel", "kernel_ms": k_avg_ms, "kernel_launches_timed": k_n,
+                         "flop_per_test": flop_per_test, "rays_per_thread": px,
+                         "peak_source": ("fp32_issue_probe (packed FFMA2 chains) run on this GPU just now" if probe
+                                         else "nominal SMs x 128 lanes x 2 x max SM clock")},
+        }
+        print(json.dumps(line))
+    if shared is not None:
+        shared.close()
+    if world > 1:
+        dist.barrier()
+        if peer is not None:
+            peer.close()
+        dist.destroy_process_group()
+
+
 # ---- reference arm -------------------------------------------------------------------------------
 _REF = {}
 
@@ -394,7 +524,7 @@ def run_reference(args):
     import multiprocessing as mp
     from opencl_ray_tracer_b200 import host_scene as hs
     from oracle.oracle import ref_available
-    w, h, ns, nc, seed = WORKLOADS[args.workload]
+    w, h, ns, nc, seed = WORKLOADS[SEQUENCE[args.workload][0] if args.workload in SEQUENCE else args.workload]
     scene = hs.random_scene(w, h, ns, nc, seed)
     kind = "reference" if (ref_available() and scene.cube_recipes is not None) else "port"
     cores = os.cpu_count() or 1
@@ -430,7 +560,8 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_s * 1e3 / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32 (f64 triangle test)",
         "data": "synthetic",
-        "config": {"workload": workload_name(args.workload)},
+        "config": {"workload": (workload_name(args.workload) if args.workload in WORKLOADS else
+                                "%s: frame 0 of the orbit of %s" % (args.workload, workload_name(SEQUENCE[args.workload][0])))},
         "tests_per_s": mrays * 1e6 * (ns + nc),
         "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -447,6 +578,9 @@ def main():
     if args.impl == "reference":
         if rank == 0:
             run_reference(args)
+        return
+    if args.workload in SEQUENCE:
+        run_sequence(args)
         return
     r = run_ours(args)
     from opencl_ray_tracer_b200 import capi as capi_mod

@@ -57,11 +57,12 @@ class PeerFrame:
     de-interleave pass.  `dist` is torch.distributed (NCCL in production, gloo in the tests) and is
     used for the 64-byte handle broadcast and for the per-frame "every rank has finished" token."""
 
-    def __init__(self, dist, ctx, width, height, rank, world, device=None):
+    def __init__(self, dist, ctx, width, height, rank, world, device=None, n_frames=1):
         import torch
         self.dist, self.ctx, self.rank, self.world = dist, ctx, rank, world
-        self.width, self.height = width, height
-        self.nbytes = 4 * width * height
+        self.width, self.height, self.n_frames = width, height, n_frames
+        self.frame_bytes = 4 * width * height
+        self.nbytes = self.frame_bytes * n_frames       # n_frames > 1: a frame sequence, back to back
         self.ptr, self.owner = None, rank == 0
         dev = device if device is not None else ("cuda" if dist.get_backend() == "nccl" else "cpu")
         ok, hb = 1, torch.zeros(64, dtype=torch.uint8)
@@ -85,11 +86,11 @@ class PeerFrame:
         if not self.ok:
             self.close()
 
-    def render(self, camera, band_rows, stream=0):
-        """This rank's bands into the shared frame, then the completion token (stream ordered on
-        NCCL; the caller synchronises before a gloo token)."""
+    def render(self, camera, band_rows, stream=0, frame=0):
+        """This rank's bands into frame `frame` of the shared buffer (stream ordered on NCCL; the
+        caller synchronises before a gloo token)."""
         self.ctx.render_bands_frame(self.width, self.height, camera, band_rows, self.rank, self.world,
-                                    self.ptr, stream)
+                                    self.ptr + frame * self.frame_bytes, stream)
 
     def fence(self):
         self.dist.all_reduce(self.token)
@@ -101,7 +102,8 @@ class PeerFrame:
         class _Raw:
             pass
         raw = _Raw()
-        raw.__cuda_array_interface__ = {"shape": (self.height, self.width, 4), "typestr": "|u1",
+        shape = (self.height, self.width, 4) if self.n_frames == 1 else (self.n_frames, self.height, self.width, 4)
+        raw.__cuda_array_interface__ = {"shape": shape, "typestr": "|u1",
                                         "data": (int(self.ptr), False), "version": 3, "strides": None}
         return torch.as_tensor(raw, device="cuda")
 
