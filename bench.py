@@ -219,12 +219,19 @@ def run_ours(args):
 
     # N > 1: every rank's kernel stores its bands straight into rank 0's frame over NVLink (CUDA IPC
     # mapping); falls back to the NCCL gather + de-interleave kernel if IPC is refused.
+    # Frame slots: frame f goes to slot f % 3; a slot is handed back to the ranks by a collective that runs
+    # on a side stream, off the frame's critical path (rank 0 "consumes" a frame right after it is complete).
     peer = None
+    PEER_SLOTS = 3
     if world > 1 and not args.no_peer:
-        peer = bands.PeerFrame(dist, ctx, w, h, rank, world)
+        peer = bands.PeerFrame(dist, ctx, w, h, rank, world, n_frames=PEER_SLOTS)
         if not peer.ok:
             peer = None
     peer_frame = peer.as_tensor() if (peer and rank == 0) else None
+    side = torch.cuda.Stream(priority=-1) if peer else None
+    side_token = torch.zeros(1, dtype=torch.int32, device="cuda")
+    released = [None] * PEER_SLOTS
+    state = {"frame": 0, "signals": True}
     # N > 1, end to end: one frame in shared host memory; every rank's GPU delivers its own bands into it
     shared = bands.SharedHostFrame(dist, w, h, rank, world) if world > 1 else None
 
@@ -238,6 +245,21 @@ def run_ours(args):
         return 0
 
     def device_step():
+        if peer and state["signals"]:
+            slot = state["frame"] % PEER_SLOTS
+            if released[slot] is not None:
+                stream.wait_event(released[slot])          # rank 0 has let go of the frame that was in this slot
+            peer.render(cam, BAND_ROWS, sptr, frame=slot, signal=True)   # last CTA bumps rank 0's signal word
+            peer.wait_all(sptr)                            # rank 0: stream waits for all ranks' signals (no collective)
+            done = torch.cuda.Event()
+            done.record(stream)
+            side.wait_event(done)
+            with torch.cuda.stream(side):
+                dist.all_reduce(side_token)                # slot release, overlapped with the next frames
+                released[slot] = torch.cuda.Event()
+                released[slot].record(side)
+            state["frame"] += 1
+            return 1
         if peer:
             peer.render(cam, BAND_ROWS, sptr)
             peer.fence()                   # 4-byte all-reduce on this stream: every rank's stores have landed
@@ -265,6 +287,14 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     # ---- device-resident timing (value) -------------------------------------------------------
+    if peer:
+        try:                               # stream memory operations present?  (else: collective fence)
+            device_step()
+        except capi.RtbError:
+            state["signals"] = False
+        ok = torch.tensor([1 if state["signals"] else 0], dtype=torch.int32, device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        state["signals"] = bool(int(ok.item()))
     for _ in range(max(args.warmup, 3)):
         device_step()
     barrier()
@@ -316,7 +346,7 @@ def run_ours(args):
         shared.close()
     return dict(rank=rank, world=world, w=w, h=h, ns=ns, nc=nc, seed=seed, scene=scene, ctx=ctx,
                 ms_per_step=ms_per_step, wall_ms_per_step=wall * 1e3 / args.steps, k_avg_ms=k_avg_ms, k_n=k_n,
-                launches=launches, clocks=sampler.result(), peer=bool(peer), e2e_s=e2e_s, h2d=h2d_per_step, d2h=d2h_per_step,
+                launches=launches, clocks=sampler.result(), peer=bool(peer), signals=bool(peer and state["signals"]), e2e_s=e2e_s, h2d=h2d_per_step, d2h=d2h_per_step,
                 my_rows=my_rows)
 
 
@@ -611,7 +641,9 @@ def main():
                        "parallelism": "interleaved %d-row bands over %d GPU(s)%s" % (
                            BAND_ROWS, r["world"],
                            "" if r["world"] == 1 else
-                           (", kernels store into rank 0's frame over NVLink peer memory + 4-byte NCCL all-reduce as the fence"
+                           (", kernels store into rank 0's frame over NVLink peer memory; fence = " +
+                            ("each launch's last CTA bumps a signal word in rank 0's memory, rank 0's stream waits on it (cuStreamWaitValue32); "
+                             "3 frame slots, released by an all-reduce on a side stream" if r["signals"] else "4-byte NCCL all-reduce")
                             if r["peer"] else ", NCCL gather to rank 0 + de-interleave kernel")),
                        "l2": "256 MiB buffer written between timed iterations (L2 flush); per-step CUDA events"},
             "tests_per_s": mrays * 1e6 * (ns + nc),

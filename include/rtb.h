@@ -135,9 +135,24 @@ int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origi
 int rtb_host_register(void* p, size_t bytes);
 int rtb_host_unregister(void* p);
 
+/* As rtb_render_bands_frame, and the launch's last CTA adds 1 (system-scope atomic) to the 32-bit
+ * word d_signal -- typically the signal word of rank 0's peer frame, at
+ * frame + rtb_peer_frame_signal_offset(bytes) -- once all of this rank's stores are ordered before
+ * it.  Rank 0 then orders "every rank's bands have landed" on its stream with
+ * rtb_stream_wait_signal(ctx, signal, world * frames_so_far, stream): no collective on the frame's
+ * critical path.  rtb_stream_wait_signal returns RTB_ERR_UNSUPPORTED without stream memory
+ * operations (use a collective as the fence then). */
+int rtb_render_bands_frame_signal(rtb_ctx* ctx, int width, int height, const float origin0[4],
+                                  const float dU[4], const float dV[4], const float rayDir[4],
+                                  int band_rows, int band_rank, int band_world, void* d_frame_rgba8,
+                                  void* d_signal, void* cuda_stream);
+int rtb_stream_wait_signal(rtb_ctx* ctx, void* d_signal, unsigned int value, void* cuda_stream);
+size_t rtb_peer_frame_signal_offset(size_t bytes);
+
 /* A device frame buffer other processes (one per GPU) can map: create on the owning rank (returns
  * the device pointer and a 64-byte CUDA IPC handle to hand to the peers, e.g. with a broadcast),
  * open on the peers, close on both (owner != 0 frees the allocation). */
+/* The allocation is bytes rounded up to 256, followed by 256 zeroed bytes of signal words. */
 int rtb_peer_frame_create(rtb_ctx* ctx, size_t bytes, void** d_ptr, unsigned char handle_out[64]);
 int rtb_peer_frame_open(rtb_ctx* ctx, const unsigned char handle[64], void** d_ptr);
 int rtb_peer_frame_close(rtb_ctx* ctx, void* d_ptr, int owner);

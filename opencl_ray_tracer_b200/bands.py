@@ -83,16 +83,30 @@ class PeerFrame:
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         self.ok = bool(int(flag.item()))
         self.token = torch.zeros(1, dtype=torch.int32).to(dev)
+        # signal word of the allocation (rank 0's memory): every rank's launch adds 1 when its bands have landed
+        self.signal_ptr = (self.ptr + ctx.lib.rtb_peer_frame_signal_offset(self.nbytes)) if self.ptr else None
+        self.signals_expected = 0
         if not self.ok:
             self.close()
 
-    def render(self, camera, band_rows, stream=0, frame=0):
+    def render(self, camera, band_rows, stream=0, frame=0, signal=False):
         """This rank's bands into frame `frame` of the shared buffer (stream ordered on NCCL; the
-        caller synchronises before a gloo token)."""
+        caller synchronises before a gloo token).  signal=True: the launch's last CTA bumps rank 0's
+        signal word (see wait_all)."""
         self.ctx.render_bands_frame(self.width, self.height, camera, band_rows, self.rank, self.world,
-                                    self.ptr + frame * self.frame_bytes, stream)
+                                    self.ptr + frame * self.frame_bytes, stream, self.signal_ptr if signal else 0)
+        if signal:
+            self.signals_expected += self.world
+
+    def wait_all(self, stream=0):
+        """Rank 0: `stream` waits until every rank's launches signalled so far have landed (a stream
+        memory operation on rank 0's own signal word; no collective).  Raises RtbError
+        (RTB_ERR_UNSUPPORTED) where stream memory operations are unavailable."""
+        if self.rank == 0:
+            self.ctx.stream_wait_signal(self.signal_ptr, self.signals_expected, stream)
 
     def fence(self):
+        """Collective fence (all ranks): also what releases a frame slot for reuse."""
         self.dist.all_reduce(self.token)
 
     def as_tensor(self):

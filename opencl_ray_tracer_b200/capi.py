@@ -27,7 +27,8 @@ EXPORTED_SYMBOLS = [
     "rtb_launch_count", "rtb_kernel_ms_avg", "rtb_debug_pack", "rtb_debug_pack_bounds", "rtb_debug_grid_shape", "rtb_version",
     "rtb_assemble_bands_device", "rtb_transfer_bytes", "rtb_render_bands_frame", "rtb_peer_frame_create",
     "rtb_peer_frame_open", "rtb_peer_frame_close", "rtb_debug_device_records", "rtb_render_bands_host",
-    "rtb_host_register", "rtb_host_unregister",
+    "rtb_host_register", "rtb_host_unregister", "rtb_render_bands_frame_signal", "rtb_stream_wait_signal",
+    "rtb_peer_frame_signal_offset",
 ]
 
 
@@ -69,6 +70,10 @@ def load_library(path=None):
     lib.rtb_render_bands_host.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, C.c_int, C.c_int, vp, fp]
     lib.rtb_host_register.argtypes = [vp, C.c_size_t]
     lib.rtb_host_unregister.argtypes = [vp]
+    lib.rtb_render_bands_frame_signal.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, C.c_int, C.c_int, vp, vp, vp]
+    lib.rtb_stream_wait_signal.argtypes = [vp, vp, C.c_uint, vp]
+    lib.rtb_peer_frame_signal_offset.argtypes = [C.c_size_t]
+    lib.rtb_peer_frame_signal_offset.restype = C.c_size_t
     lib.rtb_peer_frame_create.argtypes = [vp, C.c_size_t, C.POINTER(vp), C.POINTER(C.c_ubyte)]
     lib.rtb_peer_frame_open.argtypes = [vp, C.POINTER(C.c_ubyte), C.POINTER(vp)]
     lib.rtb_peer_frame_close.argtypes = [vp, vp, C.c_int]
@@ -256,12 +261,18 @@ class Context:
             C.c_void_p(d_rgba8 or None), C.c_void_p(d_prim_id or None), C.c_void_p(d_rgba_i32 or None),
             C.c_void_p(stream or None)))
 
-    def render_bands_frame(self, width, height, camera, band_rows, rank, world, d_frame_rgba8, stream=0):
-        """This rank's bands written straight into a whole frame (own or peer-mapped memory)."""
+    def render_bands_frame(self, width, height, camera, band_rows, rank, world, d_frame_rgba8, stream=0, d_signal=0):
+        """This rank's bands written straight into a whole frame (own or peer-mapped memory); with
+        d_signal the launch's last CTA adds 1 to that word when all of its stores are ordered."""
         o0, du, dv, d = [_f32(v) for v in camera]
-        self._check(self.lib.rtb_render_bands_frame(
+        self._check(self.lib.rtb_render_bands_frame_signal(
             self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d), band_rows, rank, world,
-            C.c_void_p(d_frame_rgba8), C.c_void_p(stream or None)))
+            C.c_void_p(d_frame_rgba8), C.c_void_p(d_signal or None), C.c_void_p(stream or None)))
+
+    def stream_wait_signal(self, d_signal, value, stream=0):
+        """Makes `stream` wait until the 32-bit word at d_signal has reached `value` (wrap-safe >=)."""
+        self._check(self.lib.rtb_stream_wait_signal(self._h, C.c_void_p(d_signal), C.c_uint(value & 0xFFFFFFFF),
+                                                    C.c_void_p(stream or None)))
 
     def render_bands_host(self, width, height, camera, band_rows, rank, world, host_frame):
         """This rank's bands into a whole HOST frame (numpy uint8 [H, W, 4], e.g. over shared memory);
@@ -340,6 +351,10 @@ def host_alloc(nbytes):
     arr = np.frombuffer(buf, dtype=np.uint8)
     arr_ptr = p.value
     return arr, arr_ptr
+
+
+def peer_frame_signal_offset(nbytes):
+    return int(load_library().rtb_peer_frame_signal_offset(C.c_size_t(nbytes)))
 
 
 def host_register(arr):

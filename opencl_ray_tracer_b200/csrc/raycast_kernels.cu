@@ -276,9 +276,16 @@ raycast_grid_kernel(const GridParams p) {
     constexpr int kChunk = TAB ? kTabPrims : kChunkPrims;   // primitives per staged chunk
     static_assert(kBoundGroup % G == 0, "the host pads the bound list to kBoundGroup");
     static_assert(!TAB || (kThreads % kTileH == 0 && kTileH <= 8), "row table: a thread always builds the same row");
-    __shared__ __align__(128) float4 stage[2][2 * kChunk];
-    __shared__ __align__(16) float4 rowtab[TAB ? 2 : 1][TAB ? kTabPrims * kTileH : 1];
+    // One raw buffer: [bound records, 2 stages][row table, 2 stages]; after the loop the primitive-split
+    // merge area (S > 1) reuses it from offset 0.
+    constexpr int kStageBytes = (int)sizeof(float4) * 2 * 2 * kChunk;
+    constexpr int kTabBytes = TAB ? (int)sizeof(float4) * 2 * kTabPrims * kTileH : 0;
+    constexpr int kMergeBytes = (S > 1) ? 8 * WARPS_X * WARPS_Y * (S - 1) * PX * 32 : 0;
+    constexpr int kSmemBytes = (kStageBytes + kTabBytes > kMergeBytes) ? kStageBytes + kTabBytes : kMergeBytes;
+    __shared__ __align__(128) unsigned char smem_raw[kSmemBytes];
     __shared__ __align__(8) uint64_t full_bar[2];
+    float4 (*stage)[2 * kChunk] = reinterpret_cast<float4 (*)[2 * kChunk]>(smem_raw);
+    float4 (*rowtab)[kTabPrims * kTileH] = reinterpret_cast<float4 (*)[kTabPrims * kTileH]>(smem_raw + kStageBytes);
     (void)kThreads;
 
     const int tid = threadIdx.x;
@@ -370,8 +377,10 @@ raycast_grid_kernel(const GridParams p) {
     // ---- merge of the primitive splits (S > 1) -----------------------------------------------
     const bool owner = (split == 0);  // the warp of a tile that shades and stores
     if constexpr (S > 1) {
-        __shared__ float m_best[WARPS_X * WARPS_Y * (S > 1 ? S - 1 : 1)][PX][32];
-        __shared__ int m_id[WARPS_X * WARPS_Y * (S > 1 ? S - 1 : 1)][PX][32];
+        constexpr int kSlots = WARPS_X * WARPS_Y * (S > 1 ? S - 1 : 1);
+        float (*m_best)[PX][32] = reinterpret_cast<float (*)[PX][32]>(smem_raw);
+        int (*m_id)[PX][32] = reinterpret_cast<int (*)[PX][32]>(smem_raw + sizeof(float) * kSlots * PX * 32);
+        __syncthreads();  // every warp has left the dense loop: the staging area is free for the merge
         if (split > 0) {
 #pragma unroll
             for (int q = 0; q < PX; ++q) {
@@ -400,23 +409,36 @@ raycast_grid_kernel(const GridParams p) {
     // ---- nearest-hit shading + stores -------------------------------------------------------
     if (owner && lrow < p.local_rows && gy < p.height && x0 < p.width) shade_and_store<PX>(p, st, x0, lrow, gy);
 
-    // ---- progress: lets the host start copying finished row chunks while the launch still runs --
-    // The launch's rows are cut into chunks of p.progress_rows rows; the last CTA of a chunk to
-    // finish publishes p.progress_epoch in the chunk's flag word, on which the copy stream waits
-    // (cuStreamWaitValue32, rtb_render).  Counter reset by that same CTA: one launch at a time.
-    if (p.progress != nullptr) {
+    // ---- completion signals --------------------------------------------------------------------
+    // progress: the launch's rows are cut into chunks of p.progress_rows rows; the last CTA of a chunk
+    //   to finish publishes p.progress_epoch in the chunk's flag word, on which the copy stream waits
+    //   (cuStreamWaitValue32, rtb_render): finished rows leave for the host while the launch runs.
+    // done_signal: the last CTA of the whole launch adds 1 to a word that may live in ANOTHER GPU's
+    //   memory (rank 0's peer frame, over NVLink): rank 0's stream waits until every rank has signalled,
+    //   which replaces a collective as the "all bands have landed" fence of a multi-GPU frame.
+    // Counters are reset by the CTA that completes them: one launch per context at a time.
+    if (p.progress != nullptr || p.done_signal != nullptr) {
         __syncthreads();  // every store of this CTA is ordered before thread 0's fence
         if (tid == 0) {
             __threadfence_system();
-            const int row0 = blockIdx.y * kTileH;
-            const int chunk = row0 / p.progress_rows;
-            const int c0 = chunk * p.progress_rows;
-            const int c1 = min(c0 + p.progress_rows, p.local_rows);
-            const unsigned expected = gridDim.x * (unsigned)((c1 - c0 + kTileH - 1) / kTileH);
-            if (atomicAdd(&p.progress[chunk], 1u) + 1u == expected) {
-                p.progress[chunk] = 0u;
-                __threadfence_system();
-                *reinterpret_cast<volatile unsigned*>(&p.progress[kMaxProgressChunks + chunk]) = p.progress_epoch;
+            if (p.progress != nullptr) {
+                const int row0 = blockIdx.y * kTileH;
+                const int chunk = row0 / p.progress_rows;
+                const int c0 = chunk * p.progress_rows;
+                const int c1 = min(c0 + p.progress_rows, p.local_rows);
+                const unsigned expected = gridDim.x * (unsigned)((c1 - c0 + kTileH - 1) / kTileH);
+                if (atomicAdd(&p.progress[chunk], 1u) + 1u == expected) {
+                    p.progress[chunk] = 0u;
+                    __threadfence_system();
+                    *reinterpret_cast<volatile unsigned*>(&p.progress[kMaxProgressChunks + chunk]) = p.progress_epoch;
+                }
+            }
+            if (p.done_signal != nullptr) {
+                if (atomicAdd(p.done_counter, 1u) + 1u == gridDim.x * gridDim.y) {
+                    *p.done_counter = 0u;
+                    __threadfence_system();
+                    atomicAdd_system(p.done_signal, 1u);
+                }
             }
         }
     }
@@ -538,6 +560,9 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) 
         case 7: return launch_variant<16, 2, 1, 4, 4, 2>(p, stream);
         case 9: return launch_variant<4, 2, 2, 4, 8>(p, stream);
         case 10: return launch_variant<16, 2, 2, 4, 4, 1, true>(p, stream);  // row table (production at C3)
+        case 20: return launch_variant<16, 2, 1, 4, 4, 2, true>(p, stream);  // 2 warps per 128x4 tile
+        case 21: return launch_variant<16, 1, 1, 4, 4, 4, true>(p, stream);  // 4 warps per tile
+        case 22: return launch_variant<16, 1, 1, 4, 2, 8, true>(p, stream);  // 8 warps per tile
         case 11: return launch_variant<16, 2, 2, 4, 3, 1, true>(p, stream);
         case 13: return launch_variant<16, 2, 2, 2, 4, 1, true>(p, stream);
         case 15: return launch_variant<8, 2, 2, 4, 8, 1, true>(p, stream);
@@ -591,6 +616,18 @@ cudaError_t launch_assemble(const AssembleParams& p, cudaStream_t stream) {
     const unsigned per_row = (unsigned)((p.row_bytes / 16 + 255) / 256);
     dim3 grid(per_row < 1 ? 1 : (per_row > 8 ? 8 : per_row), (unsigned)p.height);
     assemble_bands_kernel<<<grid, 256, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+namespace {
+__global__ void signal_only_kernel(unsigned int* signal) {
+    __threadfence_system();
+    atomicAdd_system(signal, 1u);
+}
+}  // namespace
+
+cudaError_t launch_signal_only(unsigned int* d_signal, cudaStream_t stream) {
+    signal_only_kernel<<<1, 1, 0, stream>>>(d_signal);
     return cudaGetLastError();
 }
 

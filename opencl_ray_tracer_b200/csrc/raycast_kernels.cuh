@@ -39,6 +39,10 @@ struct GridParams {
     unsigned int* progress;
     int progress_rows;
     unsigned int progress_epoch;
+    // Launch-completion signal (nullable): done_counter = this context's CTA counter, done_signal = the
+    // word the last CTA increments with a system-scope atomic (own or peer memory).
+    unsigned int* done_counter;
+    unsigned int* done_signal;
     RtbCam cam;
 };
 
@@ -75,6 +79,7 @@ struct GridLaunchShape { int px, wx, wy, split; dim3 grid, block; size_t smem; }
 GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count);
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream);
 cudaError_t launch_rays(const RaysParams& p, cudaStream_t stream);
+cudaError_t launch_signal_only(unsigned int* d_signal, cudaStream_t stream);  // a rank with no rows still signals
 cudaError_t configure_kernels();  // one-time cudaFuncSetAttribute calls
 
 }  // namespace rtb

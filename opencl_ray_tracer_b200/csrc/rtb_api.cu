@@ -33,7 +33,7 @@ struct rtb_ctx {
     cudaEvent_t ev_chunk[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     // In-launch progress (rtb_render): the grid kernel publishes finished row chunks in d_progress and
     // copy_stream waits on the flag words with cuStreamWaitValue32 (fetched through the runtime).
-    unsigned int* d_progress = nullptr;  // 2 * kMaxProgressChunks words
+    unsigned int* d_progress = nullptr;  // 2 * kMaxProgressChunks words + the launch-done CTA counter
     unsigned int progress_epoch = 0;
     CUresult (*stream_wait_value32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int) = nullptr;
     std::string last_error;
@@ -200,8 +200,8 @@ int rtb_init(rtb_ctx** out, int n_devices, const int* device_ids) {
         cudaEventCreate(&ctx->ev_total0) != cudaSuccess || cudaEventCreate(&ctx->ev_total1) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->ev_rec, cudaEventDisableTiming) != cudaSuccess ||
         cudaMalloc(&ctx->d_bad, sizeof(int)) != cudaSuccess ||
-        cudaMalloc(&ctx->d_progress, 2 * kMaxProgressChunks * sizeof(unsigned int)) != cudaSuccess ||
-        cudaMemset(ctx->d_progress, 0, 2 * kMaxProgressChunks * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMalloc(&ctx->d_progress, (2 * kMaxProgressChunks + 8) * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMemset(ctx->d_progress, 0, (2 * kMaxProgressChunks + 8) * sizeof(unsigned int)) != cudaSuccess ||
         cudaMallocHost(&ctx->h_bad, sizeof(int)) != cudaSuccess || configure_kernels() != cudaSuccess) {
         rtb_shutdown(ctx);
         return RTB_ERR_CUDA;
@@ -384,9 +384,11 @@ int ensure_host_scene(rtb_ctx* ctx) {
 // Enqueues one grid-kernel launch (with its timing event pair) on `stream`.
 int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width, int height, int band_rows,
                  int band_rank, int band_world, int local_rows, void* d_rgba8, void* d_id, void* d_i32,
-                 cudaStream_t stream, int out_global_rows = 0, int progress_rows = 0) {
+                 cudaStream_t stream, int out_global_rows = 0, int progress_rows = 0, void* done_signal = nullptr) {
     GridParams p;
     p.out_global_rows = out_global_rows;
+    p.done_counter = ctx->d_progress + 2 * kMaxProgressChunks;
+    p.done_signal = static_cast<unsigned int*>(done_signal);
     p.progress = progress_rows > 0 ? ctx->d_progress : nullptr;
     p.progress_rows = progress_rows > 0 ? progress_rows : 1;
     p.progress_epoch = ctx->progress_epoch;
@@ -468,6 +470,27 @@ int rtb_render_bands_device(rtb_ctx* ctx, int width, int height, const float ori
 int rtb_render_bands_frame(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
                            const float dV[4], const float rayDir[4], int band_rows, int band_rank,
                            int band_world, void* d_frame_rgba8, void* cuda_stream) {
+    return rtb_render_bands_frame_signal(ctx, width, height, origin0, dU, dV, rayDir, band_rows, band_rank, band_world,
+                                         d_frame_rgba8, nullptr, cuda_stream);
+}
+
+size_t rtb_peer_frame_signal_offset(size_t bytes) { return (bytes + 255) & ~(size_t)255; }
+
+int rtb_stream_wait_signal(rtb_ctx* ctx, void* d_signal, unsigned int value, void* cuda_stream) {
+    if (!ctx || !d_signal) return RTB_ERR_INVALID_ARG;
+    if (!ctx->stream_wait_value32) return fail(ctx, RTB_ERR_UNSUPPORTED, "stream memory operations are unavailable");
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->stream;
+    if (ctx->stream_wait_value32(stream, reinterpret_cast<CUdeviceptr>(d_signal), value, CU_STREAM_WAIT_VALUE_GEQ) !=
+        CUDA_SUCCESS)
+        return fail(ctx, RTB_ERR_CUDA, "cuStreamWaitValue32 failed");
+    if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
+    return RTB_OK;
+}
+
+int rtb_render_bands_frame_signal(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+                                  const float dV[4], const float rayDir[4], int band_rows, int band_rank,
+                                  int band_world, void* d_frame_rgba8, void* d_signal, void* cuda_stream) {
     int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
     if (rc != RTB_OK) return rc;
     if (band_rows <= 0 || band_rows % 4 != 0 || band_world <= 0 || band_rank < 0 || band_rank >= band_world ||
@@ -481,8 +504,12 @@ int rtb_render_bands_frame(rtb_ctx* ctx, int width, int height, const float orig
     rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, stream);
     if (rc != RTB_OK) return rc;
     const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
+    if (local_rows <= 0 && d_signal) {  // nothing to render: the signal still has to arrive
+        static_assert(sizeof(unsigned int) == 4, "signal words are 32 bit");
+        RTB_CUDA(ctx, launch_signal_only(static_cast<unsigned int*>(d_signal), stream));
+    }
     rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, band_rows, band_rank, band_world, local_rows,
-                      d_frame_rgba8, nullptr, nullptr, stream, 1);
+                      d_frame_rgba8, nullptr, nullptr, stream, 1, 0, d_signal);
     if (rc != RTB_OK) return rc;
     if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
     return RTB_OK;
@@ -493,7 +520,10 @@ int rtb_peer_frame_create(rtb_ctx* ctx, size_t bytes, void** d_ptr, unsigned cha
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "rtb.h promises a 64-byte handle");
     RTB_CUDA(ctx, cudaSetDevice(ctx->device));
     *d_ptr = nullptr;
-    RTB_CUDA(ctx, cudaMalloc(d_ptr, bytes));  // a whole allocation: IPC handles name allocations
+    // a whole allocation (IPC handles name allocations): the frame(s), then 256 bytes of signal words
+    const size_t sig = rtb_peer_frame_signal_offset(bytes);
+    RTB_CUDA(ctx, cudaMalloc(d_ptr, sig + 256));
+    RTB_CUDA(ctx, cudaMemset(static_cast<uint8_t*>(*d_ptr) + sig, 0, 256));
     cudaIpcMemHandle_t h;
     const cudaError_t e = cudaIpcGetMemHandle(&h, *d_ptr);
     if (e != cudaSuccess) {

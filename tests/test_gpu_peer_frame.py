@@ -32,10 +32,23 @@ def _worker(rank, world, port, w, h, band_rows, q):
         pf.render(capi.REFERENCE_CAMERA, band_rows)   # stream 0 -> synchronous in the context
         torch.cuda.synchronize()
         pf.fence()                                    # gloo: every rank's kernel has completed
+        ok = True
         if rank == 0:
             whole = ctx.render(w, h, want=("rgba8",))["rgba8"]
             got = pf.as_tensor().cpu().numpy()
-            q.put(bool(np.array_equal(got, whole)))
+            ok = bool(np.array_equal(got, whole))
+            pf.as_tensor().zero_()
+            torch.cuda.synchronize()
+        dist.barrier()
+        # the same frame with the signal fence: each launch's last CTA bumps rank 0's signal word and
+        # rank 0 waits on it with a stream memory operation -- no collective before the frame is read
+        for _ in range(2):
+            pf.render(capi.REFERENCE_CAMERA, band_rows, signal=True)
+        if rank == 0:
+            pf.wait_all()                             # blocks until 2 frames x world signals have arrived
+            got = pf.as_tensor().cpu().numpy()
+            ok = ok and bool(np.array_equal(got, whole)) and pf.signals_expected == 2 * world
+            q.put(ok)
         dist.barrier()
         pf.close()
         ctx.close()
