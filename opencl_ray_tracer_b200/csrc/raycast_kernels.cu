@@ -267,9 +267,10 @@ __device__ __forceinline__ void shade_and_store(const GridParams& p, PixelState<
 // stage.  The values are those of rtb_bound_row_w / rtb_bound_row_c, computed once per row
 // instead of once per thread (16 threads of a CTA share a row).
 template <int PX, int WARPS_X, int WARPS_Y, int G = kBoundGroup, int MIN_CTAS = (PX >= 16 ? 3 : 4), int S = 1,
-          bool TAB = false>
+          bool TAB = false, int TP = kTabPrims>
 __global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y * S, MIN_CTAS)
 raycast_grid_kernel(const GridParams p) {
+    constexpr int kTabPrims = TP;  // primitives per staged chunk of the row-table variants
     constexpr int kThreads = 32 * WARPS_X * WARPS_Y * S;
     constexpr int kTileW = WARPS_X * 8 * PX;
     constexpr int kTileH = WARPS_Y * 4;
@@ -539,12 +540,12 @@ GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
 }
 
 // Experiment hook (profiles/): RTB_GRID_VARIANT=n picks another tiling of the same kernel.
-template <int PX, int WX, int WY, int G, int MINB, int S = 1, bool TAB = false>
+template <int PX, int WX, int WY, int G, int MINB, int S = 1, bool TAB = false, int TP = kTabPrims>
 cudaError_t launch_variant(const GridParams& p, cudaStream_t stream) {
     GridLaunchShape s = shape_of<PX, WX, WY>(p.width, p.local_rows);
     s.block = dim3(32 * WX * WY * S);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
-    raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB><<<s.grid, s.block, 0, stream>>>(p);
+    raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP><<<s.grid, s.block, 0, stream>>>(p);
     return cudaGetLastError();
 }
 
@@ -555,16 +556,9 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) 
     }();
     switch (variant) {
         case 1: return launch_variant<16, 2, 2, 4, 4>(p, stream);            // row terms per thread (round-1 v2 kernel)
-        case 2: return launch_variant<16, 2, 4, 4, 3>(p, stream);            // 256 x 16 tile, per-thread row terms
-        case 6: return launch_variant<8, 2, 2, 4, 8>(p, stream);
-        case 7: return launch_variant<16, 2, 1, 4, 4, 2>(p, stream);
-        case 9: return launch_variant<4, 2, 2, 4, 8>(p, stream);
         case 10: return launch_variant<16, 2, 2, 4, 4, 1, true>(p, stream);  // row table (production at C3)
         case 20: return launch_variant<16, 2, 1, 4, 4, 2, true>(p, stream);  // 2 warps per 128x4 tile
-        case 21: return launch_variant<16, 1, 1, 4, 4, 4, true>(p, stream);  // 4 warps per tile
-        case 22: return launch_variant<16, 1, 1, 4, 2, 8, true>(p, stream);  // 8 warps per tile
-        case 11: return launch_variant<16, 2, 2, 4, 3, 1, true>(p, stream);
-        case 13: return launch_variant<16, 2, 2, 2, 4, 1, true>(p, stream);
+        case 31: return launch_variant<16, 2, 2, 4, 6, 1, true, 64>(p, stream);  // 6 CTAs/SM (<= 85 registers)
         case 15: return launch_variant<8, 2, 2, 4, 8, 1, true>(p, stream);
         default: break;
     }

@@ -192,7 +192,7 @@ int rtb_init(rtb_ctx** out, int n_devices, const int* device_ids) {
     ctx->device = dev;
     ctx->sm_count = prop.multiProcessorCount;
     cudaDeviceGetAttribute(&ctx->clock_khz, cudaDevAttrClockRate, dev);
-    std::snprintf(ctx->name, sizeof ctx->name, "%s", prop.name);
+    std::snprintf(ctx->name, sizeof ctx->name, "%.127s", prop.name);
     bool chunk_ok = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
     for (int i = 0; i < 8 && chunk_ok; ++i)
         chunk_ok = cudaEventCreateWithFlags(&ctx->ev_chunk[i], cudaEventDisableTiming) == cudaSuccess;

@@ -47,7 +47,7 @@ def child(workload, flush, reps):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", default="c3")
-    ap.add_argument("--variants", default="0,16,10,11,12,13,14")
+    ap.add_argument("--variants", default="0,1,10,15,20,31")
     ap.add_argument("--flush", action="store_true")
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--child", action="store_true")
