@@ -411,7 +411,7 @@ raycast_grid_kernel(const GridParams p) {
     if (owner && lrow < p.local_rows && gy < p.height && x0 < p.width) shade_and_store<PX>(p, st, x0, lrow, gy);
 
     // ---- completion signals --------------------------------------------------------------------
-    // progress: the launch's rows are cut into chunks of p.progress_rows rows; the last CTA of a chunk
+    // progress: the launch's rows are cut into chunks [progress_bound[c], progress_bound[c+1]); the last CTA of a chunk
     //   to finish publishes p.progress_epoch in the chunk's flag word, on which the copy stream waits
     //   (cuStreamWaitValue32, rtb_render): finished rows leave for the host while the launch runs.
     // done_signal: the last CTA of the whole launch adds 1 to a word that may live in ANOTHER GPU's
@@ -421,16 +421,20 @@ raycast_grid_kernel(const GridParams p) {
     if (p.progress != nullptr || p.done_signal != nullptr) {
         __syncthreads();  // every store of this CTA is ordered before thread 0's fence
         if (tid == 0) {
-            __threadfence_system();
+            // device scope orders the stores for this GPU's copy engine and stream waits (both read
+            // through L2); stores into a peer's memory and the peer signal need system scope
+            if (p.done_signal != nullptr || p.fence_system) __threadfence_system();
+            else __threadfence();
             if (p.progress != nullptr) {
                 const int row0 = blockIdx.y * kTileH;
-                const int chunk = row0 / p.progress_rows;
-                const int c0 = chunk * p.progress_rows;
-                const int c1 = min(c0 + p.progress_rows, p.local_rows);
+                int chunk = 0;
+                while (chunk + 1 < p.progress_chunks && row0 >= p.progress_bound[chunk + 1]) ++chunk;
+                const int c0 = p.progress_bound[chunk], c1 = p.progress_bound[chunk + 1];
                 const unsigned expected = gridDim.x * (unsigned)((c1 - c0 + kTileH - 1) / kTileH);
                 if (atomicAdd(&p.progress[chunk], 1u) + 1u == expected) {
                     p.progress[chunk] = 0u;
-                    __threadfence_system();
+                    if (p.fence_system) __threadfence_system();
+                    else __threadfence();
                     *reinterpret_cast<volatile unsigned*>(&p.progress[kMaxProgressChunks + chunk]) = p.progress_epoch;
                 }
             }

@@ -35,14 +35,17 @@ struct GridParams {
     int4* out_i32;                          // nullable
     int vec_ok;                             // outputs 16-byte aligned and width % 4 == 0
     // Progress words (nullable): [0, kMaxProgressChunks) CTA counters, [kMaxProgressChunks, 2x) flags.
-    // Chunk c = local rows [c*progress_rows, (c+1)*progress_rows); progress_rows is a multiple of 16.
+    // Chunk c = local rows [progress_bound[c], progress_bound[c+1]); the bounds are multiples of 16
+    // (except the last, = local_rows), ascending, progress_chunks of them in use.
     unsigned int* progress;
-    int progress_rows;
+    int progress_chunks;
+    int progress_bound[kMaxProgressChunks + 1];
     unsigned int progress_epoch;
     // Launch-completion signal (nullable): done_counter = this context's CTA counter, done_signal = the
     // word the last CTA increments with a system-scope atomic (own or peer memory).
     unsigned int* done_counter;
     unsigned int* done_signal;
+    int fence_system;                       // 1: system-scope fences also for the progress flags (debug knob)
     RtbCam cam;
 };
 

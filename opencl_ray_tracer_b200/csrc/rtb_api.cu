@@ -381,16 +381,38 @@ int ensure_host_scene(rtb_ctx* ctx) {
     return RTB_OK;
 }
 
+// Row chunks in which a launch reports progress (rtb_render, rtb_render_bands_host): about 2 MB of
+// output each, bounds on multiples of `unit` rows (a multiple of 16); returns the number of chunks.
+// The copy stream is nearly as busy as the kernel (C3: 0.6 ms of PCIe time under a 0.76 ms launch), so
+// the copies have to start early and every stream wait (1-2 us of the copy stream's time) counts:
+// measured on C3, device span of rtb_render: 16 x 2 MB 0.83 ms; 64 x 0.5 MB with copies grouped by four
+// 0.89 ms; sizes shrinking towards the end (8, 8, 8, 4, 2, 1, 0.5, 0.5 MB) 0.93 ms.
+int plan_progress_chunks(int rows, size_t row_bytes, int unit, int bound[kMaxProgressChunks + 1]) {
+    size_t want = (row_bytes * (size_t)rows + (2u << 20) - 1) / (2u << 20);
+    if (want < 1) want = 1;
+    if (want > (size_t)kMaxProgressChunks) want = kMaxProgressChunks;
+    int chunk_rows = (int)(((size_t)rows + want - 1) / want);
+    chunk_rows = (chunk_rows + unit - 1) / unit * unit;
+    const int n = (rows + chunk_rows - 1) / chunk_rows;
+    for (int i = 0; i < n; ++i) bound[i] = i * chunk_rows;
+    bound[n] = rows;
+    return n;
+}
+
 // Enqueues one grid-kernel launch (with its timing event pair) on `stream`.
 int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width, int height, int band_rows,
                  int band_rank, int band_world, int local_rows, void* d_rgba8, void* d_id, void* d_i32,
-                 cudaStream_t stream, int out_global_rows = 0, int progress_rows = 0, void* done_signal = nullptr) {
+                 cudaStream_t stream, int out_global_rows = 0, int progress_chunks = 0, const int* progress_bound = nullptr,
+                 void* done_signal = nullptr) {
     GridParams p;
     p.out_global_rows = out_global_rows;
+    static const int fence_sys = [] { const char* e = std::getenv("RTB_PROGRESS_FENCE_SYSTEM"); return (e && e[0] == '1') ? 1 : 0; }();
+    p.fence_system = fence_sys;
     p.done_counter = ctx->d_progress + 2 * kMaxProgressChunks;
     p.done_signal = static_cast<unsigned int*>(done_signal);
-    p.progress = progress_rows > 0 ? ctx->d_progress : nullptr;
-    p.progress_rows = progress_rows > 0 ? progress_rows : 1;
+    p.progress = progress_chunks > 0 ? ctx->d_progress : nullptr;
+    p.progress_chunks = progress_chunks;
+    for (int i = 0; i <= kMaxProgressChunks; ++i) p.progress_bound[i] = (progress_chunks > 0 && i <= progress_chunks) ? progress_bound[i] : 0;
     p.progress_epoch = ctx->progress_epoch;
     p.width = width; p.height = height;
     p.band_rows = band_rows; p.band_rank = band_rank; p.band_world = band_world;
@@ -509,7 +531,7 @@ int rtb_render_bands_frame_signal(rtb_ctx* ctx, int width, int height, const flo
         RTB_CUDA(ctx, launch_signal_only(static_cast<unsigned int*>(d_signal), stream));
     }
     rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, band_rows, band_rank, band_world, local_rows,
-                      d_frame_rgba8, nullptr, nullptr, stream, 1, 0, d_signal);
+                      d_frame_rgba8, nullptr, nullptr, stream, 1, 0, nullptr, d_signal);
     if (rc != RTB_OK) return rc;
     if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
     return RTB_OK;
@@ -608,26 +630,21 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
         if (host[i]) row_bytes += elem[i] * (size_t)width;
     cudaStream_t cs = st;
     if (any_host && ctx->stream_wait_value32 && height >= 64) {
-        // ONE launch for the whole frame; the kernel publishes finished row chunks (about 2 MB of
-        // output each, at most kMaxProgressChunks) and copy_stream copies chunk k to the host as soon
+        // ONE launch for the whole frame; the kernel publishes finished row chunks (plan_progress_chunks)
+        // and copy_stream copies chunk k to the host as soon
         // as its flag shows this frame's epoch, while later rows are still being rendered.  (The
         // reference's OpenCL path does one blocking clEnqueueMapBuffer after the kernel,
         // MainState.cpp:876-886.)
-        size_t want = (row_bytes * (size_t)height + (2u << 20) - 1) / (2u << 20);
-        if (want < 1) want = 1;
-        if (want > (size_t)kMaxProgressChunks) want = kMaxProgressChunks;
-        int chunk_rows = (int)(((size_t)height + want - 1) / want);
-        chunk_rows = (chunk_rows + 15) & ~15;
-        const int n_chunks = (height + chunk_rows - 1) / chunk_rows;
+        int bound[kMaxProgressChunks + 1];
+        const int n_chunks = plan_progress_chunks(height, row_bytes, 16, bound);
         cs = ctx->copy_stream;
         ctx->progress_epoch += 1;
         if (ctx->progress_epoch == 0) ctx->progress_epoch = 1;
         rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, 16, 0, 1, height, host[0] ? ctx->d_out[0] : nullptr,
-                          host[1] ? ctx->d_out[1] : nullptr, host[2] ? ctx->d_out[2] : nullptr, st, 0, chunk_rows);
+                          host[1] ? ctx->d_out[1] : nullptr, host[2] ? ctx->d_out[2] : nullptr, st, 0, n_chunks, bound);
         if (rc != RTB_OK) return rc;
         for (int k = 0; k < n_chunks; ++k) {
-            const int y0 = k * chunk_rows;
-            const int rows = (height - y0 < chunk_rows) ? (height - y0) : chunk_rows;
+            const int y0 = bound[k], rows = bound[k + 1] - bound[k];
             const CUdeviceptr flag = reinterpret_cast<CUdeviceptr>(ctx->d_progress + kMaxProgressChunks + k);
             if (ctx->stream_wait_value32(cs, flag, ctx->progress_epoch, CU_STREAM_WAIT_VALUE_EQ) != CUDA_SUCCESS)
                 return fail(ctx, RTB_ERR_CUDA, "cuStreamWaitValue32 failed");
@@ -704,12 +721,8 @@ int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origi
         // chunk = whole bands (and a multiple of 16 rows, the progress granularity): about 2 MB each
         int unit = band_rows;
         while (unit % 16 != 0) unit *= 2;
-        size_t want = (row_bytes * (size_t)local_rows + (2u << 20) - 1) / (2u << 20);
-        if (want < 1) want = 1;
-        if (want > (size_t)kMaxProgressChunks) want = kMaxProgressChunks;
-        int chunk_rows = (int)(((size_t)local_rows + want - 1) / want);
-        chunk_rows = (chunk_rows + unit - 1) / unit * unit;
-        const int n_chunks = (local_rows + chunk_rows - 1) / chunk_rows;
+        int bound[kMaxProgressChunks + 1];
+        const int n_chunks = plan_progress_chunks(local_rows, row_bytes, unit, bound);
         const bool flags = ctx->stream_wait_value32 != nullptr;
         cudaStream_t cs = flags ? ctx->copy_stream : st;
         if (flags) {
@@ -717,12 +730,11 @@ int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origi
             if (ctx->progress_epoch == 0) ctx->progress_epoch = 1;
         }
         rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, band_rows, band_rank, band_world, local_rows,
-                          ctx->d_out[0], nullptr, nullptr, st, 0, flags ? chunk_rows : 0);
+                          ctx->d_out[0], nullptr, nullptr, st, 0, flags ? n_chunks : 0, bound);
         if (rc != RTB_OK) return rc;
         const size_t band_bytes = row_bytes * (size_t)band_rows;
         for (int k = 0; k < n_chunks; ++k) {
-            const int l0 = k * chunk_rows;
-            const int rows = (local_rows - l0 < chunk_rows) ? (local_rows - l0) : chunk_rows;
+            const int l0 = bound[k], rows = bound[k + 1] - bound[k];
             if (flags) {
                 const CUdeviceptr flag = reinterpret_cast<CUdeviceptr>(ctx->d_progress + kMaxProgressChunks + k);
                 if (ctx->stream_wait_value32(cs, flag, ctx->progress_epoch, CU_STREAM_WAIT_VALUE_EQ) != CUDA_SUCCESS)
