@@ -82,7 +82,12 @@ template <int PX>
 struct PixelState {
     uint64_t u2[PX / 2];  // camera u of rays (2j, 2j+1), packed for FFMA2
     float best[PX];
-    int id[PX];
+    // The winning primitive ids live in (dynamic) shared memory, one column per thread: they are read
+    // and written only in the rare exact update and in the epilogue, and the 16 registers they would
+    // pin for the whole dense loop are what lets the next group's table entries be prefetched.
+    int* sid;
+    int sid_stride;
+    __device__ __forceinline__ int& id(int q) const { return sid[q * sid_stride]; }
     __device__ __forceinline__ float u(int q) const {
         float lo, hi;
         unpack2(u2[q >> 1], lo, hi);
@@ -108,7 +113,7 @@ __device__ __forceinline__ void exact_update(const GridParams& p, int prim, floa
             const float f0 = n0 + s0.width, f1 = n1 + s1.width, f2 = n2 + s2.width;
             const float tn = fmaxf(fmaxf(n0, n1), n2);
             const float tf = fminf(fminf(f0, f1), f2);
-            rtb_cube_update(tn, tf, prim, st.best[q], st.id[q]);
+            rtb_cube_update(tn, tf, prim, st.best[q], st.id(q));
         }
     } else if (prim < p.n_cubes + p.n_spheres) {
         const float4 r = __ldg(p.sph_rec + (size_t)(prim - p.n_cubes));
@@ -119,7 +124,7 @@ __device__ __forceinline__ void exact_update(const GridParams& p, int prim, floa
         for (int q = 0; q < PX; ++q) {
             const float rad = rtb_sphere_rad(sp, radv, st.u(q));
             const float wpix = fmaf(p.cam.tau_u, st.u(q), wv);
-            rtb_sphere_update(sp, rad, wpix, prim, st.best[q], st.id[q]);
+            rtb_sphere_update(sp, rad, wpix, prim, st.best[q], st.id(q));
         }
     }
 }
@@ -203,18 +208,75 @@ __device__ __forceinline__ void bound_group_tab(const GridParams& p, const float
     }
 }
 
+// One primitive's bound on this thread's PX rays: AND of the IEEE patterns of q (bit 30 = "q >= 2").
+template <int PX>
+__device__ __forceinline__ uint32_t bound_test(const float4 t, const PixelState<PX>& st) {
+    const uint64_t S2 = pack2(t.x, t.x), W2 = pack2(t.y, t.y), C2 = pack2(t.z, t.z);
+    uint32_t a = 0xFFFFFFFFu;
+#pragma unroll
+    for (int j = 0; j < PX / 2; ++j) {
+        const uint64_t w2 = ffma2(st.u2[j], S2, W2);
+        const uint64_t q2 = ffma2(w2, w2, C2);
+        uint32_t q0, q1;
+        unpack2u(q2, q0, q1);
+        a &= q0 & q1;
+    }
+    return a;
+}
+
+// The dense loop over one staged chunk, software-pipelined: the table entries of the next two
+// primitives are requested (LDS.128 off a running pointer, no address arithmetic on the critical
+// path) while the current two are being tested, so no warp waits for shared memory at the top of a
+// group (before: 19 % of the stall samples sat on the first FFMA2 after the loads and on the IMAD
+// feeding their address).  Groups of 4 primitives per vote; this warp takes groups split, split+S, ...
+template <int PX, int ROWS, int S>
+__device__ __forceinline__ void dense_chunk_tab(const GridParams& p, const float4* __restrict__ tab, int cnt,
+                                                int first_prim, int split, float v, PixelState<PX>& st) {
+    constexpr int G = 4;
+    int j = split * G;
+    if (j >= cnt) return;
+    const float4* t = tab + j * ROWS;
+    float4 c0 = t[0], c1 = t[ROWS];
+#pragma unroll 1
+    for (; j < cnt; j += S * G) {
+        const float4 c2 = t[2 * ROWS], c3 = t[3 * ROWS];
+        uint32_t acc[G];
+        acc[0] = bound_test<PX>(c0, st);
+        acc[1] = bound_test<PX>(c1, st);
+        // next group's first two entries; past the end the last group is read again (stays inside the table)
+        const int jn = min(j + S * G, cnt - G);
+        const float4* tn = tab + jn * ROWS;
+        c0 = tn[0];
+        c1 = tn[ROWS];
+        acc[2] = bound_test<PX>(c2, st);
+        acc[3] = bound_test<PX>(c3, st);
+        const uint32_t all = acc[0] & acc[1] & acc[2] & acc[3];
+        if (__any_sync(0xFFFFFFFFu, (all & RTB_BOUND_FAIL_BIT) == 0u)) {
+#pragma unroll 1
+            for (int g = 0; g < G; ++g) {
+                uint32_t a = acc[0];
+#pragma unroll
+                for (int h = 1; h < G; ++h) a = (g == h) ? acc[h] : a;
+                if (__any_sync(0xFFFFFFFFu, (a & RTB_BOUND_FAIL_BIT) == 0u)) exact_update<PX>(p, first_prim + j + g, v, st);
+            }
+        }
+        t = tn;
+    }
+}
+
 // Nearest-hit shading (rtb_shade) + 128-bit coalesced stores of one thread's PX pixels.
 template <int PX>
 __device__ __forceinline__ void shade_and_store(const GridParams& p, PixelState<PX>& st, int x0, int lrow, int gy) {
     uint32_t rgba8[PX];
     int32_t rgba[PX][4];
+    int ids[PX];
 #pragma unroll
     for (int q = 0; q < PX; ++q) {
         float cr = 0.f, cg = 0.f, cb = 0.f;
-        if (st.best[q] == RTB_MISS_T) st.id[q] = -1;
-        if (st.id[q] >= 0) {
-            const float4 col = (st.id[q] < p.n_cubes) ? __ldg(p.cube_col + st.id[q])
-                                                      : __ldg(p.sph_col + (st.id[q] - p.n_cubes));
+        ids[q] = (st.best[q] == RTB_MISS_T) ? -1 : st.id(q);
+        if (ids[q] >= 0) {
+            const float4 col = (ids[q] < p.n_cubes) ? __ldg(p.cube_col + ids[q])
+                                                    : __ldg(p.sph_col + (ids[q] - p.n_cubes));
             cr = col.x; cg = col.y; cb = col.z;
         }
         rtb_shade(st.best[q], cr, cg, cb, rgba[q]);
@@ -234,7 +296,7 @@ __device__ __forceinline__ void shade_and_store(const GridParams& p, PixelState<
 #pragma unroll
             for (int q = 0; q < PX; q += 4)
                 *reinterpret_cast<int4*>(p.out_id + row_off + x0 + q) =
-                    make_int4(st.id[q], st.id[q + 1], st.id[q + 2], st.id[q + 3]);
+                    make_int4(ids[q], ids[q + 1], ids[q + 2], ids[q + 3]);
         }
         if (p.out_i32) {
 #pragma unroll
@@ -246,7 +308,7 @@ __device__ __forceinline__ void shade_and_store(const GridParams& p, PixelState<
         for (int q = 0; q < PX; ++q) {
             if (x0 + q < p.width) {
                 if (p.out_rgba8) p.out_rgba8[row_off + x0 + q] = rgba8[q];
-                if (p.out_id) p.out_id[row_off + x0 + q] = st.id[q];
+                if (p.out_id) p.out_id[row_off + x0 + q] = ids[q];
                 if (p.out_i32) {
                     int32_t* o = reinterpret_cast<int32_t*>(p.out_i32) + 4 * (row_off + x0 + q);
                     o[0] = rgba[q][0]; o[1] = rgba[q][1]; o[2] = rgba[q][2]; o[3] = rgba[q][3];
@@ -267,7 +329,7 @@ __device__ __forceinline__ void shade_and_store(const GridParams& p, PixelState<
 // stage.  The values are those of rtb_bound_row_w / rtb_bound_row_c, computed once per row
 // instead of once per thread (16 threads of a CTA share a row).
 template <int PX, int WARPS_X, int WARPS_Y, int G = kBoundGroup, int MIN_CTAS = (PX >= 16 ? 3 : 4), int S = 1,
-          bool TAB = false, int TP = kTabPrims>
+          bool TAB = false, int TP = kTabPrims, bool PIPE = true>
 __global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y * S, MIN_CTAS)
 raycast_grid_kernel(const GridParams p) {
     constexpr int kTabPrims = TP;  // primitives per staged chunk of the row-table variants
@@ -324,14 +386,18 @@ raycast_grid_kernel(const GridParams p) {
         if (n_chunks > 1) issue(1);
     }
 
+    extern __shared__ int dyn_ids[];  // [PX][kThreads] winning primitive ids (see PixelState)
     PixelState<PX> st;
+    st.sid = dyn_ids + tid;
+    st.sid_stride = kThreads;
     const float fy = (float)gy;
     const float v = rtb_cam_v(p.cam, fy);
 #pragma unroll
     for (int q = 0; q < PX; q += 2) {
         st.u2[q >> 1] = pack2(rtb_cam_u(p.cam, (float)(x0 + q), fy), rtb_cam_u(p.cam, (float)(x0 + q + 1), fy));
         st.best[q] = st.best[q + 1] = RTB_MISS_T;
-        st.id[q] = st.id[q + 1] = -1;
+        st.id(q) = -1;
+        st.id(q + 1) = -1;
     }
 
     // row-table build: thread t always fills CTA row t % kTileH (kThreads is a multiple of kTileH)
@@ -362,9 +428,13 @@ raycast_grid_kernel(const GridParams p) {
             __syncthreads();
             if (tid == 0 && k + 2 < n_chunks) issue(k + 2);
             const float4* tab = &rowtab[b][wy * 4 + ly];
+            if constexpr (PIPE && G == 4) {
+                dense_chunk_tab<PX, kTileH, S>(p, tab, cnt, first, split, v, st);
+            } else {
 #pragma unroll 1
-            for (int j = split * G; j < cnt; j += S * G)
-                bound_group_tab<PX, G, kTileH>(p, tab + j * kTileH, first + j, v, st);
+                for (int j = split * G; j < cnt; j += S * G)
+                    bound_group_tab<PX, G, kTileH>(p, tab + j * kTileH, first + j, v, st);
+            }
         } else {
 #pragma unroll 1
             for (int j = split * G; j < cnt; j += S * G) bound_group<PX, G>(p, &stage[b][2 * j], first + j, v, st);
@@ -386,7 +456,7 @@ raycast_grid_kernel(const GridParams p) {
 #pragma unroll
             for (int q = 0; q < PX; ++q) {
                 m_best[tile_warp * (S - 1) + split - 1][q][lane] = st.best[q];
-                m_id[tile_warp * (S - 1) + split - 1][q][lane] = st.id[q];
+                m_id[tile_warp * (S - 1) + split - 1][q][lane] = st.id(q);
             }
         }
         __syncthreads();
@@ -398,9 +468,10 @@ raycast_grid_kernel(const GridParams p) {
                     const float ob = m_best[tile_warp * (S - 1) + o][q][lane];
                     const int oi = m_id[tile_warp * (S - 1) + o][q][lane];
                     // same winner as one ascending pass: nearest t, ties to the lowest primitive index
-                    if (ob < st.best[q] || (ob == st.best[q] && oi >= 0 && (st.id[q] < 0 || oi < st.id[q]))) {
+                    const int mine = st.id(q);
+                    if (ob < st.best[q] || (ob == st.best[q] && oi >= 0 && (mine < 0 || oi < mine))) {
                         st.best[q] = ob;
-                        st.id[q] = oi;
+                        st.id(q) = oi;
                     }
                 }
             }
@@ -544,13 +615,32 @@ GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
 }
 
 // Experiment hook (profiles/): RTB_GRID_VARIANT=n picks another tiling of the same kernel.
-template <int PX, int WX, int WY, int G, int MINB, int S = 1, bool TAB = false, int TP = kTabPrims>
+// Launch of one instantiation: the id columns are dynamic shared memory (PX x threads ints); together
+// with the static staging / table area that can pass 48 KB, which needs the opt-in attribute (set once
+// per instantiation and device).
+template <int PX, int WX, int WY, int G, int MINB, int S, bool TAB, int TP, bool PIPE>
+cudaError_t launch_instance(const GridParams& p, dim3 grid, cudaStream_t stream) {
+    constexpr int kThreads = 32 * WX * WY * S;
+    constexpr int kDyn = PX * kThreads * (int)sizeof(int);
+    static thread_local int configured_device = -1;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (configured_device != dev) {
+        e = cudaFuncSetAttribute(raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP, PIPE>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, kDyn);
+        if (e != cudaSuccess) return e;
+        configured_device = dev;
+    }
+    raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP, PIPE><<<grid, dim3(kThreads), kDyn, stream>>>(p);
+    return cudaGetLastError();
+}
+
+template <int PX, int WX, int WY, int G, int MINB, int S = 1, bool TAB = false, int TP = kTabPrims, bool PIPE = true>
 cudaError_t launch_variant(const GridParams& p, cudaStream_t stream) {
     GridLaunchShape s = shape_of<PX, WX, WY>(p.width, p.local_rows);
-    s.block = dim3(32 * WX * WY * S);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
-    raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP><<<s.grid, s.block, 0, stream>>>(p);
-    return cudaGetLastError();
+    return launch_instance<PX, WX, WY, G, MINB, S, TAB, TP, PIPE>(p, s.grid, stream);
 }
 
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) {
@@ -563,20 +653,16 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) 
         case 10: return launch_variant<16, 2, 2, 4, 4, 1, true>(p, stream);  // row table (production at C3)
         case 20: return launch_variant<16, 2, 1, 4, 4, 2, true>(p, stream);  // 2 warps per 128x4 tile
         case 31: return launch_variant<16, 2, 2, 4, 6, 1, true, 64>(p, stream);  // 6 CTAs/SM (<= 85 registers)
+        case 11: return launch_variant<16, 2, 2, 4, 4, 1, true, kTabPrims, false>(p, stream);  // row table, loads not pipelined
         case 15: return launch_variant<8, 2, 2, 4, 8, 1, true>(p, stream);
         default: break;
     }
     const GridLaunchShape s = grid_launch_shape(p.width, p.local_rows, sm_count);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
-    if (s.px == 16 && s.wy == 2)
-        raycast_grid_kernel<16, 2, 2, kBoundGroup, 4, 1, true><<<s.grid, s.block, 0, stream>>>(p);
-    else if (s.px == 16)
-        raycast_grid_kernel<16, 2, 1, kBoundGroup, 4, 2, true><<<s.grid, s.block, 0, stream>>>(p);
-    else if (s.px == 8)
-        raycast_grid_kernel<8, 2, 2, kBoundGroup, 8, 1, true><<<s.grid, s.block, 0, stream>>>(p);
-    else
-        raycast_grid_kernel<4, 2, 2, kBoundGroup, 8, 1, true><<<s.grid, s.block, 0, stream>>>(p);
-    return cudaGetLastError();
+    if (s.px == 16 && s.wy == 2) return launch_instance<16, 2, 2, kBoundGroup, 4, 1, true, kTabPrims, true>(p, s.grid, stream);
+    if (s.px == 16) return launch_instance<16, 2, 1, kBoundGroup, 4, 2, true, kTabPrims, true>(p, s.grid, stream);
+    if (s.px == 8) return launch_instance<8, 2, 2, kBoundGroup, 8, 1, true, kTabPrims, true>(p, s.grid, stream);
+    return launch_instance<4, 2, 2, kBoundGroup, 8, 1, true, kTabPrims, true>(p, s.grid, stream);
 }
 
 cudaError_t launch_rays(const RaysParams& p, cudaStream_t stream) {
