@@ -71,6 +71,19 @@ const char* rtb_error_string(int status);
 /* Detail text of the last failure on this context (CUDA error string, offending cube index...). */
 const char* rtb_last_error_message(const rtb_ctx* ctx);
 
+/* Per-context switches; every render entry point below obeys them.  No counterpart in the
+ * reference (its only switch is enum Mode, MainState.h:48-52).
+ *   RTB_OPT_TILE_CULL (0 | 1, default 0): 1 = render with raycast_cull_kernel.  Every CTA first
+ *     tests each primitive's conservative screen-space bound against its whole 256 x 8 pixel tile
+ *     and runs the per-ray tests only for the survivors: the pixels are byte-identical to the
+ *     default kernel's (the cull is a statement about the values the per-ray bound would compute),
+ *     the work drops from O(rays x primitives) to O(tiles x primitives + rays x survivors).
+ *     The default (0) is the dense O(rays x primitives) kernel that BASELINE.json's roofline
+ *     point is quoted on. */
+typedef enum rtb_option { RTB_OPT_TILE_CULL = 1 } rtb_option;
+int rtb_set_option(rtb_ctx* ctx, int option, int value);
+int rtb_get_option(const rtb_ctx* ctx, int option, int* value);
+
 /* Replaces the 6 clCreateBuffer + clEnqueueWriteBuffer pairs for the scene
  * (MainState.cpp:677-839) and the clSetKernelArg calls 1-7 (:747-753).  The arrays are copied to
  * the device as they are (the caller may free them on return) and stay resident until the next

@@ -28,8 +28,10 @@ EXPORTED_SYMBOLS = [
     "rtb_assemble_bands_device", "rtb_transfer_bytes", "rtb_render_bands_frame", "rtb_peer_frame_create",
     "rtb_peer_frame_open", "rtb_peer_frame_close", "rtb_debug_device_records", "rtb_render_bands_host",
     "rtb_host_register", "rtb_host_unregister", "rtb_render_bands_frame_signal", "rtb_stream_wait_signal",
-    "rtb_peer_frame_signal_offset",
+    "rtb_peer_frame_signal_offset", "rtb_set_option", "rtb_get_option",
 ]
+
+RTB_OPT_TILE_CULL = 1
 
 
 class RtbError(RuntimeError):
@@ -72,6 +74,8 @@ def load_library(path=None):
     lib.rtb_host_unregister.argtypes = [vp]
     lib.rtb_render_bands_frame_signal.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, C.c_int, C.c_int, vp, vp, vp]
     lib.rtb_stream_wait_signal.argtypes = [vp, vp, C.c_uint, vp]
+    lib.rtb_set_option.argtypes = [vp, C.c_int, C.c_int]
+    lib.rtb_get_option.argtypes = [vp, C.c_int, C.POINTER(C.c_int)]
     lib.rtb_peer_frame_signal_offset.argtypes = [C.c_size_t]
     lib.rtb_peer_frame_signal_offset.restype = C.c_size_t
     lib.rtb_peer_frame_create.argtypes = [vp, C.c_size_t, C.POINTER(vp), C.POINTER(C.c_ubyte)]
@@ -195,6 +199,15 @@ class Context:
 
     def __exit__(self, *a):
         self.close()
+
+    def set_option(self, option, value):
+        """rtb_set_option, e.g. set_option(RTB_OPT_TILE_CULL, 1)."""
+        self._check(self.lib.rtb_set_option(self._h, int(option), int(value)))
+
+    def get_option(self, option):
+        v = C.c_int()
+        self._check(self.lib.rtb_get_option(self._h, int(option), C.byref(v)))
+        return v.value
 
     def device_info(self):
         sm, khz = C.c_int(), C.c_int()

@@ -318,6 +318,45 @@ __device__ __forceinline__ void shade_and_store(const GridParams& p, PixelState<
     }
 }
 
+// ---- completion signals -------------------------------------------------------------------------
+// progress: the launch's rows are cut into chunks [progress_bound[c], progress_bound[c+1]); the last CTA of a chunk
+//   to finish publishes p.progress_epoch in the chunk's flag word, on which the copy stream waits
+//   (cuStreamWaitValue32, rtb_render): finished rows leave for the host while the launch runs.
+// done_signal: the last CTA of the whole launch adds 1 to a word that may live in ANOTHER GPU's
+//   memory (rank 0's peer frame, over NVLink): rank 0's stream waits until every rank has signalled,
+//   which replaces a collective as the "all bands have landed" fence of a multi-GPU frame.
+// Counters are reset by the CTA that completes them: one launch per context at a time.
+// Called by every thread of the CTA after its stores; tile_h = pixel rows per CTA.
+__device__ __forceinline__ void signal_completion(const GridParams& p, int tile_h) {
+    if (p.progress == nullptr && p.done_signal == nullptr) return;
+    __syncthreads();  // every store of this CTA is ordered before thread 0's fence
+    if (threadIdx.x != 0) return;
+    // device scope orders the stores for this GPU's copy engine and stream waits (both read
+    // through L2); stores into a peer's memory and the peer signal need system scope
+    if (p.done_signal != nullptr || p.fence_system) __threadfence_system();
+    else __threadfence();
+    if (p.progress != nullptr) {
+        const int row0 = blockIdx.y * tile_h;
+        int chunk = 0;
+        while (chunk + 1 < p.progress_chunks && row0 >= p.progress_bound[chunk + 1]) ++chunk;
+        const int c0 = p.progress_bound[chunk], c1 = p.progress_bound[chunk + 1];
+        const unsigned expected = gridDim.x * (unsigned)((c1 - c0 + tile_h - 1) / tile_h);
+        if (atomicAdd(&p.progress[chunk], 1u) + 1u == expected) {
+            p.progress[chunk] = 0u;
+            if (p.fence_system) __threadfence_system();
+            else __threadfence();
+            *reinterpret_cast<volatile unsigned*>(&p.progress[kMaxProgressChunks + chunk]) = p.progress_epoch;
+        }
+    }
+    if (p.done_signal != nullptr) {
+        if (atomicAdd(p.done_counter, 1u) + 1u == gridDim.x * gridDim.y) {
+            *p.done_counter = 0u;
+            __threadfence_system();
+            atomicAdd_system(p.done_signal, 1u);
+        }
+    }
+}
+
 // S > 1: S warps share one pixel tile and split the primitive list between them (groups of G,
 // round robin); their nearest hits are merged through shared memory before shading.  Used when a
 // launch has too few pixel tiles to load every scheduler evenly (the per-GPU share of a frame on 8
@@ -481,43 +520,146 @@ raycast_grid_kernel(const GridParams p) {
     // ---- nearest-hit shading + stores -------------------------------------------------------
     if (owner && lrow < p.local_rows && gy < p.height && x0 < p.width) shade_and_store<PX>(p, st, x0, lrow, gy);
 
-    // ---- completion signals --------------------------------------------------------------------
-    // progress: the launch's rows are cut into chunks [progress_bound[c], progress_bound[c+1]); the last CTA of a chunk
-    //   to finish publishes p.progress_epoch in the chunk's flag word, on which the copy stream waits
-    //   (cuStreamWaitValue32, rtb_render): finished rows leave for the host while the launch runs.
-    // done_signal: the last CTA of the whole launch adds 1 to a word that may live in ANOTHER GPU's
-    //   memory (rank 0's peer frame, over NVLink): rank 0's stream waits until every rank has signalled,
-    //   which replaces a collective as the "all bands have landed" fence of a multi-GPU frame.
-    // Counters are reset by the CTA that completes them: one launch per context at a time.
-    if (p.progress != nullptr || p.done_signal != nullptr) {
-        __syncthreads();  // every store of this CTA is ordered before thread 0's fence
-        if (tid == 0) {
-            // device scope orders the stores for this GPU's copy engine and stream waits (both read
-            // through L2); stores into a peer's memory and the peer signal need system scope
-            if (p.done_signal != nullptr || p.fence_system) __threadfence_system();
-            else __threadfence();
-            if (p.progress != nullptr) {
-                const int row0 = blockIdx.y * kTileH;
-                int chunk = 0;
-                while (chunk + 1 < p.progress_chunks && row0 >= p.progress_bound[chunk + 1]) ++chunk;
-                const int c0 = p.progress_bound[chunk], c1 = p.progress_bound[chunk + 1];
-                const unsigned expected = gridDim.x * (unsigned)((c1 - c0 + kTileH - 1) / kTileH);
-                if (atomicAdd(&p.progress[chunk], 1u) + 1u == expected) {
-                    p.progress[chunk] = 0u;
-                    if (p.fence_system) __threadfence_system();
-                    else __threadfence();
-                    *reinterpret_cast<volatile unsigned*>(&p.progress[kMaxProgressChunks + chunk]) = p.progress_epoch;
-                }
-            }
-            if (p.done_signal != nullptr) {
-                if (atomicAdd(p.done_counter, 1u) + 1u == gridDim.x * gridDim.y) {
-                    *p.done_counter = 0u;
-                    __threadfence_system();
-                    atomicAdd_system(p.done_signal, 1u);
-                }
+    signal_completion(p, kTileH);
+}
+
+// ---- tile-culled variant (GridParams::tile_cull) ------------------------------------------------
+// Same pixels, same arithmetic, far fewer tests: before a CTA's rays see a primitive, the CTA asks
+// whether the primitive's conic bound can be passed by ANY ray of its 256 x 8 pixel tile
+// (rtb_bound_tile_misses: a conservative statement about the very values the dense test would
+// compute).  Every thread tests 4 primitives per batch (records straight from global / L2 into
+// registers, the next batch's loads in flight during the tests: each record has exactly one
+// reader, so there is nothing to share through shared memory); the survivors are compacted IN ORDER
+// (ballots + cross-warp prefix: ties between primitives are broken by index, so the exact updates
+// must stay in ascending order) into a list of bound records + primitive index, and only that list
+// -- a few primitives per tile in the scenes of SURVEY.md s8d -- goes through the per-ray bound
+// (same rtb_bound_row_w/_c/ FFMA2 arithmetic as the dense kernel) and the reference-exact update.
+// Work per CTA: n_bound tile tests + survivors x rays ray tests, instead of n_bound x rays.
+template <int PX, int WARPS_X, int WARPS_Y, int MIN_CTAS>
+__global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y, MIN_CTAS)
+raycast_cull_kernel(const GridParams p) {
+    constexpr int kWarps = WARPS_X * WARPS_Y;
+    constexpr int kThreads = 32 * kWarps;
+    constexpr int kTileW = WARPS_X * 8 * PX;
+    constexpr int kTileH = WARPS_Y * 4;
+    constexpr int kUnr = 4;                  // primitives per thread and batch
+    constexpr int kBatch = kThreads * kUnr;
+    constexpr int kListCap = 2 * kBatch;     // survivors held before a pass over the rays is forced
+    __shared__ __align__(16) float4 list[2 * kListCap];  // (sA, k1, k0, e), (cv, primitive index, -, -)
+    __shared__ int wcount[2][kUnr][kWarps];
+    __shared__ float row_v[kTileH], row_ua[kTileH], row_ub[kTileH];
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int wx = warp % WARPS_X, wy = warp / WARPS_X;
+    const int lx = lane & 7, ly = lane >> 3;
+    const int x0 = blockIdx.x * kTileW + (wx * 8 + lx) * PX;
+    const int lrow = blockIdx.y * kTileH + wy * 4 + ly;
+    const int lb = lrow / p.band_rows;
+    const int gy = (lb * p.band_world + p.band_rank) * p.band_rows + (lrow - lb * p.band_rows);
+    const int n_bound = p.n_bound;
+    const int n_batches = (n_bound + kBatch - 1) / kBatch;
+
+    // first batch of records: in flight while the pixel state is set up
+    float4 r0[kUnr];
+    float cv[kUnr];
+    auto load_batch = [&](int k) {
+#pragma unroll
+        for (int u = 0; u < kUnr; ++u) {
+            const int i = k * kBatch + u * kThreads + tid;
+            if (i < n_bound) {
+                r0[u] = __ldg(p.bound_rec + 2 * (size_t)i);
+                cv[u] = __ldg(reinterpret_cast<const float*>(p.bound_rec + 2 * (size_t)i + 1));
             }
         }
+    };
+    if (n_batches > 0) load_batch(0);
+
+    if (tid < kTileH) {  // the tile's rows: v, and u of the first and the last pixel column
+        const int trow = blockIdx.y * kTileH + tid;
+        const int tlb = trow / p.band_rows;
+        const float ty = (float)((tlb * p.band_world + p.band_rank) * p.band_rows + (trow - tlb * p.band_rows));
+        row_v[tid] = rtb_cam_v(p.cam, ty);
+        row_ua[tid] = rtb_cam_u(p.cam, (float)(blockIdx.x * kTileW), ty);
+        row_ub[tid] = rtb_cam_u(p.cam, (float)(blockIdx.x * kTileW + kTileW - 1), ty);
     }
+
+    extern __shared__ int dyn_ids[];
+    PixelState<PX> st;
+    st.sid = dyn_ids + tid;
+    st.sid_stride = kThreads;
+    const float fy = (float)gy;
+    const float v = rtb_cam_v(p.cam, fy);
+#pragma unroll
+    for (int q = 0; q < PX; q += 2) {
+        st.u2[q >> 1] = pack2(rtb_cam_u(p.cam, (float)(x0 + q), fy), rtb_cam_u(p.cam, (float)(x0 + q + 1), fy));
+        st.best[q] = st.best[q + 1] = RTB_MISS_T;
+        st.id(q) = -1;
+        st.id(q + 1) = -1;
+    }
+    __syncthreads();
+    // u is monotone in x on a row, so a row's u values lie between those of its two end pixels
+    float u_min = row_ua[0], u_max = row_ua[0], v_min = row_v[0], v_max = row_v[0];
+#pragma unroll
+    for (int r = 0; r < kTileH; ++r) {
+        u_min = fminf(u_min, fminf(row_ua[r], row_ub[r]));
+        u_max = fmaxf(u_max, fmaxf(row_ua[r], row_ub[r]));
+        v_min = fminf(v_min, row_v[r]);
+        v_max = fmaxf(v_max, row_v[r]);
+    }
+
+    const uint32_t lanes_below = (1u << lane) - 1u;
+    int total = 0;  // survivors in the list (the same value in every thread)
+    for (int k = 0; k < n_batches; ++k) {
+        const int b = k & 1;
+        RtbBound bd[kUnr];
+        uint32_t ballot[kUnr];
+#pragma unroll
+        for (int u = 0; u < kUnr; ++u) {
+            bd[u].sA = r0[u].x; bd[u].k1 = r0[u].y; bd[u].k0 = r0[u].z; bd[u].e = r0[u].w; bd[u].cv = cv[u];
+        }
+        if (k + 1 < n_batches) load_batch(k + 1);
+#pragma unroll
+        for (int u = 0; u < kUnr; ++u) {
+            const bool keep = (k * kBatch + u * kThreads + tid < n_bound) &&
+                              !rtb_bound_tile_misses(bd[u], u_min, u_max, v_min, v_max);
+            ballot[u] = __ballot_sync(0xFFFFFFFFu, keep);
+            if (lane == 0) wcount[b][u][warp] = __popc(ballot[u]);
+        }
+        // counts visible (wcount[b] is next written two batches on, behind the barrier of batch
+        // k+1, which a thread reaches only after reading this batch's counts)
+        __syncthreads();
+#pragma unroll
+        for (int u = 0; u < kUnr; ++u) {
+            int slot = total + __popc(ballot[u] & lanes_below);
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) {
+                const int c = wcount[b][u][w];
+                if (w < warp) slot += c;
+                total += c;
+            }
+            if ((ballot[u] >> lane) & 1u) {
+                list[2 * slot] = make_float4(bd[u].sA, bd[u].k1, bd[u].k0, bd[u].e);
+                list[2 * slot + 1] = make_float4(bd[u].cv, __int_as_float(k * kBatch + u * kThreads + tid), 0.f, 0.f);
+            }
+        }
+        if (total > kListCap - kBatch || k == n_batches - 1) {  // the next batch might not fit / no next batch
+            __syncthreads();  // list complete
+#pragma unroll 1
+            for (int j = 0; j < total; ++j) {
+                const float4 a = list[2 * j], c = list[2 * j + 1];
+                const RtbBound s = {a.x, a.y, a.z, a.w, c.x, 0.f, 0.f, 0.f};
+                const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), rtb_bound_row_c(s, v), 0.f);
+                const uint32_t acc = bound_test<PX>(t, st);
+                if (__any_sync(0xFFFFFFFFu, (acc & RTB_BOUND_FAIL_BIT) == 0u)) exact_update<PX>(p, __float_as_int(c.y), v, st);
+            }
+            total = 0;
+            if (k != n_batches - 1) __syncthreads();  // every warp has read the list before it is refilled
+        }
+    }
+
+    if (lrow < p.local_rows && gy < p.height && x0 < p.width) shade_and_store<PX>(p, st, x0, lrow, gy);
+    signal_completion(p, kTileH);
 }
 
 }  // namespace
@@ -643,7 +785,27 @@ cudaError_t launch_variant(const GridParams& p, cudaStream_t stream) {
     return launch_instance<PX, WX, WY, G, MINB, S, TAB, TP, PIPE>(p, s.grid, stream);
 }
 
+template <int PX, int WX, int WY, int MINB>
+cudaError_t launch_cull_instance(const GridParams& p, cudaStream_t stream) {
+    constexpr int kThreads = 32 * WX * WY;
+    constexpr int kDyn = PX * kThreads * (int)sizeof(int);
+    const GridLaunchShape s = shape_of<PX, WX, WY>(p.width, p.local_rows);
+    if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
+    static thread_local int configured_device = -1;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (configured_device != dev) {
+        e = cudaFuncSetAttribute(raycast_cull_kernel<PX, WX, WY, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, kDyn);
+        if (e != cudaSuccess) return e;
+        configured_device = dev;
+    }
+    raycast_cull_kernel<PX, WX, WY, MINB><<<s.grid, dim3(kThreads), kDyn, stream>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) {
+    if (p.tile_cull) return launch_cull_instance<16, 2, 2, 4>(p, stream);
     static const int variant = [] {
         const char* e = std::getenv("RTB_GRID_VARIANT");
         return e ? std::atoi(e) : 0;

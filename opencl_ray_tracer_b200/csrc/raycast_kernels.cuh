@@ -46,6 +46,7 @@ struct GridParams {
     unsigned int* done_counter;
     unsigned int* done_signal;
     int fence_system;                       // 1: system-scope fences also for the progress flags (debug knob)
+    int tile_cull;                          // 1: raycast_cull_kernel (primitives culled per CTA tile; same pixels)
     RtbCam cam;
 };
 

@@ -118,6 +118,34 @@ RTB_HD float rtb_bound_q(float sA, float rowW, float rowC, float u) {
     return fmaf(w, w, rowC);
 }
 
+// Tile cull (RTB_OPT_TILE_CULL, raycast_cull_kernel): can NO ray of a pixel tile pass the bound of a
+// primitive?  The tile is given by the ranges of the camera coordinates its rays take: u in
+// [u_min, u_max], v in [v_min, v_max] (min / max over the very values the kernel computes for the
+// tile's pixels).  The answer is a statement about the values rtb_bound_q would compute, derived
+// from the monotonicity of each rounded operation, not from real-number geometry plus a margin:
+//   rowW = fmaf(k1, v, k0) is monotone in v        => rowW of every row lies in [r_lo, r_hi]
+//   w = fmaf(u, sA, rowW) is monotone in u and rowW => w of every ray lies in [w_lo, w_hi]
+//   dv = v - cv is monotone in v, rowC = (e*dv)*dv is even and non-decreasing in |dv| for e >= 0
+//                                                   => rowC of every row >= c_min >= 0
+//   q = fmaf(w, w, rowC) is non-decreasing in |w| and rowC
+//                                                   => q of every ray >= fmaf(wm, wm, c_min)
+// with wm the smallest |w| the interval allows.  All these q are >= 0, where "bit 30 set" is exactly
+// "q >= 2": if this returns true, every ray of the tile fails the bound, and dropping the primitive
+// for the tile cannot change a pixel.  NaNs make a comparison false (keep) or make every ray's q
+// NaN as well (bit 30 set).  tests/emu checks the claim against rtb_bound_q pixel by pixel.
+RTB_HD bool rtb_bound_tile_misses(const RtbBound& b, float u_min, float u_max, float v_min, float v_max) {
+    const float ra = rtb_bound_row_w(b, v_min), rb = rtb_bound_row_w(b, v_max);
+    const float r_lo = fminf(ra, rb), r_hi = fmaxf(ra, rb);
+    const bool up = b.sA >= 0.0f;
+    const float w_lo = fmaf(up ? u_min : u_max, b.sA, r_lo);
+    const float w_hi = fmaf(up ? u_max : u_min, b.sA, r_hi);
+    const float wm = (w_lo > 0.0f) ? w_lo : ((w_hi < 0.0f) ? -w_hi : 0.0f);
+    const float da = v_min - b.cv, db = v_max - b.cv;
+    const float dm = (da > 0.0f) ? da : ((db < 0.0f) ? db : 0.0f);
+    const float c_min = (b.e * dm) * dm;
+    return b.e >= 0.0f && fmaf(wm, wm, c_min) >= 2.0f;
+}
+
 // Depth-fog shade + (int) truncation, MainState.cpp:397-407, misc/Utility.cpp:109-116,
 // MainState.cpp:952-955.  Same operation order as the reference; no contraction.
 RTB_HD void rtb_shade(float closest, float cr, float cg, float cb, int32_t out[4]) {

@@ -78,6 +78,7 @@ struct rtb_ctx {
     double kernel_ms_sum = 0.0;
     int kernel_ms_n = 0;
     unsigned long long launches = 0;
+    int tile_cull = 0;  // RTB_OPT_TILE_CULL
 };
 
 namespace {
@@ -409,6 +410,7 @@ int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width
     p.out_global_rows = out_global_rows;
     static const int fence_sys = [] { const char* e = std::getenv("RTB_PROGRESS_FENCE_SYSTEM"); return (e && e[0] == '1') ? 1 : 0; }();
     p.fence_system = fence_sys;
+    p.tile_cull = ctx->tile_cull;
     p.done_counter = ctx->d_progress + 2 * kMaxProgressChunks;
     p.done_signal = static_cast<unsigned int*>(done_signal);
     p.progress = progress_chunks > 0 ? ctx->d_progress : nullptr;
@@ -912,6 +914,26 @@ int rtb_device_info(const rtb_ctx* ctx, int* sm_count, int* sm_clock_khz, char* 
     if (sm_clock_khz) *sm_clock_khz = ctx->clock_khz;
     if (name && name_cap) std::snprintf(name, name_cap, "%s", ctx->name);
     return RTB_OK;
+}
+
+int rtb_set_option(rtb_ctx* ctx, int option, int value) {
+    if (!ctx) return RTB_ERR_INVALID_ARG;
+    switch (option) {
+        case RTB_OPT_TILE_CULL:
+            if (value != 0 && value != 1) return fail(ctx, RTB_ERR_INVALID_ARG, "RTB_OPT_TILE_CULL takes 0 or 1");
+            ctx->tile_cull = value;
+            return RTB_OK;
+        default:
+            return fail(ctx, RTB_ERR_INVALID_ARG, "unknown option");
+    }
+}
+
+int rtb_get_option(const rtb_ctx* ctx, int option, int* value) {
+    if (!ctx || !value) return RTB_ERR_INVALID_ARG;
+    switch (option) {
+        case RTB_OPT_TILE_CULL: *value = ctx->tile_cull; return RTB_OK;
+        default: return RTB_ERR_INVALID_ARG;
+    }
 }
 
 unsigned long long rtb_launch_count(const rtb_ctx* ctx) { return ctx ? ctx->launches : 0ull; }

@@ -99,3 +99,50 @@ extern "C" int emu_check_bounds(int width, int height, const float* cam8, int nc
     out[0] = viol; out[1] = pass; out[2] = foot; out[3] = (long long)width * height * (nc + ns);
     return 0;
 }
+
+// Tile cull of raycast_cull_kernel (rtb_bound_tile_misses): for every tile_w x tile_h pixel tile
+// and primitive, the cull may say "miss" only if rtb_bound_q fails (bit 30 set) on every pixel of
+// the tile.  out[0] = violations (culled although some pixel passes), out[1] = culled pairs,
+// out[2] = pairs in which no pixel passes (what an ideal cull would drop), out[3] = pairs.
+extern "C" int emu_check_tile_cull(int width, int height, const float* cam8, int n_bound, const float* bound_rec,
+                                   int tile_w, int tile_h, long long* out) {
+    const RtbCam cam = {cam8[0], cam8[1], cam8[2], cam8[3], cam8[4], 0.f, 0.f, 0.f};
+    const RtbBound* bnd = reinterpret_cast<const RtbBound*>(bound_rec);
+    const int tx = (width + tile_w - 1) / tile_w, ty = (height + tile_h - 1) / tile_h;
+    long long viol = 0, culled = 0, empty = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : viol, culled, empty)
+    for (int t = 0; t < tx * ty; ++t) {
+        const int x_lo = (t % tx) * tile_w, y_lo = (t / tx) * tile_h;
+        // the kernel's ranges: all tile_h rows and both end columns of the full tile, in or out of the frame
+        float u_min = 0.f, u_max = 0.f, v_min = 0.f, v_max = 0.f;
+        for (int r = 0; r < tile_h; ++r) {
+            const float fy = (float)(y_lo + r);
+            const float v = rtb_cam_v(cam, fy);
+            const float ua = rtb_cam_u(cam, (float)x_lo, fy), ub = rtb_cam_u(cam, (float)(x_lo + tile_w - 1), fy);
+            if (r == 0) { u_min = u_max = ua; v_min = v_max = v; }
+            u_min = fminf(u_min, fminf(ua, ub)); u_max = fmaxf(u_max, fmaxf(ua, ub));
+            v_min = fminf(v_min, v); v_max = fmaxf(v_max, v);
+        }
+        for (int i = 0; i < n_bound; ++i) {
+            const RtbBound& b = bnd[i];
+            const bool miss = rtb_bound_tile_misses(b, u_min, u_max, v_min, v_max);
+            bool any_pass = false;
+            for (int r = 0; r < tile_h && !any_pass; ++r) {
+                const float fy = (float)(y_lo + r);
+                const float v = rtb_cam_v(cam, fy);
+                const float rw = rtb_bound_row_w(b, v), rc = rtb_bound_row_c(b, v);
+                for (int x = x_lo; x < x_lo + tile_w; ++x) {
+                    const float q = rtb_bound_q(b.sA, rw, rc, rtb_cam_u(cam, (float)x, fy));
+                    uint32_t bits;
+                    __builtin_memcpy(&bits, &q, 4);
+                    if ((bits & RTB_BOUND_FAIL_BIT) == 0u) { any_pass = true; break; }
+                }
+            }
+            culled += miss;
+            empty += !any_pass;
+            viol += (miss && any_pass);
+        }
+    }
+    out[0] = viol; out[1] = culled; out[2] = empty; out[3] = (long long)tx * ty * n_bound;
+    return 0;
+}

@@ -107,6 +107,17 @@ class Emulator:
                                  ip(rgba), ip(pid), fp(tt))
         return rgba, pid, tt
 
+    def check_tile_cull(self, scene, w, h, camera=None, tile_w=256, tile_h=8):
+        """Walks raycast_cull_kernel's tile test: dict(violations, culled, empty, total) over (tile, primitive) pairs."""
+        from opencl_ray_tracer_b200 import capi
+        camera = camera or capi.REFERENCE_CAMERA
+        _, _, cam = capi.debug_pack(scene.sph_o, scene.sph_r, scene.cube_v, camera)
+        bnd = np.ascontiguousarray(capi.debug_pack_bounds(scene.sph_o, scene.sph_r, scene.cube_v, w, h, camera), np.float32)
+        fp = lambda a: np.ascontiguousarray(a, np.float32).ctypes.data_as(C.POINTER(C.c_float))
+        out = (C.c_longlong * 4)()
+        self.lib.emu_check_tile_cull(w, h, fp(cam), len(bnd), fp(bnd), tile_w, tile_h, out)
+        return {"violations": out[0], "culled": out[1], "empty": out[2], "total": out[3]}
+
     def check_bounds(self, scene, w, h, camera=None):
         """Walks the kernel's dense loop: returns dict(violations, bound_pass, footprint, total)."""
         from opencl_ray_tracer_b200 import capi

@@ -64,3 +64,39 @@ def test_tiny_huge_and_offscreen_primitives(emu, built_libs):
     from oracle.oracle import Scene
     sc2 = Scene(sc.sph_o, sph_r.astype(np.float32), sc.sph_c, cube_v, sc.cube_c)
     _check(emu, sc2, 256, 192)
+
+
+# ---- tile cull (RTB_OPT_TILE_CULL, rtb_bound_tile_misses) ---------------------------------------
+# raycast_cull_kernel drops a primitive for a whole 256 x 8 pixel tile when the tile test says "miss";
+# that is only allowed when the per-ray bound fails on every pixel of the tile.
+
+def _check_cull(emu, sc, w, h, cam=None, min_efficiency=None, **kw):
+    r = emu.check_tile_cull(sc, w, h, cam, **kw)
+    assert r["violations"] == 0, r
+    assert r["culled"] <= r["empty"] <= r["total"]
+    if min_efficiency is not None and r["empty"]:
+        assert r["culled"] / r["empty"] >= min_efficiency, r
+    return r
+
+
+def test_tile_cull_scene1_and_kats(emu):
+    _check_cull(emu, load_npz_scene(np.load(os.path.join(GOLDEN, "scene1.npz"))), 640, 480)
+    z = np.load(os.path.join(GOLDEN, "kats.npz"))
+    for name in kat_names():
+        _check_cull(emu, load_npz_scene(z, name + "/"), 64, 48)
+        _check_cull(emu, load_npz_scene(z, name + "/"), 64, 48, tile_w=16, tile_h=4)
+
+
+@pytest.mark.parametrize("w,h,ns,nc,seed", [(640, 480, 100, 100, 7), (333, 201, 40, 3, 11), (1920, 1080, 64, 64, 2)])
+def test_tile_cull_random_scenes(emu, built_libs, w, h, ns, nc, seed):
+    from opencl_ray_tracer_b200 import host_scene as hs
+    r = _check_cull(emu, to_oracle_scene(hs.random_scene(w, h, ns, nc, seed)), w, h, min_efficiency=0.9)
+    assert r["culled"] > 0.5 * r["total"]  # the cull actually culls
+
+
+@pytest.mark.parametrize("k", [1, 17, 45, 90, 119])
+def test_tile_cull_orbit_cameras(emu, built_libs, k):
+    from opencl_ray_tracer_b200 import host_scene as hs
+    sc = to_oracle_scene(hs.random_scene(480, 360, 48, 48, 9))
+    _check_cull(emu, sc, 480, 360, hs.orbit_camera(480, 360, k))
+    _check_cull(emu, sc, 480, 360, hs.orbit_camera(480, 360, k), tile_w=64, tile_h=8)

@@ -1,0 +1,89 @@
+"""RTB_OPT_TILE_CULL: raycast_cull_kernel drops, per CTA tile, the primitives whose conic bound no
+ray of the tile can pass (rtb_bound_row_misses, a statement about the values the dense per-ray test
+would compute).  It must therefore write exactly the bytes of the dense kernel -- all three
+outputs, every entry point, any camera -- while being much faster on SURVEY.md s8d's scenes."""
+import numpy as np
+import pytest
+
+from opencl_ray_tracer_b200 import capi, host_scene as hs
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def ctx(gpu_ctx):
+    yield gpu_ctx
+    gpu_ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
+
+
+def _both(ctx, w, h, cam, want=("rgba8", "prim_id", "rgba_i32")):
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
+    dense = ctx.render(w, h, cam, want=want)
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, 1)
+    assert ctx.get_option(capi.RTB_OPT_TILE_CULL) == 1
+    culled = ctx.render(w, h, cam, want=want)
+    return dense, culled
+
+
+@pytest.mark.parametrize("w,h,ns,nc,seed,k", [
+    (640, 480, 100, 100, 7, 0), (1920, 1080, 64, 64, 2, 0), (3840, 2160, 512, 512, 3, 0),
+    (3840, 2160, 512, 512, 3, 11), (3840, 2160, 512, 512, 3, 47), (333, 201, 40, 3, 11, 40),
+    (640, 360, 769, 257, 13, 0), (512, 256, 0, 64, 5, 1), (512, 256, 64, 0, 6, 119),
+    (128, 64, 400, 300, 17, 0),    # > 256 survivors per tile: the list is flushed mid-way
+    (250, 40, 900, 131, 19, 7),
+])
+def test_culled_frame_is_the_dense_frame(ctx, w, h, ns, nc, seed, k):
+    ctx.set_scene(*hs.random_scene(max(w, 64), max(h, 64), ns, nc, seed).as_tuple())
+    cam = capi.REFERENCE_CAMERA if k == 0 else hs.orbit_camera(w, h, k)
+    dense, culled = _both(ctx, w, h, cam)
+    for key in ("rgba8", "prim_id", "rgba_i32"):
+        assert np.array_equal(dense[key], culled[key]), key
+    assert (dense["prim_id"] >= 0).any()
+
+
+@pytest.mark.parametrize("which", [1, 2, 3])
+def test_reference_scenes(ctx, which):
+    ctx.set_scene(*hs.reference_scene(which).as_tuple())
+    dense, culled = _both(ctx, 640, 480, capi.REFERENCE_CAMERA)
+    for key in ("rgba8", "prim_id", "rgba_i32"):
+        assert np.array_equal(dense[key], culled[key]), key
+
+
+def test_bands_and_device_entry_points(ctx):
+    import torch
+    w, h = 1920, 1080
+    ctx.set_scene(*hs.random_scene(w, h, 64, 64, 2).as_tuple())
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
+    full = ctx.render(w, h, want=("rgba8",))["rgba8"]
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, 1)
+    for world in (2, 3):
+        for rank in range(world):
+            rows = ctx.band_local_rows(h, 16, rank, world)
+            buf = torch.zeros((rows, w, 4), dtype=torch.uint8, device="cuda")
+            ctx.render_bands_device(w, h, capi.REFERENCE_CAMERA, 16, rank, world, d_rgba8=buf.data_ptr())
+            got = buf.cpu().numpy()
+            sel = [y for y in range(h) if (y // 16) % world == rank]
+            assert np.array_equal(got, full[sel])
+    # whole host frame through the in-launch progress chunks
+    frame = np.zeros((h, w, 4), np.uint8)
+    ctx.render_bands_host(w, h, capi.REFERENCE_CAMERA, 16, 0, 1, frame)
+    assert np.array_equal(frame, full)
+
+
+def test_culled_kernel_is_much_faster_at_c3(ctx):
+    w, h = 3840, 2160
+    ctx.set_scene(*hs.random_scene(w, h, 512, 512, 3).as_tuple())
+    t = {}
+    for mode in (0, 1):
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, mode)
+        ctx.render(w, h, want=("rgba8",))
+        t[mode] = min(ctx.render(w, h, want=("rgba8",))["kernel_ms"] for _ in range(3))
+    assert t[1] < t[0] / 4, t
+
+
+def test_unknown_option_is_rejected(ctx):
+    with pytest.raises(capi.RtbError) as e:
+        ctx.set_option(99, 1)
+    assert e.value.status == 1
+    with pytest.raises(capi.RtbError):
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, 2)

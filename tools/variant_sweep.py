@@ -14,7 +14,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-WORKLOADS = {"c2": (1920, 1080, 64, 64, 2), "c3": (3840, 2160, 512, 512, 3), "c4": (7680, 4320, 2048, 2048, 4)}
+WORKLOADS = {"c1r": (640, 480, 100, 100, 7), "c2": (1920, 1080, 64, 64, 2), "c3": (3840, 2160, 512, 512, 3), "c4": (7680, 4320, 2048, 2048, 4)}
 
 
 def child(workload, flush, reps):
@@ -22,6 +22,8 @@ def child(workload, flush, reps):
     from opencl_ray_tracer_b200 import capi, host_scene as hs
     w, h, ns, nc, seed = WORKLOADS[workload]
     ctx = capi.Context(0)
+    if os.environ.get("RTB_SWEEP_TILE_CULL") == "1":
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, 1)
     ctx.set_scene(*hs.random_scene(w, h, ns, nc, seed).as_tuple())
     buf = torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda")
     fl = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") if flush else None
@@ -38,7 +40,7 @@ def child(workload, flush, reps):
         stream.synchronize()
     ms, n = ctx.kernel_ms_avg(reset=True)
     digest = hashlib.sha1(buf.cpu().numpy().tobytes()).hexdigest()[:16]
-    print(json.dumps({"variant": int(os.environ.get("RTB_GRID_VARIANT", "0")), "workload": workload,
+    print(json.dumps({"variant": "cull" if os.environ.get("RTB_SWEEP_TILE_CULL") == "1" else int(os.environ.get("RTB_GRID_VARIANT", "0")), "workload": workload,
                       "kernel_ms": round(ms, 4), "launches": n, "mrays_s": round(w * h / ms / 1e3, 1),
                       "flush": bool(flush), "frame_sha1": digest}))
     ctx.close()
@@ -58,11 +60,13 @@ def main():
     ref = None
     for v in a.variants.split(","):
         env = dict(os.environ, RTB_GRID_VARIANT=v)
+        if v == "cull":  # the tile-culled kernel (RTB_OPT_TILE_CULL) instead of a dense variant
+            env = dict(os.environ, RTB_GRID_VARIANT="0", RTB_SWEEP_TILE_CULL="1")
         cmd = [sys.executable, os.path.abspath(__file__), "--child", "--workload", a.workload, "--reps", str(a.reps)]
         if a.flush:
             cmd.append("--flush")
         out = subprocess.run(cmd, env=env, capture_output=True, text=True)
-        line = out.stdout.strip().splitlines()[-1] if out.stdout.strip() else json.dumps({"variant": int(v), "error": out.stderr[-300:]})
+        line = out.stdout.strip().splitlines()[-1] if out.stdout.strip() else json.dumps({"variant": v, "error": out.stderr[-300:]})
         try:
             j = json.loads(line)
             if ref is None and "frame_sha1" in j:
