@@ -264,23 +264,31 @@ __device__ __forceinline__ void dense_chunk_tab(const GridParams& p, const float
     }
 }
 
-// Nearest-hit shading (rtb_shade) + 128-bit coalesced stores of one thread's PX pixels.
+// Nearest-hit shading (rtb_shade) + 128-bit coalesced stores of one thread's PX pixels.  The colour
+// loads of four pixels are issued together (predicated, no branch around them), so a thread waits
+// for L1/L2 four times, not PX times.
 template <int PX>
 __device__ __forceinline__ void shade_and_store(const GridParams& p, PixelState<PX>& st, int x0, int lrow, int gy) {
     uint32_t rgba8[PX];
     int32_t rgba[PX][4];
     int ids[PX];
 #pragma unroll
-    for (int q = 0; q < PX; ++q) {
-        float cr = 0.f, cg = 0.f, cb = 0.f;
-        ids[q] = (st.best[q] == RTB_MISS_T) ? -1 : st.id(q);
-        if (ids[q] >= 0) {
-            const float4 col = (ids[q] < p.n_cubes) ? __ldg(p.cube_col + ids[q])
-                                                    : __ldg(p.sph_col + (ids[q] - p.n_cubes));
-            cr = col.x; cg = col.y; cb = col.z;
+    for (int q0 = 0; q0 < PX; q0 += 4) {
+        float4 col[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int q = q0 + i;
+            ids[q] = (st.best[q] == RTB_MISS_T) ? -1 : st.id(q);
+            const float4* src = (ids[q] < p.n_cubes) ? p.cube_col + ids[q] : p.sph_col + (ids[q] - p.n_cubes);
+            col[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ids[q] >= 0) col[i] = __ldg(src);
         }
-        rtb_shade(st.best[q], cr, cg, cb, rgba[q]);
-        rgba8[q] = rtb_pack_rgba8(rgba[q]);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int q = q0 + i;
+            rtb_shade(st.best[q], col[i].x, col[i].y, col[i].z, rgba[q]);
+            rgba8[q] = rtb_pack_rgba8(rgba[q]);
+        }
     }
     // packed band buffer (row = local row) or a whole frame -- e.g. rank 0's, mapped over NVLink
     const size_t row_off = (size_t)(p.out_global_rows ? gy : lrow) * p.width;
