@@ -99,10 +99,9 @@ struct PixelState {
 // of raycast_math.h that tests/emu replays).  Reached only from the rare "some ray of this warp
 // is inside the primitive's conic bound" branch, so its records come straight from global/L2.
 template <int PX>
-__device__ __forceinline__ void exact_update(const GridParams& p, int prim, float v, PixelState<PX>& st) {
+__device__ __forceinline__ void exact_update_rec(const GridParams& p, int prim, const float4 r0, const float4 r1,
+                                                 const float4 r2, float v, PixelState<PX>& st) {
     if (prim < p.n_cubes) {
-        const float4 r0 = __ldg(p.cube_rec + 3 * (size_t)prim + 0), r1 = __ldg(p.cube_rec + 3 * (size_t)prim + 1),
-                     r2 = __ldg(p.cube_rec + 3 * (size_t)prim + 2);
         const RtbSlab s0 = {r0.x, r0.y, r0.z, r0.w}, s1 = {r1.x, r1.y, r1.z, r1.w}, s2 = {r2.x, r2.y, r2.z, r2.w};
         const float b0 = rtb_slab_base(s0, v), b1 = rtb_slab_base(s1, v), b2 = rtb_slab_base(s2, v);
 #pragma unroll
@@ -116,8 +115,7 @@ __device__ __forceinline__ void exact_update(const GridParams& p, int prim, floa
             rtb_cube_update(tn, tf, prim, st.best[q], st.id(q));
         }
     } else if (prim < p.n_cubes + p.n_spheres) {
-        const float4 r = __ldg(p.sph_rec + (size_t)(prim - p.n_cubes));
-        const RtbSphere sp = {r.x, r.y, r.z, r.w};
+        const RtbSphere sp = {r0.x, r0.y, r0.z, r0.w};
         const float radv = rtb_sphere_radv(sp, v);
         const float wv = p.cam.tau_v * v;
 #pragma unroll
@@ -126,6 +124,18 @@ __device__ __forceinline__ void exact_update(const GridParams& p, int prim, floa
             const float wpix = fmaf(p.cam.tau_u, st.u(q), wv);
             rtb_sphere_update(sp, rad, wpix, prim, st.best[q], st.id(q));
         }
+    }
+}
+
+// The same update with the exact records fetched from global / L2 (cube: 3 slab records, sphere: 1).
+template <int PX>
+__device__ __forceinline__ void exact_update(const GridParams& p, int prim, float v, PixelState<PX>& st) {
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (prim < p.n_cubes) {
+        exact_update_rec<PX>(p, prim, __ldg(p.cube_rec + 3 * (size_t)prim + 0), __ldg(p.cube_rec + 3 * (size_t)prim + 1),
+                             __ldg(p.cube_rec + 3 * (size_t)prim + 2), v, st);
+    } else if (prim < p.n_cubes + p.n_spheres) {
+        exact_update_rec<PX>(p, prim, __ldg(p.sph_rec + (size_t)(prim - p.n_cubes)), z, z, v, st);
     }
 }
 
@@ -670,6 +680,273 @@ raycast_cull_kernel(const GridParams p) {
     signal_completion(p, kTileH);
 }
 
+
+// ---- binned variant (GridParams::tile_cull == 2) ------------------------------------------------
+// The per-CTA scan above makes every one of a frame's CTAs read and test the whole primitive list
+// (C3: 4050 CTAs x 1024 tile tests, 32 KB of records each, two batches deep).  Here the same test is
+// made once per (tile, primitive) by a separate small launch that is organised the other way round,
+// and the render CTAs only read the answer:
+//
+//   bin_tiles_kernel    warp = (one tile column, 32 vertically consecutive tiles, one word of 32
+//                       primitives).  Lane l first tests primitive l of the word against the UNION of
+//                       the 32 tiles' coordinate ranges (rtb_bound_tile_misses on a larger range is the
+//                       same statement about more rays), then every lane tests the few primitives that
+//                       survive (ballot; their records travel by shuffle) against its own tile and writes
+//                       one 32-bit word: bins[word][tile], bit j = "primitive 32*word + j may be seen by
+//                       a ray of this tile".  No atomics, no clearing pass, the same words on every run.
+//   raycast_binned_kernel   CTA = tile.  Reads its words (one per thread), expands the set bits IN
+//                       ASCENDING PRIMITIVE ORDER (CTA-wide prefix sum; the strict '<' of the nearest-hit
+//                       update breaks ties by index) into a list in shared memory, all threads fetch the
+//                       listed primitives' bound + exact records in ONE round of loads, and the warps run
+//                       the per-ray bound and the reference-exact update from shared memory.  A warp none
+//                       of whose rays passed any bound stores the miss colour without shading.
+//
+// The decision per (tile, primitive) is the one the per-CTA scan makes, so the frame is again the
+// dense kernel's, byte for byte.
+template <int TILE_W, int TILE_H>
+__device__ __forceinline__ void tile_uv_range(const GridParams& p, int tx, int ty, float& u_min, float& u_max,
+                                              float& v_min, float& v_max) {
+    // ranges over the very values the render kernels compute for the tile's rays: all TILE_H rows
+    // (u is monotone in x on a row, so a row's u values lie between those of its two end pixels)
+#pragma unroll
+    for (int r = 0; r < TILE_H; ++r) {
+        const int trow = ty * TILE_H + r;
+        const int tlb = trow / p.band_rows;
+        const float fy = (float)((tlb * p.band_world + p.band_rank) * p.band_rows + (trow - tlb * p.band_rows));
+        const float v = rtb_cam_v(p.cam, fy);
+        const float ua = rtb_cam_u(p.cam, (float)(tx * TILE_W), fy);
+        const float ub = rtb_cam_u(p.cam, (float)(tx * TILE_W + TILE_W - 1), fy);
+        if (r == 0) { u_min = fminf(ua, ub); u_max = fmaxf(ua, ub); v_min = v_max = v; }
+        else {
+            u_min = fminf(u_min, fminf(ua, ub));
+            u_max = fmaxf(u_max, fmaxf(ua, ub));
+            v_min = fminf(v_min, v);
+            v_max = fmaxf(v_max, v);
+        }
+    }
+}
+
+constexpr int kBinWarps = 8;  // warps (= words) per CTA of the binning launch
+
+template <int TILE_W, int TILE_H>
+__global__ void __launch_bounds__(32 * kBinWarps) bin_tiles_kernel(const GridParams p, int tiles_x, int tiles_y) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int sy_count = (tiles_y + 31) / 32;
+    const int tx = blockIdx.x / sy_count, sy = blockIdx.x - tx * sy_count;
+    const int word = blockIdx.y * kBinWarps + warp;
+    if (word >= p.bin_words) return;
+    const int ty_raw = sy * 32 + lane;
+    const int ty = min(ty_raw, tiles_y - 1);  // lanes past the last tile row repeat it (their word is not stored)
+    float u_min, u_max, v_min, v_max;
+    tile_uv_range<TILE_W, TILE_H>(p, tx, ty, u_min, u_max, v_min, v_max);
+    float su_min = u_min, su_max = u_max, sv_min = v_min, sv_max = v_max;  // union over the warp's tiles
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        su_min = fminf(su_min, __shfl_xor_sync(0xFFFFFFFFu, su_min, d));
+        su_max = fmaxf(su_max, __shfl_xor_sync(0xFFFFFFFFu, su_max, d));
+        sv_min = fminf(sv_min, __shfl_xor_sync(0xFFFFFFFFu, sv_min, d));
+        sv_max = fmaxf(sv_max, __shfl_xor_sync(0xFFFFFFFFu, sv_max, d));
+    }
+    const int prim = word * 32 + lane;
+    RtbBound b = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    bool keep = false;
+    if (prim < p.n_bound) {
+        const float4 r0 = __ldg(p.bound_rec + 2 * (size_t)prim);
+        b.sA = r0.x; b.k1 = r0.y; b.k0 = r0.z; b.e = r0.w;
+        b.cv = __ldg(reinterpret_cast<const float*>(p.bound_rec + 2 * (size_t)prim + 1));
+        keep = !rtb_bound_tile_misses(b, su_min, su_max, sv_min, sv_max);
+    }
+    uint32_t cand = __ballot_sync(0xFFFFFFFFu, keep);
+    uint32_t out = 0u;
+    while (cand) {
+        const int j = __ffs(cand) - 1;
+        cand &= cand - 1u;
+        RtbBound c = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        c.sA = __shfl_sync(0xFFFFFFFFu, b.sA, j);
+        c.k1 = __shfl_sync(0xFFFFFFFFu, b.k1, j);
+        c.k0 = __shfl_sync(0xFFFFFFFFu, b.k0, j);
+        c.e = __shfl_sync(0xFFFFFFFFu, b.e, j);
+        c.cv = __shfl_sync(0xFFFFFFFFu, b.cv, j);
+        if (!rtb_bound_tile_misses(c, u_min, u_max, v_min, v_max)) out |= 1u << j;
+    }
+    if (ty_raw < tiles_y) p.bins[(size_t)word * ((size_t)tiles_x * tiles_y) + (size_t)tx * tiles_y + ty_raw] = out;
+}
+
+// Shading + stores four pixels at a time (few live registers); `hit` false = every pixel of the
+// thread is a miss and `st` was never touched.
+template <int PX>
+__device__ __forceinline__ void shade_store_groups(const GridParams& p, const PixelState<PX>& st, bool hit, int x0,
+                                                   int lrow, int gy) {
+    const size_t row_off = (size_t)(p.out_global_rows ? gy : lrow) * p.width;
+    const bool full = p.vec_ok && (x0 + PX <= p.width);
+    int32_t miss[4];
+    rtb_shade(RTB_MISS_T, 0.f, 0.f, 0.f, miss);
+    const uint32_t miss8 = rtb_pack_rgba8(miss);
+#pragma unroll
+    for (int q0 = 0; q0 < PX; q0 += 4) {
+        uint32_t rgba8[4];
+        int32_t rgba[4][4];
+        int ids[4];
+        bool any = false;
+        if (hit) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) any = any || (st.best[q0 + i] != RTB_MISS_T);
+        }
+        if (any) {
+            float4 col[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int q = q0 + i;
+                ids[i] = (st.best[q] == RTB_MISS_T) ? -1 : st.id(q);
+                const float4* src = (ids[i] < p.n_cubes) ? p.cube_col + ids[i] : p.sph_col + (ids[i] - p.n_cubes);
+                col[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (ids[i] >= 0) col[i] = __ldg(src);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                rtb_shade(st.best[q0 + i], col[i].x, col[i].y, col[i].z, rgba[i]);
+                rgba8[i] = rtb_pack_rgba8(rgba[i]);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                ids[i] = -1;
+                rgba8[i] = miss8;
+                rgba[i][0] = miss[0]; rgba[i][1] = miss[1]; rgba[i][2] = miss[2]; rgba[i][3] = miss[3];
+            }
+        }
+        if (full) {
+            if (p.out_rgba8)
+                *reinterpret_cast<uint4*>(p.out_rgba8 + row_off + x0 + q0) = make_uint4(rgba8[0], rgba8[1], rgba8[2], rgba8[3]);
+            if (p.out_id) *reinterpret_cast<int4*>(p.out_id + row_off + x0 + q0) = make_int4(ids[0], ids[1], ids[2], ids[3]);
+            if (p.out_i32) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    p.out_i32[row_off + x0 + q0 + i] = make_int4(rgba[i][0], rgba[i][1], rgba[i][2], rgba[i][3]);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int x = x0 + q0 + i;
+                if (x < p.width) {
+                    if (p.out_rgba8) p.out_rgba8[row_off + x] = rgba8[i];
+                    if (p.out_id) p.out_id[row_off + x] = ids[i];
+                    if (p.out_i32) {
+                        int32_t* o = reinterpret_cast<int32_t*>(p.out_i32) + 4 * (row_off + x);
+                        o[0] = rgba[i][0]; o[1] = rgba[i][1]; o[2] = rgba[i][2]; o[3] = rgba[i][3];
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <int PX, int WARPS_X, int WARPS_Y, int MIN_CTAS>
+__global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y, MIN_CTAS)
+raycast_binned_kernel(const GridParams p) {
+    constexpr int kWarps = WARPS_X * WARPS_Y;
+    constexpr int kThreads = 32 * kWarps;
+    constexpr int kTileW = WARPS_X * 8 * PX;
+    constexpr int kTileH = WARPS_Y * 4;
+    constexpr int kCap = 64;  // listed primitives per pass over the rays
+    __shared__ __align__(16) float4 s_rec[kCap][5];  // bound record (2) + exact records (cube 3, sphere 1)
+    __shared__ int s_prim[kCap];
+    __shared__ int s_wsum[kWarps];
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int wx = warp % WARPS_X, wy = warp / WARPS_X;
+    const int lx = lane & 7, ly = lane >> 3;
+    const int x0 = blockIdx.x * kTileW + (wx * 8 + lx) * PX;
+    const int lrow = blockIdx.y * kTileH + wy * 4 + ly;
+    const int lb = lrow / p.band_rows;
+    const int gy = (lb * p.band_world + p.band_rank) * p.band_rows + (lrow - lb * p.band_rows);
+    const size_t n_tiles = (size_t)gridDim.x * gridDim.y;
+    const size_t tile = (size_t)blockIdx.x * gridDim.y + blockIdx.y;
+    const int n_words = p.bin_words;
+
+    extern __shared__ int dyn_ids[];
+    PixelState<PX> st;
+    st.sid = dyn_ids + tid;
+    st.sid_stride = kThreads;
+    const float fy = (float)gy;
+    const float v = rtb_cam_v(p.cam, fy);
+    bool st_ready = false;  // the pixel state is set up when the tile's first primitive turns up
+    bool warp_hit = false;  // some ray of this warp passed some bound
+
+    for (int base = 0; base < n_words; base += kThreads) {
+        const int w = base + tid;
+        const uint32_t m = (w < n_words) ? __ldg(p.bins + (size_t)w * n_tiles + tile) : 0u;
+        if (!__syncthreads_or(m != 0u)) continue;
+        // CTA-wide exclusive prefix of the popcounts: list position of each thread's first primitive
+        const int c = __popc(m);
+        int incl = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        if (lane == 31) s_wsum[warp] = incl;
+        __syncthreads();
+        int off = incl - c, total = 0;
+#pragma unroll
+        for (int k = 0; k < kWarps; ++k) {
+            const int s = s_wsum[k];
+            if (k < warp) off += s;
+            total += s;
+        }
+        if (!st_ready) {
+#pragma unroll
+            for (int q = 0; q < PX; q += 2) {
+                st.u2[q >> 1] = pack2(rtb_cam_u(p.cam, (float)(x0 + q), fy), rtb_cam_u(p.cam, (float)(x0 + q + 1), fy));
+                st.best[q] = st.best[q + 1] = RTB_MISS_T;
+                st.id(q) = -1;
+                st.id(q + 1) = -1;
+            }
+            st_ready = true;
+        }
+        for (int pass = 0; pass < total; pass += kCap) {
+            {
+                uint32_t mm = m;
+                int pos = off - pass;
+                while (mm != 0u && pos < kCap) {
+                    const int j = __ffs(mm) - 1;
+                    mm &= mm - 1u;
+                    if (pos >= 0) s_prim[pos] = w * 32 + j;
+                    ++pos;
+                }
+            }
+            __syncthreads();
+            const int n = min(kCap, total - pass);
+            for (int i = tid; i < n * 5; i += kThreads) {
+                const int e = i / 5, part = i - e * 5;
+                const int prim = s_prim[e];
+                float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (part < 2) r = __ldg(p.bound_rec + 2 * (size_t)prim + part);
+                else if (prim < p.n_cubes) r = __ldg(p.cube_rec + 3 * (size_t)prim + (part - 2));
+                else if (part == 2 && prim < p.n_cubes + p.n_spheres) r = __ldg(p.sph_rec + (size_t)(prim - p.n_cubes));
+                s_rec[e][part] = r;
+            }
+            __syncthreads();
+#pragma unroll 1
+            for (int e = 0; e < n; ++e) {
+                const float4 a = s_rec[e][0];
+                const RtbBound s = {a.x, a.y, a.z, a.w, s_rec[e][1].x, 0.f, 0.f, 0.f};
+                const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), rtb_bound_row_c(s, v), 0.f);
+                const uint32_t acc = bound_test<PX>(t, st);
+                if (__any_sync(0xFFFFFFFFu, (acc & RTB_BOUND_FAIL_BIT) == 0u)) {
+                    warp_hit = true;
+                    exact_update_rec<PX>(p, s_prim[e], s_rec[e][2], s_rec[e][3], s_rec[e][4], v, st);
+                }
+            }
+            __syncthreads();  // every warp is done with the list before it is refilled
+        }
+    }
+
+    if (lrow < p.local_rows && gy < p.height && x0 < p.width) shade_store_groups<PX>(p, st, warp_hit, x0, lrow, gy);
+    signal_completion(p, kTileH);
+}
+
 }  // namespace
 
 // ---- explicit-origin kernel (rtb_render_rays) --------------------------------------------------
@@ -812,7 +1089,35 @@ cudaError_t launch_cull_instance(const GridParams& p, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
+// Tile geometry of the binned render (tile_cull == 2): the bins are laid out for exactly this tiling.
+constexpr int kBinPX = 16, kBinWX = 2, kBinWY = 2;
+constexpr int kBinTileW = kBinWX * 8 * kBinPX, kBinTileH = kBinWY * 4;
+
+size_t grid_bin_words(int width, int local_rows, int n_bound) {
+    const size_t tiles = (size_t)((width + kBinTileW - 1) / kBinTileW) * (size_t)((local_rows + kBinTileH - 1) / kBinTileH);
+    return tiles * (size_t)((n_bound + 31) / 32);
+}
+
+static cudaError_t launch_binned(const GridParams& p, cudaStream_t stream) {
+    constexpr int kThreads = 32 * kBinWX * kBinWY;
+    constexpr int kDyn = kBinPX * kThreads * (int)sizeof(int);
+    constexpr int kMinCtas = 6;
+    const GridLaunchShape s = shape_of<kBinPX, kBinWX, kBinWY>(p.width, p.local_rows);
+    if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
+    if (p.bin_words > 0) {
+        if (p.bins == nullptr) return cudaErrorInvalidValue;
+        const int tiles_x = (int)s.grid.x, tiles_y = (int)s.grid.y;
+        dim3 bgrid((unsigned)(tiles_x * ((tiles_y + 31) / 32)), (unsigned)((p.bin_words + kBinWarps - 1) / kBinWarps));
+        bin_tiles_kernel<kBinTileW, kBinTileH><<<bgrid, 32 * kBinWarps, 0, stream>>>(p, tiles_x, tiles_y);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    raycast_binned_kernel<kBinPX, kBinWX, kBinWY, kMinCtas><<<s.grid, dim3(kThreads), kDyn, stream>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) {
+    if (p.tile_cull == 2) return launch_binned(p, stream);
     if (p.tile_cull) return launch_cull_instance<16, 2, 2, 4>(p, stream);
     static const int variant = [] {
         const char* e = std::getenv("RTB_GRID_VARIANT");

@@ -47,6 +47,9 @@ struct GridParams {
     unsigned int* done_signal;
     int fence_system;                       // 1: system-scope fences also for the progress flags (debug knob)
     int tile_cull;                          // 1: raycast_cull_kernel (primitives culled per CTA tile; same pixels)
+                                            // 2: bin_tiles_kernel + raycast_binned_kernel (the cull made once per frame)
+    uint32_t* bins;                         // tile_cull == 2: [bin_words][tiles] words, grid_bin_words() of them
+    int bin_words;                          // ceil(n_bound / 32)
     RtbCam cam;
 };
 
@@ -81,6 +84,8 @@ cudaError_t launch_assemble(const AssembleParams& p, cudaStream_t stream);
 struct GridLaunchShape { int px, wx, wy, split; dim3 grid, block; size_t smem; };
 
 GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count);
+// 32-bit words of GridParams::bins a launch of this size needs (tile_cull == 2).
+size_t grid_bin_words(int width, int local_rows, int n_bound);
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream);
 cudaError_t launch_rays(const RaysParams& p, cudaStream_t stream);
 cudaError_t launch_signal_only(unsigned int* d_signal, cudaStream_t stream);  // a rank with no rows still signals

@@ -79,6 +79,8 @@ struct rtb_ctx {
     int kernel_ms_n = 0;
     unsigned long long launches = 0;
     int tile_cull = 0;  // RTB_OPT_TILE_CULL
+    void* d_bins = nullptr;        // tile_cull == 2: per-tile primitive bit words of the launch in flight, grow-only
+    size_t d_bins_cap = 0;
 };
 
 namespace {
@@ -240,6 +242,7 @@ void rtb_shutdown(rtb_ctx* ctx) {
     cudaFree(ctx->d_boxes);
     cudaFree(ctx->d_bad);
     cudaFree(ctx->d_progress);
+    cudaFree(ctx->d_bins);
     if (ctx->h_bad) cudaFreeHost(ctx->h_bad);
     if (ctx->h_rec) cudaFreeHost(ctx->h_rec);
     for (int i = 0; i < 3; ++i) cudaFree(ctx->d_out[i]);
@@ -411,6 +414,16 @@ int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width
     static const int fence_sys = [] { const char* e = std::getenv("RTB_PROGRESS_FENCE_SYSTEM"); return (e && e[0] == '1') ? 1 : 0; }();
     p.fence_system = fence_sys;
     p.tile_cull = ctx->tile_cull;
+    p.bins = nullptr;
+    p.bin_words = 0;
+    if (ctx->tile_cull == 2) {
+        const int n_bound = bound_count(ctx);
+        const size_t words = grid_bin_words(width, local_rows, n_bound);
+        const int rc = ensure_device(ctx, &ctx->d_bins, &ctx->d_bins_cap, (words ? words : 1) * sizeof(uint32_t));
+        if (rc != RTB_OK) return rc;
+        p.bins = static_cast<uint32_t*>(ctx->d_bins);
+        p.bin_words = (n_bound + 31) / 32;
+    }
     p.done_counter = ctx->d_progress + 2 * kMaxProgressChunks;
     p.done_signal = static_cast<unsigned int*>(done_signal);
     p.progress = progress_chunks > 0 ? ctx->d_progress : nullptr;
@@ -920,7 +933,7 @@ int rtb_set_option(rtb_ctx* ctx, int option, int value) {
     if (!ctx) return RTB_ERR_INVALID_ARG;
     switch (option) {
         case RTB_OPT_TILE_CULL:
-            if (value != 0 && value != 1) return fail(ctx, RTB_ERR_INVALID_ARG, "RTB_OPT_TILE_CULL takes 0 or 1");
+            if (value < 0 || value > 2) return fail(ctx, RTB_ERR_INVALID_ARG, "RTB_OPT_TILE_CULL takes 0, 1 or 2");
             ctx->tile_cull = value;
             return RTB_OK;
         default:

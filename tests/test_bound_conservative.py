@@ -100,3 +100,14 @@ def test_tile_cull_orbit_cameras(emu, built_libs, k):
     sc = to_oracle_scene(hs.random_scene(480, 360, 48, 48, 9))
     _check_cull(emu, sc, 480, 360, hs.orbit_camera(480, 360, k))
     _check_cull(emu, sc, 480, 360, hs.orbit_camera(480, 360, k), tile_w=64, tile_h=8)
+
+
+# The binned mode (RTB_OPT_TILE_CULL = 2, bin_tiles_kernel) asks the same question first for the union of
+# 32 vertically consecutive tiles (a 256 x 256 pixel block), then per tile: the same function on a larger range.
+@pytest.mark.parametrize("w,h,ns,nc,seed,k", [(640, 480, 100, 100, 7, 0), (1920, 1080, 64, 64, 2, 0), (480, 360, 48, 48, 9, 33)])
+def test_tile_cull_super_tiles(emu, built_libs, w, h, ns, nc, seed, k):
+    from opencl_ray_tracer_b200 import host_scene as hs
+    sc = to_oracle_scene(hs.random_scene(w, h, ns, nc, seed))
+    cam = None if k == 0 else hs.orbit_camera(w, h, k)
+    r = _check_cull(emu, sc, w, h, cam, tile_w=256, tile_h=256)
+    assert r["culled"] > 0  # the coarse level culls as well

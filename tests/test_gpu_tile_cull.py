@@ -1,7 +1,9 @@
-"""RTB_OPT_TILE_CULL: raycast_cull_kernel drops, per CTA tile, the primitives whose conic bound no
-ray of the tile can pass (rtb_bound_row_misses, a statement about the values the dense per-ray test
-would compute).  It must therefore write exactly the bytes of the dense kernel -- all three
-outputs, every entry point, any camera -- while being much faster on SURVEY.md s8d's scenes."""
+"""RTB_OPT_TILE_CULL: raycast_cull_kernel (1) drops, per CTA tile, the primitives whose conic bound no
+ray of the tile can pass (rtb_bound_tile_misses, a statement about the values the dense per-ray test
+would compute); the binned mode (2) makes the same decision once per frame in bin_tiles_kernel and
+raycast_binned_kernel renders from the per-tile bit words.  Both must therefore write exactly the bytes
+of the dense kernel -- all three outputs, every entry point, any camera -- while being much faster on
+SURVEY.md s8d's scenes."""
 import numpy as np
 import pytest
 
@@ -16,11 +18,14 @@ def ctx(gpu_ctx):
     gpu_ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
 
 
-def _both(ctx, w, h, cam, want=("rgba8", "prim_id", "rgba_i32")):
+MODES = [1, 2]
+
+
+def _both(ctx, w, h, cam, mode, want=("rgba8", "prim_id", "rgba_i32")):
     ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
     dense = ctx.render(w, h, cam, want=want)
-    ctx.set_option(capi.RTB_OPT_TILE_CULL, 1)
-    assert ctx.get_option(capi.RTB_OPT_TILE_CULL) == 1
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, mode)
+    assert ctx.get_option(capi.RTB_OPT_TILE_CULL) == mode
     culled = ctx.render(w, h, cam, want=want)
     return dense, culled
 
@@ -31,31 +36,49 @@ def _both(ctx, w, h, cam, want=("rgba8", "prim_id", "rgba_i32")):
     (640, 360, 769, 257, 13, 0), (512, 256, 0, 64, 5, 1), (512, 256, 64, 0, 6, 119),
     (128, 64, 400, 300, 17, 0),    # > 256 survivors per tile: the list is flushed mid-way
     (250, 40, 900, 131, 19, 7),
+    (96, 40, 3000, 2000, 23, 0),   # 5000 primitives: more words than a CTA has threads, many passes
+    (1000, 700, 1, 0, 29, 0), (64, 48, 0, 1, 31, 0),
 ])
-def test_culled_frame_is_the_dense_frame(ctx, w, h, ns, nc, seed, k):
+@pytest.mark.parametrize("mode", MODES)
+def test_culled_frame_is_the_dense_frame(ctx, mode, w, h, ns, nc, seed, k):
     ctx.set_scene(*hs.random_scene(max(w, 64), max(h, 64), ns, nc, seed).as_tuple())
     cam = capi.REFERENCE_CAMERA if k == 0 else hs.orbit_camera(w, h, k)
-    dense, culled = _both(ctx, w, h, cam)
+    dense, culled = _both(ctx, w, h, cam, mode)
     for key in ("rgba8", "prim_id", "rgba_i32"):
         assert np.array_equal(dense[key], culled[key]), key
     assert (dense["prim_id"] >= 0).any()
 
 
+@pytest.mark.parametrize("mode", MODES)
+def test_empty_scene_and_single_outputs(ctx, mode):
+    ctx.set_scene(*hs.random_scene(640, 480, 0, 0, 1).as_tuple())
+    dense, culled = _both(ctx, 203, 77, capi.REFERENCE_CAMERA, mode)
+    for key in ("rgba8", "prim_id", "rgba_i32"):
+        assert np.array_equal(dense[key], culled[key]), key
+    assert (culled["prim_id"] == -1).all()
+    ctx.set_scene(*hs.random_scene(640, 480, 30, 30, 3).as_tuple())
+    for want in (("rgba8",), ("prim_id",), ("rgba_i32",)):
+        dense, culled = _both(ctx, 640, 480, capi.REFERENCE_CAMERA, mode, want=want)
+        assert np.array_equal(dense[want[0]], culled[want[0]])
+
+
+@pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("which", [1, 2, 3])
-def test_reference_scenes(ctx, which):
+def test_reference_scenes(ctx, which, mode):
     ctx.set_scene(*hs.reference_scene(which).as_tuple())
-    dense, culled = _both(ctx, 640, 480, capi.REFERENCE_CAMERA)
+    dense, culled = _both(ctx, 640, 480, capi.REFERENCE_CAMERA, mode)
     for key in ("rgba8", "prim_id", "rgba_i32"):
         assert np.array_equal(dense[key], culled[key]), key
 
 
-def test_bands_and_device_entry_points(ctx):
+@pytest.mark.parametrize("mode", MODES)
+def test_bands_and_device_entry_points(ctx, mode):
     import torch
     w, h = 1920, 1080
     ctx.set_scene(*hs.random_scene(w, h, 64, 64, 2).as_tuple())
     ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
     full = ctx.render(w, h, want=("rgba8",))["rgba8"]
-    ctx.set_option(capi.RTB_OPT_TILE_CULL, 1)
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, mode)
     for world in (2, 3):
         for rank in range(world):
             rows = ctx.band_local_rows(h, 16, rank, world)
@@ -74,11 +97,11 @@ def test_culled_kernel_is_much_faster_at_c3(ctx):
     w, h = 3840, 2160
     ctx.set_scene(*hs.random_scene(w, h, 512, 512, 3).as_tuple())
     t = {}
-    for mode in (0, 1):
+    for mode in (0, 1, 2):
         ctx.set_option(capi.RTB_OPT_TILE_CULL, mode)
         ctx.render(w, h, want=("rgba8",))
         t[mode] = min(ctx.render(w, h, want=("rgba8",))["kernel_ms"] for _ in range(3))
-    assert t[1] < t[0] / 4, t
+    assert t[1] < t[0] / 4 and t[2] < t[0] / 4, t
 
 
 def test_unknown_option_is_rejected(ctx):
@@ -86,4 +109,4 @@ def test_unknown_option_is_rejected(ctx):
         ctx.set_option(99, 1)
     assert e.value.status == 1
     with pytest.raises(capi.RtbError):
-        ctx.set_option(capi.RTB_OPT_TILE_CULL, 2)
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, 3)

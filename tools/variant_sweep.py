@@ -22,8 +22,9 @@ def child(workload, flush, reps):
     from opencl_ray_tracer_b200 import capi, host_scene as hs
     w, h, ns, nc, seed = WORKLOADS[workload]
     ctx = capi.Context(0)
-    if os.environ.get("RTB_SWEEP_TILE_CULL") == "1":
-        ctx.set_option(capi.RTB_OPT_TILE_CULL, 1)
+    cull = int(os.environ.get("RTB_SWEEP_TILE_CULL", "0"))
+    if cull:
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, cull)
     ctx.set_scene(*hs.random_scene(w, h, ns, nc, seed).as_tuple())
     buf = torch.zeros((h, w, 4), dtype=torch.uint8, device="cuda")
     fl = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") if flush else None
@@ -40,7 +41,7 @@ def child(workload, flush, reps):
         stream.synchronize()
     ms, n = ctx.kernel_ms_avg(reset=True)
     digest = hashlib.sha1(buf.cpu().numpy().tobytes()).hexdigest()[:16]
-    print(json.dumps({"variant": "cull" if os.environ.get("RTB_SWEEP_TILE_CULL") == "1" else int(os.environ.get("RTB_GRID_VARIANT", "0")), "workload": workload,
+    print(json.dumps({"variant": {1: "cull", 2: "binned"}[cull] if cull else int(os.environ.get("RTB_GRID_VARIANT", "0")), "workload": workload,
                       "kernel_ms": round(ms, 4), "launches": n, "mrays_s": round(w * h / ms / 1e3, 1),
                       "flush": bool(flush), "frame_sha1": digest}))
     ctx.close()
@@ -60,8 +61,8 @@ def main():
     ref = None
     for v in a.variants.split(","):
         env = dict(os.environ, RTB_GRID_VARIANT=v)
-        if v == "cull":  # the tile-culled kernel (RTB_OPT_TILE_CULL) instead of a dense variant
-            env = dict(os.environ, RTB_GRID_VARIANT="0", RTB_SWEEP_TILE_CULL="1")
+        if v in ("cull", "binned"):  # the tile-culled kernels (RTB_OPT_TILE_CULL = 1 | 2) instead of a dense variant
+            env = dict(os.environ, RTB_GRID_VARIANT="0", RTB_SWEEP_TILE_CULL="1" if v == "cull" else "2")
         cmd = [sys.executable, os.path.abspath(__file__), "--child", "--workload", a.workload, "--reps", str(a.reps)]
         if a.flush:
             cmd.append("--flush")
