@@ -706,24 +706,13 @@ raycast_cull_kernel(const GridParams p) {
 template <int TILE_W, int TILE_H>
 __device__ __forceinline__ void tile_uv_range(const GridParams& p, int tx, int ty, float& u_min, float& u_max,
                                               float& v_min, float& v_max) {
-    // ranges over the very values the render kernels compute for the tile's rays: all TILE_H rows
-    // (u is monotone in x on a row, so a row's u values lie between those of its two end pixels)
-#pragma unroll
-    for (int r = 0; r < TILE_H; ++r) {
-        const int trow = ty * TILE_H + r;
-        const int tlb = trow / p.band_rows;
-        const float fy = (float)((tlb * p.band_world + p.band_rank) * p.band_rows + (trow - tlb * p.band_rows));
-        const float v = rtb_cam_v(p.cam, fy);
-        const float ua = rtb_cam_u(p.cam, (float)(tx * TILE_W), fy);
-        const float ub = rtb_cam_u(p.cam, (float)(tx * TILE_W + TILE_W - 1), fy);
-        if (r == 0) { u_min = fminf(ua, ub); u_max = fmaxf(ua, ub); v_min = v_max = v; }
-        else {
-            u_min = fminf(u_min, fminf(ua, ub));
-            u_max = fmaxf(u_max, fmaxf(ua, ub));
-            v_min = fminf(v_min, v);
-            v_max = fmaxf(v_max, v);
-        }
-    }
+    // ranges over the very values the render kernel computes for the tile's rays (rtb_tile_uv_range:
+    // the extremes sit on the corners); frame rows of the tile's first and last local row
+    const int ra = ty * TILE_H, rb = ra + TILE_H - 1;
+    const int ba = ra / p.band_rows, bb = rb / p.band_rows;
+    const float ya = (float)((ba * p.band_world + p.band_rank) * p.band_rows + (ra - ba * p.band_rows));
+    const float yb = (float)((bb * p.band_world + p.band_rank) * p.band_rows + (rb - bb * p.band_rows));
+    rtb_tile_uv_range(p.cam, (float)(tx * TILE_W), (float)(tx * TILE_W + TILE_W - 1), ya, yb, &u_min, &u_max, &v_min, &v_max);
 }
 
 constexpr int kBinWarps = 8;  // warps (= words) per CTA of the binning launch
@@ -772,93 +761,99 @@ __global__ void __launch_bounds__(32 * kBinWarps) bin_tiles_kernel(const GridPar
     if (ty_raw < tiles_y) p.bins[(size_t)word * ((size_t)tiles_x * tiles_y) + (size_t)tx * tiles_y + ty_raw] = out;
 }
 
-// Shading + stores four pixels at a time (few live registers); `hit` false = every pixel of the
-// thread is a miss and `st` was never touched.
+// Shading + stores four pixels at a time, as a ROLLED loop (the nearest-hit registers are rotated down by
+// four after each group so that the body always reads best[0..3]: the epilogue is 4x smaller, and this
+// kernel's straight-line code has to stay inside the 32 KB instruction cache).  `hit` false = every pixel of
+// the warp is a miss and `st` was never touched: constants only.
 template <int PX>
-__device__ __forceinline__ void shade_store_groups(const GridParams& p, const PixelState<PX>& st, bool hit, int x0,
-                                                   int lrow, int gy) {
-    const size_t row_off = (size_t)(p.out_global_rows ? gy : lrow) * p.width;
-    const bool full = p.vec_ok && (x0 + PX <= p.width);
-    int32_t miss[4];
-    rtb_shade(RTB_MISS_T, 0.f, 0.f, 0.f, miss);
-    const uint32_t miss8 = rtb_pack_rgba8(miss);
+__device__ __forceinline__ void store_group(const GridParams& p, size_t px_off, int x, bool full, const uint32_t rgba8[4],
+                                            const int32_t rgba[4][4], const int ids[4]) {
+    if (full) {
+        if (p.out_rgba8) *reinterpret_cast<uint4*>(p.out_rgba8 + px_off) = make_uint4(rgba8[0], rgba8[1], rgba8[2], rgba8[3]);
+        if (p.out_id) *reinterpret_cast<int4*>(p.out_id + px_off) = make_int4(ids[0], ids[1], ids[2], ids[3]);
+        if (p.out_i32) {
 #pragma unroll
-    for (int q0 = 0; q0 < PX; q0 += 4) {
-        uint32_t rgba8[4];
-        int32_t rgba[4][4];
-        int ids[4];
-        bool any = false;
-        if (hit) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) any = any || (st.best[q0 + i] != RTB_MISS_T);
+            for (int i = 0; i < 4; ++i) p.out_i32[px_off + i] = make_int4(rgba[i][0], rgba[i][1], rgba[i][2], rgba[i][3]);
         }
-        if (any) {
-            float4 col[4];
+    } else {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int q = q0 + i;
-                ids[i] = (st.best[q] == RTB_MISS_T) ? -1 : st.id(q);
-                const float4* src = (ids[i] < p.n_cubes) ? p.cube_col + ids[i] : p.sph_col + (ids[i] - p.n_cubes);
-                col[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (ids[i] >= 0) col[i] = __ldg(src);
-            }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                rtb_shade(st.best[q0 + i], col[i].x, col[i].y, col[i].z, rgba[i]);
-                rgba8[i] = rtb_pack_rgba8(rgba[i]);
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                ids[i] = -1;
-                rgba8[i] = miss8;
-                rgba[i][0] = miss[0]; rgba[i][1] = miss[1]; rgba[i][2] = miss[2]; rgba[i][3] = miss[3];
-            }
-        }
-        if (full) {
-            if (p.out_rgba8)
-                *reinterpret_cast<uint4*>(p.out_rgba8 + row_off + x0 + q0) = make_uint4(rgba8[0], rgba8[1], rgba8[2], rgba8[3]);
-            if (p.out_id) *reinterpret_cast<int4*>(p.out_id + row_off + x0 + q0) = make_int4(ids[0], ids[1], ids[2], ids[3]);
-            if (p.out_i32) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    p.out_i32[row_off + x0 + q0 + i] = make_int4(rgba[i][0], rgba[i][1], rgba[i][2], rgba[i][3]);
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int x = x0 + q0 + i;
-                if (x < p.width) {
-                    if (p.out_rgba8) p.out_rgba8[row_off + x] = rgba8[i];
-                    if (p.out_id) p.out_id[row_off + x] = ids[i];
-                    if (p.out_i32) {
-                        int32_t* o = reinterpret_cast<int32_t*>(p.out_i32) + 4 * (row_off + x);
-                        o[0] = rgba[i][0]; o[1] = rgba[i][1]; o[2] = rgba[i][2]; o[3] = rgba[i][3];
-                    }
+        for (int i = 0; i < 4; ++i) {
+            if (x + i < p.width) {
+                if (p.out_rgba8) p.out_rgba8[px_off + i] = rgba8[i];
+                if (p.out_id) p.out_id[px_off + i] = ids[i];
+                if (p.out_i32) {
+                    int32_t* o = reinterpret_cast<int32_t*>(p.out_i32) + 4 * (px_off + i);
+                    o[0] = rgba[i][0]; o[1] = rgba[i][1]; o[2] = rgba[i][2]; o[3] = rgba[i][3];
                 }
             }
         }
     }
 }
 
-template <int PX, int WARPS_X, int WARPS_Y, int MIN_CTAS>
+template <int PX>
+__device__ __forceinline__ void shade_store_groups(const GridParams& p, PixelState<PX>& st, bool hit, int x0, int lrow,
+                                                   int gy) {
+    const size_t row_off = (size_t)(p.out_global_rows ? gy : lrow) * p.width + x0;
+    const bool full = p.vec_ok && (x0 + PX <= p.width);
+    int32_t miss[4];
+    rtb_shade(RTB_MISS_T, 0.f, 0.f, 0.f, miss);
+    const uint32_t miss8 = rtb_pack_rgba8(miss);
+    if (!hit) {
+        const uint32_t rgba8[4] = {miss8, miss8, miss8, miss8};
+        const int ids[4] = {-1, -1, -1, -1};
+        int32_t rgba[4][4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { rgba[i][0] = miss[0]; rgba[i][1] = miss[1]; rgba[i][2] = miss[2]; rgba[i][3] = miss[3]; }
+#pragma unroll 1
+        for (int q0 = 0; q0 < PX; q0 += 4) store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids);
+        return;
+    }
+#pragma unroll 1
+    for (int q0 = 0; q0 < PX; q0 += 4) {
+        uint32_t rgba8[4];
+        int32_t rgba[4][4];
+        int ids[4];
+        float4 col[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            ids[i] = (st.best[i] == RTB_MISS_T) ? -1 : st.id(q0 + i);
+            const float4* src = (ids[i] < p.n_cubes) ? p.cube_col + ids[i] : p.sph_col + (ids[i] - p.n_cubes);
+            col[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ids[i] >= 0) col[i] = __ldg(src);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            rtb_shade(st.best[i], col[i].x, col[i].y, col[i].z, rgba[i]);
+            rgba8[i] = rtb_pack_rgba8(rgba[i]);
+        }
+        store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids);
+#pragma unroll
+        for (int i = 0; i + 4 < PX; ++i) st.best[i] = st.best[i + 4];
+    }
+}
+
+// Geometry: a thread holds PX horizontally adjacent rays, a warp is LX lanes wide and 32 / LX rows tall
+// (LX = 2, PX = 16: 32 x 16 pixels -- close to square, so that a primitive's exact update and shading run
+// in few warps), a CTA = WARPS_X x WARPS_Y warps = one tile of the bins.
+template <int PX, int LX, int WARPS_X, int WARPS_Y, int MIN_CTAS>
 __global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y, MIN_CTAS)
 raycast_binned_kernel(const GridParams p) {
     constexpr int kWarps = WARPS_X * WARPS_Y;
     constexpr int kThreads = 32 * kWarps;
-    constexpr int kTileW = WARPS_X * 8 * PX;
-    constexpr int kTileH = WARPS_Y * 4;
+    constexpr int kWarpRows = 32 / LX;
+    constexpr int kTileW = WARPS_X * LX * PX;
+    constexpr int kTileH = WARPS_Y * kWarpRows;
     constexpr int kCap = 64;  // listed primitives per pass over the rays
     __shared__ __align__(16) float4 s_rec[kCap][5];  // bound record (2) + exact records (cube 3, sphere 1)
     __shared__ int s_prim[kCap];
-    __shared__ int s_wsum[kWarps];
+    __shared__ int s_wsum[2][kWarps];
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const int wx = warp % WARPS_X, wy = warp / WARPS_X;
-    const int lx = lane & 7, ly = lane >> 3;
-    const int x0 = blockIdx.x * kTileW + (wx * 8 + lx) * PX;
-    const int lrow = blockIdx.y * kTileH + wy * 4 + ly;
+    const int lx = lane % LX, ly = lane / LX;
+    const int x0 = blockIdx.x * kTileW + (wx * LX + lx) * PX;
+    const int lrow = blockIdx.y * kTileH + wy * kWarpRows + ly;
     const int lb = lrow / p.band_rows;
     const int gy = (lb * p.band_world + p.band_rank) * p.band_rows + (lrow - lb * p.band_rows);
     const size_t n_tiles = (size_t)gridDim.x * gridDim.y;
@@ -874,11 +869,13 @@ raycast_binned_kernel(const GridParams p) {
     bool st_ready = false;  // the pixel state is set up when the tile's first primitive turns up
     bool warp_hit = false;  // some ray of this warp passed some bound
 
-    for (int base = 0; base < n_words; base += kThreads) {
+    int chunk = 0;
+    for (int base = 0; base < n_words; base += kThreads, ++chunk) {
         const int w = base + tid;
         const uint32_t m = (w < n_words) ? __ldg(p.bins + (size_t)w * n_tiles + tile) : 0u;
-        if (!__syncthreads_or(m != 0u)) continue;
-        // CTA-wide exclusive prefix of the popcounts: list position of each thread's first primitive
+        // CTA-wide exclusive prefix of the popcounts: list position of each thread's first primitive.
+        // (s_wsum is double buffered: a warp that writes chunk k+2's sums has passed the barrier of chunk
+        // k+1, which every thread reaches only after reading chunk k's.)
         const int c = __popc(m);
         int incl = c;
 #pragma unroll
@@ -886,48 +883,53 @@ raycast_binned_kernel(const GridParams p) {
             const int t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
             if (lane >= d) incl += t;
         }
-        if (lane == 31) s_wsum[warp] = incl;
+        if (lane == 31) s_wsum[chunk & 1][warp] = incl;
         __syncthreads();
         int off = incl - c, total = 0;
 #pragma unroll
         for (int k = 0; k < kWarps; ++k) {
-            const int s = s_wsum[k];
+            const int s = s_wsum[chunk & 1][k];
             if (k < warp) off += s;
             total += s;
         }
+        if (total == 0) continue;
         if (!st_ready) {
+            const float fx0 = (float)x0, row_term = p.cam.l12 * fy;
 #pragma unroll
             for (int q = 0; q < PX; q += 2) {
-                st.u2[q >> 1] = pack2(rtb_cam_u(p.cam, (float)(x0 + q), fy), rtb_cam_u(p.cam, (float)(x0 + q + 1), fy));
-                st.best[q] = st.best[q + 1] = RTB_MISS_T;
-                st.id(q) = -1;
-                st.id(q + 1) = -1;
+                // fmaf(l11, (float)(x0 + q), l12 * fy) = rtb_cam_u: (float)x0 + (float)q is exact
+                st.u2[q >> 1] = pack2(fmaf(p.cam.l11, fx0 + (float)q, row_term), fmaf(p.cam.l11, fx0 + (float)(q + 1), row_term));
+                st.best[q] = st.best[q + 1] = RTB_MISS_T;  // ids are read only where best != miss
             }
             st_ready = true;
         }
         for (int pass = 0; pass < total; pass += kCap) {
-            {
+            {   // the thread that owns a bit fetches that primitive's records (one round of loads per pass)
                 uint32_t mm = m;
                 int pos = off - pass;
                 while (mm != 0u && pos < kCap) {
                     const int j = __ffs(mm) - 1;
                     mm &= mm - 1u;
-                    if (pos >= 0) s_prim[pos] = w * 32 + j;
+                    if (pos >= 0) {
+                        const int prim = w * 32 + j;
+                        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                        const float4 b0 = __ldg(p.bound_rec + 2 * (size_t)prim), b1 = __ldg(p.bound_rec + 2 * (size_t)prim + 1);
+                        float4 e0 = z, e1 = z, e2 = z;
+                        if (prim < p.n_cubes) {
+                            e0 = __ldg(p.cube_rec + 3 * (size_t)prim);
+                            e1 = __ldg(p.cube_rec + 3 * (size_t)prim + 1);
+                            e2 = __ldg(p.cube_rec + 3 * (size_t)prim + 2);
+                        } else if (prim < p.n_cubes + p.n_spheres) {
+                            e0 = __ldg(p.sph_rec + (size_t)(prim - p.n_cubes));
+                        }
+                        s_prim[pos] = prim;
+                        s_rec[pos][0] = b0; s_rec[pos][1] = b1; s_rec[pos][2] = e0; s_rec[pos][3] = e1; s_rec[pos][4] = e2;
+                    }
                     ++pos;
                 }
             }
             __syncthreads();
             const int n = min(kCap, total - pass);
-            for (int i = tid; i < n * 5; i += kThreads) {
-                const int e = i / 5, part = i - e * 5;
-                const int prim = s_prim[e];
-                float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (part < 2) r = __ldg(p.bound_rec + 2 * (size_t)prim + part);
-                else if (prim < p.n_cubes) r = __ldg(p.cube_rec + 3 * (size_t)prim + (part - 2));
-                else if (part == 2 && prim < p.n_cubes + p.n_spheres) r = __ldg(p.sph_rec + (size_t)(prim - p.n_cubes));
-                s_rec[e][part] = r;
-            }
-            __syncthreads();
 #pragma unroll 1
             for (int e = 0; e < n; ++e) {
                 const float4 a = s_rec[e][0];
@@ -939,7 +941,7 @@ raycast_binned_kernel(const GridParams p) {
                     exact_update_rec<PX>(p, s_prim[e], s_rec[e][2], s_rec[e][3], s_rec[e][4], v, st);
                 }
             }
-            __syncthreads();  // every warp is done with the list before it is refilled
+            if (pass + kCap < total || base + kThreads < n_words) __syncthreads();  // list is refilled
         }
     }
 
@@ -1090,8 +1092,9 @@ cudaError_t launch_cull_instance(const GridParams& p, cudaStream_t stream) {
 }
 
 // Tile geometry of the binned render (tile_cull == 2): the bins are laid out for exactly this tiling.
-constexpr int kBinPX = 16, kBinWX = 2, kBinWY = 2;
-constexpr int kBinTileW = kBinWX * 8 * kBinPX, kBinTileH = kBinWY * 4;
+constexpr int kBinPX = 16, kBinLX = 2, kBinWX = 2, kBinWY = 2;
+constexpr int kBinTileW = kBinWX * kBinLX * kBinPX, kBinTileH = kBinWY * (32 / kBinLX);
+static_assert(kBinTileH == kBinnedTileRows, "rtb_api.cu aligns the progress chunks to the tile height");
 
 size_t grid_bin_words(int width, int local_rows, int n_bound) {
     const size_t tiles = (size_t)((width + kBinTileW - 1) / kBinTileW) * (size_t)((local_rows + kBinTileH - 1) / kBinTileH);
@@ -1102,17 +1105,17 @@ static cudaError_t launch_binned(const GridParams& p, cudaStream_t stream) {
     constexpr int kThreads = 32 * kBinWX * kBinWY;
     constexpr int kDyn = kBinPX * kThreads * (int)sizeof(int);
     constexpr int kMinCtas = 6;
-    const GridLaunchShape s = shape_of<kBinPX, kBinWX, kBinWY>(p.width, p.local_rows);
-    if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
+    const int tiles_x = (p.width + kBinTileW - 1) / kBinTileW, tiles_y = (p.local_rows + kBinTileH - 1) / kBinTileH;
+    if (tiles_x <= 0 || tiles_y <= 0) return cudaSuccess;
     if (p.bin_words > 0) {
         if (p.bins == nullptr) return cudaErrorInvalidValue;
-        const int tiles_x = (int)s.grid.x, tiles_y = (int)s.grid.y;
         dim3 bgrid((unsigned)(tiles_x * ((tiles_y + 31) / 32)), (unsigned)((p.bin_words + kBinWarps - 1) / kBinWarps));
         bin_tiles_kernel<kBinTileW, kBinTileH><<<bgrid, 32 * kBinWarps, 0, stream>>>(p, tiles_x, tiles_y);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
-    raycast_binned_kernel<kBinPX, kBinWX, kBinWY, kMinCtas><<<s.grid, dim3(kThreads), kDyn, stream>>>(p);
+    raycast_binned_kernel<kBinPX, kBinLX, kBinWX, kBinWY, kMinCtas>
+        <<<dim3((unsigned)tiles_x, (unsigned)tiles_y), dim3(kThreads), kDyn, stream>>>(p);
     return cudaGetLastError();
 }
 

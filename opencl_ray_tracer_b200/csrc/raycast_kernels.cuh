@@ -15,6 +15,8 @@ constexpr int kChunkPrims = 512;
 constexpr int kTabPrims = 128;
 // Row chunks a launch can report as finished while it is still running (rtb_render's pipelined copies).
 constexpr int kMaxProgressChunks = 32;
+// Pixel rows of a tile of the binned render (tile_cull == 2); progress chunks must not cut a tile.
+constexpr int kBinnedTileRows = 32;
 // Primitives per warp vote in the dense loop; the host pads the bound list to a multiple of it.
 constexpr int kBoundGroup = 4;
 

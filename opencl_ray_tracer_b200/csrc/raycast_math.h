@@ -146,14 +146,52 @@ RTB_HD bool rtb_bound_tile_misses(const RtbBound& b, float u_min, float u_max, f
     return b.e >= 0.0f && fmaf(wm, wm, c_min) >= 2.0f;
 }
 
+// Coordinate ranges of the rays of the pixel rectangle [x_a, x_b] x [y_a, y_b] (frame coordinates as
+// floats): u = fmaf(l11, x, l12*y) is non-decreasing or non-increasing in x for fixed y and in y for
+// fixed x (a rounded product by a constant and fmaf in its addend are monotone), v = l22*y is
+// monotone in y, so the extremes over the rectangle's pixels are attained at its four corners --
+// exactly, for the rounded values.  tests/emu compares with the loop over every row.
+RTB_HD void rtb_tile_uv_range(const RtbCam& c, float x_a, float x_b, float y_a, float y_b, float* u_min,
+                              float* u_max, float* v_min, float* v_max) {
+    const float u0 = rtb_cam_u(c, x_a, y_a), u1 = rtb_cam_u(c, x_b, y_a);
+    const float u2 = rtb_cam_u(c, x_a, y_b), u3 = rtb_cam_u(c, x_b, y_b);
+    const float va = rtb_cam_v(c, y_a), vb = rtb_cam_v(c, y_b);
+    *u_min = fminf(fminf(u0, u1), fminf(u2, u3));
+    *u_max = fmaxf(fmaxf(u0, u1), fmaxf(u2, u3));
+    *v_min = fminf(va, vb);
+    *v_max = fmaxf(va, vb);
+}
+
 // Depth-fog shade + (int) truncation, MainState.cpp:397-407, misc/Utility.cpp:109-116,
 // MainState.cpp:952-955.  Same operation order as the reference; no contraction.
+//
+// x / 180.0f, correctly rounded (the reference's IEEE divide), without the divide: with
+// c = RN(1/180), q0 = x*c, r = fmaf(-q0, 180, x), q = fmaf(r, c, q0) equals RN(x/180) for EVERY float
+// with 1e-30 <= |x| <= FLT_MAX -- checked exhaustively over all bit patterns
+// (tests/emu emu_check_div180, tests/test_kernel_math_emulated.py); below 1e-30 (186 415 patterns
+// whose quotient is subnormal or nearly so) the real divide is used.  3 FP32 instructions per pixel
+// instead of the ~12 of div.rn.f32.
+#ifdef __CUDACC__
+#define RTB_COLD __noinline__
+#else
+#define RTB_COLD __attribute__((noinline))
+#endif
+RTB_COLD RTB_HD float rtb_div180_ieee(float x) { return x / 180.0f; }  // out of line: never runs in a frame
+RTB_HD float rtb_div180(float x) {
+    const float c = 0x1.6c16c2p-8f;                 // RN(1/180)
+    const float q0 = x * c;
+    const float r = fmaf(-q0, 180.0f, x);
+    const float q = fmaf(r, c, q0);
+    if (!(fabsf(x) >= 1e-30f)) return rtb_div180_ieee(x);  // tiny, zero or NaN: the real divide
+    return q;
+}
+
 RTB_HD void rtb_shade(float closest, float cr, float cg, float cb, int32_t out[4]) {
     if (closest == RTB_MISS_T) {
         out[0] = 0; out[1] = 0; out[2] = 0; out[3] = 255;
         return;
     }
-    const float norm = (closest - 0.0f) / (180.0f - 0.0f);
+    const float norm = rtb_div180(closest - 0.0f);  // (closest - 0) / (180 - 0), misc/Utility.cpp:109-116
     const float k = 255.0f - (norm * 255.0f);
     out[0] = (int32_t)(k * cr);
     out[1] = (int32_t)(k * cg);

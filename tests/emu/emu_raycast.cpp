@@ -123,6 +123,11 @@ extern "C" int emu_check_tile_cull(int width, int height, const float* cam8, int
             u_min = fminf(u_min, fminf(ua, ub)); u_max = fmaxf(u_max, fmaxf(ua, ub));
             v_min = fminf(v_min, v); v_max = fmaxf(v_max, v);
         }
+        {   // the four-corner form used by bin_tiles_kernel must give the very same ranges
+            float cu0, cu1, cv0, cv1;
+            rtb_tile_uv_range(cam, (float)x_lo, (float)(x_lo + tile_w - 1), (float)y_lo, (float)(y_lo + tile_h - 1), &cu0, &cu1, &cv0, &cv1);
+            if (cu0 != u_min || cu1 != u_max || cv0 != v_min || cv1 != v_max) viol += n_bound;
+        }
         for (int i = 0; i < n_bound; ++i) {
             const RtbBound& b = bnd[i];
             const bool miss = rtb_bound_tile_misses(b, u_min, u_max, v_min, v_max);
@@ -145,4 +150,25 @@ extern "C" int emu_check_tile_cull(int width, int height, const float* cam8, int
     }
     out[0] = viol; out[1] = culled; out[2] = empty; out[3] = (long long)tx * ty * n_bound;
     return 0;
+}
+
+// rtb_div180 (raycast_math.h) against the IEEE divide on every stride-th bit pattern in
+// [first_bits, last_bits] (Inf / NaN skipped).  Returns the number of mismatches.
+extern "C" long long emu_check_div180(unsigned first_bits, unsigned last_bits, unsigned stride) {
+    long long bad = 0;
+    const long long n = ((long long)last_bits - (long long)first_bits) / stride + 1;
+#pragma omp parallel for schedule(static) reduction(+ : bad)
+    for (long long k = 0; k < n; ++k) {
+        const uint32_t b = (uint32_t)((long long)first_bits + k * stride);
+        float x;
+        __builtin_memcpy(&x, &b, 4);
+        if (!(fabsf(x) <= 3.4028234663852886e38f)) continue;  // Inf / NaN
+        const volatile float d = 180.0f;
+        const float ref = x / d, got = rtb_div180(x);
+        uint32_t a, c;
+        __builtin_memcpy(&a, &ref, 4);
+        __builtin_memcpy(&c, &got, 4);
+        bad += (a != c);
+    }
+    return bad;
 }

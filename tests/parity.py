@@ -118,6 +118,12 @@ class Emulator:
         self.lib.emu_check_tile_cull(w, h, fp(cam), len(bnd), fp(bnd), tile_w, tile_h, out)
         return {"violations": out[0], "culled": out[1], "empty": out[2], "total": out[3]}
 
+    def check_div180(self, first_bits, last_bits, stride=1):
+        """rtb_div180 vs the IEEE divide on every stride-th float bit pattern in [first_bits, last_bits]: mismatches."""
+        self.lib.emu_check_div180.restype = C.c_longlong
+        self.lib.emu_check_div180.argtypes = [C.c_uint, C.c_uint, C.c_uint]
+        return int(self.lib.emu_check_div180(first_bits, last_bits, stride))
+
     def check_bounds(self, scene, w, h, camera=None):
         """Walks the kernel's dense loop: returns dict(violations, bound_pass, footprint, total)."""
         from opencl_ray_tracer_b200 import capi

@@ -65,3 +65,11 @@ def test_reference_scene_windows_within_tolerance(emu):
     d = np.abs((got[..., :3] & 0xFF) - (z["rgba"][..., :3] & 0xFF))
     d = np.minimum(d, 256 - d).max(-1)
     assert (d <= 1).mean() >= 0.995  # window is small and silhouette-dense; ids are checked elsewhere
+
+
+def test_div180_is_the_ieee_divide_on_every_float(emu):
+    """rtb_shade's x / 180 without a divide (rtb_div180): bit-identical to the IEEE quotient on EVERY non-negative
+    float (all 2^31 patterns incl. subnormals, zero and the guarded range below 1e-30) and on every 5th negative one
+    (the operations are sign-symmetric)."""
+    assert emu.check_div180(0x00000000, 0x7F7FFFFF) == 0
+    assert emu.check_div180(0x80000000, 0xFF7FFFFF, 5) == 0
