@@ -790,9 +790,11 @@ __device__ __forceinline__ void store_group(const GridParams& p, size_t px_off, 
     }
 }
 
+// Called by EVERY lane of the warp (the per-group vote needs them all); `inside` false = this thread's pixels
+// lie outside the frame or the launch's rows and nothing is stored for it.
 template <int PX>
-__device__ __forceinline__ void shade_store_groups(const GridParams& p, PixelState<PX>& st, bool hit, int x0, int lrow,
-                                                   int gy) {
+__device__ __forceinline__ void shade_store_groups(const GridParams& p, PixelState<PX>& st, bool hit, bool inside, int x0,
+                                                   int lrow, int gy) {
     const size_t row_off = (size_t)(p.out_global_rows ? gy : lrow) * p.width + x0;
     const bool full = p.vec_ok && (x0 + PX <= p.width);
     int32_t miss[4];
@@ -804,8 +806,10 @@ __device__ __forceinline__ void shade_store_groups(const GridParams& p, PixelSta
         int32_t rgba[4][4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) { rgba[i][0] = miss[0]; rgba[i][1] = miss[1]; rgba[i][2] = miss[2]; rgba[i][3] = miss[3]; }
+        if (inside) {
 #pragma unroll 1
-        for (int q0 = 0; q0 < PX; q0 += 4) store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids);
+            for (int q0 = 0; q0 < PX; q0 += 4) store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids);
+        }
         return;
     }
 #pragma unroll 1
@@ -814,6 +818,19 @@ __device__ __forceinline__ void shade_store_groups(const GridParams& p, PixelSta
         int32_t rgba[4][4];
         int ids[4];
         float4 col[4];
+        const bool mine = inside && (st.best[0] != RTB_MISS_T || st.best[1] != RTB_MISS_T || st.best[2] != RTB_MISS_T ||
+                                     st.best[3] != RTB_MISS_T);
+        if (!__any_sync(0xFFFFFFFFu, mine)) {  // no lane of the warp has a hit among these four pixels
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                ids[i] = -1; rgba8[i] = miss8;
+                rgba[i][0] = miss[0]; rgba[i][1] = miss[1]; rgba[i][2] = miss[2]; rgba[i][3] = miss[3];
+            }
+            if (inside) store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids);
+#pragma unroll
+            for (int i = 0; i + 4 < PX; ++i) st.best[i] = st.best[i + 4];
+            continue;
+        }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             ids[i] = (st.best[i] == RTB_MISS_T) ? -1 : st.id(q0 + i);
@@ -826,7 +843,7 @@ __device__ __forceinline__ void shade_store_groups(const GridParams& p, PixelSta
             rtb_shade(st.best[i], col[i].x, col[i].y, col[i].z, rgba[i]);
             rgba8[i] = rtb_pack_rgba8(rgba[i]);
         }
-        store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids);
+        if (inside) store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids);
 #pragma unroll
         for (int i = 0; i + 4 < PX; ++i) st.best[i] = st.best[i + 4];
     }
@@ -945,7 +962,7 @@ raycast_binned_kernel(const GridParams p) {
         }
     }
 
-    if (lrow < p.local_rows && gy < p.height && x0 < p.width) shade_store_groups<PX>(p, st, warp_hit, x0, lrow, gy);
+    shade_store_groups<PX>(p, st, warp_hit, lrow < p.local_rows && gy < p.height && x0 < p.width, x0, lrow, gy);
     signal_completion(p, kTileH);
 }
 
@@ -1091,36 +1108,65 @@ cudaError_t launch_cull_instance(const GridParams& p, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
-// Tile geometry of the binned render (tile_cull == 2): the bins are laid out for exactly this tiling.
-constexpr int kBinPX = 16, kBinLX = 2, kBinWX = 2, kBinWY = 2;
-constexpr int kBinTileW = kBinWX * kBinLX * kBinPX, kBinTileH = kBinWY * (32 / kBinLX);
-static_assert(kBinTileH == kBinnedTileRows, "rtb_api.cu aligns the progress chunks to the tile height");
+// Tile geometry of the binned render (tile_cull == 2).  The bins are laid out for exactly the tiling of the
+// render kernel that reads them.  RTB_BINNED_VARIANT=n (experiment hook, profiles/) picks another tiling.
+struct BinnedTiling { int tile_w, tile_h; };
+static int binned_variant() {
+    static const int v = [] {
+        const char* e = std::getenv("RTB_BINNED_VARIANT");
+        return e ? std::atoi(e) : 0;
+    }();
+    return v;
+}
+static BinnedTiling binned_tiling() {
+    switch (binned_variant()) {
+        case 2: return {128, 16};
+        case 3: return {64, 16};
+        case 4: return {64, 16};
+        case 5: return {32, 16};
+        default: return {64, 32};
+    }
+}
+
+int binned_tile_rows() { return binned_tiling().tile_h; }
 
 size_t grid_bin_words(int width, int local_rows, int n_bound) {
-    const size_t tiles = (size_t)((width + kBinTileW - 1) / kBinTileW) * (size_t)((local_rows + kBinTileH - 1) / kBinTileH);
+    const BinnedTiling t = binned_tiling();
+    const size_t tiles = (size_t)((width + t.tile_w - 1) / t.tile_w) * (size_t)((local_rows + t.tile_h - 1) / t.tile_h);
     return tiles * (size_t)((n_bound + 31) / 32);
 }
 
+template <int PX, int LX, int WX, int WY, int MINB>
 static cudaError_t launch_binned(const GridParams& p, cudaStream_t stream) {
-    constexpr int kThreads = 32 * kBinWX * kBinWY;
-    constexpr int kDyn = kBinPX * kThreads * (int)sizeof(int);
-    constexpr int kMinCtas = 6;
-    const int tiles_x = (p.width + kBinTileW - 1) / kBinTileW, tiles_y = (p.local_rows + kBinTileH - 1) / kBinTileH;
+    constexpr int kThreads = 32 * WX * WY;
+    constexpr int kDyn = PX * kThreads * (int)sizeof(int);
+    constexpr int kTileW = WX * LX * PX, kTileH = WY * (32 / LX);
+    const int tiles_x = (p.width + kTileW - 1) / kTileW, tiles_y = (p.local_rows + kTileH - 1) / kTileH;
     if (tiles_x <= 0 || tiles_y <= 0) return cudaSuccess;
     if (p.bin_words > 0) {
         if (p.bins == nullptr) return cudaErrorInvalidValue;
         dim3 bgrid((unsigned)(tiles_x * ((tiles_y + 31) / 32)), (unsigned)((p.bin_words + kBinWarps - 1) / kBinWarps));
-        bin_tiles_kernel<kBinTileW, kBinTileH><<<bgrid, 32 * kBinWarps, 0, stream>>>(p, tiles_x, tiles_y);
+        bin_tiles_kernel<kTileW, kTileH><<<bgrid, 32 * kBinWarps, 0, stream>>>(p, tiles_x, tiles_y);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
-    raycast_binned_kernel<kBinPX, kBinLX, kBinWX, kBinWY, kMinCtas>
-        <<<dim3((unsigned)tiles_x, (unsigned)tiles_y), dim3(kThreads), kDyn, stream>>>(p);
+    raycast_binned_kernel<PX, LX, WX, WY, MINB><<<dim3((unsigned)tiles_x, (unsigned)tiles_y), dim3(kThreads), kDyn, stream>>>(p);
     return cudaGetLastError();
 }
 
+static cudaError_t launch_binned_variant(const GridParams& p, cudaStream_t stream) {
+    switch (binned_variant()) {
+        case 1: return launch_binned<16, 2, 2, 2, 8>(p, stream);   // 64 registers
+        case 2: return launch_binned<16, 2, 4, 1, 6>(p, stream);   // 128 x 16 tiles
+        case 3: return launch_binned<16, 2, 2, 1, 12>(p, stream);  // 64 x 16 tiles, 2 warps
+        case 4: return launch_binned<16, 4, 1, 2, 12>(p, stream);  // 64 x 8 warps, 64 x 16 tiles
+        case 5: return launch_binned<16, 2, 1, 1, 24>(p, stream);  // one warp per tile
+        default: return launch_binned<16, 2, 2, 2, 6>(p, stream);  // 64 x 32 tiles, 4 warps of 32 x 16 pixels
+    }
+}
+
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) {
-    if (p.tile_cull == 2) return launch_binned(p, stream);
+    if (p.tile_cull == 2) return launch_binned_variant(p, stream);
     if (p.tile_cull) return launch_cull_instance<16, 2, 2, 4>(p, stream);
     static const int variant = [] {
         const char* e = std::getenv("RTB_GRID_VARIANT");

@@ -15,8 +15,6 @@ constexpr int kChunkPrims = 512;
 constexpr int kTabPrims = 128;
 // Row chunks a launch can report as finished while it is still running (rtb_render's pipelined copies).
 constexpr int kMaxProgressChunks = 32;
-// Pixel rows of a tile of the binned render (tile_cull == 2); progress chunks must not cut a tile.
-constexpr int kBinnedTileRows = 32;
 // Primitives per warp vote in the dense loop; the host pads the bound list to a multiple of it.
 constexpr int kBoundGroup = 4;
 
@@ -88,6 +86,8 @@ struct GridLaunchShape { int px, wx, wy, split; dim3 grid, block; size_t smem; }
 GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count);
 // 32-bit words of GridParams::bins a launch of this size needs (tile_cull == 2).
 size_t grid_bin_words(int width, int local_rows, int n_bound);
+// Pixel rows of a tile of the binned render (a multiple of 16); progress chunks must not cut a tile.
+int binned_tile_rows();
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream);
 cudaError_t launch_rays(const RaysParams& p, cudaStream_t stream);
 cudaError_t launch_signal_only(unsigned int* d_signal, cudaStream_t stream);  // a rank with no rows still signals

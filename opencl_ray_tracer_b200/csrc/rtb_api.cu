@@ -652,7 +652,7 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
         // reference's OpenCL path does one blocking clEnqueueMapBuffer after the kernel,
         // MainState.cpp:876-886.)
         int bound[kMaxProgressChunks + 1];
-        const int n_chunks = plan_progress_chunks(height, row_bytes, ctx->tile_cull == 2 ? kBinnedTileRows : 16, bound);
+        const int n_chunks = plan_progress_chunks(height, row_bytes, ctx->tile_cull == 2 ? binned_tile_rows() : 16, bound);
         cs = ctx->copy_stream;
         ctx->progress_epoch += 1;
         if (ctx->progress_epoch == 0) ctx->progress_epoch = 1;
@@ -736,7 +736,7 @@ int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origi
     if (local_rows > 0) {
         // chunk = whole bands (and a multiple of 16 rows, the progress granularity): about 2 MB each
         int unit = band_rows;
-        while (unit % (ctx->tile_cull == 2 ? kBinnedTileRows : 16) != 0) unit *= 2;
+        while (unit % (ctx->tile_cull == 2 ? binned_tile_rows() : 16) != 0) unit *= 2;
         int bound[kMaxProgressChunks + 1];
         const int n_chunks = plan_progress_chunks(local_rows, row_bytes, unit, bound);
         const bool flags = ctx->stream_wait_value32 != nullptr;

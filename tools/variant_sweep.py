@@ -41,7 +41,7 @@ def child(workload, flush, reps):
         stream.synchronize()
     ms, n = ctx.kernel_ms_avg(reset=True)
     digest = hashlib.sha1(buf.cpu().numpy().tobytes()).hexdigest()[:16]
-    print(json.dumps({"variant": {1: "cull", 2: "binned"}[cull] if cull else int(os.environ.get("RTB_GRID_VARIANT", "0")), "workload": workload,
+    print(json.dumps({"variant": ({1: "cull", 2: "binned"}[cull] + (":" + os.environ["RTB_BINNED_VARIANT"] if cull == 2 and "RTB_BINNED_VARIANT" in os.environ else "")) if cull else int(os.environ.get("RTB_GRID_VARIANT", "0")), "workload": workload,
                       "kernel_ms": round(ms, 4), "launches": n, "mrays_s": round(w * h / ms / 1e3, 1),
                       "flush": bool(flush), "frame_sha1": digest}))
     ctx.close()
@@ -61,8 +61,10 @@ def main():
     ref = None
     for v in a.variants.split(","):
         env = dict(os.environ, RTB_GRID_VARIANT=v)
-        if v in ("cull", "binned"):  # the tile-culled kernels (RTB_OPT_TILE_CULL = 1 | 2) instead of a dense variant
+        if v == "cull" or v.startswith("binned"):  # the tile-culled kernels (RTB_OPT_TILE_CULL = 1 | 2); binned:N = tiling N
             env = dict(os.environ, RTB_GRID_VARIANT="0", RTB_SWEEP_TILE_CULL="1" if v == "cull" else "2")
+            if ":" in v:
+                env["RTB_BINNED_VARIANT"] = v.split(":")[1]
         cmd = [sys.executable, os.path.abspath(__file__), "--child", "--workload", a.workload, "--reps", str(a.reps)]
         if a.flush:
             cmd.append("--flush")
