@@ -57,6 +57,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-peer", action="store_true", help="N > 1: NCCL gather instead of peer-memory stores")
+    ap.add_argument("--no-binned", action="store_true", help="skip the second pass with the binned tile cull (RTB_OPT_TILE_CULL = 2)")
     return ap.parse_args()
 
 
@@ -289,68 +290,81 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident timing (value) -------------------------------------------------------
-    if peer:
-        try:                               # stream memory operations present?  (else: collective fence)
+    def timed_pass(first):
+        """Device-resident timing (value) and end-to-end timing (e2e) of the render mode currently set."""
+        # ---- device-resident timing (value) -------------------------------------------------------
+        if peer and first:
+            try:                               # stream memory operations present?  (else: collective fence)
+                device_step()
+            except capi.RtbError:
+                state["signals"] = False
+            ok = torch.tensor([1 if state["signals"] else 0], dtype=torch.int32, device="cuda")
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            state["signals"] = bool(int(ok.item()))
+        for _ in range(max(args.warmup, 3)):
             device_step()
-        except capi.RtbError:
-            state["signals"] = False
-        ok = torch.tensor([1 if state["signals"] else 0], dtype=torch.int32, device="cuda")
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-        state["signals"] = bool(int(ok.item()))
-    for _ in range(max(args.warmup, 3)):
-        device_step()
-    barrier()
-    ctx.kernel_ms_avg(reset=True)
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    launches = 0
-    barrier()
-    wall0 = time.perf_counter()
-    for a, b in ev:
-        flush.zero_()                      # L2 flush between timed iterations (not timed)
-        a.record(stream)
-        launches += device_step()
-        b.record(stream)
-    barrier()
-    wall = time.perf_counter() - wall0
-    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
-    k_avg_ms, k_n = ctx.kernel_ms_avg(reset=True)
-    sampler.stop_flag = True
-    sampler.join()
-    t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms = float(t.item())
-    ms_per_step = dev_ms / args.steps
+        barrier()
+        ctx.kernel_ms_avg(reset=True)
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        launches = 0
+        barrier()
+        wall0 = time.perf_counter()
+        for a, b in ev:
+            flush.zero_()                      # L2 flush between timed iterations (not timed)
+            a.record(stream)
+            launches += device_step()
+            b.record(stream)
+        barrier()
+        wall = time.perf_counter() - wall0
+        dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+        k_avg_ms, k_n = ctx.kernel_ms_avg(reset=True)
+        sampler.stop_flag = True
+        sampler.join()
+        t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms = float(t.item())
+        ms_per_step = dev_ms / args.steps
 
-    # ---- end-to-end timing through the C ABI with host buffers (e2e) ---------------------------
-    for _ in range(3):
-        e2e_step()
-    barrier()
-    h2d0, d2h0 = ctx.transfer_bytes()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    barrier()
-    e2e_s = time.perf_counter() - t0
-    h2d1, d2h1 = ctx.transfer_bytes()
-    t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_s = float(t.item())
-    # bytes this rank moved; summed over the ranks below (every rank uploads the scene, each downloads its bands)
-    tb = torch.tensor([float(h2d1 - h2d0), float(d2h1 - d2h0)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(tb)
-    h2d_per_step, d2h_per_step = float(tb[0].item()) / args.steps, float(tb[1].item()) / args.steps
+        # ---- end-to-end timing through the C ABI with host buffers (e2e) ---------------------------
+        for _ in range(3):
+            e2e_step()
+        barrier()
+        h2d0, d2h0 = ctx.transfer_bytes()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        barrier()
+        e2e_s = time.perf_counter() - t0
+        h2d1, d2h1 = ctx.transfer_bytes()
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+        # bytes this rank moved; summed over the ranks below (every rank uploads the scene, each downloads its bands)
+        tb = torch.tensor([float(h2d1 - h2d0), float(d2h1 - d2h0)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tb)
+        h2d_per_step, d2h_per_step = float(tb[0].item()) / args.steps, float(tb[1].item()) / args.steps
+        return dict(ms_per_step=ms_per_step, wall_ms_per_step=wall * 1e3 / args.steps, k_avg_ms=k_avg_ms, k_n=k_n,
+                    launches=launches, clocks=sampler.result(), e2e_s=e2e_s, h2d=h2d_per_step, d2h=d2h_per_step)
+
+    dense = timed_pass(True)
+    # The same frame with the tile cull made once per frame (RTB_OPT_TILE_CULL = 2: bin_tiles_kernel +
+    # raycast_binned_kernel, byte-identical output): reported beside the dense O(rays x primitives) numbers.
+    binned = None
+    if not args.no_binned:
+        ref_frame = d_frame.clone() if world == 1 else None
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, 2)
+        binned = timed_pass(False)
+        binned["same_frame_as_dense"] = bool(torch.equal(ref_frame, d_frame)) if world == 1 else None
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
     if shared is not None:
         shared.close()
     return dict(rank=rank, world=world, w=w, h=h, ns=ns, nc=nc, seed=seed, scene=scene, ctx=ctx,
-                ms_per_step=ms_per_step, wall_ms_per_step=wall * 1e3 / args.steps, k_avg_ms=k_avg_ms, k_n=k_n,
-                launches=launches, clocks=sampler.result(), peer=bool(peer), signals=bool(peer and state["signals"]), e2e_s=e2e_s, h2d=h2d_per_step, d2h=d2h_per_step,
-                my_rows=my_rows)
+                peer=bool(peer), signals=bool(peer and state["signals"]), my_rows=my_rows, binned=binned, **dense)
 
 
 def run_sequence(args):
@@ -674,6 +688,24 @@ def main():
                          "framebuffer_write_gbs": r["my_rows"] * w * 4 / k_s / 1e9 if k_s > 0 else None,
                          "hbm_peak_gbs": peaks.get("hbm_gbs"), "hbm_peak_source": peaks_src},
         }
+        if r["binned"]:
+            bn = r["binned"]
+            bk_s = bn["k_avg_ms"] * 1e-3
+            frame_bytes = r["my_rows"] * w * 4
+            line["binned"] = {
+                "what": "the same frame, byte for byte, with RTB_OPT_TILE_CULL = 2: bin_tiles_kernel decides once per frame which primitives "
+                        "a 64x32-pixel tile can see, raycast_binned_kernel runs the per-ray tests for those only (not O(rays x primitives): "
+                        "no tests/s or FP32 fraction is claimed for it)",
+                "value": n_px / (bn["ms_per_step"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": bn["ms_per_step"],
+                "kernels_ms": bn["k_avg_ms"], "gpu_launches": 2 * bn["launches"], "same_frame_as_dense": bn["same_frame_as_dense"],
+                "e2e": {"value": n_px * args.steps / bn["e2e_s"] / 1e6, "unit": "Mrays/s", "ms_per_step": bn["e2e_s"] * 1e3 / args.steps,
+                        "h2d_bytes_per_step": bn["h2d"], "d2h_bytes_per_step": bn["d2h"]},
+                "roofline": {"bound": "hbm", "achieved": frame_bytes / bk_s / 1e9 if bk_s > 0 else None, "peak": peaks.get("hbm_gbs"),
+                             "unit": "GB/s", "frac": (frame_bytes / bk_s / 1e9 / peaks["hbm_gbs"]) if (bk_s > 0 and peaks.get("hbm_gbs")) else None,
+                             "traffic": None, "kernel": "bin_tiles_kernel + raycast_binned_kernel",
+                             "algorithmic_bytes": "the frame write, 4 B per ray (this rank's rows)", "peak_source": peaks_src},
+                "clocks": bn["clocks"],
+            }
         if r["world"] == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_port(r["scene"], w, h, args.cpu_seconds)
         print(json.dumps(line))

@@ -719,6 +719,9 @@ constexpr int kBinWarps = 8;  // warps (= words) per CTA of the binning launch
 
 template <int TILE_W, int TILE_H>
 __global__ void __launch_bounds__(32 * kBinWarps) bin_tiles_kernel(const GridParams p, int tiles_x, int tiles_y) {
+    // the render launch that follows may be scheduled now (programmatic dependent launch); it still waits
+    // for this whole grid to finish before it reads a bin word
+    asm volatile("griddepcontrol.launch_dependents;");
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int sy_count = (tiles_y + 31) / 32;
     const int tx = blockIdx.x / sy_count, sy = blockIdx.x - tx * sy_count;
@@ -886,10 +889,13 @@ raycast_binned_kernel(const GridParams p) {
     bool st_ready = false;  // the pixel state is set up when the tile's first primitive turns up
     bool warp_hit = false;  // some ray of this warp passed some bound
 
+    // Launched as a programmatic dependent of bin_tiles_kernel: everything above overlapped with that
+    // grid's tail; from here on its bin words (and everything earlier in the stream) are visible.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     int chunk = 0;
     for (int base = 0; base < n_words; base += kThreads, ++chunk) {
         const int w = base + tid;
-        const uint32_t m = (w < n_words) ? __ldg(p.bins + (size_t)w * n_tiles + tile) : 0u;
+        const uint32_t m = (w < n_words) ? __ldcg(p.bins + (size_t)w * n_tiles + tile) : 0u;
         // CTA-wide exclusive prefix of the popcounts: list position of each thread's first primitive.
         // (s_wsum is double buffered: a warp that writes chunk k+2's sums has passed the barrier of chunk
         // k+1, which every thread reaches only after reading chunk k's.)
@@ -1118,6 +1124,10 @@ static int binned_variant() {
     }();
     return v;
 }
+static bool pdl_enabled() {  // RTB_NO_PDL=1: plain stream order between the two launches (experiment / fallback knob)
+    static const bool on = [] { const char* e = std::getenv("RTB_NO_PDL"); return !(e && e[0] == '1'); }();
+    return on;
+}
 static BinnedTiling binned_tiling() {
     switch (binned_variant()) {
         case 2: return {128, 16};
@@ -1150,8 +1160,17 @@ static cudaError_t launch_binned(const GridParams& p, cudaStream_t stream) {
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
-    raycast_binned_kernel<PX, LX, WX, WY, MINB><<<dim3((unsigned)tiles_x, (unsigned)tiles_y), dim3(kThreads), kDyn, stream>>>(p);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)tiles_x, (unsigned)tiles_y);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = kDyn;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, raycast_binned_kernel<PX, LX, WX, WY, MINB>, p);
 }
 
 static cudaError_t launch_binned_variant(const GridParams& p, cudaStream_t stream) {

@@ -171,12 +171,12 @@ RTB_HD void rtb_tile_uv_range(const RtbCam& c, float x_a, float x_b, float y_a, 
 // (tests/emu emu_check_div180, tests/test_kernel_math_emulated.py); below 1e-30 (186 415 patterns
 // whose quotient is subnormal or nearly so) the real divide is used.  3 FP32 instructions per pixel
 // instead of the ~12 of div.rn.f32.
-#ifdef __CUDACC__
-#define RTB_COLD __noinline__
+#if defined(__CUDACC__)
+#define RTB_COLD static __host__ __device__ __noinline__
 #else
-#define RTB_COLD __attribute__((noinline))
+#define RTB_COLD static __attribute__((noinline, unused))
 #endif
-RTB_COLD RTB_HD float rtb_div180_ieee(float x) { return x / 180.0f; }  // out of line: never runs in a frame
+RTB_COLD float rtb_div180_ieee(float x) { return x / 180.0f; }  // out of line: never runs in a frame
 RTB_HD float rtb_div180(float x) {
     const float c = 0x1.6c16c2p-8f;                 // RN(1/180)
     const float q0 = x * c;

@@ -12,9 +12,13 @@ sys.path.insert(0, ROOT)
 from opencl_ray_tracer_b200 import capi, host_scene as hs  # noqa: E402
 
 w, h, ns, nc, seed = 3840, 2160, 512, 512, 3
-if len(sys.argv) > 1 and sys.argv[1] == "c4":
+if "c4" in sys.argv[1:]:
     w, h, ns, nc, seed = 7680, 4320, 2048, 2048, 4
 ctx = capi.Context(0)
+if "binned" in sys.argv[1:]:
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, 2)
+elif "cull" in sys.argv[1:]:
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, 1)
 scene = hs.random_scene(w, h, ns, nc, seed)
 arrs = scene.as_tuple()
 buf, ptr = capi.host_alloc(w * h * 4)
@@ -29,7 +33,7 @@ for i in range(25):
     if i >= 5:
         ts.append((t1 - t0) * 1e3); tr.append((t2 - t1) * 1e3); tot.append(r["total_ms"]); ker.append(r["kernel_ms"])
 med = lambda a: float(np.median(a))
-print(json.dumps({"frame": "%dx%d, %d prims" % (w, h, ns + nc), "set_scene_ms": round(med(ts), 4), "render_wall_ms": round(med(tr), 4),
+print(json.dumps({"frame": "%dx%d, %d prims" % (w, h, ns + nc), "tile_cull": ctx.get_option(capi.RTB_OPT_TILE_CULL), "set_scene_ms": round(med(ts), 4), "render_wall_ms": round(med(tr), 4),
                   "render_device_span_ms": round(med(tot), 4), "grid_kernel_ms": round(med(ker), 4),
                   "e2e_ms": round(med(ts) + med(tr), 4)}))
 # same with the scene left resident (render only)
