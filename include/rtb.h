@@ -73,13 +73,19 @@ const char* rtb_last_error_message(const rtb_ctx* ctx);
 
 /* Per-context switches; every render entry point below obeys them.  No counterpart in the
  * reference (its only switch is enum Mode, MainState.h:48-52).
- *   RTB_OPT_TILE_CULL (0 | 1, default 0): 1 = render with raycast_cull_kernel.  Every CTA first
- *     tests each primitive's conservative screen-space bound against its whole 256 x 8 pixel tile
- *     and runs the per-ray tests only for the survivors: the pixels are byte-identical to the
- *     default kernel's (the cull is a statement about the values the per-ray bound would compute),
- *     the work drops from O(rays x primitives) to O(tiles x primitives + rays x survivors).
- *     The default (0) is the dense O(rays x primitives) kernel that BASELINE.json's roofline
- *     point is quoted on. */
+ *   RTB_OPT_TILE_CULL (0 | 1 | 2, default 0): which kernels render.  The pixels are byte-identical in all
+ *     three modes (the culls are statements about the values the per-ray bound would compute).
+ *     0 = the dense O(rays x primitives) kernel that BASELINE.json's roofline point is quoted on.
+ *     1 = raycast_cull_kernel: every CTA first tests each primitive's conservative screen-space bound
+ *         against its whole 256 x 8 pixel tile and runs the per-ray tests only for the survivors:
+ *         O(tiles x primitives + rays x survivors) in one launch.
+ *     2 = binned: bin_tiles_kernel makes that decision once per frame (two-level test, one 32-bit word
+ *         per 64 x 32 pixel tile and 32 primitives, grow-only device buffer owned by the context),
+ *         raycast_binned_kernel then renders every tile from its words.  Two launches per frame, the
+ *         second a programmatic dependent of the first; the fastest mode on SURVEY.md s8d's scenes.
+ *         With mode 1 or 2 rtb_render copies the frame to the host in one piece behind the launch
+ *         (the launch is much shorter than the PCIe time, there is nothing to overlap).
+ */
 typedef enum rtb_option { RTB_OPT_TILE_CULL = 1 } rtb_option;
 int rtb_set_option(rtb_ctx* ctx, int option, int value);
 int rtb_get_option(const rtb_ctx* ctx, int option, int* value);

@@ -82,6 +82,14 @@ int RenderState::update() {
     return RTB_OK;
 }
 
+int RenderState::setTileCull(int mode) {
+    if (!ctx_) return initStatus_;
+    const int rc = rtb_set_option(ctx_, RTB_OPT_TILE_CULL, mode);
+    if (rc != RTB_OK) lastError = rtb_last_error_message(ctx_);
+    start = true;
+    return rc;
+}
+
 int RenderState::executeRayTracerCUDA() {
     pixels.resize((size_t)pixelCount * 4);
     primIds.resize((size_t)pixelCount);

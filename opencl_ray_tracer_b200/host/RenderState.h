@@ -38,6 +38,8 @@ public:
     void setScene(int scene, uint64_t seed = 1);
     void setRandomScene(int ns, int nc, uint64_t seed);
     void requestRender() { start = true; }
+    // rtb_set_option(RTB_OPT_TILE_CULL): 0 dense kernel, 1 per-tile cull, 2 binned (same pixels, include/rtb.h).
+    int setTileCull(int mode);
 
     // One pass of MainState::update's render branch (MainState.cpp:180-237): rebuild the scene if it
     // changed, clear `pixels`, run the current mode, convert to the RGBA8 image.  Returns an

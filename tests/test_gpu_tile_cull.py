@@ -110,3 +110,21 @@ def test_unknown_option_is_rejected(ctx):
     assert e.value.status == 1
     with pytest.raises(capi.RtbError):
         ctx.set_option(capi.RTB_OPT_TILE_CULL, 3)
+
+
+def test_cli_frames_are_identical_in_every_mode(tmp_path):
+    """raycast_cli --tile-cull 0|1|2 (RenderState::setTileCull): the PNG files are the same bytes."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "opencl_ray_tracer_b200", "raycast_cli")
+    data = []
+    for mode in (0, 1, 2):
+        out = str(tmp_path / ("m%d.png" % mode))
+        r = subprocess.run([exe, "--scene", "random", "--spheres", "80", "--cubes", "70", "--seed", "5", "--width", "800",
+                            "--height", "600", "--tile-cull", str(mode), "--out", out], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, r.stderr
+        data.append(open(out, "rb").read())
+    assert data[0] == data[1] == data[2] and len(data[0]) > 1000
+    r = subprocess.run([exe, "--tile-cull", "7"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 2
