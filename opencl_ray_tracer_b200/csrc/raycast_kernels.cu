@@ -1131,9 +1131,6 @@ static bool pdl_enabled() {  // RTB_NO_PDL=1: plain stream order between the two
 static BinnedTiling binned_tiling() {
     switch (binned_variant()) {
         case 2: return {128, 16};
-        case 3: return {64, 16};
-        case 4: return {64, 16};
-        case 5: return {32, 16};
         default: return {64, 32};
     }
 }
@@ -1177,9 +1174,9 @@ static cudaError_t launch_binned_variant(const GridParams& p, cudaStream_t strea
     switch (binned_variant()) {
         case 1: return launch_binned<16, 2, 2, 2, 8>(p, stream);   // 64 registers
         case 2: return launch_binned<16, 2, 4, 1, 6>(p, stream);   // 128 x 16 tiles
-        case 3: return launch_binned<16, 2, 2, 1, 12>(p, stream);  // 64 x 16 tiles, 2 warps
-        case 4: return launch_binned<16, 4, 1, 2, 12>(p, stream);  // 64 x 8 warps, 64 x 16 tiles
-        case 5: return launch_binned<16, 2, 1, 1, 24>(p, stream);  // one warp per tile
+        // measured and dropped (profiles/r01_variant_sweep_binned_v3_tilings.jsonl; C3 / C4 ms against 0.0339 / 0.109):
+        // 64 x 16 tiles of two 32 x 16 warps 0.0356 / 0.132; of two 64 x 8 warps 0.0376 / 0.136; one warp per 32 x 16
+        // tile 0.0392 / 0.190
         default: return launch_binned<16, 2, 2, 2, 6>(p, stream);  // 64 x 32 tiles, 4 warps of 32 x 16 pixels
     }
 }
