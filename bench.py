@@ -401,6 +401,7 @@ def run_sequence(args):
         if world == 1:
             ctx.render_sequence_device(w, h, flat, d_out.data_ptr())     # blocking
             return
+        ctx.prepack_cameras(w, h, flat, sptr)          # the frames' records are packed ahead on the context's side stream
         for f in range(n_frames):
             peer.render(cams[f], BAND_ROWS, sptr, frame=f)
         peer.fence()
@@ -442,6 +443,13 @@ def run_sequence(args):
     sampler.stop_flag = True
     sampler.join()
     k_avg_ms, k_n = ctx.kernel_ms_avg(reset=True)
+    # the same sequence with the binned tile cull (RTB_OPT_TILE_CULL = 2, byte-identical frames), device-resident
+    binned_s = None
+    if not args.no_binned:
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, 2)
+        device_step()
+        binned_s = timed(device_step, steps) / steps
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
     e2e_step()
     e2e_steps = max(1, steps // 4)
     h2d0, d2h0 = ctx.transfer_bytes()
@@ -486,6 +494,10 @@ def run_sequence(args):
                          "peak_source": ("fp32_issue_probe (packed FFMA2 chains) run on this GPU just now" if probe
                                          else "nominal SMs x 128 lanes x 2 x max SM clock")},
         }
+        if binned_s:
+            line["binned"] = {"what": "the same sequence rendered with RTB_OPT_TILE_CULL = 2 (bin_tiles_kernel + raycast_binned_kernel per frame, "
+                                      "byte-identical frames), device-resident", "frames_per_s": n_frames / binned_s,
+                              "ms_per_frame": binned_s * 1e3 / n_frames, "value": n_frames * n_px / binned_s / 1e6, "unit": "Mrays/s"}
         print(json.dumps(line))
     if shared is not None:
         shared.close()

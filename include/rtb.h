@@ -190,6 +190,17 @@ int rtb_assemble_bands_device(rtb_ctx* ctx, int width, int height, int band_rows
 int rtb_render_sequence_device(rtb_ctx* ctx, int width, int height, int n_frames,
                                const float* cameras, void* d_rgba8, float* kernel_ms_total);
 
+/* Packs the per-frame records of up to 256 cameras AHEAD of their frames (16 floats each: origin0, dU, dV,
+ * rayDir), on a side stream of the context and behind whatever is already enqueued on `stream` (NULL = the
+ * context's own stream).  A later rtb_render* call whose camera and frame size equal one of them skips its
+ * own pack and only makes its stream wait for that camera's: the FP64 pack launch (one thread per primitive,
+ * ~20 us) leaves the frame's critical path -- what rtb_render_sequence_device does internally, offered for
+ * callers that drive the frames themselves (one process per GPU, rtb_render_bands_frame per frame).  Every call
+ * packs anew (nothing is reused from an earlier call); the slots are dropped by the next rtb_prepack_cameras,
+ * rtb_render_sequence_device or rtb_set_scene.  Cameras beyond the capacity are simply packed by their own
+ * render call.  No counterpart in the reference (it has one fixed camera, MainState.cpp:37-50). */
+int rtb_prepack_cameras(rtb_ctx* ctx, int width, int height, int n_cameras, const float* cameras, void* stream);
+
 /* Pinned host allocations for the e2e path (pageable buffers work too, only slower). */
 int rtb_host_alloc(void** out, size_t bytes);
 void rtb_host_free(void* p);

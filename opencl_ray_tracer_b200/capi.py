@@ -28,7 +28,7 @@ EXPORTED_SYMBOLS = [
     "rtb_assemble_bands_device", "rtb_transfer_bytes", "rtb_render_bands_frame", "rtb_peer_frame_create",
     "rtb_peer_frame_open", "rtb_peer_frame_close", "rtb_debug_device_records", "rtb_render_bands_host",
     "rtb_host_register", "rtb_host_unregister", "rtb_render_bands_frame_signal", "rtb_stream_wait_signal",
-    "rtb_peer_frame_signal_offset", "rtb_set_option", "rtb_get_option",
+    "rtb_peer_frame_signal_offset", "rtb_set_option", "rtb_get_option", "rtb_prepack_cameras",
 ]
 
 RTB_OPT_TILE_CULL = 1
@@ -74,6 +74,7 @@ def load_library(path=None):
     lib.rtb_host_unregister.argtypes = [vp]
     lib.rtb_render_bands_frame_signal.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, C.c_int, C.c_int, vp, vp, vp]
     lib.rtb_stream_wait_signal.argtypes = [vp, vp, C.c_uint, vp]
+    lib.rtb_prepack_cameras.argtypes = [vp, C.c_int, C.c_int, C.c_int, fp, vp]
     lib.rtb_set_option.argtypes = [vp, C.c_int, C.c_int]
     lib.rtb_get_option.argtypes = [vp, C.c_int, C.POINTER(C.c_int)]
     lib.rtb_peer_frame_signal_offset.argtypes = [C.c_size_t]
@@ -199,6 +200,11 @@ class Context:
 
     def __exit__(self, *a):
         self.close()
+
+    def prepack_cameras(self, width, height, cameras, stream=None):
+        """rtb_prepack_cameras: `cameras` = array (n, 16) of origin0, dU, dV, rayDir per frame."""
+        cams = np.ascontiguousarray(cameras, np.float32).reshape(-1, 16)
+        self._check(self.lib.rtb_prepack_cameras(self._h, int(width), int(height), len(cams), _fp(cams), C.c_void_p(stream or 0)))
 
     def set_option(self, option, value):
         """rtb_set_option, e.g. set_option(RTB_OPT_TILE_CULL, 1)."""

@@ -81,6 +81,16 @@ struct rtb_ctx {
     int tile_cull = 0;  // RTB_OPT_TILE_CULL
     void* d_bins = nullptr;        // tile_cull == 2: per-tile primitive bit words of the launch in flight, grow-only
     size_t d_bins_cap = 0;
+    // Records packed ahead of their frames (rtb_prepack_cameras, rtb_render_sequence_device): slot s holds the
+    // records of cam_slots[s].cam16 at width x height, packed on pack_stream; `ready` is recorded behind its pack.
+    struct CamSlot { float cam16[16]; cudaEvent_t ready; };
+    std::vector<CamSlot> cam_slots;      // events are created once and reused
+    int cam_slots_used = 0, cam_slots_w = 0, cam_slots_h = 0;
+    float4* d_cam_rec = nullptr;
+    size_t d_cam_rec_cap = 0;            // in float4
+    size_t cam_slot_stride = 0;          // float4 per slot
+    cudaStream_t pack_stream = nullptr;
+    cudaEvent_t ev_prepack = nullptr;
 };
 
 namespace {
@@ -243,6 +253,10 @@ void rtb_shutdown(rtb_ctx* ctx) {
     cudaFree(ctx->d_bad);
     cudaFree(ctx->d_progress);
     cudaFree(ctx->d_bins);
+    cudaFree(ctx->d_cam_rec);
+    for (auto& s : ctx->cam_slots) cudaEventDestroy(s.ready);
+    if (ctx->pack_stream) cudaStreamDestroy(ctx->pack_stream);
+    if (ctx->ev_prepack) cudaEventDestroy(ctx->ev_prepack);
     if (ctx->h_bad) cudaFreeHost(ctx->h_bad);
     if (ctx->h_rec) cudaFreeHost(ctx->h_rec);
     for (int i = 0; i < 3; ++i) cudaFree(ctx->d_out[i]);
@@ -265,6 +279,7 @@ int rtb_set_scene(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins, cons
     RTB_CUDA(ctx, cudaSetDevice(ctx->device));
     ctx->have_scene = false;
     ctx->packed_valid = false;
+    ctx->cam_slots_used = 0;
     ctx->host_scene_valid = false;
     cudaStream_t st = ctx->stream;
     RTB_CUDA(ctx, cudaStreamSynchronize(st));
@@ -350,13 +365,23 @@ int enqueue_pack(rtb_ctx* ctx, const CameraFrame& cf, int width, int height, flo
     return RTB_OK;
 }
 
-// Packs this frame's records on the device, unless d_rec already holds the records of exactly this
-// camera (same 16 floats, same frame size, same scene).
+// Makes this frame's records available to `stream` and returns where they are: a slot packed ahead of time for
+// exactly this camera and frame size (rtb_prepack_cameras; the stream then waits for that pack), d_rec if it
+// already holds them (same 16 floats, same frame size, same scene), else d_rec after a pack on `stream`.
 int upload_frame_records(rtb_ctx* ctx, const CameraFrame& cf, int width, int height, const float* o0,
-                         const float* du, const float* dv, const float* dir, cudaStream_t stream) {
+                         const float* du, const float* dv, const float* dir, cudaStream_t stream, const float4** rec) {
     float cam16[16];
     std::memcpy(cam16, o0, 16); std::memcpy(cam16 + 4, du, 16);
     std::memcpy(cam16 + 8, dv, 16); std::memcpy(cam16 + 12, dir, 16);
+    *rec = ctx->d_rec;
+    if (ctx->cam_slots_used > 0 && ctx->cam_slots_w == width && ctx->cam_slots_h == height) {
+        for (int s = 0; s < ctx->cam_slots_used; ++s)
+            if (std::memcmp(cam16, ctx->cam_slots[(size_t)s].cam16, sizeof cam16) == 0) {
+                RTB_CUDA(ctx, cudaStreamWaitEvent(stream, ctx->cam_slots[(size_t)s].ready, 0));
+                *rec = ctx->d_cam_rec + (size_t)s * ctx->cam_slot_stride;
+                return RTB_OK;
+            }
+    }
     if (ctx->packed_valid && ctx->packed_w == width && ctx->packed_h == height &&
         std::memcmp(cam16, ctx->packed_cam, sizeof cam16) == 0)
         return RTB_OK;
@@ -365,6 +390,55 @@ int upload_frame_records(rtb_ctx* ctx, const CameraFrame& cf, int width, int hei
     std::memcpy(ctx->packed_cam, cam16, sizeof cam16);
     ctx->packed_w = width; ctx->packed_h = height;
     ctx->packed_valid = true;
+    return RTB_OK;
+}
+
+// Packs the records of n cameras into slots on pack_stream, behind everything already enqueued on `stream`
+// (earlier frames may still be reading the slots).  Always packs: nothing is kept from an earlier call.
+constexpr int kMaxCamSlots = 256;
+int prepack_cameras(rtb_ctx* ctx, int width, int height, int n, const float* cameras, cudaStream_t stream) {
+    ctx->cam_slots_used = 0;
+    if (n <= 0) return RTB_OK;
+    if (n > kMaxCamSlots) n = kMaxCamSlots;
+    const size_t stride = frame_records(ctx);
+    while (n > 1 && stride * (size_t)n * sizeof(float4) > ((size_t)256 << 20)) n /= 2;  // at most 256 MB of records
+    if (!ctx->pack_stream) {
+        int lo = 0, hi = 0;
+        RTB_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        RTB_CUDA(ctx, cudaStreamCreateWithPriority(&ctx->pack_stream, cudaStreamNonBlocking, hi));
+        RTB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_prepack, cudaEventDisableTiming));
+    }
+    if (ctx->d_cam_rec_cap < stride * (size_t)n) {
+        RTB_CUDA(ctx, cudaDeviceSynchronize());
+        if (ctx->d_cam_rec) RTB_CUDA(ctx, cudaFree(ctx->d_cam_rec));
+        ctx->d_cam_rec = nullptr; ctx->d_cam_rec_cap = 0;
+        RTB_CUDA(ctx, cudaMalloc(&ctx->d_cam_rec, stride * (size_t)n * sizeof(float4)));
+        ctx->d_cam_rec_cap = stride * (size_t)n;
+    }
+    while ((int)ctx->cam_slots.size() < n) {
+        rtb_ctx::CamSlot s;
+        std::memset(s.cam16, 0, sizeof s.cam16);
+        RTB_CUDA(ctx, cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming));
+        ctx->cam_slots.push_back(s);
+    }
+    ctx->cam_slot_stride = stride;
+    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_prepack, stream));
+    RTB_CUDA(ctx, cudaStreamWaitEvent(ctx->pack_stream, ctx->ev_prepack, 0));
+    for (int s = 0; s < n; ++s) {
+        const float* c = cameras + 16 * (size_t)s;
+        CameraFrame cf;
+        if (!camera_prepare(c, c + 4, c + 8, c + 12, &cf)) {
+            char buf[96];
+            std::snprintf(buf, sizeof buf, "degenerate camera %d", s);
+            return fail(ctx, RTB_ERR_CAMERA, buf);
+        }
+        const int rc = enqueue_pack(ctx, cf, width, height, ctx->d_cam_rec + (size_t)s * stride, ctx->pack_stream);
+        if (rc != RTB_OK) return rc;
+        RTB_CUDA(ctx, cudaEventRecord(ctx->cam_slots[(size_t)s].ready, ctx->pack_stream));
+        std::memcpy(ctx->cam_slots[(size_t)s].cam16, c, 16 * sizeof(float));
+        ctx->cam_slots_used = s + 1;
+    }
+    ctx->cam_slots_w = width; ctx->cam_slots_h = height;
     return RTB_OK;
 }
 
@@ -452,7 +526,7 @@ int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width
     RTB_CUDA(ctx, launch_grid(p, ctx->sm_count, stream));
     RTB_CUDA(ctx, cudaEventRecord(ev.b, stream));
     ctx->ev_pending.push_back(ev);
-    ctx->launches += 1;
+    ctx->launches += (p.tile_cull == 2 && p.bin_words > 0) ? 2 : 1;  // bin_tiles_kernel + raycast_binned_kernel
     if (ctx->ev_pending.size() > 1024) return resolve_pending(ctx);
     return RTB_OK;
 }
@@ -495,10 +569,11 @@ int rtb_render_bands_device(rtb_ctx* ctx, int width, int height, const float ori
     if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
         return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
     cudaStream_t stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->stream;
-    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, stream);
+    const float4* frame_rec = nullptr;
+    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, stream, &frame_rec);
     if (rc != RTB_OK) return rc;
     const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
-    rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, band_rows, band_rank, band_world, local_rows,
+    rc = enqueue_grid(ctx, cf.cam, frame_rec, width, height, band_rows, band_rank, band_world, local_rows,
                       d_rgba8, d_prim_id, d_rgba_i32, stream);
     if (rc != RTB_OK) return rc;
     if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
@@ -539,14 +614,15 @@ int rtb_render_bands_frame_signal(rtb_ctx* ctx, int width, int height, const flo
     if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
         return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
     cudaStream_t stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->stream;
-    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, stream);
+    const float4* frame_rec = nullptr;
+    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, stream, &frame_rec);
     if (rc != RTB_OK) return rc;
     const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
     if (local_rows <= 0 && d_signal) {  // nothing to render: the signal still has to arrive
         static_assert(sizeof(unsigned int) == 4, "signal words are 32 bit");
         RTB_CUDA(ctx, launch_signal_only(static_cast<unsigned int*>(d_signal), stream));
     }
-    rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, band_rows, band_rank, band_world, local_rows,
+    rc = enqueue_grid(ctx, cf.cam, frame_rec, width, height, band_rows, band_rank, band_world, local_rows,
                       d_frame_rgba8, nullptr, nullptr, stream, 1, 0, nullptr, d_signal);
     if (rc != RTB_OK) return rc;
     if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
@@ -637,7 +713,8 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
     const double k_sum0 = ctx->kernel_ms_sum;
     cudaStream_t st = ctx->stream;
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total0, st));
-    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, st);
+    const float4* frame_rec = nullptr;
+    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, st, &frame_rec);
     if (rc != RTB_OK) return rc;
     const bool any_host = host[0] || host[1] || host[2];
     const size_t elem[3] = {4, 4, 16};
@@ -658,7 +735,7 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
         cs = ctx->copy_stream;
         ctx->progress_epoch += 1;
         if (ctx->progress_epoch == 0) ctx->progress_epoch = 1;
-        rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, 16, 0, 1, height, host[0] ? ctx->d_out[0] : nullptr,
+        rc = enqueue_grid(ctx, cf.cam, frame_rec, width, height, 16, 0, 1, height, host[0] ? ctx->d_out[0] : nullptr,
                           host[1] ? ctx->d_out[1] : nullptr, host[2] ? ctx->d_out[2] : nullptr, st, 0, n_chunks, bound);
         if (rc != RTB_OK) return rc;
         for (int k = 0; k < n_chunks; ++k) {
@@ -688,7 +765,7 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
             void* d[3];
             for (int i = 0; i < 3; ++i)
                 d[i] = host[i] ? static_cast<uint8_t*>(ctx->d_out[i]) + elem[i] * (size_t)y0 * width : nullptr;
-            rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, chunk_rows, k, n_chunks, rows, d[0], d[1], d[2], st);
+            rc = enqueue_grid(ctx, cf.cam, frame_rec, width, height, chunk_rows, k, n_chunks, rows, d[0], d[1], d[2], st);
             if (rc != RTB_OK) return rc;
             if (n_chunks > 1) {
                 RTB_CUDA(ctx, cudaEventRecord(ctx->ev_chunk[k], st));
@@ -733,7 +810,8 @@ int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origi
     if (rc != RTB_OK) return rc;
     const double k_sum0 = ctx->kernel_ms_sum;
     cudaStream_t st = ctx->stream;
-    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, st);
+    const float4* frame_rec = nullptr;
+    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, st, &frame_rec);
     if (rc != RTB_OK) return rc;
     if (local_rows > 0) {
         // chunk = whole bands (and a multiple of 16 rows, the progress granularity): about 2 MB each
@@ -747,7 +825,7 @@ int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origi
             ctx->progress_epoch += 1;
             if (ctx->progress_epoch == 0) ctx->progress_epoch = 1;
         }
-        rc = enqueue_grid(ctx, cf.cam, ctx->d_rec, width, height, band_rows, band_rank, band_world, local_rows,
+        rc = enqueue_grid(ctx, cf.cam, frame_rec, width, height, band_rows, band_rank, band_world, local_rows,
                           ctx->d_out[0], nullptr, nullptr, st, 0, flags ? n_chunks : 0, bound);
         if (rc != RTB_OK) return rc;
         const size_t band_bytes = row_bytes * (size_t)band_rows;
@@ -890,27 +968,42 @@ int rtb_render_sequence_device(rtb_ctx* ctx, int width, int height, int n_frames
     if (rc != RTB_OK) return rc;
     const double k0 = ctx->kernel_ms_sum;
     const size_t frame_bytes = 4 * (size_t)width * height;
-    for (int f = 0; f < n_frames; ++f) {
-        const float* c = cameras + 16 * (size_t)f;
-        CameraFrame cf;
-        if (!camera_prepare(c, c + 4, c + 8, c + 12, &cf)) {
-            char buf[96];
-            std::snprintf(buf, sizeof buf, "degenerate camera in frame %d", f);
-            cudaStreamSynchronize(st);
-            return fail(ctx, RTB_ERR_CAMERA, buf);
+    // The records of up to kMaxCamSlots frames are packed ahead on pack_stream (one small FP64 launch per
+    // frame, ~20 us each) while the main stream renders: frame f's launch only waits for ITS pack.
+    for (int f0 = 0; f0 < n_frames;) {
+        rc = prepack_cameras(ctx, width, height, n_frames - f0, cameras + 16 * (size_t)f0, st);
+        if (rc != RTB_OK) { cudaDeviceSynchronize(); ctx->cam_slots_used = 0; return rc; }
+        const int batch = ctx->cam_slots_used;
+        for (int s = 0; s < batch; ++s) {
+            const int f = f0 + s;
+            const float* c = cameras + 16 * (size_t)f;
+            CameraFrame cf;
+            camera_prepare(c, c + 4, c + 8, c + 12, &cf);  // checked by prepack_cameras
+            RTB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->cam_slots[(size_t)s].ready, 0));
+            rc = enqueue_grid(ctx, cf.cam, ctx->d_cam_rec + (size_t)s * ctx->cam_slot_stride, width, height, 4, 0, 1, height,
+                              static_cast<uint8_t*>(d_rgba8) + frame_bytes * (size_t)f, nullptr, nullptr, st);
+            if (rc != RTB_OK) { cudaDeviceSynchronize(); ctx->cam_slots_used = 0; return rc; }
         }
-        float4* rec = ctx->d_rec;
-        rc = enqueue_pack(ctx, cf, width, height, rec, st);
-        if (rc != RTB_OK) return rc;
-        rc = enqueue_grid(ctx, cf.cam, rec, width, height, 4, 0, 1, height,
-                          static_cast<uint8_t*>(d_rgba8) + frame_bytes * (size_t)f, nullptr, nullptr, st);
-        if (rc != RTB_OK) return rc;
+        f0 += batch;
     }
+    ctx->cam_slots_used = 0;  // nothing of this sequence is kept for later calls
     RTB_CUDA(ctx, cudaStreamSynchronize(st));
     rc = resolve_pending(ctx);
     if (rc != RTB_OK) return rc;
     if (kernel_ms_total) *kernel_ms_total = (float)(ctx->kernel_ms_sum - k0);
     return RTB_OK;
+}
+
+int rtb_prepack_cameras(rtb_ctx* ctx, int width, int height, int n_cameras, const float* cameras, void* stream) {
+    if (!ctx) return RTB_ERR_INVALID_ARG;
+    if (n_cameras < 0 || (n_cameras > 0 && !cameras)) return fail(ctx, RTB_ERR_INVALID_ARG, "null cameras");
+    if (n_cameras == 0) { ctx->cam_slots_used = 0; return RTB_OK; }
+    int rc = check_frame_args(ctx, width, height, cameras, cameras + 4, cameras + 8, cameras + 12);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    rc = prepack_cameras(ctx, width, height, n_cameras, cameras, stream ? static_cast<cudaStream_t>(stream) : ctx->stream);
+    if (rc != RTB_OK) ctx->cam_slots_used = 0;
+    return rc;
 }
 
 int rtb_host_alloc(void** out, size_t bytes) {
