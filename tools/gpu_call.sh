@@ -1,4 +1,5 @@
 set -x
 mkdir -p gpurun_out
-timeout -k 5 300 python -m pytest tests/test_gpu_prepack.py tests/test_gpu_tile_cull.py tests/test_gpu_bands_and_fullsize.py -x -q 2>&1 | tail -15
-timeout -k 5 300 python bench.py --workload c5 --steps 3 --warmup 1 > gpurun_out/bench_c5_n1_v7.json 2> gpurun_out/bench_c5_n1_v7.err; tail -c 1800 gpurun_out/bench_c5_n1_v7.json; tail -3 gpurun_out/bench_c5_n1_v7.err
+N=${NGPU:-8}
+timeout -k 5 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N > gpurun_out/bench_c3_n${N}_v7.json 2> gpurun_out/bench_c3_n${N}_v7.err; tail -c 400 gpurun_out/bench_c3_n${N}_v7.json; tail -3 gpurun_out/bench_c3_n${N}_v7.err
+timeout -k 5 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus $N --workload c5 --steps 3 --warmup 1 > gpurun_out/bench_c5_n${N}_v7.json 2> gpurun_out/bench_c5_n${N}_v7.err; tail -c 600 gpurun_out/bench_c5_n${N}_v7.json; tail -3 gpurun_out/bench_c5_n${N}_v7.err
