@@ -112,12 +112,15 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(s)}
 
 
-def ncu_traffic_bytes(workload):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, from the
-    committed ncu --set full capture (profiles/r01_ncu_traffic.json); None for other workloads."""
+def ncu_traffic_bytes(workload, key=None):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel (key = "binned": of the
+    two launches of a binned frame), from the committed ncu --set full captures (profiles/r01_ncu_traffic.json);
+    None for other workloads."""
     try:
         j = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))
         if j.get("workload") == workload:
+            if key:
+                j = j[key]
             return j["dram_bytes_read"] + j["dram_bytes_write"]
     except Exception:
         pass
@@ -714,7 +717,9 @@ def main():
                         "h2d_bytes_per_step": bn["h2d"], "d2h_bytes_per_step": bn["d2h"]},
                 "roofline": {"bound": "hbm", "achieved": frame_bytes / bk_s / 1e9 if bk_s > 0 else None, "peak": peaks.get("hbm_gbs"),
                              "unit": "GB/s", "frac": (frame_bytes / bk_s / 1e9 / peaks["hbm_gbs"]) if (bk_s > 0 and peaks.get("hbm_gbs")) else None,
-                             "traffic": None, "kernel": "bin_tiles_kernel + raycast_binned_kernel",
+                             "traffic": ncu_traffic_bytes(args.workload, "binned") if r["world"] == 1 else None,
+                             "traffic_unit": "bytes of DRAM traffic per frame (ncu capture in profiles/, not this run): the frame stays in the 126 MB L2",
+                             "kernel": "bin_tiles_kernel + raycast_binned_kernel",
                              "algorithmic_bytes": "the frame write, 4 B per ray (this rank's rows)", "peak_source": peaks_src},
                 "clocks": bn["clocks"],
             }
