@@ -1,5 +1,5 @@
 set -x
 mkdir -p gpurun_out
-timeout -k 5 400 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref_c3_v7.json 2> gpurun_out/bench_ref_c3_v7.err; tail -c 900 gpurun_out/bench_ref_c3_v7.json; tail -3 gpurun_out/bench_ref_c3_v7.err
-timeout -k 5 300 ncu --set full --clock-control none --import-source on -k regex:raycast_grid -c 1 --launch-skip 3 -o gpurun_out/grid_full_v7 python tools/variant_sweep.py --child --workload c3 --reps 2 --flush > gpurun_out/ncu_grid.log 2>&1; tail -2 gpurun_out/ncu_grid.log
-timeout -k 5 300 ncu --metrics sm__sass_thread_inst_executed_op_ffma_pred_on.sum,sm__sass_thread_inst_executed_op_fadd_pred_on.sum,sm__sass_thread_inst_executed_op_fmul_pred_on.sum,sm__cycles_elapsed.max,gpu__time_duration.sum,smsp__inst_executed.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -k regex:"raycast_grid|binned|bin_tiles" -c 6 --csv --log-file gpurun_out/sass_ops_v7.csv python tools/variant_sweep.py --workload c3 --variants 0,binned --reps 2 --flush > gpurun_out/ncu_ops.log 2>&1; tail -2 gpurun_out/ncu_ops.log
+timeout -k 5 600 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log; tail -3 gpurun_out/pytest_gpu.log
+timeout -k 5 200 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; tail -1 gpurun_out/smoke.log | cut -c1-200
+timeout -k 5 400 python bench.py > gpurun_out/bench_c3_v8.json 2> gpurun_out/bench_c3_v8.err; tail -c 300 gpurun_out/bench_c3_v8.json; tail -3 gpurun_out/bench_c3_v8.err
