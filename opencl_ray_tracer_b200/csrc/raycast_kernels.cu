@@ -386,7 +386,7 @@ __device__ __forceinline__ void signal_completion(const GridParams& p, int tile_
 // stage.  The values are those of rtb_bound_row_w / rtb_bound_row_c, computed once per row
 // instead of once per thread (16 threads of a CTA share a row).
 template <int PX, int WARPS_X, int WARPS_Y, int G = kBoundGroup, int MIN_CTAS = (PX >= 16 ? 3 : 4), int S = 1,
-          bool TAB = false, int TP = kTabPrims, bool PIPE = true>
+          bool TAB = false, int TP = kTabPrims, int PIPE = 1>
 __global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y * S, MIN_CTAS)
 raycast_grid_kernel(const GridParams p) {
     constexpr int kTabPrims = TP;  // primitives per staged chunk of the row-table variants
@@ -485,7 +485,7 @@ raycast_grid_kernel(const GridParams p) {
             __syncthreads();
             if (tid == 0 && k + 2 < n_chunks) issue(k + 2);
             const float4* tab = &rowtab[b][wy * 4 + ly];
-            if constexpr (PIPE && G == 4) {
+            if constexpr (PIPE != 0 && G == 4) {
                 dense_chunk_tab<PX, kTileH, S>(p, tab, cnt, first, split, v, st);
             } else {
 #pragma unroll 1
@@ -1035,7 +1035,8 @@ GridLaunchShape shape_of(int width, int local_rows) {
 struct Tiling { int px, wx, wy, split; double cost; };
 static const Tiling kTilings[] = {
     {16, 2, 2, 1, 1.00},  // 256 x 8 pixels, 4 warps
-    {16, 2, 1, 2, 1.00},  // 256 x 4 pixels, 4 warps, two per tile: short band sets (8-GPU frames)
+    {16, 2, 1, 2, 1.07},  // 256 x 4 pixels, 4 warps, two per tile: short band sets (8-GPU frames); +7 %: table rows per
+                          // pixel doubled, nearest-hit merge (C3 0.756 vs 0.704 ms; at C2's 128 primitives it lost 18 %)
     {8, 2, 2, 1, 1.10},   // 128 x 8 pixels
     {4, 2, 2, 1, 1.35},   //  64 x 8 pixels: small frames
 };
@@ -1070,7 +1071,7 @@ GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
 // Launch of one instantiation: the id columns are dynamic shared memory (PX x threads ints); together
 // with the static staging / table area that can pass 48 KB, which needs the opt-in attribute (set once
 // per instantiation and device).
-template <int PX, int WX, int WY, int G, int MINB, int S, bool TAB, int TP, bool PIPE>
+template <int PX, int WX, int WY, int G, int MINB, int S, bool TAB, int TP, int PIPE>
 cudaError_t launch_instance(const GridParams& p, dim3 grid, cudaStream_t stream) {
     constexpr int kThreads = 32 * WX * WY * S;
     constexpr int kDyn = PX * kThreads * (int)sizeof(int);
@@ -1088,7 +1089,7 @@ cudaError_t launch_instance(const GridParams& p, dim3 grid, cudaStream_t stream)
     return cudaGetLastError();
 }
 
-template <int PX, int WX, int WY, int G, int MINB, int S = 1, bool TAB = false, int TP = kTabPrims, bool PIPE = true>
+template <int PX, int WX, int WY, int G, int MINB, int S = 1, bool TAB = false, int TP = kTabPrims, int PIPE = 1>
 cudaError_t launch_variant(const GridParams& p, cudaStream_t stream) {
     GridLaunchShape s = shape_of<PX, WX, WY>(p.width, p.local_rows);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
@@ -1194,6 +1195,8 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) 
         case 20: return launch_variant<16, 2, 1, 4, 4, 2, true>(p, stream);  // 2 warps per 128x4 tile
         case 31: return launch_variant<16, 2, 2, 4, 6, 1, true, 64>(p, stream);  // 6 CTAs/SM (<= 85 registers)
         case 11: return launch_variant<16, 2, 2, 4, 4, 1, true, kTabPrims, false>(p, stream);  // row table, loads not pipelined
+        // measured and dropped: two groups (8 primitives) per loop iteration to halve the loop control on the uniform
+        // pipe: C3 0.7025 -> 0.7126 ms, C4 10.528 -> 10.684 ms (profiles/r01_variant_sweep_unroll2.jsonl)
         case 15: return launch_variant<8, 2, 2, 4, 8, 1, true>(p, stream);
         default: break;
     }

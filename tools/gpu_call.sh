@@ -1,5 +1,2 @@
-set -x
 mkdir -p gpurun_out
-timeout -k 5 600 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log; tail -3 gpurun_out/pytest_gpu.log
-timeout -k 5 200 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; tail -1 gpurun_out/smoke.log | cut -c1-200
-timeout -k 5 400 python bench.py > gpurun_out/bench_c3_v8.json 2> gpurun_out/bench_c3_v8.err; tail -c 300 gpurun_out/bench_c3_v8.json; tail -3 gpurun_out/bench_c3_v8.err
+for wl in c2 c1r; do timeout -k 5 200 python tools/variant_sweep.py --workload $wl --variants 0,10,15,20 --flush --reps 50; done > gpurun_out/sweep_small.jsonl 2>&1; cut -c1-140 gpurun_out/sweep_small.jsonl
