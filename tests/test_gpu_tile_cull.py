@@ -128,3 +128,20 @@ def test_cli_frames_are_identical_in_every_mode(tmp_path):
     assert data[0] == data[1] == data[2] and len(data[0]) > 1000
     r = subprocess.run([exe, "--tile-cull", "7"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 2
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("world,band_rows", [(2, 16), (3, 16), (8, 16), (3, 4), (2, 48)])
+def test_host_frame_assembled_from_every_ranks_bands(ctx, mode, world, band_rows):
+    """rtb_render_bands_host for every rank of a world (one GPU plays them all): the bands, delivered through the
+    in-launch progress chunks, make up the dense frame -- tiles that straddle bands and chunk bounds included."""
+    w, h = 1000, 700
+    ctx.set_scene(*hs.random_scene(w, h, 70, 70, 41).as_tuple())
+    cam = hs.orbit_camera(w, h, 7)
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
+    full = ctx.render(w, h, cam, want=("rgba8",))["rgba8"]
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, mode)
+    frame = np.zeros((h, w, 4), np.uint8)
+    for rank in range(world):
+        ctx.render_bands_host(w, h, cam, band_rows, rank, world, frame)
+    assert np.array_equal(frame, full)

@@ -1,2 +1,2 @@
 mkdir -p gpurun_out
-for wl in c2 c1r; do timeout -k 5 200 python tools/variant_sweep.py --workload $wl --variants 0,10,15,20 --flush --reps 50; done > gpurun_out/sweep_small.jsonl 2>&1; cut -c1-140 gpurun_out/sweep_small.jsonl
+timeout -k 5 300 python -m pytest tests/test_gpu_tile_cull.py -x -q 2>&1 | tail -12
