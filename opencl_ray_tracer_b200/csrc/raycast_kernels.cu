@@ -1177,7 +1177,8 @@ static cudaError_t launch_binned_variant(const GridParams& p, cudaStream_t strea
         case 2: return launch_binned<16, 2, 4, 1, 6>(p, stream);   // 128 x 16 tiles
         // measured and dropped (profiles/r01_variant_sweep_binned_v3_tilings.jsonl; C3 / C4 ms against 0.0339 / 0.109):
         // 64 x 16 tiles of two 32 x 16 warps 0.0356 / 0.132; of two 64 x 8 warps 0.0376 / 0.136; one warp per 32 x 16
-        // tile 0.0392 / 0.190
+        // tile 0.0392 / 0.190; per-warp lists instead of one per CTA (no CTA barrier, every warp expands the tile's words
+        // itself) 0.0333 / 0.134 against 0.0322 / 0.106 (profiles/r01_variant_sweep_binned_v5_warp_lists.jsonl)
         default: return launch_binned<16, 2, 2, 2, 6>(p, stream);  // 64 x 32 tiles, 4 warps of 32 x 16 pixels
     }
 }
