@@ -139,107 +139,100 @@ __device__ __forceinline__ void exact_update(const GridParams& p, int prim, floa
     }
 }
 
-// The dense test: G primitives of a staged chunk against this thread's PX rays.  Per ray and
-// primitive 2 FMA as one FFMA2 per ray pair and stage (conic bound q) + half a LOP3 (AND of the
-// IEEE patterns: bit 30 survives only if every ray has q >= 2); per thread and primitive
-// 1 LDS.128 + 1 LDS.32 + 4 FP32 ops (row terms);
-// one warp vote per G primitives.
+#define RTB_Q_FAIL_BIT 0x40000000u  // bit 30 of a float q >= 0: set <=> q >= 2 (or Inf / NaN)
+
+// One primitive's bound on this thread's PX rays: t = (sA, rowW, h, rowC); true if some ray of the thread
+// passes.  w = sA*u + rowW is ONE packed FFMA2 per ray pair.  The pass test then runs on two pipes at once:
+//   * KQ ray pairs take the q form: a second FFMA2 (q = w*w + rowC, FMA pipe) and one LOP3 that ANDs both IEEE
+//     patterns into an accumulator ("q >= 2" is bit 30);
+//   * the other pairs take the half-width form |w| < h: a 3-input FMNMX with |.| on both new operands folds them
+//     into a running minimum (ALU pipe, no second FMA).
+// The ray set "|w| < h" contains the set "fmaf(w, w, rowC) < 2" (raycast_math.h), which contains the footprint:
+// either test may be used on any ray.  With KQ = 0 the FMA pipe idles while the 16-lane ALU pipe does 8 FMNMX3
+// per primitive; with KQ = PX/2 (the former kernel) it is the other way round.  NaNs drop out of fminf and set
+// bit 30, Inf never beats h: such rays fail both tests.
+template <int PX, int KQ>
+__device__ __forceinline__ bool bound_test(const float4 t, const PixelState<PX>& st) {
+    static_assert(KQ >= 0 && KQ <= PX / 2, "KQ counts ray pairs");
+    const uint64_t S2 = pack2(t.x, t.x), W2 = pack2(t.y, t.y);
+    float m = __int_as_float(0x7f800000);
+    uint32_t a = 0xFFFFFFFFu;
+    if constexpr (KQ > 0) {
+        const uint64_t C2 = pack2(t.w, t.w);
+#pragma unroll
+        for (int j = 0; j < KQ; ++j) {
+            const uint64_t w2 = ffma2(st.u2[j], S2, W2);
+            const uint64_t q2 = ffma2(w2, w2, C2);
+            uint32_t q0, q1;
+            unpack2u(q2, q0, q1);
+            a &= q0 & q1;
+        }
+    }
+#pragma unroll
+    for (int j = KQ; j < PX / 2; ++j) {
+        const uint64_t w2 = ffma2(st.u2[j], S2, W2);
+        float lo, hi;
+        unpack2(w2, lo, hi);
+        m = fminf(fminf(m, fabsf(lo)), fabsf(hi));
+    }
+    bool pass = (KQ < PX / 2) && (m < t.z);
+    if constexpr (KQ > 0) pass = pass || ((a & RTB_Q_FAIL_BIT) == 0u);
+    return pass;
+}
+
+// The vote of a group of G primitives and, behind it, the exact updates of those whose bound some ray of the
+// warp passed.
 template <int PX, int G>
+__device__ __forceinline__ void resolve_group(const GridParams& p, const bool (&pass)[G], int first_prim, float v,
+                                              PixelState<PX>& st) {
+    bool any = false;
+#pragma unroll
+    for (int g = 0; g < G; ++g) any = any || pass[g];
+    if (__any_sync(0xFFFFFFFFu, any)) {
+        uint32_t mask = 0u;
+#pragma unroll
+        for (int g = 0; g < G; ++g) mask |= pass[g] ? (1u << g) : 0u;
+#pragma unroll 1
+        for (int g = 0; g < G; ++g)
+            if (__any_sync(0xFFFFFFFFu, (mask >> g) & 1u)) exact_update<PX>(p, first_prim + g, v, st);
+    }
+}
+
+// The dense test without a row table: G primitives of a staged chunk against this thread's PX rays, the row
+// terms (rowW, rowC, h) computed per thread and primitive.
+template <int PX, int G, int KQ>
 __device__ __forceinline__ void bound_group(const GridParams& p, const float4* __restrict__ rec, int first_prim,
                                             float v, PixelState<PX>& st) {
-    uint32_t acc[G];
+    bool pass[G];
 #pragma unroll
     for (int g = 0; g < G; ++g) {
         const float4 r0 = rec[2 * g];                                 // sA, k1, k0, e
         const float r1 = *reinterpret_cast<const float*>(rec + 2 * g + 1);  // cv
         const RtbBound b = {r0.x, r0.y, r0.z, r0.w, r1, 0.f, 0.f, 0.f};
-        const float rowW = rtb_bound_row_w(b, v), rowC = rtb_bound_row_c(b, v);
-        // w = sA*u + rowW; q = w*w + rowC on two rays per FFMA2 (same roundings per ray as rtb_bound_q)
-        const uint64_t S2 = pack2(b.sA, b.sA), W2 = pack2(rowW, rowW), C2 = pack2(rowC, rowC);
-        uint32_t a = 0xFFFFFFFFu;
-#pragma unroll
-        for (int j = 0; j < PX / 2; ++j) {
-            const uint64_t w2 = ffma2(st.u2[j], S2, W2);
-            const uint64_t q2 = ffma2(w2, w2, C2);
-            uint32_t q0, q1;
-            unpack2u(q2, q0, q1);
-            a &= q0 & q1;
-        }
-        acc[g] = a;
+        const float c = rtb_bound_row_c(b, v);
+        pass[g] = bound_test<PX, KQ>(make_float4(b.sA, rtb_bound_row_w(b, v), rtb_bound_h_of_c(c), c), st);
     }
-    uint32_t all = acc[0];
-#pragma unroll
-    for (int g = 1; g < G; ++g) all &= acc[g];
-    if (__any_sync(0xFFFFFFFFu, (all & RTB_BOUND_FAIL_BIT) == 0u)) {
-#pragma unroll 1
-        for (int g = 0; g < G; ++g) {
-            uint32_t a = acc[0];
-#pragma unroll
-            for (int h = 1; h < G; ++h) a = (g == h) ? acc[h] : a;
-            if (__any_sync(0xFFFFFFFFu, (a & RTB_BOUND_FAIL_BIT) == 0u)) exact_update<PX>(p, first_prim + g, v, st);
-        }
-    }
+    resolve_group<PX, G>(p, pass, first_prim, v, st);
 }
 
 // Same dense test with the per-row terms taken from the CTA's row table (built once per chunk by
-// all threads, see the kernel): ONE LDS.128 (sA, rowW, rowC, -) per thread and primitive and no
-// scalar FP32 work in the loop -- 16 FFMA2 + 8 LOP3 + 1 LDS for the 16 rays of a thread.
-// `tab` points at this thread's row of the first primitive; consecutive primitives are ROWS apart.
-template <int PX, int G, int ROWS>
+// all threads, see the kernel): ONE LDS.128 (sA, rowW, h, rowC) per thread and primitive and no
+// scalar FP32 work in the loop.  `tab` points at this thread's row of the first primitive; consecutive
+// primitives are ROWS apart.
+template <int PX, int G, int ROWS, int KQ>
 __device__ __forceinline__ void bound_group_tab(const GridParams& p, const float4* __restrict__ tab, int first_prim,
                                                 float v, PixelState<PX>& st) {
-    uint32_t acc[G];
+    bool pass[G];
 #pragma unroll
-    for (int g = 0; g < G; ++g) {
-        const float4 t = tab[g * ROWS];
-        const uint64_t S2 = pack2(t.x, t.x), W2 = pack2(t.y, t.y), C2 = pack2(t.z, t.z);
-        uint32_t a = 0xFFFFFFFFu;
-#pragma unroll
-        for (int j = 0; j < PX / 2; ++j) {
-            const uint64_t w2 = ffma2(st.u2[j], S2, W2);
-            const uint64_t q2 = ffma2(w2, w2, C2);
-            uint32_t q0, q1;
-            unpack2u(q2, q0, q1);
-            a &= q0 & q1;
-        }
-        acc[g] = a;
-    }
-    uint32_t all = acc[0];
-#pragma unroll
-    for (int g = 1; g < G; ++g) all &= acc[g];
-    if (__any_sync(0xFFFFFFFFu, (all & RTB_BOUND_FAIL_BIT) == 0u)) {
-#pragma unroll 1
-        for (int g = 0; g < G; ++g) {
-            uint32_t a = acc[0];
-#pragma unroll
-            for (int h = 1; h < G; ++h) a = (g == h) ? acc[h] : a;
-            if (__any_sync(0xFFFFFFFFu, (a & RTB_BOUND_FAIL_BIT) == 0u)) exact_update<PX>(p, first_prim + g, v, st);
-        }
-    }
-}
-
-// One primitive's bound on this thread's PX rays: AND of the IEEE patterns of q (bit 30 = "q >= 2").
-template <int PX>
-__device__ __forceinline__ uint32_t bound_test(const float4 t, const PixelState<PX>& st) {
-    const uint64_t S2 = pack2(t.x, t.x), W2 = pack2(t.y, t.y), C2 = pack2(t.z, t.z);
-    uint32_t a = 0xFFFFFFFFu;
-#pragma unroll
-    for (int j = 0; j < PX / 2; ++j) {
-        const uint64_t w2 = ffma2(st.u2[j], S2, W2);
-        const uint64_t q2 = ffma2(w2, w2, C2);
-        uint32_t q0, q1;
-        unpack2u(q2, q0, q1);
-        a &= q0 & q1;
-    }
-    return a;
+    for (int g = 0; g < G; ++g) pass[g] = bound_test<PX, KQ>(tab[g * ROWS], st);
+    resolve_group<PX, G>(p, pass, first_prim, v, st);
 }
 
 // The dense loop over one staged chunk, software-pipelined: the table entries of the next two
 // primitives are requested (LDS.128 off a running pointer, no address arithmetic on the critical
 // path) while the current two are being tested, so no warp waits for shared memory at the top of a
-// group (before: 19 % of the stall samples sat on the first FFMA2 after the loads and on the IMAD
-// feeding their address).  Groups of 4 primitives per vote; this warp takes groups split, split+S, ...
-template <int PX, int ROWS, int S>
+// group.  Groups of 4 primitives per vote; this warp takes groups split, split+S, ...
+template <int PX, int ROWS, int S, int KQ>
 __device__ __forceinline__ void dense_chunk_tab(const GridParams& p, const float4* __restrict__ tab, int cnt,
                                                 int first_prim, int split, float v, PixelState<PX>& st) {
     constexpr int G = 4;
@@ -250,26 +243,17 @@ __device__ __forceinline__ void dense_chunk_tab(const GridParams& p, const float
 #pragma unroll 1
     for (; j < cnt; j += S * G) {
         const float4 c2 = t[2 * ROWS], c3 = t[3 * ROWS];
-        uint32_t acc[G];
-        acc[0] = bound_test<PX>(c0, st);
-        acc[1] = bound_test<PX>(c1, st);
+        bool pass[G];
+        pass[0] = bound_test<PX, KQ>(c0, st);
+        pass[1] = bound_test<PX, KQ>(c1, st);
         // next group's first two entries; past the end the last group is read again (stays inside the table)
         const int jn = min(j + S * G, cnt - G);
         const float4* tn = tab + jn * ROWS;
         c0 = tn[0];
         c1 = tn[ROWS];
-        acc[2] = bound_test<PX>(c2, st);
-        acc[3] = bound_test<PX>(c3, st);
-        const uint32_t all = acc[0] & acc[1] & acc[2] & acc[3];
-        if (__any_sync(0xFFFFFFFFu, (all & RTB_BOUND_FAIL_BIT) == 0u)) {
-#pragma unroll 1
-            for (int g = 0; g < G; ++g) {
-                uint32_t a = acc[0];
-#pragma unroll
-                for (int h = 1; h < G; ++h) a = (g == h) ? acc[h] : a;
-                if (__any_sync(0xFFFFFFFFu, (a & RTB_BOUND_FAIL_BIT) == 0u)) exact_update<PX>(p, first_prim + j + g, v, st);
-            }
-        }
+        pass[2] = bound_test<PX, KQ>(c2, st);
+        pass[3] = bound_test<PX, KQ>(c3, st);
+        resolve_group<PX, G>(p, pass, first_prim + j, v, st);
         t = tn;
     }
 }
@@ -386,7 +370,7 @@ __device__ __forceinline__ void signal_completion(const GridParams& p, int tile_
 // stage.  The values are those of rtb_bound_row_w / rtb_bound_row_c, computed once per row
 // instead of once per thread (16 threads of a CTA share a row).
 template <int PX, int WARPS_X, int WARPS_Y, int G = kBoundGroup, int MIN_CTAS = (PX >= 16 ? 3 : 4), int S = 1,
-          bool TAB = false, int TP = kTabPrims, int PIPE = 1>
+          bool TAB = false, int TP = kTabPrims, int PIPE = 1, int KQ = 0>
 __global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y * S, MIN_CTAS)
 raycast_grid_kernel(const GridParams p) {
     constexpr int kTabPrims = TP;  // primitives per staged chunk of the row-table variants
@@ -477,7 +461,8 @@ raycast_grid_kernel(const GridParams p) {
                 const float4 r0 = stage[b][2 * prim];
                 const float r1 = *reinterpret_cast<const float*>(&stage[b][2 * prim + 1]);
                 const RtbBound bd = {r0.x, r0.y, r0.z, r0.w, r1, 0.f, 0.f, 0.f};
-                rowtab[b][i] = make_float4(bd.sA, rtb_bound_row_w(bd, tab_v), rtb_bound_row_c(bd, tab_v), 0.f);
+                const float rc = rtb_bound_row_c(bd, tab_v);
+                rowtab[b][i] = make_float4(bd.sA, rtb_bound_row_w(bd, tab_v), rtb_bound_h_of_c(rc), rc);
             }
             // table b is complete; stage[b] has been consumed and may be refilled.  Table b is next
             // rebuilt two chunks on, behind the barrier of chunk k+1, which a warp only reaches
@@ -486,15 +471,15 @@ raycast_grid_kernel(const GridParams p) {
             if (tid == 0 && k + 2 < n_chunks) issue(k + 2);
             const float4* tab = &rowtab[b][wy * 4 + ly];
             if constexpr (PIPE != 0 && G == 4) {
-                dense_chunk_tab<PX, kTileH, S>(p, tab, cnt, first, split, v, st);
+                dense_chunk_tab<PX, kTileH, S, KQ>(p, tab, cnt, first, split, v, st);
             } else {
 #pragma unroll 1
                 for (int j = split * G; j < cnt; j += S * G)
-                    bound_group_tab<PX, G, kTileH>(p, tab + j * kTileH, first + j, v, st);
+                    bound_group_tab<PX, G, kTileH, KQ>(p, tab + j * kTileH, first + j, v, st);
             }
         } else {
 #pragma unroll 1
-            for (int j = split * G; j < cnt; j += S * G) bound_group<PX, G>(p, &stage[b][2 * j], first + j, v, st);
+            for (int j = split * G; j < cnt; j += S * G) bound_group<PX, G, KQ>(p, &stage[b][2 * j], first + j, v, st);
             if (k + 2 < n_chunks) {
                 __syncthreads();  // every warp is done reading stage[b] before TMA refills it
                 if (tid == 0) issue(k + 2);
@@ -667,9 +652,9 @@ raycast_cull_kernel(const GridParams p) {
             for (int j = 0; j < total; ++j) {
                 const float4 a = list[2 * j], c = list[2 * j + 1];
                 const RtbBound s = {a.x, a.y, a.z, a.w, c.x, 0.f, 0.f, 0.f};
-                const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), rtb_bound_row_c(s, v), 0.f);
-                const uint32_t acc = bound_test<PX>(t, st);
-                if (__any_sync(0xFFFFFFFFu, (acc & RTB_BOUND_FAIL_BIT) == 0u)) exact_update<PX>(p, __float_as_int(c.y), v, st);
+                // few primitives reach this loop: the q form (two FFMA2 per ray pair) saves the square root of the half-width
+                const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), 0.f, rtb_bound_row_c(s, v));
+                if (__any_sync(0xFFFFFFFFu, bound_test<PX, PX / 2>(t, st))) exact_update<PX>(p, __float_as_int(c.y), v, st);
             }
             total = 0;
             if (k != n_batches - 1) __syncthreads();  // every warp has read the list before it is refilled
@@ -957,9 +942,9 @@ raycast_binned_kernel(const GridParams p) {
             for (int e = 0; e < n; ++e) {
                 const float4 a = s_rec[e][0];
                 const RtbBound s = {a.x, a.y, a.z, a.w, s_rec[e][1].x, 0.f, 0.f, 0.f};
-                const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), rtb_bound_row_c(s, v), 0.f);
-                const uint32_t acc = bound_test<PX>(t, st);
-                if (__any_sync(0xFFFFFFFFu, (acc & RTB_BOUND_FAIL_BIT) == 0u)) {
+                // few primitives reach this loop: the q form (two FFMA2 per ray pair) saves the square root of the half-width
+                const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), 0.f, rtb_bound_row_c(s, v));
+                if (__any_sync(0xFFFFFFFFu, bound_test<PX, PX / 2>(t, st))) {
                     warp_hit = true;
                     exact_update_rec<PX>(p, s_prim[e], s_rec[e][2], s_rec[e][3], s_rec[e][4], v, st);
                 }
@@ -1035,10 +1020,10 @@ GridLaunchShape shape_of(int width, int local_rows) {
 struct Tiling { int px, wx, wy, split; double cost; };
 static const Tiling kTilings[] = {
     {16, 2, 2, 1, 1.00},  // 256 x 8 pixels, 4 warps
-    {16, 2, 1, 2, 1.07},  // 256 x 4 pixels, 4 warps, two per tile: short band sets (8-GPU frames); +7 %: table rows per
-                          // pixel doubled, nearest-hit merge (C3 0.756 vs 0.704 ms; at C2's 128 primitives it lost 18 %)
-    {8, 2, 2, 1, 1.10},   // 128 x 8 pixels
-    {4, 2, 2, 1, 1.35},   //  64 x 8 pixels: small frames
+    {16, 2, 1, 2, 1.08},  // 256 x 4 pixels, 4 warps, two per tile: short band sets (8-GPU frames); +8 %: table rows per
+                          // pixel doubled, nearest-hit merge (C3 0.653 vs 0.603 ms)
+    {8, 2, 2, 1, 1.23},   // 128 x 8 pixels (C3 0.741 ms: the per-primitive LDS / compare / loop is shared by 8 rays only)
+    {4, 2, 2, 1, 1.60},   //  64 x 8 pixels: small frames
 };
 
 // The CTA scheduler spreads a grid evenly over the SMs and a CTA's warps over the 4 schedulers of
@@ -1071,7 +1056,7 @@ GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
 // Launch of one instantiation: the id columns are dynamic shared memory (PX x threads ints); together
 // with the static staging / table area that can pass 48 KB, which needs the opt-in attribute (set once
 // per instantiation and device).
-template <int PX, int WX, int WY, int G, int MINB, int S, bool TAB, int TP, int PIPE>
+template <int PX, int WX, int WY, int G, int MINB, int S, bool TAB, int TP, int PIPE, int KQ = 0>
 cudaError_t launch_instance(const GridParams& p, dim3 grid, cudaStream_t stream) {
     constexpr int kThreads = 32 * WX * WY * S;
     constexpr int kDyn = PX * kThreads * (int)sizeof(int);
@@ -1080,20 +1065,20 @@ cudaError_t launch_instance(const GridParams& p, dim3 grid, cudaStream_t stream)
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     if (configured_device != dev) {
-        e = cudaFuncSetAttribute(raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP, PIPE>,
+        e = cudaFuncSetAttribute(raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP, PIPE, KQ>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, kDyn);
         if (e != cudaSuccess) return e;
         configured_device = dev;
     }
-    raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP, PIPE><<<grid, dim3(kThreads), kDyn, stream>>>(p);
+    raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP, PIPE, KQ><<<grid, dim3(kThreads), kDyn, stream>>>(p);
     return cudaGetLastError();
 }
 
-template <int PX, int WX, int WY, int G, int MINB, int S = 1, bool TAB = false, int TP = kTabPrims, int PIPE = 1>
+template <int PX, int WX, int WY, int G, int MINB, int S = 1, bool TAB = false, int TP = kTabPrims, int PIPE = 1, int KQ = 0>
 cudaError_t launch_variant(const GridParams& p, cudaStream_t stream) {
     GridLaunchShape s = shape_of<PX, WX, WY>(p.width, p.local_rows);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
-    return launch_instance<PX, WX, WY, G, MINB, S, TAB, TP, PIPE>(p, s.grid, stream);
+    return launch_instance<PX, WX, WY, G, MINB, S, TAB, TP, PIPE, KQ>(p, s.grid, stream);
 }
 
 template <int PX, int WX, int WY, int MINB>
@@ -1199,6 +1184,10 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) 
         // measured and dropped: two groups (8 primitives) per loop iteration to halve the loop control on the uniform
         // pipe: C3 0.7025 -> 0.7126 ms, C4 10.528 -> 10.684 ms (profiles/r01_variant_sweep_unroll2.jsonl)
         case 15: return launch_variant<8, 2, 2, 4, 8, 1, true>(p, stream);
+        // KQ = ray pairs (of 8) whose pass test takes the q form (second FFMA2 + LOP3) instead of |w| < h (FMNMX3); C3 ms for
+        // KQ = 0 / 1 / 2 / 3 / 4 / 6 / 8: 0.610 / 0.612 / 0.611 / 0.625 / 0.636 / 0.682 / 0.715 (profiles/r01_variant_sweep_kq.jsonl)
+        case 44: return launch_variant<16, 2, 2, 4, 4, 1, true, kTabPrims, 1, 4>(p, stream);
+        case 48: return launch_variant<16, 2, 2, 4, 4, 1, true, kTabPrims, 1, 8>(p, stream);
         default: break;
     }
     const GridLaunchShape s = grid_launch_shape(p.width, p.local_rows, sm_count);

@@ -74,10 +74,11 @@ extern "C" int emu_check_bounds(int width, int height, const float* cam8, int nc
             const float u = rtb_cam_u(cam, (float)x, fy);
             for (int i = 0; i < nc + ns; ++i) {
                 const RtbBound& b = bnd[i];
+                // the kernels' test, |w| < h; it must also accept every ray the q form (which the packer's error
+                // budget is written for) accepts
+                const bool bound_pass = rtb_bound_passes(b.sA, rtb_bound_row_w(b, v), rtb_bound_row_h(b, v), u);
                 const float q = rtb_bound_q(b.sA, rtb_bound_row_w(b, v), rtb_bound_row_c(b, v), u);
-                uint32_t bits;
-                __builtin_memcpy(&bits, &q, 4);
-                const bool bound_pass = (bits & RTB_BOUND_FAIL_BIT) == 0u;
+                if (q < 2.0f && !bound_pass) viol += 1;
                 bool in_foot;
                 if (i < nc) {
                     const RtbSlab &s0 = slabs[3 * i], &s1 = slabs[3 * i + 1], &s2 = slabs[3 * i + 2];
@@ -136,11 +137,8 @@ extern "C" int emu_check_tile_cull(int width, int height, const float* cam8, int
                 const float fy = (float)(y_lo + r);
                 const float v = rtb_cam_v(cam, fy);
                 const float rw = rtb_bound_row_w(b, v), rc = rtb_bound_row_c(b, v);
-                for (int x = x_lo; x < x_lo + tile_w; ++x) {
-                    const float q = rtb_bound_q(b.sA, rw, rc, rtb_cam_u(cam, (float)x, fy));
-                    uint32_t bits;
-                    __builtin_memcpy(&bits, &q, 4);
-                    if ((bits & RTB_BOUND_FAIL_BIT) == 0u) { any_pass = true; break; }
+                for (int x = x_lo; x < x_lo + tile_w; ++x) {  // the q form: what the culled kernels test per ray
+                    if (rtb_bound_q(b.sA, rw, rc, rtb_cam_u(cam, (float)x, fy)) < 2.0f) { any_pass = true; break; }
                 }
             }
             culled += miss;
