@@ -141,98 +141,112 @@ __device__ __forceinline__ void exact_update(const GridParams& p, int prim, floa
 
 #define RTB_Q_FAIL_BIT 0x40000000u  // bit 30 of a float q >= 0: set <=> q >= 2 (or Inf / NaN)
 
-// One primitive's bound on this thread's PX rays: t = (sA, rowW, h, rowC); true if some ray of the thread
-// passes.  w = sA*u + rowW is ONE packed FFMA2 per ray pair.  The pass test then runs on two pipes at once:
-//   * KQ ray pairs take the q form: a second FFMA2 (q = w*w + rowC, FMA pipe) and one LOP3 that ANDs both IEEE
-//     patterns into an accumulator ("q >= 2" is bit 30);
-//   * the other pairs take the half-width form |w| < h: a 3-input FMNMX with |.| on both new operands folds them
-//     into a running minimum (ALU pipe, no second FMA).
-// The ray set "|w| < h" contains the set "fmaf(w, w, rowC) < 2" (raycast_math.h), which contains the footprint:
-// either test may be used on any ray.  With KQ = 0 the FMA pipe idles while the 16-lane ALU pipe does 8 FMNMX3
-// per primitive; with KQ = PX/2 (the former kernel) it is the other way round.  NaNs drop out of fminf and set
-// bit 30, Inf never beats h: such rays fail both tests.
-template <int PX, int KQ>
-__device__ __forceinline__ bool bound_test(const float4 t, const PixelState<PX>& st) {
-    static_assert(KQ >= 0 && KQ <= PX / 2, "KQ counts ray pairs");
+// One primitive's bound on this thread's PX rays, half-width form: t = (sA, rowW, h, -); returns min |w| over the
+// rays (some ray passes <=> the result is below h).  w = sA*u + rowW is ONE packed FFMA2 per ray pair (sm_100's
+// FFMA2 with the pair operand HI_LO and scalar-broadcast coefficients), folded into the running minimum by a
+// 3-input FMNMX with |.| on both new operands: 8 FFMA2 + 8 FMNMX3 for 16 rays.  The ray set "|w| < h" contains
+// the set "fmaf(w, w, rowC) < 2" (raycast_math.h), which contains the footprint.  NaNs drop out of fminf, Inf
+// never beats h: such rays fail, as they fail the q form.
+// (Measured: keeping KQ of the 8 ray pairs on the q form -- a second FFMA2 and a LOP3 instead of the FMNMX3, to
+// load the idle FMA pipe -- gives C3 0.610 / 0.612 / 0.611 / 0.625 / 0.636 / 0.682 / 0.715 ms for KQ = 0 / 1 / 2 /
+// 3 / 4 / 6 / 8: every 2-ray instruction holds the dispatch port for 2 clocks whichever pipe it goes to, so the
+// form with the fewest of them wins; profiles/r01_variant_sweep_kq.jsonl.)
+template <int PX>
+__device__ __forceinline__ float bound_min(const float4 t, const PixelState<PX>& st) {
     const uint64_t S2 = pack2(t.x, t.x), W2 = pack2(t.y, t.y);
     float m = __int_as_float(0x7f800000);
-    uint32_t a = 0xFFFFFFFFu;
-    if constexpr (KQ > 0) {
-        const uint64_t C2 = pack2(t.w, t.w);
 #pragma unroll
-        for (int j = 0; j < KQ; ++j) {
-            const uint64_t w2 = ffma2(st.u2[j], S2, W2);
-            const uint64_t q2 = ffma2(w2, w2, C2);
-            uint32_t q0, q1;
-            unpack2u(q2, q0, q1);
-            a &= q0 & q1;
-        }
-    }
-#pragma unroll
-    for (int j = KQ; j < PX / 2; ++j) {
+    for (int j = 0; j < PX / 2; ++j) {
         const uint64_t w2 = ffma2(st.u2[j], S2, W2);
         float lo, hi;
         unpack2(w2, lo, hi);
         m = fminf(fminf(m, fabsf(lo)), fabsf(hi));
     }
-    bool pass = (KQ < PX / 2) && (m < t.z);
-    if constexpr (KQ > 0) pass = pass || ((a & RTB_Q_FAIL_BIT) == 0u);
-    return pass;
+    return m;
+}
+
+// The q form of the same bound, t = (sA, rowW, -, rowC): q = w*w + rowC as a second FFMA2, "q >= 2" is bit 30 of
+// the IEEE pattern, one LOP3 ANDs both patterns of a pair into the accumulator.  True if some ray has q < 2.
+// Used where few primitives reach the per-ray test (the culled kernels): no square root for h is needed.
+template <int PX>
+__device__ __forceinline__ bool bound_q_passes(const float4 t, const PixelState<PX>& st) {
+    const uint64_t S2 = pack2(t.x, t.x), W2 = pack2(t.y, t.y), C2 = pack2(t.w, t.w);
+    uint32_t a = 0xFFFFFFFFu;
+#pragma unroll
+    for (int j = 0; j < PX / 2; ++j) {
+        const uint64_t w2 = ffma2(st.u2[j], S2, W2);
+        const uint64_t q2 = ffma2(w2, w2, C2);
+        uint32_t q0, q1;
+        unpack2u(q2, q0, q1);
+        a &= q0 & q1;
+    }
+    return (a & RTB_Q_FAIL_BIT) == 0u;
 }
 
 // The vote of a group of G primitives and, behind it, the exact updates of those whose bound some ray of the
-// warp passed.
+// warp passed.  m[g] = min |w| of this thread's rays, h[g] = the row's half-width (kept as values: the hot path
+// is G compares into one predicate, the per-primitive compares happen only behind the vote).
 template <int PX, int G>
-__device__ __forceinline__ void resolve_group(const GridParams& p, const bool (&pass)[G], int first_prim, float v,
-                                              PixelState<PX>& st) {
+__device__ __forceinline__ void resolve_group(const GridParams& p, const float (&m)[G], const float (&h)[G], int first_prim,
+                                              float v, PixelState<PX>& st) {
     bool any = false;
 #pragma unroll
-    for (int g = 0; g < G; ++g) any = any || pass[g];
+    for (int g = 0; g < G; ++g) any = any || (m[g] < h[g]);
     if (__any_sync(0xFFFFFFFFu, any)) {
-        uint32_t mask = 0u;
-#pragma unroll
-        for (int g = 0; g < G; ++g) mask |= pass[g] ? (1u << g) : 0u;
 #pragma unroll 1
-        for (int g = 0; g < G; ++g)
-            if (__any_sync(0xFFFFFFFFu, (mask >> g) & 1u)) exact_update<PX>(p, first_prim + g, v, st);
+        for (int g = 0; g < G; ++g) {
+            float mg = m[0], hg = h[0];
+#pragma unroll
+            for (int k = 1; k < G; ++k) {
+                mg = (g == k) ? m[k] : mg;
+                hg = (g == k) ? h[k] : hg;
+            }
+            if (__any_sync(0xFFFFFFFFu, mg < hg)) exact_update<PX>(p, first_prim + g, v, st);
+        }
     }
 }
 
 // The dense test without a row table: G primitives of a staged chunk against this thread's PX rays, the row
-// terms (rowW, rowC, h) computed per thread and primitive.
-template <int PX, int G, int KQ>
+// terms (rowW, h) computed per thread and primitive.
+template <int PX, int G>
 __device__ __forceinline__ void bound_group(const GridParams& p, const float4* __restrict__ rec, int first_prim,
                                             float v, PixelState<PX>& st) {
-    bool pass[G];
+    float m[G], h[G];
 #pragma unroll
     for (int g = 0; g < G; ++g) {
         const float4 r0 = rec[2 * g];                                 // sA, k1, k0, e
         const float r1 = *reinterpret_cast<const float*>(rec + 2 * g + 1);  // cv
         const RtbBound b = {r0.x, r0.y, r0.z, r0.w, r1, 0.f, 0.f, 0.f};
-        const float c = rtb_bound_row_c(b, v);
-        pass[g] = bound_test<PX, KQ>(make_float4(b.sA, rtb_bound_row_w(b, v), rtb_bound_h_of_c(c), c), st);
+        h[g] = rtb_bound_row_h(b, v);
+        m[g] = bound_min<PX>(make_float4(b.sA, rtb_bound_row_w(b, v), h[g], 0.f), st);
     }
-    resolve_group<PX, G>(p, pass, first_prim, v, st);
+    resolve_group<PX, G>(p, m, h, first_prim, v, st);
 }
 
 // Same dense test with the per-row terms taken from the CTA's row table (built once per chunk by
-// all threads, see the kernel): ONE LDS.128 (sA, rowW, h, rowC) per thread and primitive and no
+// all threads, see the kernel): ONE LDS.128 (sA, rowW, h, -) per thread and primitive and no
 // scalar FP32 work in the loop.  `tab` points at this thread's row of the first primitive; consecutive
 // primitives are ROWS apart.
-template <int PX, int G, int ROWS, int KQ>
+template <int PX, int G, int ROWS>
 __device__ __forceinline__ void bound_group_tab(const GridParams& p, const float4* __restrict__ tab, int first_prim,
                                                 float v, PixelState<PX>& st) {
-    bool pass[G];
+    float m[G], h[G];
 #pragma unroll
-    for (int g = 0; g < G; ++g) pass[g] = bound_test<PX, KQ>(tab[g * ROWS], st);
-    resolve_group<PX, G>(p, pass, first_prim, v, st);
+    for (int g = 0; g < G; ++g) {
+        const float4 t = tab[g * ROWS];
+        h[g] = t.z;
+        m[g] = bound_min<PX>(t, st);
+    }
+    resolve_group<PX, G>(p, m, h, first_prim, v, st);
 }
 
 // The dense loop over one staged chunk, software-pipelined: the table entries of the next two
-// primitives are requested (LDS.128 off a running pointer, no address arithmetic on the critical
-// path) while the current two are being tested, so no warp waits for shared memory at the top of a
-// group.  Groups of 4 primitives per vote; this warp takes groups split, split+S, ...
-template <int PX, int ROWS, int S, int KQ>
+// primitives are requested (LDS.128 off a running pointer) while the current two are being tested, so no
+// warp waits for shared memory at the top of a group.  Groups of 4 primitives per vote; this warp takes
+// groups split, split+S, ...  (The loop counter and the clamp of the prefetch index stay integers: the
+// compiler keeps them on the uniform datapath; a version that ran on pointers moved them to the ALU pipe
+// and cost 2 %: C3 0.603 -> 0.624 ms.)
+template <int PX, int ROWS, int S>
 __device__ __forceinline__ void dense_chunk_tab(const GridParams& p, const float4* __restrict__ tab, int cnt,
                                                 int first_prim, int split, float v, PixelState<PX>& st) {
     constexpr int G = 4;
@@ -243,17 +257,18 @@ __device__ __forceinline__ void dense_chunk_tab(const GridParams& p, const float
 #pragma unroll 1
     for (; j < cnt; j += S * G) {
         const float4 c2 = t[2 * ROWS], c3 = t[3 * ROWS];
-        bool pass[G];
-        pass[0] = bound_test<PX, KQ>(c0, st);
-        pass[1] = bound_test<PX, KQ>(c1, st);
+        float m[G], h[G];
+        h[0] = c0.z; h[1] = c1.z; h[2] = c2.z; h[3] = c3.z;
+        m[0] = bound_min<PX>(c0, st);
+        m[1] = bound_min<PX>(c1, st);
         // next group's first two entries; past the end the last group is read again (stays inside the table)
         const int jn = min(j + S * G, cnt - G);
         const float4* tn = tab + jn * ROWS;
         c0 = tn[0];
         c1 = tn[ROWS];
-        pass[2] = bound_test<PX, KQ>(c2, st);
-        pass[3] = bound_test<PX, KQ>(c3, st);
-        resolve_group<PX, G>(p, pass, first_prim + j, v, st);
+        m[2] = bound_min<PX>(c2, st);
+        m[3] = bound_min<PX>(c3, st);
+        resolve_group<PX, G>(p, m, h, first_prim + j, v, st);
         t = tn;
     }
 }
@@ -370,7 +385,7 @@ __device__ __forceinline__ void signal_completion(const GridParams& p, int tile_
 // stage.  The values are those of rtb_bound_row_w / rtb_bound_row_c, computed once per row
 // instead of once per thread (16 threads of a CTA share a row).
 template <int PX, int WARPS_X, int WARPS_Y, int G = kBoundGroup, int MIN_CTAS = (PX >= 16 ? 3 : 4), int S = 1,
-          bool TAB = false, int TP = kTabPrims, int PIPE = 1, int KQ = 0>
+          bool TAB = false, int TP = kTabPrims, int PIPE = 1>
 __global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y * S, MIN_CTAS)
 raycast_grid_kernel(const GridParams p) {
     constexpr int kTabPrims = TP;  // primitives per staged chunk of the row-table variants
@@ -461,8 +476,7 @@ raycast_grid_kernel(const GridParams p) {
                 const float4 r0 = stage[b][2 * prim];
                 const float r1 = *reinterpret_cast<const float*>(&stage[b][2 * prim + 1]);
                 const RtbBound bd = {r0.x, r0.y, r0.z, r0.w, r1, 0.f, 0.f, 0.f};
-                const float rc = rtb_bound_row_c(bd, tab_v);
-                rowtab[b][i] = make_float4(bd.sA, rtb_bound_row_w(bd, tab_v), rtb_bound_h_of_c(rc), rc);
+                rowtab[b][i] = make_float4(bd.sA, rtb_bound_row_w(bd, tab_v), rtb_bound_row_h(bd, tab_v), 0.f);
             }
             // table b is complete; stage[b] has been consumed and may be refilled.  Table b is next
             // rebuilt two chunks on, behind the barrier of chunk k+1, which a warp only reaches
@@ -471,15 +485,15 @@ raycast_grid_kernel(const GridParams p) {
             if (tid == 0 && k + 2 < n_chunks) issue(k + 2);
             const float4* tab = &rowtab[b][wy * 4 + ly];
             if constexpr (PIPE != 0 && G == 4) {
-                dense_chunk_tab<PX, kTileH, S, KQ>(p, tab, cnt, first, split, v, st);
+                dense_chunk_tab<PX, kTileH, S>(p, tab, cnt, first, split, v, st);
             } else {
 #pragma unroll 1
                 for (int j = split * G; j < cnt; j += S * G)
-                    bound_group_tab<PX, G, kTileH, KQ>(p, tab + j * kTileH, first + j, v, st);
+                    bound_group_tab<PX, G, kTileH>(p, tab + j * kTileH, first + j, v, st);
             }
         } else {
 #pragma unroll 1
-            for (int j = split * G; j < cnt; j += S * G) bound_group<PX, G, KQ>(p, &stage[b][2 * j], first + j, v, st);
+            for (int j = split * G; j < cnt; j += S * G) bound_group<PX, G>(p, &stage[b][2 * j], first + j, v, st);
             if (k + 2 < n_chunks) {
                 __syncthreads();  // every warp is done reading stage[b] before TMA refills it
                 if (tid == 0) issue(k + 2);
@@ -654,7 +668,7 @@ raycast_cull_kernel(const GridParams p) {
                 const RtbBound s = {a.x, a.y, a.z, a.w, c.x, 0.f, 0.f, 0.f};
                 // few primitives reach this loop: the q form (two FFMA2 per ray pair) saves the square root of the half-width
                 const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), 0.f, rtb_bound_row_c(s, v));
-                if (__any_sync(0xFFFFFFFFu, bound_test<PX, PX / 2>(t, st))) exact_update<PX>(p, __float_as_int(c.y), v, st);
+                if (__any_sync(0xFFFFFFFFu, bound_q_passes<PX>(t, st))) exact_update<PX>(p, __float_as_int(c.y), v, st);
             }
             total = 0;
             if (k != n_batches - 1) __syncthreads();  // every warp has read the list before it is refilled
@@ -944,7 +958,7 @@ raycast_binned_kernel(const GridParams p) {
                 const RtbBound s = {a.x, a.y, a.z, a.w, s_rec[e][1].x, 0.f, 0.f, 0.f};
                 // few primitives reach this loop: the q form (two FFMA2 per ray pair) saves the square root of the half-width
                 const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), 0.f, rtb_bound_row_c(s, v));
-                if (__any_sync(0xFFFFFFFFu, bound_test<PX, PX / 2>(t, st))) {
+                if (__any_sync(0xFFFFFFFFu, bound_q_passes<PX>(t, st))) {
                     warp_hit = true;
                     exact_update_rec<PX>(p, s_prim[e], s_rec[e][2], s_rec[e][3], s_rec[e][4], v, st);
                 }
@@ -1056,7 +1070,7 @@ GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
 // Launch of one instantiation: the id columns are dynamic shared memory (PX x threads ints); together
 // with the static staging / table area that can pass 48 KB, which needs the opt-in attribute (set once
 // per instantiation and device).
-template <int PX, int WX, int WY, int G, int MINB, int S, bool TAB, int TP, int PIPE, int KQ = 0>
+template <int PX, int WX, int WY, int G, int MINB, int S, bool TAB, int TP, int PIPE>
 cudaError_t launch_instance(const GridParams& p, dim3 grid, cudaStream_t stream) {
     constexpr int kThreads = 32 * WX * WY * S;
     constexpr int kDyn = PX * kThreads * (int)sizeof(int);
@@ -1065,20 +1079,20 @@ cudaError_t launch_instance(const GridParams& p, dim3 grid, cudaStream_t stream)
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return e;
     if (configured_device != dev) {
-        e = cudaFuncSetAttribute(raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP, PIPE, KQ>,
+        e = cudaFuncSetAttribute(raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP, PIPE>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, kDyn);
         if (e != cudaSuccess) return e;
         configured_device = dev;
     }
-    raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP, PIPE, KQ><<<grid, dim3(kThreads), kDyn, stream>>>(p);
+    raycast_grid_kernel<PX, WX, WY, G, MINB, S, TAB, TP, PIPE><<<grid, dim3(kThreads), kDyn, stream>>>(p);
     return cudaGetLastError();
 }
 
-template <int PX, int WX, int WY, int G, int MINB, int S = 1, bool TAB = false, int TP = kTabPrims, int PIPE = 1, int KQ = 0>
+template <int PX, int WX, int WY, int G, int MINB, int S = 1, bool TAB = false, int TP = kTabPrims, int PIPE = 1>
 cudaError_t launch_variant(const GridParams& p, cudaStream_t stream) {
     GridLaunchShape s = shape_of<PX, WX, WY>(p.width, p.local_rows);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
-    return launch_instance<PX, WX, WY, G, MINB, S, TAB, TP, PIPE, KQ>(p, s.grid, stream);
+    return launch_instance<PX, WX, WY, G, MINB, S, TAB, TP, PIPE>(p, s.grid, stream);
 }
 
 template <int PX, int WX, int WY, int MINB>
@@ -1184,10 +1198,6 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) 
         // measured and dropped: two groups (8 primitives) per loop iteration to halve the loop control on the uniform
         // pipe: C3 0.7025 -> 0.7126 ms, C4 10.528 -> 10.684 ms (profiles/r01_variant_sweep_unroll2.jsonl)
         case 15: return launch_variant<8, 2, 2, 4, 8, 1, true>(p, stream);
-        // KQ = ray pairs (of 8) whose pass test takes the q form (second FFMA2 + LOP3) instead of |w| < h (FMNMX3); C3 ms for
-        // KQ = 0 / 1 / 2 / 3 / 4 / 6 / 8: 0.610 / 0.612 / 0.611 / 0.625 / 0.636 / 0.682 / 0.715 (profiles/r01_variant_sweep_kq.jsonl)
-        case 44: return launch_variant<16, 2, 2, 4, 4, 1, true, kTabPrims, 1, 4>(p, stream);
-        case 48: return launch_variant<16, 2, 2, 4, 4, 1, true, kTabPrims, 1, 8>(p, stream);
         default: break;
     }
     const GridLaunchShape s = grid_launch_shape(p.width, p.local_rows, sm_count);
