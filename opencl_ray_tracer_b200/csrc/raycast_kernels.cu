@@ -9,10 +9,10 @@
 // and a lane's PX RGBA8 results leave as 128-bit stores.  The conic bound records (32 B per
 // primitive) are staged global->shared in chunks with 1-D TMA bulk copies (cp.async.bulk + mbarrier
 // complete_tx), double buffered; per chunk the CTA turns them into a row table
-// (primitive, CTA row) -> (sA, rowW, rowC) that the dense loop reads with one LDS.128 per thread and
-// primitive.  Per ray pair and primitive: 2 FFMA2 (w = sA*u + rowW; q = w*w + rowC) + 1 LOP3 (AND
-// of the IEEE patterns; bit 30 = "q >= 2").  One warp vote per 4 primitives; the reference-exact
-// slab / sphere update (raycast_math.h) runs only behind it.
+// (primitive, CTA row) -> (sA, rowW, h) that the dense loop reads with one LDS.128 per thread and
+// primitive.  Per ray pair and primitive: 1 FFMA2 (w = sA*u + rowW) + 1 FMNMX3 (running min of |w|);
+// per thread and primitive one compare with the row's half-width h.  One warp vote per 4
+// primitives; the reference-exact slab / sphere update (raycast_math.h) runs only behind it.
 //
 // Compiled with -fmad=false: every FMA is an explicit fmaf() from raycast_math.h so the scalar
 // emulator in tests/emu reproduces the kernel bit for bit.
