@@ -467,7 +467,12 @@ int ensure_host_scene(rtb_ctx* ctx) {
 // 0.89 ms; sizes shrinking towards the end (8, 8, 8, 4, 2, 1, 0.5, 0.5 MB) 0.93 ms; 16 x 2 MB with the last
 // two cut in four 0.87 ms.
 int plan_progress_chunks(int rows, size_t row_bytes, int unit, int bound[kMaxProgressChunks + 1]) {
-    size_t want = (row_bytes * (size_t)rows + (2u << 20) - 1) / (2u << 20);
+    static const size_t chunk_bytes = [] {  // RTB_CHUNK_KB: experiment knob (tools/e2e_breakdown.py)
+        const char* e = std::getenv("RTB_CHUNK_KB");
+        const long kb = e ? std::atol(e) : 0;
+        return kb > 0 ? (size_t)kb << 10 : (size_t)2 << 20;
+    }();
+    size_t want = (row_bytes * (size_t)rows + chunk_bytes - 1) / chunk_bytes;
     if (want < 1) want = 1;
     if (want > (size_t)kMaxProgressChunks) want = kMaxProgressChunks;
     int chunk_rows = (int)(((size_t)rows + want - 1) / want);
