@@ -459,7 +459,7 @@ int ensure_host_scene(rtb_ctx* ctx) {
     return RTB_OK;
 }
 
-// Row chunks in which a launch reports progress (rtb_render, rtb_render_bands_host): about 2 MB of
+// Row chunks in which a launch reports progress (rtb_render, rtb_render_bands_host): 2-4 MB of
 // output each, bounds on multiples of `unit` rows (a multiple of 16); returns the number of chunks.
 // The copy stream is nearly as busy as the kernel (C3: 0.6 ms of PCIe time under a 0.76 ms launch), so
 // the copies have to start early and every stream wait (1-2 us of the copy stream's time) counts:
@@ -467,11 +467,18 @@ int ensure_host_scene(rtb_ctx* ctx) {
 // 0.89 ms; sizes shrinking towards the end (8, 8, 8, 4, 2, 1, 0.5, 0.5 MB) 0.93 ms; 16 x 2 MB with the last
 // two cut in four 0.87 ms.
 int plan_progress_chunks(int rows, size_t row_bytes, int unit, int bound[kMaxProgressChunks + 1]) {
-    static const size_t chunk_bytes = [] {  // RTB_CHUNK_KB: experiment knob (tools/e2e_breakdown.py)
+    // about an eighth of the output per chunk, between 2 and 4 MB (RTB_CHUNK_KB overrides: tools/e2e_breakdown.py).
+    // Re-measured with the 0.60 ms kernel of v8, whole C3 frame, e2e: 2 MB 0.930 ms, 3 MB 0.913, 4 MB 0.888, 6 MB 0.938,
+    // 8 MB 0.943 (profiles/r01_e2e_chunks_v8.txt): the copy stream spends ~10 us per chunk on the wait + copy launch.
+    static const size_t chunk_override = [] {
         const char* e = std::getenv("RTB_CHUNK_KB");
         const long kb = e ? std::atol(e) : 0;
-        return kb > 0 ? (size_t)kb << 10 : (size_t)2 << 20;
+        return kb > 0 ? (size_t)kb << 10 : (size_t)0;
     }();
+    size_t chunk_bytes = row_bytes * (size_t)rows / 8;
+    if (chunk_bytes < ((size_t)2 << 20)) chunk_bytes = (size_t)2 << 20;
+    if (chunk_bytes > ((size_t)4 << 20)) chunk_bytes = (size_t)4 << 20;
+    if (chunk_override) chunk_bytes = chunk_override;
     size_t want = (row_bytes * (size_t)rows + chunk_bytes - 1) / chunk_bytes;
     if (want < 1) want = 1;
     if (want > (size_t)kMaxProgressChunks) want = kMaxProgressChunks;
