@@ -1,2 +1,6 @@
+set -x
 mkdir -p gpurun_out
-for kb in 2048 3072 4096 6144 8192; do echo "chunk_kb $kb"; RTB_CHUNK_KB=$kb timeout -k 5 100 python tools/e2e_breakdown.py 2>&1 | head -1; done > gpurun_out/e2e_chunks.txt; cat gpurun_out/e2e_chunks.txt
+N=${NGPU:-2}
+for N in 2 4; do
+timeout -k 5 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2951$N bench.py --gpus $N > gpurun_out/bench_c3_n${N}_v8.json 2> gpurun_out/bench_c3_n${N}_v8.err; tail -c 200 gpurun_out/bench_c3_n${N}_v8.json; tail -3 gpurun_out/bench_c3_n${N}_v8.err
+done
