@@ -33,18 +33,20 @@ BAND_ROWS = 16
 
 # FP32 operations the shipped kernel executes per ray-primitive test (FMA = 2; min / compare / bit
 # operations / votes count 0).  Cubes and spheres go through the same dense loop: per ray ONE FMA
-# (w = sA*u + rowW, issued as FFMA2 on ray pairs) = 2 flop, then |w| is folded into a running minimum (3-input
-# FMNMX per ray pair) that is compared with the row's half-width h once per thread and primitive.  The row terms
-# (rowW: 1 FFMA; rowC: 1 FADD + 2 FMUL; h = sqrt(2 - rowC) * k: FADD + sqrt + FMUL = 8 flop) are computed once per
-# primitive and CTA pixel row into the shared-memory row table, i.e. amortised over the width of a CTA's pixel
-# tile (256 rays at the roofline point: +0.03 flop per test).  The reference-exact slab / sphere arithmetic runs
-# only on rays inside a bound (a few per mille of the tests) and is NOT counted.
-# The former kernel evaluated q = w*w + rowC per ray (a second FMA: 4.02 flop per test, 0.704 ms at C3 = 68.5 % of
-# the FP32 peak); the half-width form needs half the FMAs and runs the frame in 0.61 ms, so the FP32 fraction of the
-# shipped kernel is LOWER while every number a user sees is better.  What bounds it is the dispatch port: an FFMA2
-# and an FMNMX3 each hold it for 2 clocks and serve 2 rays, i.e. 2 clocks per test and scheduler ("dispatch" below).
+# (w = sA*u + rowW, issued as FFMA2 on ray pairs) = 2 flop, then |w| is folded into a running minimum m (3-input
+# FMNMX per ray pair); per thread and primitive one more FMA, q = m*m + rowC (compared with 2), shared by the
+# thread's rays (2 flop / 16 rays at the roofline point).  The row terms (rowW: 1 FFMA; rowC: 1 FADD + 2 FMUL =
+# 5 flop) are computed once per primitive and CTA pixel row into the shared-memory row table, i.e. amortised over
+# the width of a CTA's pixel tile (256 rays at the roofline point: +0.02 flop per test).  The reference-exact slab /
+# sphere arithmetic runs only on rays inside a bound (a few per mille of the tests) and is NOT counted.
+# Up to v7 the kernel evaluated q per ray (a second FMA: 4.02 flop per test, 0.704 ms at C3 = 68.5 % of the FP32
+# peak).  q is monotone in |w|, so the minimum over a thread's rays is the q of the smallest |w|: the same decision
+# bit for bit with half the FMAs, and the frame takes 0.585 ms -- the FP32 fraction of the shipped kernel is LOWER
+# while every number a user sees is better.  What bounds it is the dispatch port: an FFMA2 and an FMNMX3 each hold
+# it for 2 clocks and serve 2 rays, i.e. 2 clocks per test and scheduler ("dispatch" below).
 FLOP_PER_TEST_RAY = 2.0
-FLOP_PER_TEST_ROW = 8.0
+FLOP_PER_TEST_THREAD = 2.0       # q = fmaf(m, m, rowC): once per thread and primitive, shared by the thread's rays
+FLOP_PER_TEST_ROW = 5.0
 DISPATCH_CLOCKS_PER_TEST = 2.0   # per scheduler (32 lanes): FFMA2 (2 clocks / 2 rays) + FMNMX3 (2 clocks / 2 rays)
 
 
@@ -473,7 +475,7 @@ def run_sequence(args):
         sms = ctx.device_info()["sm_count"]
         my_rows = ctx.band_local_rows(h, BAND_ROWS, 0, world)
         px, tile_w = capi.debug_grid_shape(w, my_rows, sms)[:2]
-        flop_per_test = FLOP_PER_TEST_RAY + FLOP_PER_TEST_ROW / tile_w
+        flop_per_test = FLOP_PER_TEST_RAY + FLOP_PER_TEST_THREAD / px + FLOP_PER_TEST_ROW / tile_w
         probe = fp32_probe_tflops()
         peak_nominal = sms * 128 * 2 * (sampler.result()["sm_max_mhz"] or 1965.0) * 1e6 / 1e12
         achieved = my_rows * w * (ns + nc) * flop_per_test / (k_avg_ms * 1e-3) / 1e12 if k_avg_ms > 0 else 0.0
@@ -666,7 +668,7 @@ def main():
         probe = fp32_probe_tflops()
         # dominant kernel = the ray-cast grid kernel; this rank's launch covers my_rows rows
         px, tile_w = capi_mod.debug_grid_shape(w, r["my_rows"], sms)[:2]
-        flop_per_test = FLOP_PER_TEST_RAY + FLOP_PER_TEST_ROW / tile_w
+        flop_per_test = FLOP_PER_TEST_RAY + FLOP_PER_TEST_THREAD / px + FLOP_PER_TEST_ROW / tile_w
         flops_per_launch = r["my_rows"] * w * (nc + ns) * flop_per_test
         k_s = r["k_avg_ms"] * 1e-3
         achieved = flops_per_launch / k_s / 1e12 if k_s > 0 else 0.0

@@ -9,10 +9,11 @@
 // and a lane's PX RGBA8 results leave as 128-bit stores.  The conic bound records (32 B per
 // primitive) are staged global->shared in chunks with 1-D TMA bulk copies (cp.async.bulk + mbarrier
 // complete_tx), double buffered; per chunk the CTA turns them into a row table
-// (primitive, CTA row) -> (sA, rowW, h) that the dense loop reads with one LDS.128 per thread and
-// primitive.  Per ray pair and primitive: 1 FFMA2 (w = sA*u + rowW) + 1 FMNMX3 (running min of |w|);
-// per thread and primitive one compare with the row's half-width h.  One warp vote per 4
-// primitives; the reference-exact slab / sphere update (raycast_math.h) runs only behind it.
+// (primitive, CTA row) -> (sA, rowW, rowC) that the dense loop reads with one LDS.128 per thread and
+// primitive.  Per ray pair and primitive: 1 FFMA2 (w = sA*u + rowW) + 1 FMNMX3 (running min m of |w|);
+// per thread and primitive one FMA + compare, fmaf(m, m, rowC) < 2, which is the per-ray q test of the
+// thread's rays bit for bit (q is monotone in |w|).  One warp vote per 4 primitives; the
+// reference-exact slab / sphere update (raycast_math.h) runs only behind it.
 //
 // Compiled with -fmad=false: every FMA is an explicit fmaf() from raycast_math.h so the scalar
 // emulator in tests/emu reproduces the kernel bit for bit.
@@ -139,18 +140,16 @@ __device__ __forceinline__ void exact_update(const GridParams& p, int prim, floa
     }
 }
 
-#define RTB_Q_FAIL_BIT 0x40000000u  // bit 30 of a float q >= 0: set <=> q >= 2 (or Inf / NaN)
-
-// One primitive's bound on this thread's PX rays, half-width form: t = (sA, rowW, h, -); returns min |w| over the
-// rays (some ray passes <=> the result is below h).  w = sA*u + rowW is ONE packed FFMA2 per ray pair (sm_100's
-// FFMA2 with the pair operand HI_LO and scalar-broadcast coefficients), folded into the running minimum by a
-// 3-input FMNMX with |.| on both new operands: 8 FFMA2 + 8 FMNMX3 for 16 rays.  The ray set "|w| < h" contains
-// the set "fmaf(w, w, rowC) < 2" (raycast_math.h), which contains the footprint.  NaNs drop out of fminf, Inf
-// never beats h: such rays fail, as they fail the q form.
-// (Measured: keeping KQ of the 8 ray pairs on the q form -- a second FFMA2 and a LOP3 instead of the FMNMX3, to
-// load the idle FMA pipe -- gives C3 0.610 / 0.612 / 0.611 / 0.625 / 0.636 / 0.682 / 0.715 ms for KQ = 0 / 1 / 2 /
-// 3 / 4 / 6 / 8: every 2-ray instruction holds the dispatch port for 2 clocks whichever pipe it goes to, so the
-// form with the fewest of them wins; profiles/r01_variant_sweep_kq.jsonl.)
+// One primitive's bound on this thread's PX rays: t = (sA, rowW, rowC, -); returns m = min |w| over the rays.
+// w = sA*u + rowW is ONE packed FFMA2 per ray pair (sm_100's FFMA2 with the pair operand HI_LO and
+// scalar-broadcast coefficients), folded into the running minimum by a 3-input FMNMX with |.| on both new
+// operands: 8 FFMA2 + 8 FMNMX3 for 16 rays.  "Some ray has q < 2" is then fmaf(m, m, rowC) < 2, ONE FMA and one
+// compare per thread and primitive -- bit for bit the per-ray q test (raycast_math.h: q is monotone in |w|).
+// NaNs drop out of fminf, Inf gives q = Inf: such rays fail, as their own q would.
+// (Measured: keeping KQ of the 8 ray pairs on the per-ray q form -- a second FFMA2 and a LOP3 instead of the
+// FMNMX3, to load the idle FMA pipe -- gives C3 0.610 / 0.612 / 0.611 / 0.625 / 0.636 / 0.682 / 0.715 ms for
+// KQ = 0 / 1 / 2 / 3 / 4 / 6 / 8: every 2-ray instruction holds the dispatch port for 2 clocks whichever pipe it
+// goes to, so the form with the fewest of them wins; profiles/r01_variant_sweep_kq.jsonl.)
 template <int PX>
 __device__ __forceinline__ float bound_min(const float4 t, const PixelState<PX>& st) {
     const uint64_t S2 = pack2(t.x, t.x), W2 = pack2(t.y, t.y);
@@ -164,80 +163,63 @@ __device__ __forceinline__ float bound_min(const float4 t, const PixelState<PX>&
     }
     return m;
 }
-
-// The q form of the same bound, t = (sA, rowW, -, rowC): q = w*w + rowC as a second FFMA2, "q >= 2" is bit 30 of
-// the IEEE pattern, one LOP3 ANDs both patterns of a pair into the accumulator.  True if some ray has q < 2.
-// Used where few primitives reach the per-ray test (the culled kernels): no square root for h is needed.
-template <int PX>
-__device__ __forceinline__ bool bound_q_passes(const float4 t, const PixelState<PX>& st) {
-    const uint64_t S2 = pack2(t.x, t.x), W2 = pack2(t.y, t.y), C2 = pack2(t.w, t.w);
-    uint32_t a = 0xFFFFFFFFu;
-#pragma unroll
-    for (int j = 0; j < PX / 2; ++j) {
-        const uint64_t w2 = ffma2(st.u2[j], S2, W2);
-        const uint64_t q2 = ffma2(w2, w2, C2);
-        uint32_t q0, q1;
-        unpack2u(q2, q0, q1);
-        a &= q0 & q1;
-    }
-    return (a & RTB_Q_FAIL_BIT) == 0u;
-}
+__device__ __forceinline__ bool bound_passes(float m, float rowC) { return rtb_bound_q_of_w(m, rowC) < 2.0f; }
 
 // The vote of a group of G primitives and, behind it, the exact updates of those whose bound some ray of the
-// warp passed.  m[g] = min |w| of this thread's rays, h[g] = the row's half-width (kept as values: the hot path
-// is G compares into one predicate, the per-primitive compares happen only behind the vote).
+// warp passed.  m[g] = min |w| of this thread's rays, c[g] = the row's rowC (kept as values: the hot path is
+// G FMA + G compares into one predicate, the per-primitive compares happen only behind the vote).
 template <int PX, int G>
-__device__ __forceinline__ void resolve_group(const GridParams& p, const float (&m)[G], const float (&h)[G], int first_prim,
+__device__ __forceinline__ void resolve_group(const GridParams& p, const float (&m)[G], const float (&c)[G], int first_prim,
                                               float v, PixelState<PX>& st) {
     bool any = false;
 #pragma unroll
-    for (int g = 0; g < G; ++g) any = any || (m[g] < h[g]);
+    for (int g = 0; g < G; ++g) any = any || bound_passes(m[g], c[g]);
     if (__any_sync(0xFFFFFFFFu, any)) {
 #pragma unroll 1
         for (int g = 0; g < G; ++g) {
-            float mg = m[0], hg = h[0];
+            float mg = m[0], cg = c[0];
 #pragma unroll
             for (int k = 1; k < G; ++k) {
                 mg = (g == k) ? m[k] : mg;
-                hg = (g == k) ? h[k] : hg;
+                cg = (g == k) ? c[k] : cg;
             }
-            if (__any_sync(0xFFFFFFFFu, mg < hg)) exact_update<PX>(p, first_prim + g, v, st);
+            if (__any_sync(0xFFFFFFFFu, bound_passes(mg, cg))) exact_update<PX>(p, first_prim + g, v, st);
         }
     }
 }
 
 // The dense test without a row table: G primitives of a staged chunk against this thread's PX rays, the row
-// terms (rowW, h) computed per thread and primitive.
+// terms (rowW, rowC) computed per thread and primitive.
 template <int PX, int G>
 __device__ __forceinline__ void bound_group(const GridParams& p, const float4* __restrict__ rec, int first_prim,
                                             float v, PixelState<PX>& st) {
-    float m[G], h[G];
+    float m[G], c[G];
 #pragma unroll
     for (int g = 0; g < G; ++g) {
         const float4 r0 = rec[2 * g];                                 // sA, k1, k0, e
         const float r1 = *reinterpret_cast<const float*>(rec + 2 * g + 1);  // cv
         const RtbBound b = {r0.x, r0.y, r0.z, r0.w, r1, 0.f, 0.f, 0.f};
-        h[g] = rtb_bound_row_h(b, v);
-        m[g] = bound_min<PX>(make_float4(b.sA, rtb_bound_row_w(b, v), h[g], 0.f), st);
+        c[g] = rtb_bound_row_c(b, v);
+        m[g] = bound_min<PX>(make_float4(b.sA, rtb_bound_row_w(b, v), c[g], 0.f), st);
     }
-    resolve_group<PX, G>(p, m, h, first_prim, v, st);
+    resolve_group<PX, G>(p, m, c, first_prim, v, st);
 }
 
 // Same dense test with the per-row terms taken from the CTA's row table (built once per chunk by
-// all threads, see the kernel): ONE LDS.128 (sA, rowW, h, -) per thread and primitive and no
+// all threads, see the kernel): ONE LDS.128 (sA, rowW, rowC, -) per thread and primitive and no
 // scalar FP32 work in the loop.  `tab` points at this thread's row of the first primitive; consecutive
 // primitives are ROWS apart.
 template <int PX, int G, int ROWS>
 __device__ __forceinline__ void bound_group_tab(const GridParams& p, const float4* __restrict__ tab, int first_prim,
                                                 float v, PixelState<PX>& st) {
-    float m[G], h[G];
+    float m[G], c[G];
 #pragma unroll
     for (int g = 0; g < G; ++g) {
         const float4 t = tab[g * ROWS];
-        h[g] = t.z;
+        c[g] = t.z;
         m[g] = bound_min<PX>(t, st);
     }
-    resolve_group<PX, G>(p, m, h, first_prim, v, st);
+    resolve_group<PX, G>(p, m, c, first_prim, v, st);
 }
 
 // The dense loop over one staged chunk, software-pipelined: the table entries of the next two
@@ -257,8 +239,8 @@ __device__ __forceinline__ void dense_chunk_tab(const GridParams& p, const float
 #pragma unroll 1
     for (; j < cnt; j += S * G) {
         const float4 c2 = t[2 * ROWS], c3 = t[3 * ROWS];
-        float m[G], h[G];
-        h[0] = c0.z; h[1] = c1.z; h[2] = c2.z; h[3] = c3.z;
+        float m[G], c[G];
+        c[0] = c0.z; c[1] = c1.z; c[2] = c2.z; c[3] = c3.z;
         m[0] = bound_min<PX>(c0, st);
         m[1] = bound_min<PX>(c1, st);
         // next group's first two entries; past the end the last group is read again (stays inside the table)
@@ -268,7 +250,7 @@ __device__ __forceinline__ void dense_chunk_tab(const GridParams& p, const float
         c1 = tn[ROWS];
         m[2] = bound_min<PX>(c2, st);
         m[3] = bound_min<PX>(c3, st);
-        resolve_group<PX, G>(p, m, h, first_prim + j, v, st);
+        resolve_group<PX, G>(p, m, c, first_prim + j, v, st);
         t = tn;
     }
 }
@@ -476,7 +458,7 @@ raycast_grid_kernel(const GridParams p) {
                 const float4 r0 = stage[b][2 * prim];
                 const float r1 = *reinterpret_cast<const float*>(&stage[b][2 * prim + 1]);
                 const RtbBound bd = {r0.x, r0.y, r0.z, r0.w, r1, 0.f, 0.f, 0.f};
-                rowtab[b][i] = make_float4(bd.sA, rtb_bound_row_w(bd, tab_v), rtb_bound_row_h(bd, tab_v), 0.f);
+                rowtab[b][i] = make_float4(bd.sA, rtb_bound_row_w(bd, tab_v), rtb_bound_row_c(bd, tab_v), 0.f);
             }
             // table b is complete; stage[b] has been consumed and may be refilled.  Table b is next
             // rebuilt two chunks on, behind the barrier of chunk k+1, which a warp only reaches
@@ -666,9 +648,8 @@ raycast_cull_kernel(const GridParams p) {
             for (int j = 0; j < total; ++j) {
                 const float4 a = list[2 * j], c = list[2 * j + 1];
                 const RtbBound s = {a.x, a.y, a.z, a.w, c.x, 0.f, 0.f, 0.f};
-                // few primitives reach this loop: the q form (two FFMA2 per ray pair) saves the square root of the half-width
-                const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), 0.f, rtb_bound_row_c(s, v));
-                if (__any_sync(0xFFFFFFFFu, bound_q_passes<PX>(t, st))) exact_update<PX>(p, __float_as_int(c.y), v, st);
+                const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), rtb_bound_row_c(s, v), 0.f);
+                if (__any_sync(0xFFFFFFFFu, bound_passes(bound_min<PX>(t, st), t.z))) exact_update<PX>(p, __float_as_int(c.y), v, st);
             }
             total = 0;
             if (k != n_batches - 1) __syncthreads();  // every warp has read the list before it is refilled
@@ -956,9 +937,8 @@ raycast_binned_kernel(const GridParams p) {
             for (int e = 0; e < n; ++e) {
                 const float4 a = s_rec[e][0];
                 const RtbBound s = {a.x, a.y, a.z, a.w, s_rec[e][1].x, 0.f, 0.f, 0.f};
-                // few primitives reach this loop: the q form (two FFMA2 per ray pair) saves the square root of the half-width
-                const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), 0.f, rtb_bound_row_c(s, v));
-                if (__any_sync(0xFFFFFFFFu, bound_q_passes<PX>(t, st))) {
+                const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), rtb_bound_row_c(s, v), 0.f);
+                if (__any_sync(0xFFFFFFFFu, bound_passes(bound_min<PX>(t, st), t.z))) {
                     warp_hit = true;
                     exact_update_rec<PX>(p, s_prim[e], s_rec[e][2], s_rec[e][3], s_rec[e][4], v, st);
                 }
@@ -1034,8 +1014,8 @@ GridLaunchShape shape_of(int width, int local_rows) {
 struct Tiling { int px, wx, wy, split; double cost; };
 static const Tiling kTilings[] = {
     {16, 2, 2, 1, 1.00},  // 256 x 8 pixels, 4 warps
-    {16, 2, 1, 2, 1.08},  // 256 x 4 pixels, 4 warps, two per tile: short band sets (8-GPU frames); +8 %: table rows per
-                          // pixel doubled, nearest-hit merge (C3 0.653 vs 0.603 ms)
+    {16, 2, 1, 2, 1.05},  // 256 x 4 pixels, 4 warps, two per tile: short band sets (8-GPU frames); +5 %: table rows per
+                          // pixel doubled, nearest-hit merge (C3 0.615 vs 0.585 ms)
     {8, 2, 2, 1, 1.23},   // 128 x 8 pixels (C3 0.741 ms: the per-primitive LDS / compare / loop is shared by 8 rays only)
     {4, 2, 2, 1, 1.60},   //  64 x 8 pixels: small frames
 };

@@ -98,43 +98,30 @@ RTB_HD float rtb_sphere_t_reference(const float o[4], const float d[4], float ra
 // square completed in u:
 //   q(u,v) = w^2 + e*(v - cv)^2,   w = sA*u + (k1*v + k0),      footprint  =>  q < 2
 // (scaled so that fp32 evaluation error of w = fmaf(u, sA, rowW), q = fmaf(w, w, rowC) cannot push a
-// footprint ray to q >= 2; scene_pack_impl.h).  The kernels do not evaluate q.  Per row and primitive
-// they compute the half-width h = rtb_bound_h_of_c(rowC) >= sqrt(2 - rowC) once (row table), and per
-// ray only w (ONE FMA) and the test |w| < h.  This accepts every ray the q test accepts: if the
-// rounded fmaf(w, w, rowC) is below 2, the exact w^2 + rowC is below 2 (rounding is monotone and 2 is
-// a float), so |w| < sqrt(2 - rowC) <= h -- for every float w and rowC, NaN and Inf included (they
-// fail both tests).  A thread keeps min |w| over its rays (a 3-input FMNMX per ray pair) and compares
-// once per primitive.  Only rays that pass reach the reference-exact slab / sphere arithmetic above,
-// therefore the bound never changes a pixel: results are those of rtb_cube_update /
-// rtb_sphere_update alone.
+// footprint ray to q >= 2; scene_pack_impl.h).  The kernels evaluate w per ray (ONE FMA) but q only
+// once per thread and primitive: fmaf(w, w, rowC) depends on w through |w| alone and is
+// non-decreasing in |w| (rounding is monotone), so over the rays of a thread
+//     min_rays fmaf(w, w, rowC)  ==  fmaf(m, m, rowC)   with   m = min_rays |w|,
+// bit for bit.  A thread therefore keeps the running minimum of |w| (a 3-input FMNMX per ray pair)
+// and asks "fmaf(m, m, rowC) < 2" once: exactly "does some ray of mine have q < 2".  A NaN w drops
+// out of fminf (its q would be NaN: fail), Inf gives q = Inf: fail.  Only rays that pass reach the
+// reference-exact slab / sphere arithmetic above, therefore the bound never changes a pixel:
+// results are those of rtb_cube_update / rtb_sphere_update alone.
 struct RtbBound { float sA, k1, k0, e, cv, pad0, pad1, pad2; };  // 32 B: LDS.128 + LDS.32
 
-// per row: rowW = k1*v + k0, rowC = (e*(v-cv))*(v-cv), h = h_of_c(rowC);  per ray: w = sA*u + rowW, pass <=> |w| < h
+// per row: rowW = k1*v + k0, rowC = (e*(v-cv))*(v-cv);  per ray: w = sA*u + rowW;  q = w*w + rowC
 RTB_HD float rtb_bound_row_w(const RtbBound& b, float v) { return fmaf(b.k1, v, b.k0); }
 RTB_HD float rtb_bound_row_c(const RtbBound& b, float v) {
     const float dv = v - b.cv;
     return (b.e * dv) * dv;
 }
-// h >= sqrt(2 - c) for the real square root of the float c: d = RN(2 - c) >= (2 - c)(1 - 2^-24) (exact for c in
-// [1, 4]), sqrtf(d) >= sqrt(d)(1 - 2^-24), so sqrt(2 - c) <= sqrtf(d)(1 + 1.6 * 2^-24); the factor is
-// 1 + 8 * 2^-24 and its product rounds down by at most 2^-24.  Non-increasing in c (each step is monotone);
-// 0 ("no ray passes") for c >= 2 and for NaN.
-RTB_HD float rtb_bound_h_of_c(float c) {
-    const float d = 2.0f - c;
-    return (d > 0.0f) ? sqrtf(d) * 1.0000005f : 0.0f;
-}
-RTB_HD float rtb_bound_row_h(const RtbBound& b, float v) { return rtb_bound_h_of_c(rtb_bound_row_c(b, v)); }
 RTB_HD float rtb_bound_w(float sA, float rowW, float u) { return fmaf(u, sA, rowW); }
-RTB_HD bool rtb_bound_passes(float sA, float rowW, float h, float u) { return fabsf(rtb_bound_w(sA, rowW, u)) < h; }
-// The q form the packer's error budget is written for (kept for the CPU check that the kernels' test accepts
-// every ray this one accepts: tests/emu emu_check_bounds).
+RTB_HD float rtb_bound_q_of_w(float w, float rowC) { return fmaf(w, w, rowC); }
 RTB_HD float rtb_bound_q(float sA, float rowW, float rowC, float u) {
-    const float w = fmaf(u, sA, rowW);
-    return fmaf(w, w, rowC);
+    return rtb_bound_q_of_w(rtb_bound_w(sA, rowW, u), rowC);
 }
 
-// Tile cull (RTB_OPT_TILE_CULL): can NO ray of a pixel tile pass the q form of a primitive's bound (which is
-// the per-ray test the culled render kernels apply, and contains the footprint)?  The tile is given by the
+// Tile cull (RTB_OPT_TILE_CULL): can NO ray of a pixel tile pass a primitive's bound?  The tile is given by the
 // ranges of the camera coordinates its rays take: u in [u_min, u_max], v in [v_min, v_max] (min / max over the
 // very values the kernel computes for the tile's pixels).  The answer is a statement about the values
 // rtb_bound_q would compute, derived from the monotonicity of each rounded operation, not from real-number
@@ -147,8 +134,7 @@ RTB_HD float rtb_bound_q(float sA, float rowW, float rowC, float u) {
 //                                                   => q of every ray >= fmaf(wm, wm, c_min)
 // with wm the smallest |w| the interval allows: if this returns true, every ray of the tile has q >= 2, none
 // of them lies in the footprint, and dropping the primitive for the tile cannot change a pixel.  A NaN makes
-// the comparison false (keep).  tests/emu checks the claim against rtb_bound_q pixel by pixel.  (No square
-// root: the per-CTA scan of mode 1 makes this test tiles x primitives times.)
+// the comparison false (keep).  tests/emu checks the claim against rtb_bound_q pixel by pixel.
 RTB_HD bool rtb_bound_tile_misses(const RtbBound& b, float u_min, float u_max, float v_min, float v_max) {
     const float ra = rtb_bound_row_w(b, v_min), rb = rtb_bound_row_w(b, v_max);
     const float r_lo = fminf(ra, rb), r_hi = fmaxf(ra, rb);

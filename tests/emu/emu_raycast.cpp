@@ -74,11 +74,8 @@ extern "C" int emu_check_bounds(int width, int height, const float* cam8, int nc
             const float u = rtb_cam_u(cam, (float)x, fy);
             for (int i = 0; i < nc + ns; ++i) {
                 const RtbBound& b = bnd[i];
-                // the kernels' test, |w| < h; it must also accept every ray the q form (which the packer's error
-                // budget is written for) accepts
-                const bool bound_pass = rtb_bound_passes(b.sA, rtb_bound_row_w(b, v), rtb_bound_row_h(b, v), u);
                 const float q = rtb_bound_q(b.sA, rtb_bound_row_w(b, v), rtb_bound_row_c(b, v), u);
-                if (q < 2.0f && !bound_pass) viol += 1;
+                const bool bound_pass = q < 2.0f;  // NaN fails
                 bool in_foot;
                 if (i < nc) {
                     const RtbSlab &s0 = slabs[3 * i], &s1 = slabs[3 * i + 1], &s2 = slabs[3 * i + 2];
@@ -137,7 +134,7 @@ extern "C" int emu_check_tile_cull(int width, int height, const float* cam8, int
                 const float fy = (float)(y_lo + r);
                 const float v = rtb_cam_v(cam, fy);
                 const float rw = rtb_bound_row_w(b, v), rc = rtb_bound_row_c(b, v);
-                for (int x = x_lo; x < x_lo + tile_w; ++x) {  // the q form: what the culled kernels test per ray
+                for (int x = x_lo; x < x_lo + tile_w; ++x) {
                     if (rtb_bound_q(b.sA, rw, rc, rtb_cam_u(cam, (float)x, fy)) < 2.0f) { any_pass = true; break; }
                 }
             }
@@ -167,6 +164,40 @@ extern "C" long long emu_check_div180(unsigned first_bits, unsigned last_bits, u
         __builtin_memcpy(&a, &ref, 4);
         __builtin_memcpy(&c, &got, 4);
         bad += (a != c);
+    }
+    return bad;
+}
+
+// The kernels' per-thread form of the bound: over a run of `run` horizontally adjacent pixels (a thread's rays)
+// fmaf(m, m, rowC) with m = min |w| must equal the minimum of the per-ray q, bit for bit ("some ray has q < 2" is
+// then one compare per thread).  Returns the number of runs on which the two differ as a pass / fail decision or
+// as a value.
+extern "C" long long emu_check_min_form(int width, int height, const float* cam8, int n_bound, const float* bound_rec, int run) {
+    const RtbCam cam = {cam8[0], cam8[1], cam8[2], cam8[3], cam8[4], 0.f, 0.f, 0.f};
+    const RtbBound* bnd = reinterpret_cast<const RtbBound*>(bound_rec);
+    long long bad = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : bad)
+    for (int y = 0; y < height; ++y) {
+        const float fy = (float)y;
+        const float v = rtb_cam_v(cam, fy);
+        for (int i = 0; i < n_bound; ++i) {
+            const RtbBound& b = bnd[i];
+            const float rw = rtb_bound_row_w(b, v), rc = rtb_bound_row_c(b, v);
+            for (int x0 = 0; x0 < width; x0 += run) {
+                float m = __builtin_inff(), qmin = __builtin_inff();
+                bool any = false;
+                for (int x = x0; x < x0 + run; ++x) {  // past the frame's edge like the kernel's threads
+                    const float w = rtb_bound_w(b.sA, rw, rtb_cam_u(cam, (float)x, fy));
+                    m = fminf(m, fabsf(w));
+                    const float q = rtb_bound_q_of_w(w, rc);
+                    qmin = fminf(qmin, q);
+                    any = any || (q < 2.0f);
+                }
+                const float qm = rtb_bound_q_of_w(m, rc);
+                if ((qm < 2.0f) != any) bad += 1;
+                else if (qm == qm && qmin == qmin && qm != qmin) bad += 1;
+            }
+        }
     }
     return bad;
 }

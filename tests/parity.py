@@ -124,6 +124,16 @@ class Emulator:
         self.lib.emu_check_div180.argtypes = [C.c_uint, C.c_uint, C.c_uint]
         return int(self.lib.emu_check_div180(first_bits, last_bits, stride))
 
+    def check_min_form(self, scene, w, h, camera=None, run=16):
+        """fmaf(min|w|, min|w|, rowC) vs the minimum of the per-ray q over runs of `run` pixels: number of differences."""
+        from opencl_ray_tracer_b200 import capi
+        camera = camera or capi.REFERENCE_CAMERA
+        _, _, cam = capi.debug_pack(scene.sph_o, scene.sph_r, scene.cube_v, camera)
+        bnd = np.ascontiguousarray(capi.debug_pack_bounds(scene.sph_o, scene.sph_r, scene.cube_v, w, h, camera), np.float32)
+        fp = lambda a: np.ascontiguousarray(a, np.float32).ctypes.data_as(C.POINTER(C.c_float))
+        self.lib.emu_check_min_form.restype = C.c_longlong
+        return int(self.lib.emu_check_min_form(w, h, fp(cam), len(bnd), fp(bnd), run))
+
     def check_bounds(self, scene, w, h, camera=None):
         """Walks the kernel's dense loop: returns dict(violations, bound_pass, footprint, total)."""
         from opencl_ray_tracer_b200 import capi

@@ -111,3 +111,14 @@ def test_tile_cull_super_tiles(emu, built_libs, w, h, ns, nc, seed, k):
     cam = None if k == 0 else hs.orbit_camera(w, h, k)
     r = _check_cull(emu, sc, w, h, cam, tile_w=256, tile_h=256)
     assert r["culled"] > 0  # the coarse level culls as well
+
+
+# The kernels evaluate q once per thread: fmaf(m, m, rowC) with m = min |w| over the thread's rays must be the
+# minimum of the per-ray q (monotone in |w|), for runs of 16, 8 and 4 pixels (the tilings' rays per thread).
+@pytest.mark.parametrize("w,h,ns,nc,seed,k", [(640, 480, 100, 100, 7, 0), (480, 360, 48, 48, 9, 33), (333, 201, 40, 3, 11, 40)])
+def test_thread_minimum_form_equals_the_per_ray_test(emu, built_libs, w, h, ns, nc, seed, k):
+    from opencl_ray_tracer_b200 import host_scene as hs
+    sc = to_oracle_scene(hs.random_scene(w, h, ns, nc, seed))
+    cam = None if k == 0 else hs.orbit_camera(w, h, k)
+    for run in (16, 8, 4):
+        assert emu.check_min_form(sc, w, h, cam, run=run) == 0

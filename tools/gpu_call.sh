@@ -1,6 +1,3 @@
-set -x
 mkdir -p gpurun_out
-N=${NGPU:-2}
-for N in 2 4; do
-timeout -k 5 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2951$N bench.py --gpus $N > gpurun_out/bench_c3_n${N}_v8.json 2> gpurun_out/bench_c3_n${N}_v8.err; tail -c 200 gpurun_out/bench_c3_n${N}_v8.json; tail -3 gpurun_out/bench_c3_n${N}_v8.err
-done
+timeout -k 5 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+for wl in c3 c4 c2; do timeout -k 5 200 python tools/variant_sweep.py --workload $wl --variants 0,20,cull,binned --flush; done > gpurun_out/sweep_v9.jsonl 2>&1; cut -c1-125 gpurun_out/sweep_v9.jsonl
