@@ -99,7 +99,7 @@ extern "C" int emu_check_bounds(int width, int height, const float* cam8, int nc
 }
 
 // Tile cull of raycast_cull_kernel (rtb_bound_tile_misses): for every tile_w x tile_h pixel tile
-// and primitive, the cull may say "miss" only if rtb_bound_q fails (bit 30 set) on every pixel of
+// and primitive, the cull may say "miss" only if rtb_bound_q is >= 2 (or NaN) on every pixel of
 // the tile.  out[0] = violations (culled although some pixel passes), out[1] = culled pairs,
 // out[2] = pairs in which no pixel passes (what an ideal cull would drop), out[3] = pairs.
 extern "C" int emu_check_tile_cull(int width, int height, const float* cam8, int n_bound, const float* bound_rec,
