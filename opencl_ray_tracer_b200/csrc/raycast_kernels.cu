@@ -171,7 +171,7 @@ __device__ __forceinline__ bool bound_passes(float m, float rowC) { return rtb_b
 template <int PX, int G>
 __device__ __forceinline__ void resolve_group(const GridParams& p, const float (&m)[G], const float (&c)[G], int first_prim,
                                               float v, PixelState<PX>& st) {
-    bool any = false;
+    bool any = false;  // (one compare on min_g q_g instead of G compares was measured slower: C3 0.586 -> 0.610 ms)
 #pragma unroll
     for (int g = 0; g < G; ++g) any = any || bound_passes(m[g], c[g]);
     if (__any_sync(0xFFFFFFFFu, any)) {
