@@ -1175,6 +1175,9 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) 
         case 20: return launch_variant<16, 2, 1, 4, 4, 2, true>(p, stream);  // 2 warps per 128x4 tile
         case 31: return launch_variant<16, 2, 2, 4, 6, 1, true, 64>(p, stream);  // 6 CTAs/SM (<= 85 registers)
         // 5 CTAs/SM (96 registers, 128 B spilled; table of 64 / 96 primitives): C3 0.599 / 0.596 ms against 0.586 (v9)
+        // 32 rays per thread (2-warp CTAs of 256 x 8 pixels, 168 registers, 12 warps/SM; rolled epilogue): C3 0.637 ms,
+        // C4 8.84 ms against 0.586 / 8.65 -- the per-primitive overhead is shared by more rays, but 3 warps per
+        // scheduler no longer cover the FFMA2 -> FMNMX3 latency
         case 11: return launch_variant<16, 2, 2, 4, 4, 1, true, kTabPrims, false>(p, stream);  // row table, loads not pipelined
         // measured and dropped: two groups (8 primitives) per loop iteration to halve the loop control on the uniform
         // pipe: C3 0.7025 -> 0.7126 ms, C4 10.528 -> 10.684 ms (profiles/r01_variant_sweep_unroll2.jsonl)
