@@ -6,9 +6,11 @@ ray-primitive tests/s on synthetic scenes; % of FP32 peak; the CPU path timed be
   python bench.py --impl reference --gpus N --steps K ...  the reference's CPU path on the host cores
 
 One "step" = one frame of the workload.  With N > 1 (one process per GPU, torchrun) the frame is
-sharded as interleaved 16-row bands (strong scaling: the frame is fixed), the bands are gathered into
-rank 0's frame buffer over NCCL and de-interleaved by one copy kernel.  Prints ONE JSON line on
-rank 0.  Nothing here reads /root/reference.
+sharded as interleaved 16-row bands (strong scaling: the frame is fixed); every rank's kernel stores its
+bands straight into rank 0's frame over NVLink peer memory and the launch's last CTA signals rank 0
+(--no-peer: bands gathered over NCCL and de-interleaved by one copy kernel).  The headline numbers are
+the dense O(rays x primitives) kernel's; a second pass in the same run times the binned tile-cull mode
+("binned", byte-identical frames).  Prints ONE JSON line on rank 0.  Nothing here reads /root/reference.
 """
 import argparse
 import json
