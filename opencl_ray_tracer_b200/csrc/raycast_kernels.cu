@@ -866,8 +866,9 @@ raycast_binned_kernel(const GridParams p) {
     st.sid_stride = kThreads;
     const float fy = (float)gy;
     const float v = rtb_cam_v(p.cam, fy);
-    bool st_ready = false;  // the pixel state is set up when the tile's first primitive turns up
-    bool warp_hit = false;  // some ray of this warp passed some bound
+    bool warp_hit = false;  // some ray run of this warp passed some bound: the pixel state `st` is set up
+    // camera u of the thread's first and last ray, the values rtb_cam_u gives ((float)x0 + 15.0f is exact)
+    const uint64_t u_ends = pack2(fmaf(p.cam.l11, (float)x0, p.cam.l12 * fy), fmaf(p.cam.l11, (float)x0 + (float)(PX - 1), p.cam.l12 * fy));
 
     // Launched as a programmatic dependent of bin_tiles_kernel: everything above overlapped with that
     // grid's tail; from here on its bin words (and everything earlier in the stream) are visible.
@@ -896,16 +897,6 @@ raycast_binned_kernel(const GridParams p) {
             total += s;
         }
         if (total == 0) continue;
-        if (!st_ready) {
-            const float fx0 = (float)x0, row_term = p.cam.l12 * fy;
-#pragma unroll
-            for (int q = 0; q < PX; q += 2) {
-                // fmaf(l11, (float)(x0 + q), l12 * fy) = rtb_cam_u: (float)x0 + (float)q is exact
-                st.u2[q >> 1] = pack2(fmaf(p.cam.l11, fx0 + (float)q, row_term), fmaf(p.cam.l11, fx0 + (float)(q + 1), row_term));
-                st.best[q] = st.best[q + 1] = RTB_MISS_T;  // ids are read only where best != miss
-            }
-            st_ready = true;
-        }
         for (int pass = 0; pass < total; pass += kCap) {
             {   // the thread that owns a bit fetches that primitive's records (one round of loads per pass)
                 uint32_t mm = m;
@@ -937,9 +928,22 @@ raycast_binned_kernel(const GridParams p) {
             for (int e = 0; e < n; ++e) {
                 const float4 a = s_rec[e][0];
                 const RtbBound s = {a.x, a.y, a.z, a.w, s_rec[e][1].x, 0.f, 0.f, 0.f};
-                const float4 t = make_float4(s.sA, rtb_bound_row_w(s, v), rtb_bound_row_c(s, v), 0.f);
-                if (__any_sync(0xFFFFFFFFu, bound_passes(bound_min<PX>(t, st), t.z))) {
-                    warp_hit = true;
+                // span form of the bound (rtb_bound_span_m): w at the thread's two end pixels, as one FFMA2
+                const float rw = rtb_bound_row_w(s, v);
+                float wa, wb;
+                unpack2(ffma2(u_ends, pack2(s.sA, s.sA), pack2(rw, rw)), wa, wb);
+                if (__any_sync(0xFFFFFFFFu, bound_passes(rtb_bound_span_m(wa, wb), rtb_bound_row_c(s, v)))) {
+                    if (!warp_hit) {  // the warp's pixel state is set up when its first primitive turns up
+                        const float fx0 = (float)x0, row_term = p.cam.l12 * fy;
+#pragma unroll
+                        for (int q = 0; q < PX; q += 2) {
+                            // fmaf(l11, (float)(x0 + q), l12 * fy) = rtb_cam_u: (float)x0 + (float)q is exact
+                            st.u2[q >> 1] = pack2(fmaf(p.cam.l11, fx0 + (float)q, row_term),
+                                                  fmaf(p.cam.l11, fx0 + (float)(q + 1), row_term));
+                            st.best[q] = st.best[q + 1] = RTB_MISS_T;  // ids are read only where best != miss
+                        }
+                        warp_hit = true;
+                    }
                     exact_update_rec<PX>(p, s_prim[e], s_rec[e][2], s_rec[e][3], s_rec[e][4], v, st);
                 }
             }
@@ -1152,13 +1156,13 @@ static cudaError_t launch_binned(const GridParams& p, cudaStream_t stream) {
 
 static cudaError_t launch_binned_variant(const GridParams& p, cudaStream_t stream) {
     switch (binned_variant()) {
-        case 1: return launch_binned<16, 2, 2, 2, 8>(p, stream);   // 64 registers
+        case 1: return launch_binned<16, 2, 2, 2, 6>(p, stream);   // 80 registers, 6 CTAs/SM (C3 0.0338, C4 0.107 ms)
         case 2: return launch_binned<16, 2, 4, 1, 6>(p, stream);   // 128 x 16 tiles
         // measured and dropped (profiles/r01_variant_sweep_binned_v3_tilings.jsonl; C3 / C4 ms against 0.0339 / 0.109):
         // 64 x 16 tiles of two 32 x 16 warps 0.0356 / 0.132; of two 64 x 8 warps 0.0376 / 0.136; one warp per 32 x 16
         // tile 0.0392 / 0.190; per-warp lists instead of one per CTA (no CTA barrier, every warp expands the tile's words
         // itself) 0.0333 / 0.134 against 0.0322 / 0.106 (profiles/r01_variant_sweep_binned_v5_warp_lists.jsonl)
-        default: return launch_binned<16, 2, 2, 2, 6>(p, stream);  // 64 x 32 tiles, 4 warps of 32 x 16 pixels
+        default: return launch_binned<16, 2, 2, 2, 8>(p, stream);  // 64 x 32 tiles, 4 warps of 32 x 16 pixels, 64 registers (C3 0.0320, C4 0.102 ms)
     }
 }
 

@@ -120,6 +120,14 @@ RTB_HD float rtb_bound_q_of_w(float w, float rowC) { return fmaf(w, w, rowC); }
 RTB_HD float rtb_bound_q(float sA, float rowW, float rowC, float u) {
     return rtb_bound_q_of_w(rtb_bound_w(sA, rowW, u), rowC);
 }
+// A thread's rays are adjacent pixels of one row: u is monotone in x, w = fmaf(u, sA, rowW) is monotone in u, so
+// every w of the run lies between those of its two end pixels, w_a and w_b.  The distance from 0 to that interval
+// is a lower bound of min |w| over the run -- equal to it unless the run straddles w = 0 (then 0) -- hence
+// fmaf(m, m, rowC) < 2 with this m accepts every run that holds a ray with q < 2.  Used by the binned render,
+// where a few primitives meet every thread: 2 evaluations of w instead of one per ray.
+RTB_HD float rtb_bound_span_m(float w_a, float w_b) {
+    return fmaxf(fmaxf(fminf(w_a, w_b), fminf(-w_a, -w_b)), 0.0f);
+}
 
 // Tile cull (RTB_OPT_TILE_CULL): can NO ray of a pixel tile pass a primitive's bound?  The tile is given by the
 // ranges of the camera coordinates its rays take: u in [u_min, u_max], v in [v_min, v_max] (min / max over the

@@ -196,6 +196,12 @@ extern "C" long long emu_check_min_form(int width, int height, const float* cam8
                 const float qm = rtb_bound_q_of_w(m, rc);
                 if ((qm < 2.0f) != any) bad += 1;
                 else if (qm == qm && qmin == qmin && qm != qmin) bad += 1;
+                // the span form (binned render): never above the true minimum, and it accepts whenever a ray passes
+                const float wa = rtb_bound_w(b.sA, rw, rtb_cam_u(cam, (float)x0, fy));
+                const float wb = rtb_bound_w(b.sA, rw, rtb_cam_u(cam, (float)(x0 + run - 1), fy));
+                const float ms = rtb_bound_span_m(wa, wb);
+                if (ms > m) bad += 1;
+                if (any && !(rtb_bound_q_of_w(ms, rc) < 2.0f)) bad += 1;
             }
         }
     }
