@@ -32,6 +32,7 @@ WORKLOADS = {
 }
 SEQUENCE = {"c5": ("c3", 120, 3)}           # BASELINE config 5: 120-frame orbit (3 degrees per frame) of C3's scene
 BAND_ROWS = 16
+GROUP_SLOTS = 3   # frame slots of a multi-GPU job (rtb_group_join): the ranks run up to 2 frames ahead of rank 0
 
 # FP32 operations the shipped kernel executes per ray-primitive test (FMA = 2; min / compare / bit
 # operations / votes count 0).  Cubes and spheres go through the same dense loop: per ray ONE FMA
@@ -46,10 +47,22 @@ BAND_ROWS = 16
 # bit for bit with half the FMAs, and the frame takes 0.585 ms -- the FP32 fraction of the shipped kernel is LOWER
 # while every number a user sees is better.  What bounds it is the dispatch port: an FFMA2 and an FMNMX3 each hold
 # it for 2 clocks and serve 2 rays, i.e. 2 clocks per test and scheduler ("dispatch" below).
-FLOP_PER_TEST_RAY = 2.0
-FLOP_PER_TEST_THREAD = 2.0       # q = fmaf(m, m, rowC): once per thread and primitive, shared by the thread's rays
-FLOP_PER_TEST_ROW = 5.0
-DISPATCH_CLOCKS_PER_TEST = 2.0   # per scheduler (32 lanes): FFMA2 (2 clocks / 2 rays) + FMNMX3 (2 clocks / 2 rays)
+FLOP_PER_TEST = 2.0              # round 2: w' = fmaf(u, sAn, rWn), ONE FMA per ray-primitive test; nothing else is FP32 arithmetic
+PAIR_CLOCKS_FALLBACK = 5.0       # scheduler clocks per (FFMA2 + FMNMX3) pair if the probe binary is missing
+
+
+def bench_config(workload, world):
+    """The `config` object of a bench line: the SAME dict in our arm and in the reference arm (same_config)."""
+    return {"workload": workload_name(workload) if workload in WORKLOADS else
+            "c5: %d-frame orbit (%d degrees per frame about the scene centre) of %s" % (
+                SEQUENCE[workload][1], SEQUENCE[workload][2], workload_name(SEQUENCE[workload][0])),
+            "parallelism": "interleaved %d-row bands over %d GPU(s); one process per GPU, one C call per frame and rank "
+                           "(rtb_group_render: kernels store into rank 0's frame slots over NVLink peer memory, per-rank done / "
+                           "credit words, no collective in the frame loop); NCCL broadcasts the scene" % (BAND_ROWS, world)
+                           if world > 1 else "one GPU, whole frame per launch",
+            "l2": "256 MiB buffer written between timed iterations (L2 flush); per-step CUDA events on the launching stream",
+            "records": "static camera: the per-frame record pack / row table are cached after the first frame "
+                       "(moving_camera_ms_per_step times the same loop with a new camera every step)"}
 
 
 def workload_name(key):
@@ -66,7 +79,7 @@ def parse_args():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS) + sorted(SEQUENCE))
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-peer", action="store_true", help="N > 1: NCCL gather instead of peer-memory stores")
+    ap.add_argument("--no-c4", action="store_true", help="skip the BASELINE config 4 sub-record of a c3 run")
     ap.add_argument("--no-binned", action="store_true", help="skip the second pass with the binned tile cull (RTB_OPT_TILE_CULL = 2)")
     return ap.parse_args()
 
@@ -183,201 +196,211 @@ def cpu_baseline_port(scene, w, h, target_seconds):
             "tests_per_s": n_rows * w * (scene.ns + scene.nc) / dt}
 
 
-def run_ours(args):
+def _setup_dist():
     import torch
     import torch.distributed as dist
-    from opencl_ray_tracer_b200 import bands, capi, host_scene as hs
-
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus and rank == 0:
-        print("warning: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world), file=sys.stderr)
     torch.cuda.set_device(local_rank)
-    if world > 1:
+    if world > 1 and not dist.is_initialized():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    w, h, ns, nc, seed = WORKLOADS[args.workload]
-    scene = hs.random_scene(w, h, ns, nc, seed)
+    return rank, world, local_rank
+
+
+def _broadcast_scene(scene, rank, world):
+    """The scene lives on rank 0's host: the flattened arrays go to the other ranks over NCCL (north_star)."""
+    import torch
+    import torch.distributed as dist
+    from opencl_ray_tracer_b200 import host_scene as hs
+    if world == 1:
+        return scene
+    arrays = []
+    for a in scene.as_tuple():
+        g = torch.from_numpy(np.ascontiguousarray(a) if rank == 0 else np.zeros_like(a)).cuda()
+        dist.broadcast(g, 0)
+        arrays.append(g.cpu().numpy())
+    out = hs.SceneArrays(*arrays, label=scene.label)
+    out.cube_recipes = scene.cube_recipes
+    return out
+
+
+def _group_name(tag, rank, world):
+    """One name per job and workload for the ranks' shared-memory control block (rank 0 picks it)."""
+    import torch.distributed as dist
+    names = ["rtb_%s_%d_%d" % (tag, os.getpid(), int(time.time() * 1e3) % 100000000)]
     if world > 1:
-        # the scene lives on rank 0's host: broadcast the flattened arrays over NCCL (north_star)
-        arrays = []
-        for a in scene.as_tuple():
-            g = torch.from_numpy(np.ascontiguousarray(a) if rank == 0 else np.zeros_like(a)).cuda()
-            dist.broadcast(g, 0)
-            arrays.append(g.cpu().numpy())
-        scene = hs.SceneArrays(*arrays, label=scene.label)
-    ctx = capi.Context(local_rank)                # raises if librtb.so / the device is missing
+        dist.broadcast_object_list(names, 0)
+    return names[0]
+
+
+def measure_workload(args, key, ctx, rank, world, local_rank, steps, with_binned, with_moving):
+    """Times one BASELINE workload on the job's GPUs: device-resident frames (`value`), frames delivered to the host
+    through the C ABI (`e2e`), for the dense O(rays x primitives) kernel and -- with_binned -- for the binned mode.
+    world > 1: ONE C call per frame and rank (rtb_group_render / rtb_group_render_host): no collective, no Python
+    orchestration inside the frame."""
+    import torch
+    import torch.distributed as dist
+    from opencl_ray_tracer_b200 import capi, host_scene as hs
+
+    w, h, ns, nc, seed = WORKLOADS[key]
+    scene = _broadcast_scene(hs.random_scene(w, h, ns, nc, seed), rank, world)
+    ctx.set_option(capi.RTB_OPT_DEFER_SCENE_CHECK, 0)
     ctx.set_scene(*scene.as_tuple())
     cam = capi.REFERENCE_CAMERA
     n_px = w * h
-    rows_of = [ctx.band_local_rows(h, BAND_ROWS, r, world) for r in range(world)]
-    my_rows = rows_of[rank]
-    stream = torch.cuda.Stream()          # everything below (kernels, NCCL, events) runs on this stream
+    my_rows = ctx.band_local_rows(h, BAND_ROWS, rank, world)
+    stream = torch.cuda.Stream()          # everything below (kernels, events, the L2 flush) runs on this stream
     torch.cuda.set_stream(stream)
     sptr = stream.cuda_stream
-
-    if world == 1:
-        d_frame = torch.empty((h, w, 4), dtype=torch.uint8, device="cuda")
-        d_packed = d_frame
-        my_slice = d_frame
-    else:
-        if rank == 0:
-            d_packed = torch.empty((h, w, 4), dtype=torch.uint8, device="cuda")   # rank-major packed rows
-            d_frame = torch.empty((h, w, 4), dtype=torch.uint8, device="cuda")
-            my_slice = d_packed[:my_rows]
-        else:
-            d_packed = d_frame = None
-            my_slice = torch.empty((max(my_rows, 1), w, 4), dtype=torch.uint8, device="cuda")
+    grp = capi.Group(ctx, _group_name(key, rank, world), rank, world, w, h, BAND_ROWS, GROUP_SLOTS) if world > 1 else None
+    d_frame = torch.empty((h, w, 4), dtype=torch.uint8, device="cuda") if (world == 1 or rank == 0) else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
-    h_frame = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory() if rank == 0 else None
+    h_frame = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory().numpy() if world == 1 else None
+    # the step's inputs live in pinned host memory (the scene arrays in the reference's layout)
+    pinned_scene = tuple(torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).pin_memory().numpy()
+                         for a in scene.as_tuple())
+    last = {"ptr": None, "host": None}
 
-    # N > 1: every rank's kernel stores its bands straight into rank 0's frame over NVLink (CUDA IPC
-    # mapping); falls back to the NCCL gather + de-interleave kernel if IPC is refused.
-    # Frame slots: frame f goes to slot f % 3; a slot is handed back to the ranks by a collective that runs
-    # on a side stream, off the frame's critical path (rank 0 "consumes" a frame right after it is complete).
-    peer = None
-    PEER_SLOTS = 3
-    if world > 1 and not args.no_peer:
-        peer = bands.PeerFrame(dist, ctx, w, h, rank, world, n_frames=PEER_SLOTS)
-        if not peer.ok:
-            peer = None
-    peer_frame = peer.as_tensor() if (peer and rank == 0) else None
-    side = torch.cuda.Stream(priority=-1) if peer else None
-    side_token = torch.zeros(1, dtype=torch.int32, device="cuda")
-    released = [None] * PEER_SLOTS
-    state = {"frame": 0, "signals": True}
-    # N > 1, end to end: one frame in shared host memory; every rank's GPU delivers its own bands into it
-    shared = bands.SharedHostFrame(dist, w, h, rank, world) if world > 1 else None
-
-    def gather_and_assemble():
+    def device_step(camera=cam):
         if world == 1:
-            return 0
-        bands.gather_packed(dist, my_slice, d_packed, rows_of, rank, world)
-        if rank == 0:
-            ctx.assemble_bands_device(w, h, BAND_ROWS, world, 4, d_packed.data_ptr(), d_frame.data_ptr(), sptr)
-            return 1
-        return 0
-
-    def device_step():
-        if peer and state["signals"]:
-            slot = state["frame"] % PEER_SLOTS
-            if released[slot] is not None:
-                stream.wait_event(released[slot])          # rank 0 has let go of the frame that was in this slot
-            peer.render(cam, BAND_ROWS, sptr, frame=slot, signal=True)   # last CTA bumps rank 0's signal word
-            peer.wait_all(sptr)                            # rank 0: stream waits for all ranks' signals (no collective)
-            done = torch.cuda.Event()
-            done.record(stream)
-            side.wait_event(done)
-            with torch.cuda.stream(side):
-                dist.all_reduce(side_token)                # slot release, overlapped with the next frames
-                released[slot] = torch.cuda.Event()
-                released[slot].record(side)
-            state["frame"] += 1
-            return 1
-        if peer:
-            peer.render(cam, BAND_ROWS, sptr)
-            peer.fence()                   # 4-byte all-reduce on this stream: every rank's stores have landed
-            return 1
-        ctx.render_bands_device(w, h, cam, BAND_ROWS, rank, world, d_rgba8=my_slice.data_ptr(), stream=sptr)
-        return 1 + gather_and_assemble()
+            ctx.render_bands_device(w, h, camera, BAND_ROWS, 0, 1, d_rgba8=d_frame.data_ptr(), stream=sptr)
+        else:
+            last["ptr"] = grp.render(camera, sptr)       # rank 0: the frame's slot, complete in stream order
 
     def e2e_step():
         # what a caller of the C ABI does per frame with HOST data: scene arrays in, frame out
         ctx.set_scene(*pinned_scene)
         if world == 1:
-            ctx.render(w, h, cam, want=("rgba8",), out={"rgba8": h_np})
-            return 1
-        shared.render(ctx, cam, BAND_ROWS)     # blocking: this rank's bands are in the shared host frame
-        peer.fence() if peer else dist.all_reduce(token)   # 4-byte all-reduce: every rank has delivered
-        stream.synchronize()
-        return 1
-
-    h_np = h_frame.numpy() if rank == 0 else None
-    token = torch.zeros(1, dtype=torch.int32, device="cuda")
-    # the step's inputs live in pinned host memory (the scene arrays in the reference's layout)
-    pinned_scene = tuple(torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).pin_memory().numpy()
-                         for a in scene.as_tuple())
+            ctx.render(w, h, cam, want=("rgba8",), out={"rgba8": h_frame})
+            last["host"] = h_frame
+        else:
+            last["host"], _ = grp.render_host(cam)        # blocking; rank 0 returns when every rank has delivered
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed_pass(first):
-        """Device-resident timing (value) and end-to-end timing (e2e) of the render mode currently set."""
-        # ---- device-resident timing (value) -------------------------------------------------------
-        if peer and first:
-            try:                               # stream memory operations present?  (else: collective fence)
-                device_step()
-            except capi.RtbError:
-                state["signals"] = False
-            ok = torch.tensor([1 if state["signals"] else 0], dtype=torch.int32, device="cuda")
-            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-            state["signals"] = bool(int(ok.item()))
+    def all_max(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def timed_loop(step_fn, n):
+        """n steps, each between two CUDA events on the stream, L2 flushed before each (not timed); device ms summed,
+        max over ranks."""
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+        barrier()
+        wall0 = time.perf_counter()
+        for i, (a, b) in enumerate(ev):
+            flush.zero_()
+            a.record(stream)
+            step_fn(i)
+            b.record(stream)
+        barrier()
+        wall = time.perf_counter() - wall0
+        return all_max(sum(a.elapsed_time(b) for a, b in ev)) / n, wall * 1e3 / n
+
+    def timed_pass(mode):
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, mode)
         for _ in range(max(args.warmup, 3)):
             device_step()
         barrier()
         ctx.kernel_ms_avg(reset=True)
         sampler = ClockSampler(local_rank)
         sampler.start()
-        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-        launches = 0
-        barrier()
-        wall0 = time.perf_counter()
-        for a, b in ev:
-            flush.zero_()                      # L2 flush between timed iterations (not timed)
-            a.record(stream)
-            launches += device_step()
-            b.record(stream)
-        barrier()
-        wall = time.perf_counter() - wall0
-        dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+        n0 = ctx.launch_count()
+        ms_per_step, wall_ms = timed_loop(lambda i: device_step(), steps)
+        launches = ctx.launch_count() - n0
         k_avg_ms, k_n = ctx.kernel_ms_avg(reset=True)
         sampler.stop_flag = True
         sampler.join()
-        t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms = float(t.item())
-        ms_per_step = dev_ms / args.steps
-
-        # ---- end-to-end timing through the C ABI with host buffers (e2e) ---------------------------
+        out = dict(ms_per_step=ms_per_step, wall_ms_per_step=wall_ms, k_avg_ms=all_max(k_avg_ms), k_n=k_n, launches=launches,
+                   clocks=sampler.result())
+        # the same with the camera moving every step (orbit cameras): the FP64 record pack (and the dense kernel's row
+        # table) are then part of every step; with the static camera above they are cached after the first frame
+        if with_moving:
+            cams = [hs.orbit_camera(w, h, 1 + (k % 119)) for k in range(min(steps, 12) + 2)]
+            for c in cams[:2]:
+                device_step(c)
+            out["moving_ms_per_step"], _ = timed_loop(lambda i: device_step(cams[2 + i]), len(cams) - 2)
+            device_step()                      # back to the reference camera
+        barrier()
+        # ---- end to end through the C ABI with host buffers ----------------------------------------
+        ctx.set_option(capi.RTB_OPT_DEFER_SCENE_CHECK, 1)
         for _ in range(3):
             e2e_step()
         barrier()
         h2d0, d2h0 = ctx.transfer_bytes()
         t0 = time.perf_counter()
-        for _ in range(args.steps):
+        for _ in range(steps):
             e2e_step()
         barrier()
-        e2e_s = time.perf_counter() - t0
+        e2e_s = all_max(time.perf_counter() - t0)
         h2d1, d2h1 = ctx.transfer_bytes()
-        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-        # bytes this rank moved; summed over the ranks below (every rank uploads the scene, each downloads its bands)
+        ctx.set_option(capi.RTB_OPT_DEFER_SCENE_CHECK, 0)
+        # bytes this rank moved; summed over the ranks (every rank uploads the scene, each downloads its bands)
         tb = torch.tensor([float(h2d1 - h2d0), float(d2h1 - d2h0)], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(tb)
-        h2d_per_step, d2h_per_step = float(tb[0].item()) / args.steps, float(tb[1].item()) / args.steps
-        return dict(ms_per_step=ms_per_step, wall_ms_per_step=wall * 1e3 / args.steps, k_avg_ms=k_avg_ms, k_n=k_n,
-                    launches=launches, clocks=sampler.result(), e2e_s=e2e_s, h2d=h2d_per_step, d2h=d2h_per_step)
+        out.update(e2e_ms=e2e_s * 1e3 / steps, h2d=float(tb[0].item()) / steps, d2h=float(tb[1].item()) / steps)
+        return out
 
-    dense = timed_pass(True)
-    # The same frame with the tile cull made once per frame (RTB_OPT_TILE_CULL = 2: bin_tiles_kernel +
-    # raycast_binned_kernel, byte-identical output): reported beside the dense O(rays x primitives) numbers.
+    def frames_now():
+        """(device frame, host frame) of the last steps as numpy on rank 0 (None elsewhere)."""
+        torch.cuda.synchronize()
+        if rank != 0:
+            return None, None
+        dev = d_frame if world == 1 else grp.frame_tensor(last["ptr"])
+        return dev.cpu().numpy().copy(), np.array(last["host"], copy=True)
+
+    dense = timed_pass(capi.TILE_CULL_DENSE)
+    dev_dense, host_dense = frames_now()
+    # N > 1: the frame assembled from N GPUs' bands against the frame rank 0 renders on its own (dense kernel)
+    match = None
+    if world > 1:
+        barrier()
+        ok = {}
+        if rank == 0:
+            ctx.render_bands_device(w, h, cam, BAND_ROWS, 0, 1, d_rgba8=d_frame.data_ptr(), stream=sptr)
+            torch.cuda.synchronize()
+            single = d_frame.cpu().numpy()
+            ok = {"peer_store_frame": bool(np.array_equal(dev_dense, single)), "shared_host_frame": bool(np.array_equal(host_dense, single))}
+        barrier()
+        match = ok
     binned = None
-    if not args.no_binned:
-        ref_frame = d_frame.clone() if world == 1 else None
-        ctx.set_option(capi.RTB_OPT_TILE_CULL, 2)
-        binned = timed_pass(False)
-        binned["same_frame_as_dense"] = bool(torch.equal(ref_frame, d_frame)) if world == 1 else None
-        ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
-    if shared is not None:
-        shared.close()
-    return dict(rank=rank, world=world, w=w, h=h, ns=ns, nc=nc, seed=seed, scene=scene, ctx=ctx,
-                peer=bool(peer), signals=bool(peer and state["signals"]), my_rows=my_rows, binned=binned, **dense)
+    if with_binned:
+        # The same frame with the tile cull made once per frame (RTB_OPT_TILE_CULL = 2: bin_tiles_kernel +
+        # raycast_binned_kernel, byte-identical output): reported beside the dense O(rays x primitives) numbers.
+        binned = timed_pass(capi.TILE_CULL_BINNED)
+        dev_b, host_b = frames_now()
+        if rank == 0:
+            binned["same_frame_as_dense"] = bool(np.array_equal(dev_b, dev_dense) and np.array_equal(host_b, host_dense))
+            if match is not None:
+                match["binned_frame"] = binned["same_frame_as_dense"] and match["peer_store_frame"]
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_AUTO)
+    barrier()
+    if grp is not None:
+        grp.close()
+    torch.cuda.set_stream(torch.cuda.default_stream())
+    del flush, d_frame
+    return dict(key=key, w=w, h=h, ns=ns, nc=nc, seed=seed, scene=scene, my_rows=my_rows, dense=dense, binned=binned, match=match)
+
+
+def run_ours(args):
+    from opencl_ray_tracer_b200 import capi
+    rank, world, local_rank = _setup_dist()
+    if world != args.gpus and rank == 0:
+        print("warning: --gpus %d but WORLD_SIZE %d; using WORLD_SIZE" % (args.gpus, world), file=sys.stderr)
+    ctx = capi.Context(local_rank)                # raises if librtb.so / the device is missing
+    main = measure_workload(args, args.workload, ctx, rank, world, local_rank, args.steps, not args.no_binned, True)
+    c4 = None
+    if args.workload == "c3" and not args.no_c4:
+        # BASELINE config 4 (7680x4320, 4096 primitives: the config named for sharding) in every line, fewer steps
+        c4 = measure_workload(args, "c4", ctx, rank, world, local_rank, max(3, min(args.steps, 10)), not args.no_binned, False)
+    return dict(rank=rank, world=world, ctx=ctx, main=main, c4=c4)
 
 
 def run_sequence(args):
@@ -388,25 +411,21 @@ def run_sequence(args):
     import torch
     import torch.distributed as dist
     from opencl_ray_tracer_b200 import bands, capi, host_scene as hs
-    rank, world, local_rank = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    rank, world, local_rank = _setup_dist()
     base, n_frames, deg = SEQUENCE[args.workload]
     w, h, ns, nc, seed = WORKLOADS[base]
-    scene = hs.random_scene(w, h, ns, nc, seed)
+    scene = _broadcast_scene(hs.random_scene(w, h, ns, nc, seed), rank, world)
     ctx = capi.Context(local_rank)
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_DENSE)
     ctx.set_scene(*scene.as_tuple())
     cams = [hs.orbit_camera(w, h, k) for k in range(n_frames)]
     flat = np.stack([np.concatenate(c) for c in cams])
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
     sptr = stream.cuda_stream
-    peer = bands.PeerFrame(dist, ctx, w, h, rank, world, n_frames=n_frames) if world > 1 else None
-    if peer is not None and not peer.ok:
-        raise RuntimeError("CUDA IPC unavailable: the sequence bench needs the peer frame buffer")
+    # N > 1: a ring of 8 frame slots on rank 0 (the ranks run up to 7 frames ahead of rank 0's stream)
+    grp = capi.Group(ctx, _group_name("c5", rank, world), rank, world, w, h, BAND_ROWS, 8) if world > 1 else None
     d_out = torch.empty((n_frames, h, w, 4), dtype=torch.uint8, device="cuda") if world == 1 else None
-    shared = bands.SharedHostFrame(dist, w, h, rank, world) if world > 1 else None
     h_frame = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory().numpy() if world == 1 else None
     token = torch.zeros(1, dtype=torch.int32, device="cuda")
 
@@ -414,10 +433,9 @@ def run_sequence(args):
         if world == 1:
             ctx.render_sequence_device(w, h, flat, d_out.data_ptr())     # blocking
             return
-        ctx.prepack_cameras(w, h, flat, sptr)          # the frames' records are packed ahead on the context's side stream
+        grp.prepack(flat, sptr)        # the frames' records (this rank's bands) are packed ahead on the context's side stream
         for f in range(n_frames):
-            peer.render(cams[f], BAND_ROWS, sptr, frame=f)
-        peer.fence()
+            grp.render(cams[f], sptr)  # one C call per frame and rank; rank 0's stream holds every frame's completion
         stream.synchronize()
 
     def e2e_step():
@@ -425,10 +443,7 @@ def run_sequence(args):
             if world == 1:
                 ctx.render(w, h, cams[f], want=("rgba8",), out={"rgba8": h_frame})
             else:
-                shared.render(ctx, cams[f], BAND_ROWS)
-        if world > 1:
-            dist.all_reduce(token)
-            stream.synchronize()
+                grp.render_host(cams[f])
 
     def barrier():
         if world > 1:
@@ -452,7 +467,9 @@ def run_sequence(args):
     ctx.kernel_ms_avg(reset=True)
     sampler = ClockSampler(local_rank)
     sampler.start()
+    n_launch0 = ctx.launch_count()
     dev_s = timed(device_step, steps)
+    launches = ctx.launch_count() - n_launch0
     sampler.stop_flag = True
     sampler.join()
     k_avg_ms, k_n = ctx.kernel_ms_avg(reset=True)
@@ -462,7 +479,7 @@ def run_sequence(args):
         ctx.set_option(capi.RTB_OPT_TILE_CULL, 2)
         device_step()
         binned_s = timed(device_step, steps) / steps
-        ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_DENSE)
     e2e_step()
     e2e_steps = max(1, steps // 4)
     h2d0, d2h0 = ctx.transfer_bytes()
@@ -477,7 +494,7 @@ def run_sequence(args):
         sms = ctx.device_info()["sm_count"]
         my_rows = ctx.band_local_rows(h, BAND_ROWS, 0, world)
         px, tile_w = capi.debug_grid_shape(w, my_rows, sms)[:2]
-        flop_per_test = FLOP_PER_TEST_RAY + FLOP_PER_TEST_THREAD / px + FLOP_PER_TEST_ROW / tile_w
+        flop_per_test = FLOP_PER_TEST
         probe = fp32_probe_tflops()
         peak_nominal = sms * 128 * 2 * (sampler.result()["sm_max_mhz"] or 1965.0) * 1e6 / 1e12
         achieved = my_rows * w * (ns + nc) * flop_per_test / (k_avg_ms * 1e-3) / 1e12 if k_avg_ms > 0 else 0.0
@@ -486,12 +503,10 @@ def run_sequence(args):
             "metric": "Mrays/s", "value": n_frames * n_px / s_step / 1e6, "unit": "Mrays/s", "n_gpus": world,
             "steps": steps, "warmup": max(1, min(args.warmup, 3)), "ms_per_step": s_step * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "c5: %d-frame orbit (%d degrees per frame about the scene centre) of %s" % (
-                           n_frames, deg, workload_name(base)),
-                       "parallelism": "every frame as interleaved %d-row bands over %d GPU(s)%s" % (
-                           BAND_ROWS, world, "" if world == 1 else ", kernels store into rank 0's sequence buffer over NVLink peer memory, one fence per sequence"),
-                       "l2": "each step writes %d frames = %.1f GB of output (larger than L2); a step is timed as a whole (wall clock around blocking calls, max over ranks)" % (
-                           n_frames, n_frames * 4 * n_px / 1e9)},
+            "config": dict(bench_config(args.workload, world),
+                           l2="each step writes %d frames = %.1f GB of output (larger than L2); a step is timed as a whole (wall clock around blocking calls, max over ranks)" % (
+                               n_frames, n_frames * 4 * n_px / 1e9),
+                           records="moving camera: every frame's records and row table are packed (ahead, on a side stream)"),
             "frames_per_s": n_frames / s_step, "ms_per_frame": s_step * 1e3 / n_frames,
             "tests_per_s": n_frames * n_px * (ns + nc) / s_step,
             "clocks": sampler.result(),
@@ -500,9 +515,9 @@ def run_sequence(args):
                     "h2d_bytes_per_step": float(tb[0].item()) / e2e_steps, "d2h_bytes_per_step": float(tb[1].item()) / e2e_steps,
                     "ms_per_step": e2e_s * 1e3 / e2e_steps,
                     "what": "every frame rendered and delivered into a pinned (N = 1) / shared page-locked (N > 1) host frame; the scene stays resident, the step's input is the camera sequence"},
-            "gpu_launches": 2 * n_frames * steps,
+            "gpu_launches": launches,
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
-                         "traffic": None, "kernel": "raycast_grid_kernel", "kernel_ms": k_avg_ms, "kernel_launches_timed": k_n,
+                         "traffic": None, "kernel": "raycast_dense_kernel", "kernel_ms": k_avg_ms, "kernel_launches_timed": k_n,
                          "flop_per_test": flop_per_test, "rays_per_thread": px,
                          "peak_source": ("fp32_issue_probe (packed FFMA2 chains) run on this GPU just now" if probe
                                          else "nominal SMs x 128 lanes x 2 x max SM clock")},
@@ -512,12 +527,9 @@ def run_sequence(args):
                                       "byte-identical frames), device-resident", "frames_per_s": n_frames / binned_s,
                               "ms_per_frame": binned_s * 1e3 / n_frames, "value": n_frames * n_px / binned_s / 1e6, "unit": "Mrays/s"}
         print(json.dumps(line))
-    if shared is not None:
-        shared.close()
     if world > 1:
         dist.barrier()
-        if peer is not None:
-            peer.close()
+        grp.close()
         dist.destroy_process_group()
 
 
@@ -644,6 +656,110 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def pair_rate_probe():
+    """profiles/microbench/pair_rate_probe: scheduler clocks per (FFMA2 + FMNMX3) pair on this GPU, alone and with the
+    loop's other instructions mixed in -- the per-ray-pair, per-primitive cost that bounds the dense kernel."""
+    import subprocess
+    exe = os.path.join(ROOT, "profiles", "microbench", "pair_rate_probe")
+    if not os.path.isfile(exe):
+        return None
+    try:
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=60).stdout
+        res = {}
+        for line in out.splitlines():
+            j = json.loads(line)
+            if "clocks_per_ffma2_fmnmx3_pair" in j:
+                res["with_loop_overhead" if "LDS" in j["mix"] else "pair_only"] = j["clocks_per_ffma2_fmnmx3_pair"]
+            elif j.get("mix") == "8xFFMA2":
+                res["ffma2"] = j["clocks_per_instr"]
+            elif j.get("mix", "").startswith("8xFMNMX3"):
+                res["fmnmx3"] = j["clocks_per_instr"]
+        return res or None
+    except Exception:
+        return None
+
+
+def workload_record(args, r, world, ctx, peaks, peaks_src, probe, pair):
+    """The JSON fields of one measured workload (measure_workload's result `r`)."""
+    from opencl_ray_tracer_b200 import capi
+    w, h, ns, nc = r["w"], r["h"], r["ns"], r["nc"]
+    n_px = w * h
+    d = r["dense"]
+    steps = None
+    info = ctx.device_info()
+    sms = info["sm_count"]
+    sm_max = (d["clocks"]["sm_max_mhz"] or peaks.get("sm_max_mhz", 1965.0))
+    peak_nominal = sms * 128 * 2 * sm_max * 1e6 / 1e12          # TFLOP/s at the max SM clock
+    px, tile_w = capi.debug_grid_shape(w, r["my_rows"], sms)[:2]
+    k_s = d["k_avg_ms"] * 1e-3
+    tests_launch = r["my_rows"] * w * (nc + ns)
+    achieved = tests_launch * FLOP_PER_TEST / k_s / 1e12 if k_s > 0 else 0.0
+    peak = probe if probe else peak_nominal
+    pair_clk = (pair or {}).get("pair_only") or PAIR_CLOCKS_FALLBACK
+    disp_peak = sms * 4 * 32 * sm_max * 1e6 * 2.0 / pair_clk      # tests/s: 2 rays per pair, 32 lanes, 4 schedulers per SM
+    rec = {
+        "value": n_px / (d["ms_per_step"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": d["ms_per_step"],
+        "kernel_ms": d["k_avg_ms"], "step_minus_kernel_ms": d["ms_per_step"] - d["k_avg_ms"],
+        "tests_per_s": n_px * (ns + nc) / (d["ms_per_step"] * 1e-3),
+        "wall_ms_per_step_incl_flush": d["wall_ms_per_step"], "gpu_launches": d["launches"],
+        "moving_camera_ms_per_step": d.get("moving_ms_per_step"),
+        "e2e": {"value": n_px / (d["e2e_ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": d["e2e_ms"],
+                "h2d_bytes_per_step": d["h2d"], "d2h_bytes_per_step": d["d2h"]},
+        "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                     "frac": achieved / peak if peak else None,
+                     "traffic": ncu_traffic_bytes(r["key"]) if world == 1 else None,
+                     "traffic_unit": "bytes of DRAM traffic per launch (ncu capture in profiles/, not this run)",
+                     "kernel": "raycast_dense_kernel", "kernel_ms": d["k_avg_ms"], "kernel_launches_timed": d["k_n"],
+                     "flop_per_test": FLOP_PER_TEST, "rays_per_thread": px, "tile_width": tile_w,
+                     "peak_source": ("fp32_issue_probe (packed FFMA2 chains) run on this GPU just now" if probe
+                                     else "nominal SMs x 128 lanes x 2 x max SM clock"),
+                     "peak_nominal_tflops": peak_nominal, "frac_of_nominal": achieved / peak_nominal,
+                     "north_star_target_frac": 0.60,
+                     "note": "the >= 60 % FP32-FMA target of BASELINE.md is NOT met: the shipped formulation needs ONE FMA per "
+                             "ray-primitive test and its other instruction (the 3-input FMNMX of the running minimum) does not "
+                             "run in the shadow of the FMAs -- see `dispatch`",
+                     "algorithmic_flops_at_baseline_constants": {
+                         "what": "the same tests/s priced at BASELINE.md's per-ray world-space formulation (27 flop per cube test, "
+                                 "18 per sphere test) -- arithmetic this kernel does not execute; for comparison only",
+                         "tflops": (r["my_rows"] * w * (27.0 * nc + 18.0 * ns) / k_s / 1e12) if k_s > 0 else None},
+                     "dispatch": {"what": "tests per second against the measured issue cost of the loop body: one FFMA2 and one "
+                                          "FMNMX3 per ray pair and primitive = %.2f scheduler clocks (pair_rate_probe on this GPU%s); "
+                                          "peak = SMs x 4 schedulers x 32 lanes x 2 rays x max SM clock / that" % (
+                                              pair_clk, "" if pair else ": probe missing, round-2 measurement used"),
+                                  "clocks_per_pair": pair_clk, "probe": pair,
+                                  "achieved_tests_per_s": tests_launch / k_s if k_s > 0 else None,
+                                  "peak_tests_per_s": disp_peak,
+                                  "frac": (tests_launch / k_s) / disp_peak if k_s > 0 else None},
+                     "framebuffer_write_gbs": r["my_rows"] * w * 4 / k_s / 1e9 if k_s > 0 else None,
+                     "hbm_peak_gbs": peaks.get("hbm_gbs"), "hbm_peak_source": peaks_src},
+        "clocks": d["clocks"],
+    }
+    if r["binned"]:
+        bn = r["binned"]
+        bk_s = bn["k_avg_ms"] * 1e-3
+        frame_bytes = r["my_rows"] * w * 4
+        rec["binned"] = {
+            "what": "the same frame, byte for byte, with RTB_OPT_TILE_CULL = 2 (what the default, auto, picks from 64 primitives on): "
+                    "bin_tiles_kernel decides once per frame which primitives a 64x32-pixel tile can see, raycast_binned_kernel runs "
+                    "the per-ray tests for those only (not O(rays x primitives): no tests/s or FP32 fraction is claimed for it)",
+            "value": n_px / (bn["ms_per_step"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": bn["ms_per_step"],
+            "kernels_ms": bn["k_avg_ms"], "step_minus_kernel_ms": bn["ms_per_step"] - bn["k_avg_ms"], "gpu_launches": bn["launches"],
+            "moving_camera_ms_per_step": bn.get("moving_ms_per_step"), "same_frame_as_dense": bn.get("same_frame_as_dense"),
+            "e2e": {"value": n_px / (bn["e2e_ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": bn["e2e_ms"],
+                    "h2d_bytes_per_step": bn["h2d"], "d2h_bytes_per_step": bn["d2h"]},
+            "roofline": {"bound": "hbm", "achieved": frame_bytes / bk_s / 1e9 if bk_s > 0 else None, "peak": peaks.get("hbm_gbs"),
+                         "unit": "GB/s", "frac": (frame_bytes / bk_s / 1e9 / peaks["hbm_gbs"]) if (bk_s > 0 and peaks.get("hbm_gbs")) else None,
+                         "traffic": ncu_traffic_bytes(r["key"], "binned") if world == 1 else None,
+                         "traffic_unit": "bytes of DRAM traffic per frame (ncu capture in profiles/, not this run): the frame stays in the 126 MB L2",
+                         "kernel": "bin_tiles_kernel + raycast_binned_kernel",
+                         "algorithmic_bytes": "the frame write, 4 B per ray (this rank's rows)", "peak_source": peaks_src},
+            "clocks": bn["clocks"],
+        }
+    if r["match"] is not None:
+        rec["frame_matches_single_gpu"] = r["match"]
+    return rec
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -655,93 +771,50 @@ def main():
         run_sequence(args)
         return
     r = run_ours(args)
-    from opencl_ray_tracer_b200 import capi as capi_mod
     import torch.distributed as dist
+    world = r["world"]
     if r["rank"] == 0:
         peaks, peaks_src = load_peaks()
-        w, h, ns, nc = r["w"], r["h"], r["ns"], r["nc"]
-        n_px = w * h
-        s_step = r["ms_per_step"] * 1e-3
-        mrays = n_px / s_step / 1e6
-        info = r["ctx"].device_info()
-        sms = info["sm_count"]
-        sm_max = (r["clocks"]["sm_max_mhz"] or peaks.get("sm_max_mhz", 1965.0))
-        peak_nominal = sms * 128 * 2 * sm_max * 1e6 / 1e12          # TFLOP/s at the max SM clock
         probe = fp32_probe_tflops()
-        # dominant kernel = the ray-cast grid kernel; this rank's launch covers my_rows rows
-        px, tile_w = capi_mod.debug_grid_shape(w, r["my_rows"], sms)[:2]
-        flop_per_test = FLOP_PER_TEST_RAY + FLOP_PER_TEST_THREAD / px + FLOP_PER_TEST_ROW / tile_w
-        flops_per_launch = r["my_rows"] * w * (nc + ns) * flop_per_test
-        k_s = r["k_avg_ms"] * 1e-3
-        achieved = flops_per_launch / k_s / 1e12 if k_s > 0 else 0.0
-        peak = probe if probe else peak_nominal
+        pair = pair_rate_probe()
+        m = r["main"]
+        rec = workload_record(args, m, world, r["ctx"], peaks, peaks_src, probe, pair)
         line = {
-            "metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": r["world"], "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "metric": "Mrays/s", "value": rec["value"], "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": rec["ms_per_step"], "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args.workload),
-                       "parallelism": "interleaved %d-row bands over %d GPU(s)%s" % (
-                           BAND_ROWS, r["world"],
-                           "" if r["world"] == 1 else
-                           (", kernels store into rank 0's frame over NVLink peer memory; fence = " +
-                            ("each launch's last CTA bumps a signal word in rank 0's memory, rank 0's stream waits on it (cuStreamWaitValue32); "
-                             "3 frame slots, released by an all-reduce on a side stream" if r["signals"] else "4-byte NCCL all-reduce")
-                            if r["peer"] else ", NCCL gather to rank 0 + de-interleave kernel")),
-                       "l2": "256 MiB buffer written between timed iterations (L2 flush); per-step CUDA events"},
-            "tests_per_s": mrays * 1e6 * (ns + nc),
-            "wall_ms_per_step_incl_flush": r["wall_ms_per_step"],
-            "clocks": r["clocks"],
-            "e2e": {"value": n_px * args.steps / r["e2e_s"] / 1e6, "unit": "Mrays/s",
-                    "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
-                    "ms_per_step": r["e2e_s"] * 1e3 / args.steps,
-                    "what": ("rtb_set_scene (scene arrays H2D, boxes recovered on the device) + rtb_render (device record pack, ONE grid "
-                             "launch, finished row chunks copied to pinned host memory while it runs)"
-                             if r["world"] == 1 else
-                             "rtb_set_scene on every rank + rtb_render_bands_host: each GPU copies its own bands (finished chunks while its "
-                             "launch runs) over its own PCIe link into ONE frame in shared, page-locked host memory; 4-byte all-reduce as the barrier")},
-            "gpu_launches": r["launches"],
-            "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak if peak else None,
-                         "traffic": ncu_traffic_bytes(args.workload) if r["world"] == 1 else None,
-                         "traffic_unit": "bytes of DRAM traffic per launch (ncu capture in profiles/, not this run)",
-                         "kernel": "raycast_grid_kernel", "kernel_ms": r["k_avg_ms"], "kernel_launches_timed": r["k_n"],
-                         "flop_per_test": flop_per_test, "rays_per_thread": px,
-                         "peak_source": ("fp32_issue_probe (packed FFMA2 chains) run on this GPU just now" if probe
-                                         else "nominal SMs x 128 lanes x 2 x max SM clock"),
-                         "peak_nominal_tflops": peak_nominal,
-                         "frac_of_nominal": achieved / peak_nominal,
-                         "dispatch": {"what": "tests per second against the dispatch-port bound of the formulation: SMs x 4 schedulers x 32 lanes "
-                                              "x max SM clock / 2 clocks per test (one FFMA2 + one FMNMX3 per ray pair, 2 dispatch clocks each)",
-                                      "achieved_tests_per_s": r["my_rows"] * w * (nc + ns) / k_s if k_s > 0 else None,
-                                      "peak_tests_per_s": sms * 4 * 32 * sm_max * 1e6 / DISPATCH_CLOCKS_PER_TEST,
-                                      "frac": (r["my_rows"] * w * (nc + ns) / k_s) / (sms * 4 * 32 * sm_max * 1e6 / DISPATCH_CLOCKS_PER_TEST) if k_s > 0 else None},
-                         "framebuffer_write_gbs": r["my_rows"] * w * 4 / k_s / 1e9 if k_s > 0 else None,
-                         "hbm_peak_gbs": peaks.get("hbm_gbs"), "hbm_peak_source": peaks_src},
+            "config": bench_config(args.workload, world),
         }
-        if r["binned"]:
-            bn = r["binned"]
-            bk_s = bn["k_avg_ms"] * 1e-3
-            frame_bytes = r["my_rows"] * w * 4
-            line["binned"] = {
-                "what": "the same frame, byte for byte, with RTB_OPT_TILE_CULL = 2: bin_tiles_kernel decides once per frame which primitives "
-                        "a 64x32-pixel tile can see, raycast_binned_kernel runs the per-ray tests for those only (not O(rays x primitives): "
-                        "no tests/s or FP32 fraction is claimed for it)",
-                "value": n_px / (bn["ms_per_step"] * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_step": bn["ms_per_step"],
-                "kernels_ms": bn["k_avg_ms"], "gpu_launches": 2 * bn["launches"], "same_frame_as_dense": bn["same_frame_as_dense"],
-                "e2e": {"value": n_px * args.steps / bn["e2e_s"] / 1e6, "unit": "Mrays/s", "ms_per_step": bn["e2e_s"] * 1e3 / args.steps,
-                        "h2d_bytes_per_step": bn["h2d"], "d2h_bytes_per_step": bn["d2h"]},
-                "roofline": {"bound": "hbm", "achieved": frame_bytes / bk_s / 1e9 if bk_s > 0 else None, "peak": peaks.get("hbm_gbs"),
-                             "unit": "GB/s", "frac": (frame_bytes / bk_s / 1e9 / peaks["hbm_gbs"]) if (bk_s > 0 and peaks.get("hbm_gbs")) else None,
-                             "traffic": ncu_traffic_bytes(args.workload, "binned") if r["world"] == 1 else None,
-                             "traffic_unit": "bytes of DRAM traffic per frame (ncu capture in profiles/, not this run): the frame stays in the 126 MB L2",
-                             "kernel": "bin_tiles_kernel + raycast_binned_kernel",
-                             "algorithmic_bytes": "the frame write, 4 B per ray (this rank's rows)", "peak_source": peaks_src},
-                "clocks": bn["clocks"],
-            }
-        if r["world"] == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline_port(r["scene"], w, h, args.cpu_seconds)
+        for k in ("tests_per_s", "kernel_ms", "step_minus_kernel_ms", "wall_ms_per_step_incl_flush", "moving_camera_ms_per_step", "clocks"):
+            line[k] = rec[k]
+        line["e2e"] = dict(rec["e2e"], what=(
+            "rtb_set_scene (arrays staged in pinned memory, H2D, boxes recovered on the device; RTB_OPT_DEFER_SCENE_CHECK = 1: no wait "
+            "for the device) + rtb_render (device record pack + row table, ONE dense launch, finished row chunks copied to pinned "
+            "host memory while it runs)" if world == 1 else
+            "per rank and frame: rtb_set_scene + rtb_group_render_host -- each GPU copies its own bands (finished chunks while its "
+            "launch runs) over its own PCIe link into ONE frame in shared, page-locked host memory; completion and release through "
+            "counters in the ranks' shared control block (no collective)"))
+        line["gpu_launches"] = rec["gpu_launches"]
+        line["roofline"] = rec["roofline"]
+        if "binned" in rec:
+            line["binned"] = rec["binned"]
+        if "frame_matches_single_gpu" in rec:
+            line["frame_matches_single_gpu"] = rec["frame_matches_single_gpu"]
+        if r["c4"] is not None:
+            c4 = workload_record(args, r["c4"], world, r["ctx"], peaks, peaks_src, probe, pair)
+            sub = {"what": "BASELINE config 4 in the same run: " + workload_name("c4"), "steps": max(3, min(args.steps, 10))}
+            for k in ("value", "unit", "ms_per_step", "kernel_ms", "step_minus_kernel_ms", "tests_per_s", "e2e", "gpu_launches"):
+                sub[k] = c4[k]
+            sub["roofline"] = {k: c4["roofline"][k] for k in ("bound", "achieved", "peak", "unit", "frac", "frac_of_nominal", "kernel_ms", "dispatch")}
+            if "binned" in c4:
+                sub["binned"] = {k: c4["binned"][k] for k in ("value", "unit", "ms_per_step", "kernels_ms", "same_frame_as_dense", "e2e")}
+            if "frame_matches_single_gpu" in c4:
+                sub["frame_matches_single_gpu"] = c4["frame_matches_single_gpu"]
+            line["c4"] = sub
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_port(m["scene"], m["w"], m["h"], args.cpu_seconds)
         print(json.dumps(line))
-    if r["world"] > 1:
+    if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 

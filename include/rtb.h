@@ -53,13 +53,21 @@ typedef enum rtb_status {
     RTB_ERR_NOT_A_BOX = 5,    /* a cube's 36 vertices are not an affine image of Cube.cpp's    */
     RTB_ERR_CAMERA = 6,       /* degenerate camera: dU, dV, rayDir do not span a ray grid      */
     RTB_ERR_OUT_OF_MEMORY = 7,
-    RTB_ERR_UNSUPPORTED = 8   /* e.g. n_devices > 1 inside one process (use one process/GPU)   */
+    RTB_ERR_UNSUPPORTED = 8   /* e.g. no peer access between the devices of a multi-device context */
 } rtb_status;
 
+#define RTB_MAX_GROUP 16      /* devices of one context / ranks of one group */
+
 /* Replaces MainState::openCLInit (MainState.cpp:1181-1326: platform/device pick, context, queue,
- * program build, kernel).  n_devices must be 1 (one process per GPU; multi-GPU frames are sharded
- * by the caller with rtb_render_bands_device).  device_ids may be NULL
- * (= device 0).  Unlike the reference, failures are reported, not printed and ignored. */
+ * program build, kernel).  device_ids may be NULL (= devices 0 .. n_devices-1).  Unlike the reference,
+ * failures are reported, not printed and ignored.
+ * n_devices = 1: one device.  n_devices = 2 .. RTB_MAX_GROUP: the context drives that many GPUs of this box from
+ * this one process (a worker thread per device, peer access over NVLink): rtb_set_scene uploads to every device,
+ * rtb_render shards each frame as interleaved 16-row bands and every GPU delivers its bands over its own PCIe
+ * link into the caller's buffers, rtb_render_sequence_device keeps the frames on the first device (the others
+ * store their bands into it over NVLink).  Still ONE blocking call per frame, like the reference's
+ * (MainState.cpp:217-224).  The device-pointer entry points (rtb_render_bands_*, rtb_peer_frame_*, ...) are the
+ * building blocks of the one-process-per-GPU form (rtb_group_join below) and need a single-device context. */
 int rtb_init(rtb_ctx** out, int n_devices, const int* device_ids);
 
 /* Replaces the four clRelease* calls of MainState::~MainState (MainState.cpp:75-78). */
@@ -73,8 +81,10 @@ const char* rtb_last_error_message(const rtb_ctx* ctx);
 
 /* Per-context switches; every render entry point below obeys them.  No counterpart in the
  * reference (its only switch is enum Mode, MainState.h:48-52).
- *   RTB_OPT_TILE_CULL (0 | 1 | 2, default 0): which kernels render.  The pixels are byte-identical in all
- *     three modes (the culls are statements about the values the per-ray bound would compute).
+ *   RTB_OPT_TILE_CULL (0 | 1 | 2 | 3, default 3): which kernels render.  The pixels are byte-identical in all
+ *     modes (the culls are statements about the values the per-ray bound would compute).
+ *     3 = auto (the default): 2 for scenes of 64 primitives or more, else 0 -- the fastest byte-identical mode is
+ *         what a caller gets without asking.
  *     0 = the dense O(rays x primitives) kernel that BASELINE.json's roofline point is quoted on.
  *     1 = raycast_cull_kernel: every CTA first tests each primitive's conservative screen-space bound
  *         against its whole 256 x 8 pixel tile and runs the per-ray tests only for the survivors:
@@ -85,8 +95,12 @@ const char* rtb_last_error_message(const rtb_ctx* ctx);
  *         second a programmatic dependent of the first; the fastest mode on SURVEY.md s8d's scenes.
  *         With mode 1 or 2 rtb_render copies the frame to the host in one piece behind the launch
  *         (the launch is much shorter than the PCIe time, there is nothing to overlap).
+ *   RTB_OPT_DEFER_SCENE_CHECK (0 | 1, default 0): 0 = rtb_set_scene waits for the device's box check and returns
+ *     RTB_ERR_NOT_A_BOX itself.  1 = rtb_set_scene returns as soon as the arrays are staged (no wait for the
+ *     device); the verdict is returned by the next render call instead (by a blocking one after its own wait for
+ *     the frame, so nothing ever waits for the scene upload alone).
  */
-typedef enum rtb_option { RTB_OPT_TILE_CULL = 1 } rtb_option;
+typedef enum rtb_option { RTB_OPT_TILE_CULL = 1, RTB_OPT_DEFER_SCENE_CHECK = 2 } rtb_option;
 int rtb_set_option(rtb_ctx* ctx, int option, int value);
 int rtb_get_option(const rtb_ctx* ctx, int option, int* value);
 
@@ -200,6 +214,43 @@ int rtb_render_sequence_device(rtb_ctx* ctx, int width, int height, int n_frames
  * rtb_render_sequence_device or rtb_set_scene.  Cameras beyond the capacity are simply packed by their own
  * render call.  No counterpart in the reference (it has one fixed camera, MainState.cpp:37-50). */
 int rtb_prepack_cameras(rtb_ctx* ctx, int width, int height, int n_cameras, const float* cameras, void* stream);
+/* The same for a rank that renders only its row bands (the dense kernel's row table is then built for those rows
+ * only; a render call with other bands simply builds its own). */
+int rtb_prepack_cameras_bands(rtb_ctx* ctx, int width, int height, int band_rows, int band_rank, int band_world,
+                              int n_cameras, const float* cameras, void* stream);
+
+/* ---- multi-GPU frames, one process per GPU: ONE call per frame and rank, no collective, no Python -------------
+ * The ranks of a job (all on one box) meet in a POSIX shared-memory control block called `name` (any string unique
+ * to the job; rank 0 creates it).  Rank 0 owns a ring of `slots` frame slots in its device memory, mapped into every
+ * rank (CUDA IPC).  rtb_group_render enqueues, on the caller's stream (NULL = the context's, then it also waits):
+ *   every rank   wait for its credit word (slot free again) -> [record pack] -> dense / binned launch whose stores
+ *                go straight into rank 0's slot over NVLink and whose last CTA bumps this rank's done word there;
+ *   rank 0       additionally: credits for the previous frame's slot (a 1-warp kernel writing every rank's credit
+ *                word through the peer mapping), and after its own launch one stream wait per other rank's done
+ *                word.  *d_frame_out (rank 0) = the slot: complete in stream order behind this call, valid until
+ *                rank 0's NEXT rtb_group_render call is reached in stream order (whatever rank 0 enqueues on the
+ *                stream in between -- a copy, a consumer kernel -- runs before the slot is handed back).
+ * With slots >= 2 the other ranks run up to slots-1 frames ahead of rank 0's consumer.  Every rank must call it
+ * once per frame with the same camera.  Replaces, for the sharded frame, the per-render sequence of
+ * MainState.cpp:641-934 (and round 1's Python loop with an NCCL all-reduce per frame).
+ * rtb_group_render_host is the blocking host-buffer form (the multi-GPU rtb_render): every GPU copies its bands
+ * over its own PCIe link into ONE frame in shared, page-locked host memory; on rank 0 the call returns when every
+ * rank has delivered and *host_frame_out points at the frame (valid until rank 0's next call); completion and
+ * release travel through counters in the control block, not through a collective.
+ * rtb_group_prepack = rtb_prepack_cameras_bands for this rank's bands.  rtb_group_barrier: host barrier of the ranks.
+ * rtb_group_leave: collective; drains this rank's device first. */
+typedef struct rtb_group rtb_group;
+int rtb_group_join(rtb_ctx* ctx, const char* name, int rank, int world, int width, int height, int band_rows, int slots,
+                   rtb_group** out);
+int rtb_group_leave(rtb_group* g);
+int rtb_group_info(const rtb_group* g, int* rank, int* world, int* slots, int* band_rows, size_t* slot_bytes);
+const char* rtb_group_last_error(const rtb_group* g);
+int rtb_group_render(rtb_group* g, const float origin0[4], const float dU[4], const float dV[4], const float rayDir[4],
+                     void* cuda_stream, void** d_frame_out);
+int rtb_group_render_host(rtb_group* g, const float origin0[4], const float dU[4], const float dV[4], const float rayDir[4],
+                          uint8_t** host_frame_out, float* kernel_ms);
+int rtb_group_prepack(rtb_group* g, int n_cameras, const float* cameras, void* cuda_stream);
+int rtb_group_barrier(rtb_group* g);
 
 /* Pinned host allocations for the e2e path (pageable buffers work too, only slower). */
 int rtb_host_alloc(void** out, size_t bytes);
@@ -231,6 +282,16 @@ int rtb_debug_pack_bounds(int numSpheres, const float* sphereOrigins, const floa
                           int numCubes, const float* cubeVertices, int width, int height,
                           const float origin0[4], const float dU[4], const float dV[4],
                           const float rayDir[4], float* bound_rec);
+
+/* Debug/test entry: the dense kernel's row table (raycast_math.h RtbRowEntry: 2 floats per (frame row, bound
+ * record), table[(y * n_bound + i) * 2]) as the HOST packer builds it from n_bound bound records of 8 floats.
+ * Host only.  rtb_debug_device_row_table returns the table the DEVICE builds (row_table_kernel) for the rows of
+ * the given bands (other rows 0); the two must agree bit for bit.  *entries_per_row = bound records incl. padding. */
+int rtb_debug_pack_row_table(int n_bound, const float* bound_rec, int width, int height, const float origin0[4],
+                             const float dU[4], const float dV[4], const float rayDir[4], float* table);
+int rtb_debug_device_row_table(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+                               const float dV[4], const float rayDir[4], int band_rows, int band_rank, int band_world,
+                               float* table, size_t table_cap_floats, int* entries_per_row);
 
 /* Debug/test entry: packs the records of one frame ON THE DEVICE (the per-frame path of rtb_render*)
  * and copies them out: 4 floats per record in the layout of rtb_debug_pack (3 per cube, 1 per sphere)

@@ -29,9 +29,15 @@ EXPORTED_SYMBOLS = [
     "rtb_peer_frame_open", "rtb_peer_frame_close", "rtb_debug_device_records", "rtb_render_bands_host",
     "rtb_host_register", "rtb_host_unregister", "rtb_render_bands_frame_signal", "rtb_stream_wait_signal",
     "rtb_peer_frame_signal_offset", "rtb_set_option", "rtb_get_option", "rtb_prepack_cameras",
+    "rtb_prepack_cameras_bands", "rtb_debug_pack_row_table", "rtb_debug_device_row_table",
+    "rtb_group_join", "rtb_group_leave", "rtb_group_info", "rtb_group_last_error", "rtb_group_render",
+    "rtb_group_render_host", "rtb_group_prepack", "rtb_group_barrier",
 ]
 
 RTB_OPT_TILE_CULL = 1
+RTB_OPT_DEFER_SCENE_CHECK = 2
+TILE_CULL_DENSE, TILE_CULL_PER_CTA, TILE_CULL_BINNED, TILE_CULL_AUTO = 0, 1, 2, 3
+RTB_MAX_GROUP = 16
 
 
 class RtbError(RuntimeError):
@@ -49,7 +55,7 @@ def load_library(path=None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("RTB_LIB") or LIB_PATH   # RTB_LIB: tools/ A/B runs against an experiments build
     if not os.path.isfile(p):
         raise RuntimeError("librtb.so not found at %s -- run opencl_ray_tracer_b200/build.sh "
                            "(or __graft_entry__.build()); there is no CPU fallback" % p)
@@ -100,6 +106,20 @@ def load_library(path=None):
     lib.rtb_debug_device_records.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, fp, C.c_size_t,
                                              C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]
     lib.rtb_version.restype = C.c_char_p
+    lib.rtb_prepack_cameras_bands.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, fp, vp]
+    lib.rtb_debug_pack_row_table.argtypes = [C.c_int, fp, C.c_int, C.c_int, fp, fp, fp, fp, fp]
+    lib.rtb_debug_device_row_table.argtypes = [vp, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, C.c_int, C.c_int, fp,
+                                               C.c_size_t, C.POINTER(C.c_int)]
+    lib.rtb_group_join.argtypes = [vp, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+    lib.rtb_group_leave.argtypes = [vp]
+    lib.rtb_group_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                   C.POINTER(C.c_size_t)]
+    lib.rtb_group_last_error.argtypes = [vp]
+    lib.rtb_group_last_error.restype = C.c_char_p
+    lib.rtb_group_render.argtypes = [vp, fp, fp, fp, fp, vp, C.POINTER(vp)]
+    lib.rtb_group_render_host.argtypes = [vp, fp, fp, fp, fp, C.POINTER(vp), fp]
+    lib.rtb_group_prepack.argtypes = [vp, C.c_int, fp, vp]
+    lib.rtb_group_barrier.argtypes = [vp]
     if path is None:
         _lib = lib
     return lib
@@ -166,18 +186,33 @@ def debug_pack_bounds(sph_o, sph_r, cube_v, width, height, camera=REFERENCE_CAME
     return rec
 
 
-class Context:
-    """One rtb_ctx on one device (one process per GPU)."""
+def debug_pack_row_table(bound_rec, width, height, camera=REFERENCE_CAMERA):
+    """Host-side packer only: the dense kernel's row table [height, n_bound, 2] for bound records [n_bound, 8]."""
+    lib = load_library()
+    b = _f32(bound_rec).reshape(-1, 8)
+    tab = np.zeros((height, len(b), 2), np.float32)
+    o0, du, dv, d = [_f32(v) for v in camera]
+    rc = lib.rtb_debug_pack_row_table(len(b), _fp(b), int(width), int(height), _fp(o0), _fp(du), _fp(dv), _fp(d), _fp(tab))
+    if rc != RTB_OK:
+        raise RtbError(rc)
+    return tab
 
-    def __init__(self, device=0):
+
+class Context:
+    """One rtb_ctx: one device (the one-process-per-GPU form), or -- devices=[...] -- several GPUs of this box
+    driven from this process (rtb_init with n_devices > 1)."""
+
+    def __init__(self, device=0, devices=None):
         self.lib = load_library()
         self._h = C.c_void_p()
-        dev = (C.c_int * 1)(device)
-        rc = self.lib.rtb_init(C.byref(self._h), 1, dev)
+        ids = list(devices) if devices is not None else [device]
+        dev = (C.c_int * len(ids))(*ids)
+        rc = self.lib.rtb_init(C.byref(self._h), len(ids), dev)
         if rc != RTB_OK:
             self._h = C.c_void_p()
-            raise RtbError(rc, "rtb_init(device=%d)" % device)
-        self.device = device
+            raise RtbError(rc, "rtb_init(devices=%s)" % ids)
+        self.device = ids[0]
+        self.n_devices = len(ids)
         self.ns = self.nc = 0
 
     def _check(self, rc):
@@ -205,6 +240,22 @@ class Context:
         """rtb_prepack_cameras: `cameras` = array (n, 16) of origin0, dU, dV, rayDir per frame."""
         cams = np.ascontiguousarray(cameras, np.float32).reshape(-1, 16)
         self._check(self.lib.rtb_prepack_cameras(self._h, int(width), int(height), len(cams), _fp(cams), C.c_void_p(stream or 0)))
+
+    def prepack_cameras_bands(self, width, height, band_rows, rank, world, cameras, stream=None):
+        cams = np.ascontiguousarray(cameras, np.float32).reshape(-1, 16)
+        self._check(self.lib.rtb_prepack_cameras_bands(self._h, int(width), int(height), int(band_rows), int(rank), int(world),
+                                                       len(cams), _fp(cams), C.c_void_p(stream or 0)))
+
+    def debug_device_row_table(self, width, height, camera=REFERENCE_CAMERA, band_rows=16, rank=0, world=1):
+        """The dense kernel's row table as the DEVICE builds it: [height, n_bound, 2] (rows of other ranks' bands 0)."""
+        o0, du, dv, d = [_f32(v) for v in camera]
+        n = C.c_int()
+        self._check(self.lib.rtb_debug_device_row_table(self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d), band_rows,
+                                                        rank, world, None, 0, C.byref(n)))
+        tab = np.zeros((height, n.value, 2), np.float32)
+        self._check(self.lib.rtb_debug_device_row_table(self._h, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d), band_rows,
+                                                        rank, world, _fp(tab), tab.size, C.byref(n)))
+        return tab
 
     def set_option(self, option, value):
         """rtb_set_option, e.g. set_option(RTB_OPT_TILE_CULL, 1)."""
@@ -357,6 +408,69 @@ class Context:
         n = C.c_int()
         avg = self.lib.rtb_kernel_ms_avg(self._h, 1 if reset else 0, C.byref(n))
         return float(avg), n.value
+
+
+class Group:
+    """rtb_group_*: this process's membership in a multi-GPU job (one process per GPU).  Every rank constructs it
+    with the same name / sizes (collective) and calls render() / render_host() once per frame."""
+
+    def __init__(self, ctx, name, rank, world, width, height, band_rows=16, slots=3):
+        self.ctx, self.rank, self.world, self.width, self.height = ctx, rank, world, width, height
+        self.lib = ctx.lib
+        self._g = C.c_void_p()
+        rc = self.lib.rtb_group_join(ctx._h, name.encode(), rank, world, width, height, band_rows, slots, C.byref(self._g))
+        if rc != RTB_OK:
+            self._g = C.c_void_p()
+            raise RtbError(rc, (self.lib.rtb_last_error_message(ctx._h) or b"").decode())
+        sb = C.c_size_t()
+        self.lib.rtb_group_info(self._g, None, None, None, None, C.byref(sb))
+        self.slot_bytes = sb.value
+
+    def _check(self, rc):
+        if rc != RTB_OK:
+            raise RtbError(rc, (self.lib.rtb_group_last_error(self._g) or b"").decode() or
+                           (self.lib.rtb_last_error_message(self.ctx._h) or b"").decode())
+
+    def render(self, camera, stream=0):
+        """Enqueues this rank's share of the next frame; rank 0 gets the device pointer of the frame's slot."""
+        o0, du, dv, d = [_f32(v) for v in camera]
+        p = C.c_void_p()
+        self._check(self.lib.rtb_group_render(self._g, _fp(o0), _fp(du), _fp(dv), _fp(d), C.c_void_p(stream or None), C.byref(p)))
+        return p.value
+
+    def render_host(self, camera):
+        """Blocking; rank 0: (numpy uint8 [H, W, 4] view of the shared host frame, kernel ms); others: (None, kernel ms)."""
+        o0, du, dv, d = [_f32(v) for v in camera]
+        p, kms = C.c_void_p(), C.c_float()
+        self._check(self.lib.rtb_group_render_host(self._g, _fp(o0), _fp(du), _fp(dv), _fp(d), C.byref(p), C.byref(kms)))
+        if not p.value:
+            return None, kms.value
+        n = 4 * self.width * self.height
+        buf = (C.c_uint8 * n).from_address(p.value)
+        return np.frombuffer(buf, dtype=np.uint8).reshape(self.height, self.width, 4), kms.value
+
+    def prepack(self, cameras, stream=0):
+        cams = np.ascontiguousarray(cameras, np.float32).reshape(-1, 16)
+        self._check(self.lib.rtb_group_prepack(self._g, len(cams), _fp(cams), C.c_void_p(stream or None)))
+
+    def barrier(self):
+        self._check(self.lib.rtb_group_barrier(self._g))
+
+    def frame_tensor(self, ptr):
+        """torch uint8 view [H, W, 4] of a slot pointer returned by render() (rank 0)."""
+        import torch
+
+        class _Raw:
+            pass
+        raw = _Raw()
+        raw.__cuda_array_interface__ = {"shape": (self.height, self.width, 4), "typestr": "|u1",
+                                        "data": (int(ptr), False), "version": 3, "strides": None}
+        return torch.as_tensor(raw, device="cuda")
+
+    def close(self):
+        if self._g:
+            self.lib.rtb_group_leave(self._g)
+            self._g = C.c_void_p()
 
 
 def host_alloc(nbytes):

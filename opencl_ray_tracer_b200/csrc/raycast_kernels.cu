@@ -1,19 +1,18 @@
 // raycast_kernels.cu -- hand-written sm_100a kernels of the ray-cast path.
 //
-// raycast_grid_kernel replaces the OpenCL kernel `rayTracer`
+// raycast_dense_kernel replaces the OpenCL kernel `rayTracer`
 // (RayTrace/resources/shaders/rayTracer.cl:111-202) and, result-wise, the CPU loop
 // MainState::executeRayTracerCPU -> collide (RayTrace/states/MainState.cpp:936-956, :330-408).
 //
 // Mapping: one warp = an 8x4 lane tile, each lane owns PX horizontally adjacent
 // pixels (one primary ray each, held as PX/2 packed FP32 pairs), so a warp covers (8*PX) x 4 pixels
-// and a lane's PX RGBA8 results leave as 128-bit stores.  The conic bound records (32 B per
-// primitive) are staged global->shared in chunks with 1-D TMA bulk copies (cp.async.bulk + mbarrier
-// complete_tx), double buffered; per chunk the CTA turns them into a row table
-// (primitive, CTA row) -> (sA, rowW, rowC) that the dense loop reads with one LDS.128 per thread and
-// primitive.  Per ray pair and primitive: 1 FFMA2 (w = sA*u + rowW) + 1 FMNMX3 (running min m of |w|);
-// per thread and primitive one FMA + compare, fmaf(m, m, rowC) < 2, which is the per-ray q test of the
-// thread's rays bit for bit (q is monotone in |w|).  One warp vote per 4 primitives; the
-// reference-exact slab / sphere update (raycast_math.h) runs only behind it.
+// and a lane's PX RGBA8 results leave as 128-bit stores.  The per-(pixel row, primitive) entries of the
+// conservative bound -- the row table, 8 B each, built once per frame by row_table_kernel
+// (scene_pack_device.cu) -- are staged global->shared in chunks with 1-D TMA bulk copies (cp.async.bulk +
+// mbarrier complete_tx) through a 4-stage ring with full / empty mbarriers: no CTA-wide barrier in the
+// loop.  Per ray pair and primitive: 1 FFMA2 (w' = sAn*u + rWn) + 1 FMNMX3 (running min of |w'| over the
+// thread's rays AND over 8 primitives); per 8 primitives one compare (min < 1), one warp vote.  The
+// reference-exact slab / sphere update (raycast_math.h) runs only behind the vote.
 //
 // Compiled with -fmad=false: every FMA is an explicit fmaf() from raycast_math.h so the scalar
 // emulator in tests/emu reproduces the kernel bit for bit.
@@ -46,6 +45,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
             smem_u32(dst_smem)),
         "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
         : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     const uint32_t addr = smem_u32(bar);
@@ -165,6 +167,7 @@ __device__ __forceinline__ float bound_min(const float4 t, const PixelState<PX>&
 }
 __device__ __forceinline__ bool bound_passes(float m, float rowC) { return rtb_bound_q_of_w(m, rowC) < 2.0f; }
 
+#ifdef RTB_EXPERIMENTS  // helpers of the round-1 kernel (row table built per CTA), kept for A/B sweeps only
 // The vote of a group of G primitives and, behind it, the exact updates of those whose bound some ray of the
 // warp passed.  m[g] = min |w| of this thread's rays, c[g] = the row's rowC (kept as values: the hot path is
 // G FMA + G compares into one predicate, the per-primitive compares happen only behind the vote).
@@ -254,6 +257,8 @@ __device__ __forceinline__ void dense_chunk_tab(const GridParams& p, const float
         t = tn;
     }
 }
+
+#endif  // RTB_EXPERIMENTS
 
 // Nearest-hit shading (rtb_shade) + 128-bit coalesced stores of one thread's PX pixels.  The colour
 // loads of four pixels are issued together (predicated, no branch around them), so a thread waits
@@ -356,6 +361,235 @@ __device__ __forceinline__ void signal_completion(const GridParams& p, int tile_
     }
 }
 
+// ---- the dense kernel -------------------------------------------------------------------------------
+// One primitive's row entry (sAn, rWn) against this thread's PX rays, folded into running minima of |w'|: ONE
+// packed FFMA2 per ray pair (sm_100's FFMA2 with the pair operand HI_LO and scalar-broadcast coefficients) and ONE
+// 3-input FMNMX with |.| on both new operands.  The minima are kept in NCH independent chains (ray pair j feeds
+// chain j % NCH): a single chain over a group's 8 primitives x 8 ray pairs is 64 dependent FMNMX3 long and the
+// loop becomes latency-bound (measured: 2 chains 0.584 ms at C3, no faster than round 1's kernel although it
+// issues 15 % fewer instructions).  NaNs drop out of fminf, Inf stays Inf: such rays fail, as their own test would.
+#ifndef RTB_MIN_CHAINS
+#define RTB_MIN_CHAINS 8
+#endif
+constexpr int kMinChains = RTB_MIN_CHAINS;
+template <int PX>
+__device__ __forceinline__ void row_min(float sAn, float rWn, float (&m)[kMinChains], const PixelState<PX>& st) {
+    const uint64_t S2 = pack2(sAn, sAn), W2 = pack2(rWn, rWn);
+#pragma unroll
+    for (int j = 0; j < PX / 2; ++j) {
+        const uint64_t w2 = ffma2(st.u2[j], S2, W2);
+        float lo, hi;
+        unpack2(w2, lo, hi);
+        m[j % kMinChains] = fminf(fminf(m[j % kMinChains], fabsf(lo)), fabsf(hi));
+    }
+}
+__device__ __forceinline__ float min_of_chains(const float (&m)[kMinChains]) {
+    float r = m[0];
+#pragma unroll
+    for (int k = 1; k + 1 < kMinChains; k += 2) r = fminf(fminf(r, m[k]), m[k + 1]);
+    if (kMinChains % 2 == 0) r = fminf(r, m[kMinChains - 1]);
+    return r;
+}
+
+constexpr int kDenseGroup = 8;  // primitives per compare + warp vote
+
+// Behind the vote (a few per mille of the groups): which of the group's primitives was it?  Per primitive the
+// same test once more, then the reference-exact update for the rays of the warp.  Rolled: this is cold code.
+template <int PX>
+__device__ __forceinline__ void dense_group_slow(const GridParams& p, const float2* __restrict__ ent, int first_prim, float v,
+                                                 PixelState<PX>& st) {
+#pragma unroll 1
+    for (int g = 0; g < kDenseGroup; ++g) {
+        const float2 e = ent[g];
+        float m[kMinChains];
+#pragma unroll
+        for (int k = 0; k < kMinChains; ++k) m[k] = __int_as_float(0x7f800000);
+        row_min<PX>(e.x, e.y, m, st);
+        if (__any_sync(0xFFFFFFFFu, rtb_row_passes(min_of_chains(m)))) exact_update<PX>(p, first_prim + g, v, st);
+    }
+}
+
+// The dense loop over one staged chunk: `row` = this thread's pixel row of the chunk in shared memory (cnt
+// entries of 8 B, cnt a multiple of 8), read as LDS.128 = two primitives, 4 distinct addresses per warp in 4
+// different bank groups.  Groups of 8 primitives share the running minima, one compare and one vote; warp `split`
+// of the S warps of a pixel tile takes groups split, split + S, ...  The next group's entries are requested while
+// the current group is tested.
+template <int PX, int S>
+__device__ __forceinline__ void dense_chunk(const GridParams& p, const float4* __restrict__ row, int cnt, int first_prim,
+                                            int split, float v, PixelState<PX>& st) {
+    constexpr int G = kDenseGroup;
+    int j = split * G;
+    if (j >= cnt) return;
+    const float4* t = row + (j >> 1);
+    float4 a0 = t[0], a1 = t[1], a2 = t[2], a3 = t[3];
+#pragma unroll 1
+    for (; j < cnt; j += S * G) {
+        float m[kMinChains];
+#pragma unroll
+        for (int k = 0; k < kMinChains; ++k) m[k] = __int_as_float(0x7f800000);
+        // past the end the last group is read again (stays inside the chunk)
+        const int jn = min(j + S * G, cnt - G);
+        const float4* tn = row + (jn >> 1);
+        row_min<PX>(a0.x, a0.y, m, st);
+        row_min<PX>(a0.z, a0.w, m, st);
+        const float4 b0 = tn[0], b1 = tn[1];
+        row_min<PX>(a1.x, a1.y, m, st);
+        row_min<PX>(a1.z, a1.w, m, st);
+        const float4 b2 = tn[2], b3 = tn[3];
+        row_min<PX>(a2.x, a2.y, m, st);
+        row_min<PX>(a2.z, a2.w, m, st);
+        row_min<PX>(a3.x, a3.y, m, st);
+        row_min<PX>(a3.z, a3.w, m, st);
+        if (__any_sync(0xFFFFFFFFu, rtb_row_passes(min_of_chains(m))))
+            dense_group_slow<PX>(p, reinterpret_cast<const float2*>(t), first_prim + j, v, st);
+        a0 = b0; a1 = b1; a2 = b2; a3 = b3;
+        t = tn;
+    }
+}
+
+// Tile = (WARPS_X * 8 * PX) x (WARPS_Y * 4) pixels.  S > 1: S warps share one 8*PX x 4 warp tile and split the
+// primitive list between them (groups of 8, round robin); their nearest hits are merged through shared memory
+// before shading.  Used when a launch has too few pixel tiles to load every scheduler evenly (the per-GPU share
+// of a frame on 8 GPUs).  Nothing in the loop is CTA-wide: a warp waits on the chunk's `full` mbarrier (TMA
+// completion), tests, and arrives on its `empty` mbarrier; thread 0 refills a stage one chunk later, when every
+// warp has long released it.
+template <int PX, int WARPS_X, int WARPS_Y, int S, int STAGES, int CHUNK, int MIN_CTAS>
+__global__ void __launch_bounds__(32 * WARPS_X * WARPS_Y * S, MIN_CTAS)
+raycast_dense_kernel(const GridParams p) {
+    constexpr int kWarps = WARPS_X * WARPS_Y * S;
+    constexpr int kThreads = 32 * kWarps;
+    constexpr int kTileW = WARPS_X * 8 * PX;
+    constexpr int kTileH = WARPS_Y * 4;
+    static_assert(CHUNK % kDenseGroup == 0 && CHUNK % 2 == 0, "chunks hold whole vote groups");
+    // a chunk row = CHUNK entries (8 B) + 16 B: consecutive rows start 4 banks apart, so the 4 rows a warp reads
+    // with one LDS.128 never collide
+    constexpr int kRowF4 = CHUNK / 2 + 1;
+    constexpr int kStageF4 = kTileH * kRowF4;
+    constexpr int kMergeBytes = (S > 1) ? 8 * WARPS_X * WARPS_Y * (S - 1) * PX * 32 : 0;
+    constexpr int kTabBytes = STAGES * kStageF4 * (int)sizeof(float4);
+    constexpr int kSmemBytes = kTabBytes > kMergeBytes ? kTabBytes : kMergeBytes;
+    __shared__ __align__(128) unsigned char smem_raw[kSmemBytes];
+    __shared__ __align__(8) uint64_t full_bar[STAGES];
+    __shared__ __align__(8) uint64_t empty_bar[STAGES];
+    __shared__ unsigned long long row_src[kTileH];  // entry index of each tile row's first entry in p.row_tab
+    float4* tab = reinterpret_cast<float4*>(smem_raw);
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int split = warp % S, tile_warp = warp / S;  // the S warps of a tile are neighbours
+    const int wx = tile_warp % WARPS_X, wy = tile_warp / WARPS_X;
+    const int lx = lane & 7, ly = lane >> 3;
+    const int x0 = blockIdx.x * kTileW + (wx * 8 + lx) * PX;
+    const int lrow = blockIdx.y * kTileH + wy * 4 + ly;  // row in the packed (local) output
+    // interleaved row bands: local band lb -> global band lb*world + rank
+    const int lb = lrow / p.band_rows;
+    const int gy = (lb * p.band_world + p.band_rank) * p.band_rows + (lrow - lb * p.band_rows);
+
+    const int n_pad = p.n_pad;  // entries per table row: a multiple of 8
+    const int n_chunks = (n_pad + CHUNK - 1) / CHUNK;
+
+    if (tid < kTileH) {  // the table is indexed by FRAME row; rows past the frame reuse its last row (never stored)
+        const int trow = blockIdx.y * kTileH + tid;
+        const int tlb = trow / p.band_rows;
+        int tgy = (tlb * p.band_world + p.band_rank) * p.band_rows + (trow - tlb * p.band_rows);
+        tgy = min(tgy, p.height - 1);
+        row_src[tid] = (unsigned long long)tgy * (unsigned long long)n_pad;
+    }
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], kWarps);
+        }
+        fence_mbar_init();
+    }
+    __syncthreads();
+
+    auto issue = [&](int k) {  // called by thread 0 only
+        const int s = k % STAGES;
+        const int first = k * CHUNK;
+        const int cnt = min(CHUNK, n_pad - first);
+        const uint32_t bytes = (uint32_t)cnt * 8u;
+        mbar_arrive_expect_tx(&full_bar[s], bytes * kTileH);
+#pragma unroll
+        for (int r = 0; r < kTileH; ++r)
+            bulk_g2s(tab + s * kStageF4 + r * kRowF4, p.row_tab + row_src[r] + first, bytes, &full_bar[s]);
+    };
+    if (tid == 0) {
+#pragma unroll 1
+        for (int k = 0; k < STAGES && k < n_chunks; ++k) issue(k);
+    }
+
+    extern __shared__ int dyn_ids[];  // [PX][kThreads] winning primitive ids (see PixelState)
+    PixelState<PX> st;
+    st.sid = dyn_ids + tid;
+    st.sid_stride = kThreads;
+    const float fy = (float)gy;
+    const float v = rtb_cam_v(p.cam, fy);
+#pragma unroll
+    for (int q = 0; q < PX; q += 2) {
+        st.u2[q >> 1] = pack2(rtb_cam_u(p.cam, (float)(x0 + q), fy), rtb_cam_u(p.cam, (float)(x0 + q + 1), fy));
+        st.best[q] = st.best[q + 1] = RTB_MISS_T;
+        st.id(q) = -1;
+        st.id(q + 1) = -1;
+    }
+
+    const float4* my_row = tab + (wy * 4 + ly) * kRowF4;
+#pragma unroll 1
+    for (int k = 0; k < n_chunks; ++k) {
+        const int s = k % STAGES;
+        mbar_wait(&full_bar[s], (uint32_t)((k / STAGES) & 1));
+        const int first = k * CHUNK;
+        dense_chunk<PX, S>(p, my_row + s * kStageF4, min(CHUNK, n_pad - first), first, split, v, st);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[s]);  // this warp is done with the stage
+        // refill the stage of the PREVIOUS chunk: by now every warp has released it (else thread 0 waits here)
+        if (tid == 0 && k >= 1 && k - 1 + STAGES < n_chunks) {
+            mbar_wait(&empty_bar[(k - 1) % STAGES], (uint32_t)(((k - 1) / STAGES) & 1));
+            issue(k - 1 + STAGES);
+        }
+    }
+
+    // ---- merge of the primitive splits (S > 1) -----------------------------------------------
+    const bool owner = (split == 0);  // the warp of a tile that shades and stores
+    if constexpr (S > 1) {
+        constexpr int kSlots = WARPS_X * WARPS_Y * (S - 1);
+        float (*m_best)[PX][32] = reinterpret_cast<float (*)[PX][32]>(smem_raw);
+        int (*m_id)[PX][32] = reinterpret_cast<int (*)[PX][32]>(smem_raw + sizeof(float) * kSlots * PX * 32);
+        __syncthreads();  // every warp has consumed every chunk (all TMA writes have landed): the ring is free
+        if (split > 0) {
+#pragma unroll
+            for (int q = 0; q < PX; ++q) {
+                m_best[tile_warp * (S - 1) + split - 1][q][lane] = st.best[q];
+                m_id[tile_warp * (S - 1) + split - 1][q][lane] = st.id(q);
+            }
+        }
+        __syncthreads();
+        if (owner) {
+#pragma unroll 1
+            for (int o = 0; o < S - 1; ++o) {
+#pragma unroll
+                for (int q = 0; q < PX; ++q) {
+                    const float ob = m_best[tile_warp * (S - 1) + o][q][lane];
+                    const int oi = m_id[tile_warp * (S - 1) + o][q][lane];
+                    // same winner as one ascending pass: nearest t, ties to the lowest primitive index
+                    const int mine = st.id(q);
+                    if (ob < st.best[q] || (ob == st.best[q] && oi >= 0 && (mine < 0 || oi < mine))) {
+                        st.best[q] = ob;
+                        st.id(q) = oi;
+                    }
+                }
+            }
+        }
+    }
+
+    // ---- nearest-hit shading + stores -------------------------------------------------------
+    if (owner && lrow < p.local_rows && gy < p.height && x0 < p.width) shade_and_store<PX>(p, st, x0, lrow, gy);
+
+    signal_completion(p, kTileH);
+}
+
+#ifdef RTB_EXPERIMENTS  // the round-1 dense kernel (bound records staged, row table built by every CTA): A/B sweeps only
 // S > 1: S warps share one pixel tile and split the primitive list between them (groups of G,
 // round robin); their nearest hits are merged through shared memory before shading.  Used when a
 // launch has too few pixel tiles to load every scheduler evenly (the per-GPU share of a frame on 8
@@ -521,6 +755,8 @@ raycast_grid_kernel(const GridParams p) {
 
     signal_completion(p, kTileH);
 }
+
+#endif  // RTB_EXPERIMENTS
 
 // ---- tile-culled variant (GridParams::tile_cull) ------------------------------------------------
 // Same pixels, same arithmetic, far fewer tests: before a CTA's rays see a primitive, the CTA asks
@@ -1012,16 +1248,13 @@ GridLaunchShape shape_of(int width, int local_rows) {
 
 }  // namespace
 
-// Production tilings of the grid kernel: rays per thread, pixel-tile warps per CTA (x, y), warps
-// per pixel tile (primitive split), and the measured cost per ray-primitive test relative to the
-// first (profiles/r01_variant_sweeps.txt).
+// Tilings of the dense kernel: rays per thread, warp tiles per CTA (x, y), warps per warp tile (primitive
+// split), and the cost per ray-primitive test relative to the first.
 struct Tiling { int px, wx, wy, split; double cost; };
 static const Tiling kTilings[] = {
     {16, 2, 2, 1, 1.00},  // 256 x 8 pixels, 4 warps
-    {16, 2, 1, 2, 1.05},  // 256 x 4 pixels, 4 warps, two per tile: short band sets (8-GPU frames); +5 %: table rows per
-                          // pixel doubled, nearest-hit merge (C3 0.615 vs 0.585 ms)
-    {8, 2, 2, 1, 1.23},   // 128 x 8 pixels (C3 0.741 ms: the per-primitive LDS / compare / loop is shared by 8 rays only)
-    {4, 2, 2, 1, 1.60},   //  64 x 8 pixels: small frames
+    {16, 2, 1, 2, 1.03},  // 256 x 4 pixels, 4 warps, two per warp tile: nearest-hit merge, table rows read by half as many rays
+    {16, 1, 1, 4, 1.06},  // 128 x 4 pixels, 4 warps on one warp tile: short band sets (8-GPU frames), small frames
 };
 
 // The CTA scheduler spreads a grid evenly over the SMs and a CTA's warps over the 4 schedulers of
@@ -1031,6 +1264,7 @@ GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
     GridLaunchShape best;
     double best_t = 0.0;
     if (sm_count <= 0) sm_count = 1;
+    static const int forced = [] { const char* e = std::getenv("RTB_DENSE_TILING"); return e ? std::atoi(e) : -1; }();
     for (int i = 0; i < (int)(sizeof kTilings / sizeof kTilings[0]); ++i) {
         const Tiling& t = kTilings[i];
         const int tw = t.wx * 8 * t.px, th = t.wy * 4;
@@ -1042,6 +1276,7 @@ GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
         const double ctas = (double)s.grid.x * s.grid.y;
         const double warps_per_sched = std::ceil(ctas / sm_count * (t.wx * t.wy * t.split) / 4.0 - 1e-9);
         const double est = warps_per_sched * (32.0 * t.px / t.split) * t.cost;
+        if (i == forced) return s;
         if (i == 0 || est < best_t * 0.97) {  // 3 % hysteresis in favour of the earlier entry
             best = s;
             best_t = est;
@@ -1050,10 +1285,35 @@ GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
     return best;
 }
 
-// Experiment hook (profiles/): RTB_GRID_VARIANT=n picks another tiling of the same kernel.
-// Launch of one instantiation: the id columns are dynamic shared memory (PX x threads ints); together
-// with the static staging / table area that can pass 48 KB, which needs the opt-in attribute (set once
-// per instantiation and device).
+// Launch of one instantiation: the id columns are dynamic shared memory (PX x threads ints); the opt-in
+// attribute is set once per instantiation and device.
+#ifndef RTB_DENSE_STAGES
+#define RTB_DENSE_STAGES 2
+#endif
+#ifndef RTB_DENSE_CHUNK
+#define RTB_DENSE_CHUNK 256
+#endif
+constexpr int kDenseStages = RTB_DENSE_STAGES;  // ring depth of the row-table chunks
+constexpr int kDenseChunk = RTB_DENSE_CHUNK;    // primitives per chunk: 2 KB per pixel row and stage (C3: 128 x 4 stages 0.572 ms, 256 x 2 0.561)
+template <int PX, int WX, int WY, int S, int STAGES, int CHUNK, int MINB>
+cudaError_t launch_dense_instance(const GridParams& p, dim3 grid, cudaStream_t stream) {
+    constexpr int kThreads = 32 * WX * WY * S;
+    constexpr int kDyn = PX * kThreads * (int)sizeof(int);
+    static thread_local int configured_device = -1;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (configured_device != dev) {
+        e = cudaFuncSetAttribute(raycast_dense_kernel<PX, WX, WY, S, STAGES, CHUNK, MINB>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, kDyn);
+        if (e != cudaSuccess) return e;
+        configured_device = dev;
+    }
+    raycast_dense_kernel<PX, WX, WY, S, STAGES, CHUNK, MINB><<<grid, dim3(kThreads), kDyn, stream>>>(p);
+    return cudaGetLastError();
+}
+
+#ifdef RTB_EXPERIMENTS
 template <int PX, int WX, int WY, int G, int MINB, int S, bool TAB, int TP, int PIPE>
 cudaError_t launch_instance(const GridParams& p, dim3 grid, cudaStream_t stream) {
     constexpr int kThreads = 32 * WX * WY * S;
@@ -1078,6 +1338,7 @@ cudaError_t launch_variant(const GridParams& p, cudaStream_t stream) {
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
     return launch_instance<PX, WX, WY, G, MINB, S, TAB, TP, PIPE>(p, s.grid, stream);
 }
+#endif  // RTB_EXPERIMENTS
 
 template <int PX, int WX, int WY, int MINB>
 cudaError_t launch_cull_instance(const GridParams& p, cudaStream_t stream) {
@@ -1098,32 +1359,21 @@ cudaError_t launch_cull_instance(const GridParams& p, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
-// Tile geometry of the binned render (tile_cull == 2).  The bins are laid out for exactly the tiling of the
-// render kernel that reads them.  RTB_BINNED_VARIANT=n (experiment hook, profiles/) picks another tiling.
-struct BinnedTiling { int tile_w, tile_h; };
-static int binned_variant() {
-    static const int v = [] {
-        const char* e = std::getenv("RTB_BINNED_VARIANT");
-        return e ? std::atoi(e) : 0;
-    }();
-    return v;
-}
-static bool pdl_enabled() {  // RTB_NO_PDL=1: plain stream order between the two launches (experiment / fallback knob)
+// Tile geometry of the binned render (tile_cull == 2): 64 x 32 pixel tiles, four warps of 32 x 16 pixels.  The
+// bins are laid out for exactly the tiling of the render kernel that reads them.  (Measured and dropped,
+// profiles/r01_variant_sweep_binned_v3_tilings.jsonl, C3 / C4 ms against 0.0320 / 0.102: 128 x 16 tiles 0.0339 / 0.109;
+// 64 x 16 tiles of two 32 x 16 warps 0.0356 / 0.132; of two 64 x 8 warps 0.0376 / 0.136; one warp per 32 x 16 tile
+// 0.0392 / 0.190; per-warp lists instead of one per CTA 0.0333 / 0.134.)
+constexpr int kBinTileW = 64, kBinTileH = 32;
+static bool pdl_enabled() {  // RTB_NO_PDL=1: plain stream order between the two launches (fallback knob)
     static const bool on = [] { const char* e = std::getenv("RTB_NO_PDL"); return !(e && e[0] == '1'); }();
     return on;
 }
-static BinnedTiling binned_tiling() {
-    switch (binned_variant()) {
-        case 2: return {128, 16};
-        default: return {64, 32};
-    }
-}
 
-int binned_tile_rows() { return binned_tiling().tile_h; }
+int binned_tile_rows() { return kBinTileH; }
 
 size_t grid_bin_words(int width, int local_rows, int n_bound) {
-    const BinnedTiling t = binned_tiling();
-    const size_t tiles = (size_t)((width + t.tile_w - 1) / t.tile_w) * (size_t)((local_rows + t.tile_h - 1) / t.tile_h);
+    const size_t tiles = (size_t)((width + kBinTileW - 1) / kBinTileW) * (size_t)((local_rows + kBinTileH - 1) / kBinTileH);
     return tiles * (size_t)((n_bound + 31) / 32);
 }
 
@@ -1132,6 +1382,7 @@ static cudaError_t launch_binned(const GridParams& p, cudaStream_t stream) {
     constexpr int kThreads = 32 * WX * WY;
     constexpr int kDyn = PX * kThreads * (int)sizeof(int);
     constexpr int kTileW = WX * LX * PX, kTileH = WY * (32 / LX);
+    static_assert(kTileW == kBinTileW && kTileH == kBinTileH, "bins are laid out for this tiling");
     const int tiles_x = (p.width + kTileW - 1) / kTileW, tiles_y = (p.local_rows + kTileH - 1) / kTileH;
     if (tiles_x <= 0 || tiles_y <= 0) return cudaSuccess;
     if (p.bin_words > 0) {
@@ -1154,46 +1405,26 @@ static cudaError_t launch_binned(const GridParams& p, cudaStream_t stream) {
     return cudaLaunchKernelEx(&cfg, raycast_binned_kernel<PX, LX, WX, WY, MINB>, p);
 }
 
-static cudaError_t launch_binned_variant(const GridParams& p, cudaStream_t stream) {
-    switch (binned_variant()) {
-        case 1: return launch_binned<16, 2, 2, 2, 6>(p, stream);   // 80 registers, 6 CTAs/SM (C3 0.0338, C4 0.107 ms)
-        case 2: return launch_binned<16, 2, 4, 1, 6>(p, stream);   // 128 x 16 tiles
-        // measured and dropped (profiles/r01_variant_sweep_binned_v3_tilings.jsonl; C3 / C4 ms against 0.0339 / 0.109):
-        // 64 x 16 tiles of two 32 x 16 warps 0.0356 / 0.132; of two 64 x 8 warps 0.0376 / 0.136; one warp per 32 x 16
-        // tile 0.0392 / 0.190; per-warp lists instead of one per CTA (no CTA barrier, every warp expands the tile's words
-        // itself) 0.0333 / 0.134 against 0.0322 / 0.106 (profiles/r01_variant_sweep_binned_v5_warp_lists.jsonl)
-        default: return launch_binned<16, 2, 2, 2, 8>(p, stream);  // 64 x 32 tiles, 4 warps of 32 x 16 pixels, 64 registers (C3 0.0320, C4 0.102 ms)
-    }
-}
-
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) {
-    if (p.tile_cull == 2) return launch_binned_variant(p, stream);
+    if (p.tile_cull == 2) return launch_binned<16, 2, 2, 2, 8>(p, stream);  // 64 registers, 8 CTAs/SM
     if (p.tile_cull) return launch_cull_instance<16, 2, 2, 4>(p, stream);
+#ifdef RTB_EXPERIMENTS
     static const int variant = [] {
         const char* e = std::getenv("RTB_GRID_VARIANT");
         return e ? std::atoi(e) : 0;
     }();
-    switch (variant) {
-        case 1: return launch_variant<16, 2, 2, 4, 4>(p, stream);            // row terms per thread (round-1 v2 kernel)
-        case 10: return launch_variant<16, 2, 2, 4, 4, 1, true>(p, stream);  // row table (production at C3)
+    switch (variant) {  // the round-1 kernel: bound records staged, row table built per CTA (tools/variant_sweep.py)
+        case 10: return launch_variant<16, 2, 2, 4, 4, 1, true>(p, stream);  // round-1 production tiling at C3
         case 20: return launch_variant<16, 2, 1, 4, 4, 2, true>(p, stream);  // 2 warps per 128x4 tile
-        case 31: return launch_variant<16, 2, 2, 4, 6, 1, true, 64>(p, stream);  // 6 CTAs/SM (<= 85 registers)
-        // 5 CTAs/SM (96 registers, 128 B spilled; table of 64 / 96 primitives): C3 0.599 / 0.596 ms against 0.586 (v9)
-        // 32 rays per thread (2-warp CTAs of 256 x 8 pixels, 168 registers, 12 warps/SM; rolled epilogue): C3 0.637 ms,
-        // C4 8.84 ms against 0.586 / 8.65 -- the per-primitive overhead is shared by more rays, but 3 warps per
-        // scheduler no longer cover the FFMA2 -> FMNMX3 latency
-        case 11: return launch_variant<16, 2, 2, 4, 4, 1, true, kTabPrims, false>(p, stream);  // row table, loads not pipelined
-        // measured and dropped: two groups (8 primitives) per loop iteration to halve the loop control on the uniform
-        // pipe: C3 0.7025 -> 0.7126 ms, C4 10.528 -> 10.684 ms (profiles/r01_variant_sweep_unroll2.jsonl)
-        case 15: return launch_variant<8, 2, 2, 4, 8, 1, true>(p, stream);
         default: break;
     }
+#endif
+    if (p.row_tab == nullptr) return cudaErrorInvalidValue;
     const GridLaunchShape s = grid_launch_shape(p.width, p.local_rows, sm_count);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
-    if (s.px == 16 && s.wy == 2) return launch_instance<16, 2, 2, kBoundGroup, 4, 1, true, kTabPrims, true>(p, s.grid, stream);
-    if (s.px == 16) return launch_instance<16, 2, 1, kBoundGroup, 4, 2, true, kTabPrims, true>(p, s.grid, stream);
-    if (s.px == 8) return launch_instance<8, 2, 2, kBoundGroup, 8, 1, true, kTabPrims, true>(p, s.grid, stream);
-    return launch_instance<4, 2, 2, kBoundGroup, 8, 1, true, kTabPrims, true>(p, s.grid, stream);
+    if (s.split == 1) return launch_dense_instance<16, 2, 2, 1, kDenseStages, kDenseChunk, 4>(p, s.grid, stream);
+    if (s.split == 2) return launch_dense_instance<16, 2, 1, 2, kDenseStages, kDenseChunk, 4>(p, s.grid, stream);
+    return launch_dense_instance<16, 1, 1, 4, kDenseStages, kDenseChunk, 4>(p, s.grid, stream);
 }
 
 cudaError_t launch_rays(const RaysParams& p, cudaStream_t stream) {
@@ -1245,7 +1476,5 @@ cudaError_t launch_signal_only(unsigned int* d_signal, cudaStream_t stream) {
     signal_only_kernel<<<1, 1, 0, stream>>>(d_signal);
     return cudaGetLastError();
 }
-
-cudaError_t configure_kernels() { return cudaSuccess; }
 
 }  // namespace rtb

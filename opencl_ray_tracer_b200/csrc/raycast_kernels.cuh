@@ -15,8 +15,8 @@ constexpr int kChunkPrims = 512;
 constexpr int kTabPrims = 128;
 // Row chunks a launch can report as finished while it is still running (rtb_render's pipelined copies).
 constexpr int kMaxProgressChunks = 32;
-// Primitives per warp vote in the dense loop; the host pads the bound list to a multiple of it.
-constexpr int kBoundGroup = 4;
+// Primitives per warp vote in the dense loop; the host pads the bound list (and the row table) to a multiple of it.
+constexpr int kBoundGroup = 8;
 
 struct GridParams {
     int width, height;                      // full frame
@@ -28,6 +28,11 @@ struct GridParams {
     const float4* sph_rec;                  // 1 RtbSphere per sphere
     const float4* bound_rec;                // 2 float4 (RtbBound) per primitive: cubes, spheres, padding
     int n_bound;                            // n_cubes + n_spheres rounded up to kBoundGroup
+    // Row table of the dense kernel (row_table_kernel, scene_pack_device.cu): entry (frame row y, primitive i) at
+    // row_tab[y * n_pad + i] = (sAn, rWn), height rows of n_pad = n_bound entries; rows of other ranks' bands
+    // are not filled.  Unused by the culled / binned kernels.
+    const float2* row_tab;
+    int n_pad;
     const float4* cube_col;                 // (r,g,b,255)
     const float4* sph_col;
     uint32_t* out_rgba8;                    // nullable, local_rows*width
@@ -91,7 +96,6 @@ int binned_tile_rows();
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream);
 cudaError_t launch_rays(const RaysParams& p, cudaStream_t stream);
 cudaError_t launch_signal_only(unsigned int* d_signal, cudaStream_t stream);  // a rank with no rows still signals
-cudaError_t configure_kernels();  // one-time cudaFuncSetAttribute calls
 
 }  // namespace rtb
 

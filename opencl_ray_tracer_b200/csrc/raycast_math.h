@@ -129,6 +129,18 @@ RTB_HD float rtb_bound_span_m(float w_a, float w_b) {
     return fmaxf(fmaxf(fminf(w_a, w_b), fminf(-w_a, -w_b)), 0.0f);
 }
 
+// Row-table form of the same bound (the dense grid kernel).  For one (primitive, pixel row) the host / device
+// packer (scene_pack_impl.h, pack_row_entry) scales the row's (sA, rowW) by gamma ~ 1 / sqrt(2 - rowC), rounded so
+// that for every ray of the frame on that row
+//     fmaf(w, w, rowC) < 2  with  w = fmaf(u, sA, rowW)      implies      |fmaf(u, sAn, rWn)| < 1
+// (a superset test: it can only let MORE rays through to the reference-exact arithmetic, which is a no-op outside
+// a primitive's footprint).  The threshold is the same constant for every primitive and row, so the running
+// minimum of |w'| may run over SEVERAL primitives before it is compared once: 1 FFMA2 + 1 FMNMX3 per ray pair
+// and primitive and nothing else per primitive.  An entry that no ray can pass is (0, 2): |w'| = 2.
+struct RtbRowEntry { float sAn, rWn; };  // 8 B; two primitives per LDS.128
+RTB_HD float rtb_row_w(float sAn, float rWn, float u) { return fmaf(u, sAn, rWn); }
+RTB_HD bool rtb_row_passes(float m_abs_w) { return m_abs_w < 1.0f; }
+
 // Tile cull (RTB_OPT_TILE_CULL): can NO ray of a pixel tile pass a primitive's bound?  The tile is given by the
 // ranges of the camera coordinates its rays take: u in [u_min, u_max], v in [v_min, v_max] (min / max over the
 // very values the kernel computes for the tile's pixels).  The answer is a statement about the values

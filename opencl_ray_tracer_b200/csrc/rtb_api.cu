@@ -1,113 +1,26 @@
-// rtb_api.cu -- implementation of the C ABI declared in include/rtb.h.
+// rtb_api.cu -- implementation of the C ABI declared in include/rtb.h (single-device entry points;
+// multi-GPU frames: rtb_group.cu).
 //
 // Host-side replacement for MainState::openCLInit / executeRayTracerOpenCL
 // (RayTrace/states/MainState.cpp:1181-1326, :641-934): device pick, resident scene buffers,
 // per-frame camera-space pack ON the device (scene_pack_device.cu), kernel launch
 // (raycast_kernels.cu), read-back.
 // There is NO CPU path in this library.
-#include <cuda.h>  // types of the driver entry point fetched below; libcuda is NOT linked
-#include <cuda_runtime.h>
-
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
-#include <string>
-#include <vector>
 
-#include "../../include/rtb.h"
-#include "raycast_kernels.cuh"
-#include "scene_pack.h"
-#include "scene_pack_device.cuh"
+#include "rtb_internal.h"
+#include "rtb_group.h"
 
 using namespace rtb;
 
-struct EventPair { cudaEvent_t a, b; };
-
-struct rtb_ctx {
-    int device = 0;
-    int sm_count = 0;
-    int clock_khz = 0;
-    char name[128] = {0};
-    cudaStream_t stream = nullptr;
-    cudaStream_t copy_stream = nullptr;  // device->host copies of finished row chunks (rtb_render)
-    cudaEvent_t ev_chunk[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    // In-launch progress (rtb_render): the grid kernel publishes finished row chunks in d_progress and
-    // copy_stream waits on the flag words with cuStreamWaitValue32 (fetched through the runtime).
-    unsigned int* d_progress = nullptr;  // 2 * kMaxProgressChunks words + the launch-done CTA counter
-    unsigned int progress_epoch = 0;
-    CUresult (*stream_wait_value32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int) = nullptr;
-    std::string last_error;
-
-    // scene: resident on the device in the reference's layout + the boxes recovered from the cubes
-    bool have_scene = false;
-    int ns = 0, nc = 0;
-    float* d_cube_v = nullptr;     // 144 floats per cube (rayTracer.cl cubeVertices)
-    float4* d_sph_o = nullptr;
-    float* d_sph_r = nullptr;
-    Box* d_boxes = nullptr;
-    size_t d_scene_cap[4] = {0, 0, 0, 0};  // bytes: cube_v, sph_o, sph_r, boxes
-    int* d_bad = nullptr;          // lowest index of a cube that is not a box (boxes_from_vertices_kernel)
-    int* h_bad = nullptr;          // pinned
-    // host mirror of boxes / spheres, downloaded on demand (rtb_render_rays packs on the host)
-    bool host_scene_valid = false;
-    std::vector<float> sph_o, sph_r;
-    std::vector<Box> boxes;
-
-    // device buffers
-    float4* d_cube_col = nullptr;
-    float4* d_sph_col = nullptr;
-    float4* d_rec = nullptr;       // per-frame packed records (cubes then spheres), grow-only
-    size_t d_rec_cap = 0;          // in float4
-    float4* h_rec = nullptr;       // pinned staging for host-packed records (rtb_render_rays only)
-    size_t h_rec_cap = 0;
-    void* d_out[3] = {nullptr, nullptr, nullptr};  // rgba8, id, i32 frame buffers, grow-only
-    size_t d_out_cap[3] = {0, 0, 0};
-    size_t d_col_cap[2] = {0, 0};  // cube / sphere colour capacity in float4
-    // which camera the records in d_rec were packed for (skip pack + upload when unchanged)
-    bool packed_valid = false;
-    float packed_cam[16] = {0};
-    int packed_w = 0, packed_h = 0;
-    unsigned long long h2d_bytes = 0, d2h_bytes = 0;  // bytes this context copied over PCIe
-    float4* d_origins = nullptr;   // rays path
-    size_t d_origins_cap = 0;
-
-    // timing / accounting
-    cudaEvent_t ev_total0 = nullptr, ev_total1 = nullptr;
-    cudaEvent_t ev_rec = nullptr;  // last upload out of the pinned record staging area
-    std::vector<EventPair> ev_free, ev_pending;
-    double kernel_ms_sum = 0.0;
-    int kernel_ms_n = 0;
-    unsigned long long launches = 0;
-    int tile_cull = 0;  // RTB_OPT_TILE_CULL
-    void* d_bins = nullptr;        // tile_cull == 2: per-tile primitive bit words of the launch in flight, grow-only
-    size_t d_bins_cap = 0;
-    // Records packed ahead of their frames (rtb_prepack_cameras, rtb_render_sequence_device): slot s holds the
-    // records of cam_slots[s].cam16 at width x height, packed on pack_stream; `ready` is recorded behind its pack.
-    struct CamSlot { float cam16[16]; cudaEvent_t ready; };
-    std::vector<CamSlot> cam_slots;      // events are created once and reused
-    int cam_slots_used = 0, cam_slots_w = 0, cam_slots_h = 0;
-    float4* d_cam_rec = nullptr;
-    size_t d_cam_rec_cap = 0;            // in float4
-    size_t cam_slot_stride = 0;          // float4 per slot
-    cudaStream_t pack_stream = nullptr;
-    cudaEvent_t ev_prepack = nullptr;
-};
-
-namespace {
+namespace rtb {
 
 int fail(rtb_ctx* ctx, int status, const std::string& msg) {
     if (ctx) ctx->last_error = msg;
     return status;
 }
-
-#define RTB_CUDA(ctx, call)                                                                   \
-    do {                                                                                      \
-        cudaError_t e__ = (call);                                                             \
-        if (e__ != cudaSuccess) {                                                             \
-            const int st__ = (e__ == cudaErrorMemoryAllocation) ? RTB_ERR_OUT_OF_MEMORY : RTB_ERR_CUDA; \
-            return fail(ctx, st__, std::string(#call) + ": " + cudaGetErrorString(e__));      \
-        }                                                                                     \
-    } while (0)
 
 int ensure_device(rtb_ctx* ctx, void** p, size_t* cap, size_t need_bytes) {
     if (*cap >= need_bytes) return RTB_OK;
@@ -119,15 +32,75 @@ int ensure_device(rtb_ctx* ctx, void** p, size_t* cap, size_t need_bytes) {
     return RTB_OK;
 }
 
-int ensure_records(rtb_ctx* ctx, size_t n_float4, bool host_staging = false) {
-    if (n_float4 == 0) n_float4 = 1;
-    if (ctx->d_rec_cap < n_float4) {
-        if (ctx->d_rec) RTB_CUDA(ctx, cudaFree(ctx->d_rec));
-        ctx->d_rec = nullptr;
-        RTB_CUDA(ctx, cudaMalloc(&ctx->d_rec, n_float4 * sizeof(float4)));
-        ctx->d_rec_cap = n_float4;
+int resolve_pending(rtb_ctx* ctx) {
+    for (const EventPair& e : ctx->ev_pending) {
+        RTB_CUDA(ctx, cudaEventSynchronize(e.b));
+        float ms = 0.f;
+        RTB_CUDA(ctx, cudaEventElapsedTime(&ms, e.a, e.b));
+        ctx->kernel_ms_sum += ms;
+        ctx->kernel_ms_n += 1;
+        ctx->ev_free.push_back(e);
     }
-    if (host_staging && ctx->h_rec_cap < n_float4) {
+    ctx->ev_pending.clear();
+    return RTB_OK;
+}
+
+// Error path of the blocking entry points: whatever was enqueued before the failure may still be writing into
+// the caller's buffers, so nothing of this context may be in flight when the error is returned.
+void drain(rtb_ctx* ctx, cudaStream_t extra) {
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+    if (extra) cudaStreamSynchronize(extra);
+    for (const EventPair& e : ctx->ev_pending) ctx->ev_free.push_back(e);  // timings of a failed call are dropped
+    ctx->ev_pending.clear();
+    (void)cudaGetLastError();
+}
+
+// The per-context device state (frame sets, bins, progress / done words) has one writer at a time: when a call
+// arrives on another stream than the previous one, the new stream first waits for everything the old one was given.
+int order_streams(rtb_ctx* ctx, cudaStream_t stream) {
+    if (ctx->state_stream == stream) return RTB_OK;
+    if (ctx->state_stream != nullptr) {
+        if (cudaEventRecord(ctx->ev_state, ctx->state_stream) == cudaSuccess) {
+            RTB_CUDA(ctx, cudaStreamWaitEvent(stream, ctx->ev_state, 0));
+        } else {  // the old stream is gone (destroyed by the caller): its work still has to finish first
+            (void)cudaGetLastError();
+            RTB_CUDA(ctx, cudaDeviceSynchronize());
+        }
+    }
+    ctx->state_stream = stream;
+    return RTB_OK;
+}
+
+int effective_cull(const rtb_ctx* ctx) {
+    if (ctx->tile_cull != 3) return ctx->tile_cull;
+    return (ctx->nc + ctx->ns >= 64) ? 2 : 0;  // auto: binned from 64 primitives on, else the dense kernel
+}
+
+}  // namespace rtb
+
+namespace {
+
+int ensure_frame_set(rtb_ctx* ctx, FrameSet* fs, size_t n_float4, size_t n_tab) {
+    if (n_float4 == 0) n_float4 = 1;
+    void* p = fs->rec;
+    size_t cap = fs->rec_cap * sizeof(float4);
+    int rc = ensure_device(ctx, &p, &cap, n_float4 * sizeof(float4));
+    fs->rec = static_cast<float4*>(p);
+    fs->rec_cap = cap / sizeof(float4);
+    if (rc != RTB_OK) return rc;
+    if (n_tab) {
+        p = fs->tab;
+        cap = fs->tab_cap * sizeof(float2);
+        rc = ensure_device(ctx, &p, &cap, n_tab * sizeof(float2));
+        fs->tab = static_cast<float2*>(p);
+        fs->tab_cap = cap / sizeof(float2);
+    }
+    return rc;
+}
+
+int ensure_host_records(rtb_ctx* ctx, size_t n_float4) {
+    if (ctx->h_rec_cap < n_float4) {
         if (ctx->h_rec) RTB_CUDA(ctx, cudaFreeHost(ctx->h_rec));
         ctx->h_rec = nullptr;
         RTB_CUDA(ctx, cudaMallocHost(&ctx->h_rec, n_float4 * sizeof(float4)));
@@ -149,20 +122,14 @@ int take_events(rtb_ctx* ctx, EventPair* out) {
     return RTB_OK;
 }
 
-int resolve_pending(rtb_ctx* ctx) {
-    for (const EventPair& e : ctx->ev_pending) {
-        RTB_CUDA(ctx, cudaEventSynchronize(e.b));
-        float ms = 0.f;
-        RTB_CUDA(ctx, cudaEventElapsedTime(&ms, e.a, e.b));
-        ctx->kernel_ms_sum += ms;
-        ctx->kernel_ms_n += 1;
-        ctx->ev_free.push_back(e);
-    }
-    ctx->ev_pending.clear();
-    return RTB_OK;
-}
-
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+void free_frame_set(FrameSet* fs) {
+    cudaFree(fs->rec);
+    cudaFree(fs->tab);
+    if (fs->ready) cudaEventDestroy(fs->ready);
+    *fs = FrameSet();
+}
 
 }  // namespace
 
@@ -190,62 +157,29 @@ const char* rtb_last_error_message(const rtb_ctx* ctx) { return ctx ? ctx->last_
 int rtb_init(rtb_ctx** out, int n_devices, const int* device_ids) {
     if (!out) return RTB_ERR_INVALID_ARG;
     *out = nullptr;
-    if (n_devices < 1) return RTB_ERR_INVALID_ARG;
-    if (n_devices > 1) return RTB_ERR_UNSUPPORTED;
-    int count = 0;
-    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) return RTB_ERR_NO_DEVICE;
-    const int dev = device_ids ? device_ids[0] : 0;
-    if (dev < 0 || dev >= count) return RTB_ERR_NO_DEVICE;
-    if (cudaSetDevice(dev) != cudaSuccess) return RTB_ERR_NO_DEVICE;
-    cudaDeviceProp prop;
-    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return RTB_ERR_CUDA;
-    if (prop.major < 10) return RTB_ERR_NO_DEVICE;  // sm_100a binary only
-    rtb_ctx* ctx = new (std::nothrow) rtb_ctx();
-    if (!ctx) return RTB_ERR_OUT_OF_MEMORY;
-    ctx->device = dev;
-    ctx->sm_count = prop.multiProcessorCount;
-    cudaDeviceGetAttribute(&ctx->clock_khz, cudaDevAttrClockRate, dev);
-    std::snprintf(ctx->name, sizeof ctx->name, "%.127s", prop.name);
-    bool chunk_ok = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
-    for (int i = 0; i < 8 && chunk_ok; ++i)
-        chunk_ok = cudaEventCreateWithFlags(&ctx->ev_chunk[i], cudaEventDisableTiming) == cudaSuccess;
-    if (!chunk_ok || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreate(&ctx->ev_total0) != cudaSuccess || cudaEventCreate(&ctx->ev_total1) != cudaSuccess ||
-        cudaEventCreateWithFlags(&ctx->ev_rec, cudaEventDisableTiming) != cudaSuccess ||
-        cudaMalloc(&ctx->d_bad, sizeof(int)) != cudaSuccess ||
-        cudaMalloc(&ctx->d_progress, (2 * kMaxProgressChunks + 8) * sizeof(unsigned int)) != cudaSuccess ||
-        cudaMemset(ctx->d_progress, 0, (2 * kMaxProgressChunks + 8) * sizeof(unsigned int)) != cudaSuccess ||
-        cudaMallocHost(&ctx->h_bad, sizeof(int)) != cudaSuccess || configure_kernels() != cudaSuccess) {
-        rtb_shutdown(ctx);
-        return RTB_ERR_CUDA;
-    }
-    {   // optional: without it rtb_render falls back to one launch per row chunk
-        void* fn = nullptr;
-        cudaDriverEntryPointQueryResult qr;
-        const char* off = std::getenv("RTB_NO_STREAM_WAIT");
-        if (!(off && off[0] == '1') &&
-            cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &qr) == cudaSuccess &&
-            qr == cudaDriverEntryPointSuccess && fn)
-            ctx->stream_wait_value32 = reinterpret_cast<CUresult (*)(CUstream, CUdeviceptr, cuuint32_t, unsigned int)>(fn);
-        else
-            (void)cudaGetLastError();
-    }
-    *out = ctx;
-    return RTB_OK;
+    if (n_devices < 1 || n_devices > RTB_MAX_GROUP) return RTB_ERR_INVALID_ARG;
+    if (n_devices > 1) return group_init_local(out, n_devices, device_ids);  // rtb_group.cu
+    return init_single(out, device_ids ? device_ids[0] : 0);
 }
 
 void rtb_shutdown(rtb_ctx* ctx) {
     if (!ctx) return;
+    if (ctx->multi) group_shutdown_local(ctx);  // the other devices' contexts and the group itself
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+    if (ctx->pack_stream) cudaStreamSynchronize(ctx->pack_stream);
     for (const EventPair& e : ctx->ev_pending) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     for (const EventPair& e : ctx->ev_free) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     if (ctx->ev_total0) cudaEventDestroy(ctx->ev_total0);
     if (ctx->ev_total1) cudaEventDestroy(ctx->ev_total1);
     if (ctx->ev_rec) cudaEventDestroy(ctx->ev_rec);
+    if (ctx->ev_state) cudaEventDestroy(ctx->ev_state);
+    if (ctx->ev_scene) cudaEventDestroy(ctx->ev_scene);
     cudaFree(ctx->d_cube_col);
     cudaFree(ctx->d_sph_col);
-    cudaFree(ctx->d_rec);
+    free_frame_set(&ctx->cur);
+    for (auto& fs : ctx->slots) free_frame_set(&fs);
     cudaFree(ctx->d_cube_v);
     cudaFree(ctx->d_sph_o);
     cudaFree(ctx->d_sph_r);
@@ -253,12 +187,11 @@ void rtb_shutdown(rtb_ctx* ctx) {
     cudaFree(ctx->d_bad);
     cudaFree(ctx->d_progress);
     cudaFree(ctx->d_bins);
-    cudaFree(ctx->d_cam_rec);
-    for (auto& s : ctx->cam_slots) cudaEventDestroy(s.ready);
     if (ctx->pack_stream) cudaStreamDestroy(ctx->pack_stream);
     if (ctx->ev_prepack) cudaEventDestroy(ctx->ev_prepack);
     if (ctx->h_bad) cudaFreeHost(ctx->h_bad);
     if (ctx->h_rec) cudaFreeHost(ctx->h_rec);
+    if (ctx->h_scene) cudaFreeHost(ctx->h_scene);
     for (int i = 0; i < 3; ++i) cudaFree(ctx->d_out[i]);
     cudaFree(ctx->d_origins);
     for (int i = 0; i < 8; ++i)
@@ -276,13 +209,93 @@ int rtb_set_scene(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins, cons
     if (numSpheres > 0 && (!sphereOrigins || !sphereRadius || !sphereColours))
         return fail(ctx, RTB_ERR_INVALID_ARG, "null sphere array");
     if (numCubes > 0 && (!cubeVertices || !cubeColours)) return fail(ctx, RTB_ERR_INVALID_ARG, "null cube array");
+    if (ctx->multi)
+        return group_set_scene_local(ctx, numSpheres, sphereOrigins, sphereRadius, sphereColours, numCubes, cubeVertices,
+                                     cubeColours);
+    return set_scene_single(ctx, numSpheres, sphereOrigins, sphereRadius, sphereColours, numCubes, cubeVertices, cubeColours);
+}
+
+}  // extern "C"
+
+namespace rtb {
+
+int init_single(rtb_ctx** out, int dev) {
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) return RTB_ERR_NO_DEVICE;
+    if (dev < 0 || dev >= count) return RTB_ERR_NO_DEVICE;
+    if (cudaSetDevice(dev) != cudaSuccess) return RTB_ERR_NO_DEVICE;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return RTB_ERR_CUDA;
+    if (prop.major < 10) return RTB_ERR_NO_DEVICE;  // sm_100a binary only
+    rtb_ctx* ctx = new (std::nothrow) rtb_ctx();
+    if (!ctx) return RTB_ERR_OUT_OF_MEMORY;
+    ctx->device = dev;
+    ctx->sm_count = prop.multiProcessorCount;
+    cudaDeviceGetAttribute(&ctx->clock_khz, cudaDevAttrClockRate, dev);
+    std::snprintf(ctx->name, sizeof ctx->name, "%.127s", prop.name);
+    bool chunk_ok = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int i = 0; i < 8 && chunk_ok; ++i)
+        chunk_ok = cudaEventCreateWithFlags(&ctx->ev_chunk[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!chunk_ok || cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&ctx->ev_total0) != cudaSuccess || cudaEventCreate(&ctx->ev_total1) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_rec, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_state, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_scene, cudaEventDisableTiming) != cudaSuccess ||
+        cudaMalloc(&ctx->d_bad, sizeof(int)) != cudaSuccess ||
+        cudaMalloc(&ctx->d_progress, (2 * kMaxProgressChunks + 8) * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMemset(ctx->d_progress, 0, (2 * kMaxProgressChunks + 8) * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMallocHost(&ctx->h_bad, sizeof(int)) != cudaSuccess) {
+        rtb_shutdown(ctx);
+        return RTB_ERR_CUDA;
+    }
+    {   // optional: without them rtb_render falls back to one launch per row chunk, rtb_group_* to RTB_ERR_UNSUPPORTED
+        const char* off = std::getenv("RTB_NO_STREAM_WAIT");
+        if (!(off && off[0] == '1')) {
+            void* fn = nullptr;
+            cudaDriverEntryPointQueryResult qr;
+            if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &qr) == cudaSuccess &&
+                qr == cudaDriverEntryPointSuccess && fn)
+                ctx->stream_wait_value32 = reinterpret_cast<CUresult (*)(CUstream, CUdeviceptr, cuuint32_t, unsigned int)>(fn);
+            else
+                (void)cudaGetLastError();
+            fn = nullptr;
+            if (cudaGetDriverEntryPoint("cuStreamWriteValue32", &fn, cudaEnableDefault, &qr) == cudaSuccess &&
+                qr == cudaDriverEntryPointSuccess && fn)
+                ctx->stream_write_value32 = reinterpret_cast<CUresult (*)(CUstream, CUdeviceptr, cuuint32_t, unsigned int)>(fn);
+            else
+                (void)cudaGetLastError();
+        }
+    }
+    *out = ctx;
+    return RTB_OK;
+}
+
+// Blocks until the last rtb_set_scene's staging area has been consumed and its NOT_A_BOX verdict is on the host.
+int collect_scene_verdict(rtb_ctx* ctx) {
+    if (!ctx->scene_check_pending) return RTB_OK;
+    RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_scene));
+    ctx->scene_check_pending = false;
+    if (ctx->nc && *ctx->h_bad != kNoBadCube) {
+        char buf[160];
+        std::snprintf(buf, sizeof buf, "cube %d: its 36 vertices are not an affine image of the Cube.cpp vertex list",
+                      *ctx->h_bad);
+        ctx->have_scene = false;
+        return fail(ctx, RTB_ERR_NOT_A_BOX, buf);
+    }
+    return RTB_OK;
+}
+
+int set_scene_single(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins, const float* sphereRadius,
+                     const float* sphereColours, int numCubes, const float* cubeVertices, const float* cubeColours) {
     RTB_CUDA(ctx, cudaSetDevice(ctx->device));
     ctx->have_scene = false;
-    ctx->packed_valid = false;
-    ctx->cam_slots_used = 0;
+    ctx->cur.rec_valid = ctx->cur.tab_valid = false;
+    ctx->slots_used = 0;
     ctx->host_scene_valid = false;
     cudaStream_t st = ctx->stream;
-    RTB_CUDA(ctx, cudaStreamSynchronize(st));
+    int rc = order_streams(ctx, st);  // frames of the previous scene may still be reading the buffers
+    if (rc != RTB_OK) return rc;
     const size_t nc = (size_t)numCubes, ns = (size_t)numSpheres;
     {
         void* p[6] = {ctx->d_cube_v, ctx->d_sph_o, ctx->d_sph_r, ctx->d_boxes, ctx->d_cube_col, ctx->d_sph_col};
@@ -291,6 +304,9 @@ int rtb_set_scene(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins, cons
         const size_t need[6] = {144 * sizeof(float) * (nc ? nc : 1), sizeof(float4) * (ns ? ns : 1),
                                 sizeof(float) * (ns ? ns : 1), sizeof(Box) * (nc ? nc : 1),
                                 sizeof(float4) * (nc ? nc : 1), sizeof(float4) * (ns ? ns : 1)};
+        bool grow = false;
+        for (int k = 0; k < 6; ++k) grow = grow || cap[k] < need[k];
+        if (grow) RTB_CUDA(ctx, cudaDeviceSynchronize());  // cudaFree below: nothing may still read the old buffers
         int rc0 = RTB_OK;
         for (int k = 0; k < 6 && rc0 == RTB_OK; ++k) rc0 = ensure_device(ctx, &p[k], &cap[k], need[k]);
         ctx->d_cube_v = static_cast<float*>(p[0]);
@@ -304,124 +320,172 @@ int rtb_set_scene(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins, cons
         ctx->d_col_cap[1] = cap[5] / sizeof(float4);
         if (rc0 != RTB_OK) return rc0;
     }
-    // The scene goes to the device exactly as the reference lays it out (the 6 arrays of
-    // MainState.cpp:677-839); the boxes are recovered from the vertices there.
-    if (nc) {
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_cube_v, cubeVertices, 144 * sizeof(float) * nc, cudaMemcpyHostToDevice, st));
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_cube_col, cubeColours, sizeof(float4) * nc, cudaMemcpyHostToDevice, st));
+    // The caller may free its arrays on return: they are staged in the context's pinned buffer (one host
+    // memcpy) and go to the device from there, exactly as the reference lays them out (the 6 arrays of
+    // MainState.cpp:677-839); the boxes are recovered from the vertices on the device.  Nothing here waits for
+    // the GPU unless the staging area is still being read by the previous rtb_set_scene.
+    const size_t bytes[5] = {144 * sizeof(float) * nc, sizeof(float4) * nc, sizeof(float4) * ns, sizeof(float) * ns,
+                             sizeof(float4) * ns};
+    const void* src[5] = {cubeVertices, cubeColours, sphereOrigins, sphereRadius, sphereColours};
+    void* dst[5] = {ctx->d_cube_v, ctx->d_cube_col, ctx->d_sph_o, ctx->d_sph_r, ctx->d_sph_col};
+    size_t total = 0, off[5];
+    for (int k = 0; k < 5; ++k) { off[k] = total; total += (bytes[k] + 255) & ~(size_t)255; }
+    if (ctx->scene_check_pending) RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_scene));  // staging area and h_bad free again
+    ctx->scene_check_pending = false;
+    if (ctx->h_scene_cap < total) {
+        if (ctx->h_scene) RTB_CUDA(ctx, cudaFreeHost(ctx->h_scene));
+        ctx->h_scene = nullptr;
+        ctx->h_scene_cap = 0;
+        RTB_CUDA(ctx, cudaMallocHost(&ctx->h_scene, total ? total : 256));
+        ctx->h_scene_cap = total ? total : 256;
     }
-    if (ns) {
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_sph_o, sphereOrigins, sizeof(float4) * ns, cudaMemcpyHostToDevice, st));
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_sph_r, sphereRadius, sizeof(float) * ns, cudaMemcpyHostToDevice, st));
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_sph_col, sphereColours, sizeof(float4) * ns, cudaMemcpyHostToDevice, st));
-    }
+    for (int k = 0; k < 5; ++k)
+        if (bytes[k]) {
+            std::memcpy(ctx->h_scene + off[k], src[k], bytes[k]);
+            RTB_CUDA(ctx, cudaMemcpyAsync(dst[k], ctx->h_scene + off[k], bytes[k], cudaMemcpyHostToDevice, st));
+        }
     RTB_CUDA(ctx, launch_boxes_from_vertices(ctx->d_cube_v, numCubes, ctx->d_boxes, ctx->d_bad, st));
     if (nc) ctx->launches += 1;
     RTB_CUDA(ctx, cudaMemcpyAsync(ctx->h_bad, ctx->d_bad, sizeof(int), cudaMemcpyDeviceToHost, st));
-    RTB_CUDA(ctx, cudaStreamSynchronize(st));  // the caller may free its arrays on return
+    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_scene, st));
+    ctx->scene_check_pending = true;
     ctx->h2d_bytes += (144 * sizeof(float) + sizeof(float4)) * nc + (2 * sizeof(float4) + sizeof(float)) * ns;
     ctx->d2h_bytes += sizeof(int);
-    if (nc && *ctx->h_bad != kNoBadCube) {
-        char buf[160];
-        std::snprintf(buf, sizeof buf, "cube %d: its 36 vertices are not an affine image of the Cube.cpp vertex list",
-                      *ctx->h_bad);
-        return fail(ctx, RTB_ERR_NOT_A_BOX, buf);
-    }
     ctx->ns = numSpheres;
     ctx->nc = numCubes;
-    const int rc = ensure_records(ctx, 6 * nc + 4 * ns + 32);
-    if (rc != RTB_OK) return rc;
     ctx->have_scene = true;
+    // RTB_OPT_DEFER_SCENE_CHECK = 0 (default): the NOT_A_BOX verdict is this call's return value (one wait for the
+    // device); 1: the call returns at once and the next render call reports it.
+    if (!ctx->defer_scene_check) return collect_scene_verdict(ctx);
     return RTB_OK;
 }
 
-}  // extern "C"
+}  // namespace rtb
 
+namespace rtb {
 namespace {
 
-// One frame's records in d_rec / h_rec (float4 units):
+// One frame's records (FrameSet::rec, float4 units):
 //   [0, 3nc)            RtbSlab x3 per cube      (reference-exact path, read through L2)
 //   [3nc, 3nc+ns)       RtbSphere per sphere
 //   [bound_offset, +2*n_bound)  RtbBound per primitive (cubes, spheres, "never" padding up to a
-//                       multiple of kBoundGroup): the list the grid kernel stages with TMA
+//                       multiple of kBoundGroup): what the culled / binned kernels and row_table_kernel read
 size_t exact_records(const rtb_ctx* ctx) { return 3 * (size_t)ctx->nc + (size_t)ctx->ns; }
 size_t bound_offset(const rtb_ctx* ctx) { return (exact_records(ctx) + 7) & ~(size_t)7; }  // 128-byte aligned
 int bound_count(const rtb_ctx* ctx) {
     return (int)(((size_t)ctx->nc + (size_t)ctx->ns + kBoundGroup - 1) / kBoundGroup * kBoundGroup);
 }
 size_t frame_records(const rtb_ctx* ctx) { return bound_offset(ctx) + 2 * (size_t)bound_count(ctx); }
+size_t table_entries(const rtb_ctx* ctx, int height) { return (size_t)height * (size_t)bound_count(ctx); }
 
-// Enqueues the device pack of one frame's records into `dst` (scene_pack_device.cu).
-int enqueue_pack(rtb_ctx* ctx, const CameraFrame& cf, int width, int height, float4* dst, cudaStream_t stream) {
+// Enqueues the device pack of one frame's records into `fs` (scene_pack_device.cu).
+int enqueue_pack(rtb_ctx* ctx, const CameraFrame& cf, int width, int height, const float* cam16, FrameSet* fs,
+                 cudaStream_t stream) {
+    fs->rec_valid = fs->tab_valid = false;
+    int rc = ensure_frame_set(ctx, fs, frame_records(ctx) + 32, 0);
+    if (rc != RTB_OK) return rc;
     PackFrameParams pp;
     pp.cf = cf;
     pp.fe = frame_extent(cf, width, height);
     pp.nc = ctx->nc; pp.ns = ctx->ns; pp.n_bound = bound_count(ctx);
     pp.boxes = ctx->d_boxes; pp.sph_o = ctx->d_sph_o; pp.sph_r = ctx->d_sph_r;
-    pp.rec = dst;
+    pp.rec = fs->rec;
     pp.bound_off = bound_offset(ctx);
     RTB_CUDA(ctx, launch_pack_frame(pp, stream));
     ctx->launches += 1;
+    std::memcpy(fs->cam16, cam16, sizeof fs->cam16);
+    fs->w = width; fs->h = height;
+    fs->uabs = pp.fe.uabs;
+    fs->rec_valid = true;
     return RTB_OK;
 }
+
+// Enqueues the row table of the dense kernel for the rows of the given bands, behind the pack on `stream`.
+int enqueue_table(rtb_ctx* ctx, const CameraFrame& cf, FrameSet* fs, int band_rows, int band_rank, int band_world,
+                  cudaStream_t stream) {
+    fs->tab_valid = false;
+    const int rc = ensure_frame_set(ctx, fs, frame_records(ctx) + 32, table_entries(ctx, fs->h));
+    if (rc != RTB_OK) return rc;
+    RowTableParams tp;
+    tp.cam = cf.cam;
+    tp.uabs = fs->uabs;
+    tp.n_bound = bound_count(ctx);
+    tp.height = fs->h;
+    tp.band_rows = band_rows; tp.band_rank = band_rank; tp.band_world = band_world;
+    tp.local_rows = rtb_band_local_rows(fs->h, band_rows, band_rank, band_world);
+    tp.bound_rec = fs->rec + bound_offset(ctx);
+    tp.table = fs->tab;
+    RTB_CUDA(ctx, launch_row_table(tp, stream));
+    if (tp.local_rows > 0 && tp.n_bound > 0) ctx->launches += 1;
+    fs->band_rows = band_rows; fs->band_rank = band_rank; fs->band_world = band_world;
+    fs->tab_valid = true;
+    return RTB_OK;
+}
+
+bool same_bands(const FrameSet* fs, int band_rows, int band_rank, int band_world) {
+    if (fs->band_world == 1 && fs->tab_valid) return true;  // every row is filled: good for any band set
+    return fs->band_rows == band_rows && fs->band_rank == band_rank && fs->band_world == band_world;
+}
+
+}  // namespace
 
 // Makes this frame's records available to `stream` and returns where they are: a slot packed ahead of time for
-// exactly this camera and frame size (rtb_prepack_cameras; the stream then waits for that pack), d_rec if it
-// already holds them (same 16 floats, same frame size, same scene), else d_rec after a pack on `stream`.
-int upload_frame_records(rtb_ctx* ctx, const CameraFrame& cf, int width, int height, const float* o0,
-                         const float* du, const float* dv, const float* dir, cudaStream_t stream, const float4** rec) {
-    float cam16[16];
-    std::memcpy(cam16, o0, 16); std::memcpy(cam16 + 4, du, 16);
-    std::memcpy(cam16 + 8, dv, 16); std::memcpy(cam16 + 12, dir, 16);
-    *rec = ctx->d_rec;
-    if (ctx->cam_slots_used > 0 && ctx->cam_slots_w == width && ctx->cam_slots_h == height) {
-        for (int s = 0; s < ctx->cam_slots_used; ++s)
-            if (std::memcmp(cam16, ctx->cam_slots[(size_t)s].cam16, sizeof cam16) == 0) {
-                RTB_CUDA(ctx, cudaStreamWaitEvent(stream, ctx->cam_slots[(size_t)s].ready, 0));
-                *rec = ctx->d_cam_rec + (size_t)s * ctx->cam_slot_stride;
-                return RTB_OK;
-            }
+// exactly this camera and frame size (rtb_prepack_cameras; the stream then waits for that pack), ctx->cur if it
+// already holds them (same 16 floats, same frame size, same scene), else ctx->cur after a pack on `stream`.  With
+// the dense kernel selected the set's row table is made to hold the rows of the given bands as well.
+int prepare_frame(rtb_ctx* ctx, const CameraFrame& cf, int width, int height, const float* cam16, int band_rows,
+                  int band_rank, int band_world, cudaStream_t stream, const FrameSet** out) {
+    const bool need_tab = effective_cull(ctx) == 0;
+    FrameSet* fs = nullptr;
+    for (int s = 0; s < ctx->slots_used && !fs; ++s) {
+        FrameSet* c = &ctx->slots[(size_t)s];
+        if (c->rec_valid && c->w == width && c->h == height && std::memcmp(cam16, c->cam16, sizeof c->cam16) == 0) {
+            RTB_CUDA(ctx, cudaStreamWaitEvent(stream, c->ready, 0));
+            fs = c;
+        }
     }
-    if (ctx->packed_valid && ctx->packed_w == width && ctx->packed_h == height &&
-        std::memcmp(cam16, ctx->packed_cam, sizeof cam16) == 0)
-        return RTB_OK;
-    const int rc = enqueue_pack(ctx, cf, width, height, ctx->d_rec, stream);
-    if (rc != RTB_OK) return rc;
-    std::memcpy(ctx->packed_cam, cam16, sizeof cam16);
-    ctx->packed_w = width; ctx->packed_h = height;
-    ctx->packed_valid = true;
+    if (!fs) {
+        fs = &ctx->cur;
+        if (!(fs->rec_valid && fs->w == width && fs->h == height && std::memcmp(cam16, fs->cam16, sizeof fs->cam16) == 0)) {
+            const int rc = enqueue_pack(ctx, cf, width, height, cam16, fs, stream);
+            if (rc != RTB_OK) return rc;
+        }
+    }
+    if (need_tab && !(fs->tab_valid && same_bands(fs, band_rows, band_rank, band_world))) {
+        const int rc = enqueue_table(ctx, cf, fs, band_rows, band_rank, band_world, stream);
+        if (rc != RTB_OK) return rc;
+    }
+    *out = fs;
     return RTB_OK;
 }
 
-// Packs the records of n cameras into slots on pack_stream, behind everything already enqueued on `stream`
+// Packs the frame sets of n cameras into slots on pack_stream, behind everything already enqueued on `stream`
 // (earlier frames may still be reading the slots).  Always packs: nothing is kept from an earlier call.
-constexpr int kMaxCamSlots = 256;
-int prepack_cameras(rtb_ctx* ctx, int width, int height, int n, const float* cameras, cudaStream_t stream) {
-    ctx->cam_slots_used = 0;
+namespace { constexpr int kMaxCamSlots = 256; }
+int prepack_cameras(rtb_ctx* ctx, int width, int height, int band_rows, int band_rank, int band_world, int n,
+                    const float* cameras, cudaStream_t stream) {
+    ctx->slots_used = 0;
     if (n <= 0) return RTB_OK;
     if (n > kMaxCamSlots) n = kMaxCamSlots;
-    const size_t stride = frame_records(ctx);
-    while (n > 1 && stride * (size_t)n * sizeof(float4) > ((size_t)256 << 20)) n /= 2;  // at most 256 MB of records
+    const bool with_tab = effective_cull(ctx) == 0;
+    const size_t per_slot = frame_records(ctx) * sizeof(float4) + (with_tab ? table_entries(ctx, height) * sizeof(float2) : 0);
+    while (n > 1 && per_slot * (size_t)n > ((size_t)4 << 30)) n /= 2;  // at most 4 GB of frame sets
     if (!ctx->pack_stream) {
         int lo = 0, hi = 0;
         RTB_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
         RTB_CUDA(ctx, cudaStreamCreateWithPriority(&ctx->pack_stream, cudaStreamNonBlocking, hi));
         RTB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_prepack, cudaEventDisableTiming));
     }
-    if (ctx->d_cam_rec_cap < stride * (size_t)n) {
-        RTB_CUDA(ctx, cudaDeviceSynchronize());
-        if (ctx->d_cam_rec) RTB_CUDA(ctx, cudaFree(ctx->d_cam_rec));
-        ctx->d_cam_rec = nullptr; ctx->d_cam_rec_cap = 0;
-        RTB_CUDA(ctx, cudaMalloc(&ctx->d_cam_rec, stride * (size_t)n * sizeof(float4)));
-        ctx->d_cam_rec_cap = stride * (size_t)n;
+    while ((int)ctx->slots.size() < n) {
+        FrameSet fs;
+        RTB_CUDA(ctx, cudaEventCreateWithFlags(&fs.ready, cudaEventDisableTiming));
+        ctx->slots.push_back(fs);
     }
-    while ((int)ctx->cam_slots.size() < n) {
-        rtb_ctx::CamSlot s;
-        std::memset(s.cam16, 0, sizeof s.cam16);
-        RTB_CUDA(ctx, cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming));
-        ctx->cam_slots.push_back(s);
-    }
-    ctx->cam_slot_stride = stride;
+    bool grow = false;
+    for (int s = 0; s < n; ++s)
+        grow = grow || ctx->slots[(size_t)s].rec_cap < frame_records(ctx) + 32 ||
+               (with_tab && ctx->slots[(size_t)s].tab_cap < table_entries(ctx, height));
+    if (grow) RTB_CUDA(ctx, cudaDeviceSynchronize());  // buffers are re-allocated below
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_prepack, stream));
     RTB_CUDA(ctx, cudaStreamWaitEvent(ctx->pack_stream, ctx->ev_prepack, 0));
     for (int s = 0; s < n; ++s) {
@@ -432,15 +496,17 @@ int prepack_cameras(rtb_ctx* ctx, int width, int height, int n, const float* cam
             std::snprintf(buf, sizeof buf, "degenerate camera %d", s);
             return fail(ctx, RTB_ERR_CAMERA, buf);
         }
-        const int rc = enqueue_pack(ctx, cf, width, height, ctx->d_cam_rec + (size_t)s * stride, ctx->pack_stream);
+        FrameSet* fs = &ctx->slots[(size_t)s];
+        int rc = enqueue_pack(ctx, cf, width, height, c, fs, ctx->pack_stream);
+        if (rc == RTB_OK && with_tab) rc = enqueue_table(ctx, cf, fs, band_rows, band_rank, band_world, ctx->pack_stream);
         if (rc != RTB_OK) return rc;
-        RTB_CUDA(ctx, cudaEventRecord(ctx->cam_slots[(size_t)s].ready, ctx->pack_stream));
-        std::memcpy(ctx->cam_slots[(size_t)s].cam16, c, 16 * sizeof(float));
-        ctx->cam_slots_used = s + 1;
+        RTB_CUDA(ctx, cudaEventRecord(fs->ready, ctx->pack_stream));
+        ctx->slots_used = s + 1;
     }
-    ctx->cam_slots_w = width; ctx->cam_slots_h = height;
     return RTB_OK;
 }
+
+namespace {
 
 // Host mirror of the device scene (boxes, sphere centres / radii) for the host-packed rays path.
 int ensure_host_scene(rtb_ctx* ctx) {
@@ -448,6 +514,7 @@ int ensure_host_scene(rtb_ctx* ctx) {
     ctx->boxes.resize((size_t)ctx->nc);
     ctx->sph_o.resize(4 * (size_t)ctx->ns);
     ctx->sph_r.resize((size_t)ctx->ns);
+    RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the scene upload / box recovery of rtb_set_scene
     if (ctx->nc)
         RTB_CUDA(ctx, cudaMemcpy(ctx->boxes.data(), ctx->d_boxes, sizeof(Box) * (size_t)ctx->nc, cudaMemcpyDeviceToHost));
     if (ctx->ns) {
@@ -459,9 +526,11 @@ int ensure_host_scene(rtb_ctx* ctx) {
     return RTB_OK;
 }
 
+}  // namespace
+
 // Row chunks in which a launch reports progress (rtb_render, rtb_render_bands_host): 2-4 MB of
 // output each, bounds on multiples of `unit` rows (a multiple of 16); returns the number of chunks.
-// The copy stream is nearly as busy as the kernel (C3: 0.6 ms of PCIe time under a 0.76 ms launch), so
+// The copy stream is nearly as busy as the kernel (C3: 0.6 ms of PCIe time under a 0.5 ms launch), so
 // the copies have to start early and every stream wait (1-2 us of the copy stream's time) counts:
 // measured on C3, device span of rtb_render: 16 x 2 MB 0.83 ms; 64 x 0.5 MB with copies grouped by four
 // 0.89 ms; sizes shrinking towards the end (8, 8, 8, 4, 2, 1, 0.5, 0.5 MB) 0.93 ms; 16 x 2 MB with the last
@@ -488,7 +557,7 @@ int plan_progress_chunks(int rows, size_t row_bytes, int unit, int bound[kMaxPro
     for (int i = 0; i < n; ++i) bound[i] = i * chunk_rows;
     bound[n] = rows;
     // The copy stream is the longer of the two pipelines (C3: 0.60 ms of PCIe time + ~10 us per chunk against a
-    // 0.59 ms launch), so it should start early: the first chunk is cut at a quarter (RTB_CHUNK_RAMP=0: uniform).
+    // 0.5 ms launch), so it should start early: the first chunk is cut at a quarter (RTB_CHUNK_RAMP=0: uniform).
     static const bool ramp = [] { const char* e = std::getenv("RTB_CHUNK_RAMP"); return !(e && e[0] == '0'); }();
     const int first = chunk_rows / 4 / unit * unit;
     if (ramp && n >= 4 && n < kMaxProgressChunks && first >= unit) {
@@ -499,21 +568,22 @@ int plan_progress_chunks(int rows, size_t row_bytes, int unit, int bound[kMaxPro
     return n;
 }
 
-// Enqueues one grid-kernel launch (with its timing event pair) on `stream`.
-int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width, int height, int band_rows,
+// Enqueues one launch of the ray-cast kernels (with its timing event pair) on `stream`.
+int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const FrameSet* fs, int width, int height, int band_rows,
                  int band_rank, int band_world, int local_rows, void* d_rgba8, void* d_id, void* d_i32,
-                 cudaStream_t stream, int out_global_rows = 0, int progress_chunks = 0, const int* progress_bound = nullptr,
-                 void* done_signal = nullptr) {
+                 cudaStream_t stream, int out_global_rows, int progress_chunks, const int* progress_bound,
+                 void* done_signal) {
     GridParams p;
     p.out_global_rows = out_global_rows;
     static const int fence_sys = [] { const char* e = std::getenv("RTB_PROGRESS_FENCE_SYSTEM"); return (e && e[0] == '1') ? 1 : 0; }();
     p.fence_system = fence_sys;
-    p.tile_cull = ctx->tile_cull;
+    p.tile_cull = effective_cull(ctx);
     p.bins = nullptr;
     p.bin_words = 0;
-    if (ctx->tile_cull == 2) {
+    if (p.tile_cull == 2) {
         const int n_bound = bound_count(ctx);
         const size_t words = grid_bin_words(width, local_rows, n_bound);
+        if (ctx->d_bins_cap < (words ? words : 1) * sizeof(uint32_t)) RTB_CUDA(ctx, cudaDeviceSynchronize());  // an earlier launch may read the old buffer
         const int rc = ensure_device(ctx, &ctx->d_bins, &ctx->d_bins_cap, (words ? words : 1) * sizeof(uint32_t));
         if (rc != RTB_OK) return rc;
         p.bins = static_cast<uint32_t*>(ctx->d_bins);
@@ -529,10 +599,12 @@ int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const float4* d_rec, int width
     p.band_rows = band_rows; p.band_rank = band_rank; p.band_world = band_world;
     p.local_rows = local_rows;
     p.n_cubes = ctx->nc; p.n_spheres = ctx->ns;
-    p.cube_rec = d_rec;
-    p.sph_rec = d_rec + 3 * (size_t)ctx->nc;
-    p.bound_rec = d_rec + bound_offset(ctx);
+    p.cube_rec = fs->rec;
+    p.sph_rec = fs->rec + 3 * (size_t)ctx->nc;
+    p.bound_rec = fs->rec + bound_offset(ctx);
     p.n_bound = bound_count(ctx);
+    p.row_tab = (p.tile_cull == 0) ? fs->tab : nullptr;
+    p.n_pad = p.n_bound;
     p.cube_col = ctx->d_cube_col;
     p.sph_col = ctx->d_sph_col;
     p.out_rgba8 = static_cast<uint32_t*>(d_rgba8);
@@ -559,7 +631,20 @@ int check_frame_args(rtb_ctx* ctx, int width, int height, const float* o0, const
         return fail(ctx, RTB_ERR_INVALID_ARG, "bad frame size or null camera vector");
     if ((long long)width * height > (1LL << 31) - 1) return fail(ctx, RTB_ERR_INVALID_ARG, "frame too large");
     if (!ctx->have_scene) return fail(ctx, RTB_ERR_NO_SCENE, "rtb_set_scene has not been called");
+    // A deferred NOT_A_BOX verdict (RTB_OPT_DEFER_SCENE_CHECK) is reported here once the upload has finished, else by
+    // the blocking render calls after their own wait (verdict_after_sync): nothing waits for the scene upload alone.
+    if (ctx->scene_check_pending && cudaEventQuery(ctx->ev_scene) == cudaSuccess) return collect_scene_verdict(ctx);
+    (void)cudaGetLastError();
     return RTB_OK;
+}
+
+}  // namespace rtb
+
+namespace {
+
+void cam16_of(const float* o0, const float* du, const float* dv, const float* dir, float out[16]) {
+    std::memcpy(out, o0, 16); std::memcpy(out + 4, du, 16);
+    std::memcpy(out + 8, dv, 16); std::memcpy(out + 12, dir, 16);
 }
 
 }  // namespace
@@ -577,10 +662,18 @@ int rtb_band_local_rows(int height, int band_rows, int band_rank, int band_world
     return rows;
 }
 
+#define RTB_SINGLE_ONLY(ctx)                                                                                         \
+    do {                                                                                                             \
+        if ((ctx) && (ctx)->multi)                                                                                   \
+            return fail(ctx, RTB_ERR_UNSUPPORTED, "device-pointer entry points need a single-device context "        \
+                                                  "(a multi-device context renders with rtb_render / rtb_render_sequence_device)"); \
+    } while (0)
+
 int rtb_render_bands_device(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
                             const float dV[4], const float rayDir[4], int band_rows, int band_rank,
                             int band_world, void* d_rgba8, void* d_prim_id, void* d_rgba_i32,
                             void* cuda_stream) {
+    RTB_SINGLE_ONLY(ctx);
     int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
     if (rc != RTB_OK) return rc;
     if (band_rows <= 0 || band_rows % 4 != 0 || band_world <= 0 || band_rank < 0 || band_rank >= band_world)
@@ -590,13 +683,18 @@ int rtb_render_bands_device(rtb_ctx* ctx, int width, int height, const float ori
     if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
         return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
     cudaStream_t stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->stream;
-    const float4* frame_rec = nullptr;
-    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, stream, &frame_rec);
+    rc = order_streams(ctx, stream);
     if (rc != RTB_OK) return rc;
-    const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
-    rc = enqueue_grid(ctx, cf.cam, frame_rec, width, height, band_rows, band_rank, band_world, local_rows,
-                      d_rgba8, d_prim_id, d_rgba_i32, stream);
-    if (rc != RTB_OK) return rc;
+    float cam16[16];
+    cam16_of(origin0, dU, dV, rayDir, cam16);
+    const FrameSet* fs = nullptr;
+    rc = prepare_frame(ctx, cf, width, height, cam16, band_rows, band_rank, band_world, stream, &fs);
+    if (rc == RTB_OK) {
+        const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
+        rc = enqueue_grid(ctx, cf.cam, fs, width, height, band_rows, band_rank, band_world, local_rows,
+                          d_rgba8, d_prim_id, d_rgba_i32, stream);
+    }
+    if (rc != RTB_OK) { drain(ctx, stream); return rc; }
     if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
     return RTB_OK;
 }
@@ -625,6 +723,7 @@ int rtb_stream_wait_signal(rtb_ctx* ctx, void* d_signal, unsigned int value, voi
 int rtb_render_bands_frame_signal(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
                                   const float dV[4], const float rayDir[4], int band_rows, int band_rank,
                                   int band_world, void* d_frame_rgba8, void* d_signal, void* cuda_stream) {
+    RTB_SINGLE_ONLY(ctx);
     int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
     if (rc != RTB_OK) return rc;
     if (band_rows <= 0 || band_rows % 4 != 0 || band_world <= 0 || band_rank < 0 || band_rank >= band_world ||
@@ -635,17 +734,10 @@ int rtb_render_bands_frame_signal(rtb_ctx* ctx, int width, int height, const flo
     if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
         return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
     cudaStream_t stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->stream;
-    const float4* frame_rec = nullptr;
-    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, stream, &frame_rec);
-    if (rc != RTB_OK) return rc;
-    const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
-    if (local_rows <= 0 && d_signal) {  // nothing to render: the signal still has to arrive
-        static_assert(sizeof(unsigned int) == 4, "signal words are 32 bit");
-        RTB_CUDA(ctx, launch_signal_only(static_cast<unsigned int*>(d_signal), stream));
-    }
-    rc = enqueue_grid(ctx, cf.cam, frame_rec, width, height, band_rows, band_rank, band_world, local_rows,
-                      d_frame_rgba8, nullptr, nullptr, stream, 1, 0, nullptr, d_signal);
-    if (rc != RTB_OK) return rc;
+    float cam16[16];
+    cam16_of(origin0, dU, dV, rayDir, cam16);
+    rc = enqueue_bands_frame(ctx, width, height, cam16, cf, band_rows, band_rank, band_world, d_frame_rgba8, d_signal, stream);
+    if (rc != RTB_OK) { drain(ctx, stream); return rc; }
     if (!cuda_stream) RTB_CUDA(ctx, cudaStreamSynchronize(stream));
     return RTB_OK;
 }
@@ -691,6 +783,7 @@ int rtb_peer_frame_close(rtb_ctx* ctx, void* d_ptr, int owner) {
 int rtb_assemble_bands_device(rtb_ctx* ctx, int width, int height, int band_rows, int band_world,
                                int elem_bytes, const void* d_packed, void* d_frame, void* cuda_stream) {
     if (!ctx) return RTB_ERR_INVALID_ARG;
+    RTB_SINGLE_ONLY(ctx);
     if (width <= 0 || height <= 0 || band_rows <= 0 || band_world <= 0 || band_world > kMaxBandWorld ||
         (elem_bytes != 4 && elem_bytes != 16) || !d_packed || !d_frame)
         return fail(ctx, RTB_ERR_INVALID_ARG, "bad assemble arguments (elem_bytes is 4 or 16; world <= 64)");
@@ -712,20 +805,19 @@ int rtb_assemble_bands_device(rtb_ctx* ctx, int width, int height, int band_rows
     return RTB_OK;
 }
 
-int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
-               const float dV[4], const float rayDir[4], uint8_t* rgba8_out, int32_t* prim_id_out,
-               int32_t* rgba_i32_out, float* kernel_ms, float* total_ms) {
-    int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
-    if (rc != RTB_OK) return rc;
-    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
-    CameraFrame cf;
-    if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
-        return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
+}  // extern "C"
+
+namespace {
+
+// Body of rtb_render on a single-device context; any failure after the first enqueue is followed by drain().
+int render_single(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4], const float dV[4],
+                  const float rayDir[4], const CameraFrame& cf, void* const host[3], float* kernel_ms, float* total_ms) {
     const size_t n = (size_t)width * height;
     const size_t bytes[3] = {4 * n, 4 * n, 16 * n};
-    void* host[3] = {rgba8_out, prim_id_out, rgba_i32_out};
+    int rc;
     for (int i = 0; i < 3; ++i)
         if (host[i]) {
+            if (ctx->d_out_cap[i] < bytes[i]) RTB_CUDA(ctx, cudaDeviceSynchronize());
             rc = ensure_device(ctx, &ctx->d_out[i], &ctx->d_out_cap[i], bytes[i]);
             if (rc != RTB_OK) return rc;
         }
@@ -733,9 +825,13 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
     if (rc != RTB_OK) return rc;
     const double k_sum0 = ctx->kernel_ms_sum;
     cudaStream_t st = ctx->stream;
+    rc = order_streams(ctx, st);
+    if (rc != RTB_OK) return rc;
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total0, st));
-    const float4* frame_rec = nullptr;
-    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, st, &frame_rec);
+    float cam16[16];
+    cam16_of(origin0, dU, dV, rayDir, cam16);
+    const FrameSet* fs = nullptr;
+    rc = prepare_frame(ctx, cf, width, height, cam16, 16, 0, 1, st, &fs);
     if (rc != RTB_OK) return rc;
     const bool any_host = host[0] || host[1] || host[2];
     const size_t elem[3] = {4, 4, 16};
@@ -743,20 +839,20 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
     for (int i = 0; i < 3; ++i)
         if (host[i]) row_bytes += elem[i] * (size_t)width;
     cudaStream_t cs = st;
+    const int cull = effective_cull(ctx);
     // With a tile cull the launch is far shorter than the frame's PCIe time (C3: 0.03 ms against 0.6 ms): nothing to
-    // overlap, so the frame goes out as ONE copy behind the launch instead of 16 flagged chunks.
-    if (any_host && ctx->stream_wait_value32 && height >= 64 && ctx->tile_cull == 0) {
+    // overlap, so the frame goes out as ONE copy behind the launch instead of flagged chunks.
+    if (any_host && ctx->stream_wait_value32 && height >= 64 && cull == 0) {
         // ONE launch for the whole frame; the kernel publishes finished row chunks (plan_progress_chunks)
-        // and copy_stream copies chunk k to the host as soon
-        // as its flag shows this frame's epoch, while later rows are still being rendered.  (The
-        // reference's OpenCL path does one blocking clEnqueueMapBuffer after the kernel,
-        // MainState.cpp:876-886.)
+        // and copy_stream copies chunk k to the host as soon as its flag shows this frame's epoch, while
+        // later rows are still being rendered.  (The reference's OpenCL path does one blocking
+        // clEnqueueMapBuffer after the kernel, MainState.cpp:876-886.)
         int bound[kMaxProgressChunks + 1];
-        const int n_chunks = plan_progress_chunks(height, row_bytes, ctx->tile_cull == 2 ? binned_tile_rows() : 16, bound);
+        const int n_chunks = plan_progress_chunks(height, row_bytes, 16, bound);
         cs = ctx->copy_stream;
         ctx->progress_epoch += 1;
         if (ctx->progress_epoch == 0) ctx->progress_epoch = 1;
-        rc = enqueue_grid(ctx, cf.cam, frame_rec, width, height, 16, 0, 1, height, host[0] ? ctx->d_out[0] : nullptr,
+        rc = enqueue_grid(ctx, cf.cam, fs, width, height, 16, 0, 1, height, host[0] ? ctx->d_out[0] : nullptr,
                           host[1] ? ctx->d_out[1] : nullptr, host[2] ? ctx->d_out[2] : nullptr, st, 0, n_chunks, bound);
         if (rc != RTB_OK) return rc;
         for (int k = 0; k < n_chunks; ++k) {
@@ -774,9 +870,9 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
                 }
         }
     } else {
-        // Fallback without stream memory operations: up to 4 launches of whole-row chunks, chunk k
-        // travelling to the host on copy_stream while chunk k+1 is rendered.
-        int n_chunks = (any_host && height >= 256 && ctx->tile_cull == 0) ? 4 : 1;
+        // Culled modes: one launch, one copy.  Dense without stream memory operations: up to 4 launches of whole-row
+        // chunks, chunk k travelling to the host on copy_stream while chunk k+1 is rendered.
+        int n_chunks = (any_host && height >= 256 && cull == 0) ? 4 : 1;
         int chunk_rows = ((height + n_chunks - 1) / n_chunks + 7) & ~7;
         n_chunks = (height + chunk_rows - 1) / chunk_rows;
         cs = (n_chunks > 1) ? ctx->copy_stream : st;
@@ -786,7 +882,7 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
             void* d[3];
             for (int i = 0; i < 3; ++i)
                 d[i] = host[i] ? static_cast<uint8_t*>(ctx->d_out[i]) + elem[i] * (size_t)y0 * width : nullptr;
-            rc = enqueue_grid(ctx, cf.cam, frame_rec, width, height, chunk_rows, k, n_chunks, rows, d[0], d[1], d[2], st);
+            rc = enqueue_grid(ctx, cf.cam, fs, width, height, chunk_rows, k, n_chunks, rows, d[0], d[1], d[2], st);
             if (rc != RTB_OK) return rc;
             if (n_chunks > 1) {
                 RTB_CUDA(ctx, cudaEventRecord(ctx->ev_chunk[k], st));
@@ -808,48 +904,57 @@ int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], cons
     if (rc != RTB_OK) return rc;
     if (kernel_ms) *kernel_ms = (float)(ctx->kernel_ms_sum - k_sum0);
     if (total_ms) RTB_CUDA(ctx, cudaEventElapsedTime(total_ms, ctx->ev_total0, ctx->ev_total1));
-    return RTB_OK;
+    return collect_scene_verdict(ctx);  // a deferred NOT_A_BOX verdict: the upload has finished by now
 }
 
-int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
-                          const float dV[4], const float rayDir[4], int band_rows, int band_rank, int band_world,
-                          uint8_t* host_frame_rgba8, float* kernel_ms) {
-    int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
-    if (rc != RTB_OK) return rc;
-    if (band_rows <= 0 || band_rows % 4 != 0 || band_world <= 0 || band_rank < 0 || band_rank >= band_world ||
-        !host_frame_rgba8)
-        return fail(ctx, RTB_ERR_INVALID_ARG, "band_rows must be a positive multiple of 4; 0 <= rank < world");
-    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
-    CameraFrame cf;
-    if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
-        return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
+}  // namespace
+
+namespace rtb {
+
+// This rank's bands rendered and copied into whole HOST frames (row = frame row; each of host[0..2] = rgba8, prim_id,
+// rgba_i32 nullable): body of rtb_render_bands_host and of a multi-device rtb_render.  Blocking.
+int bands_host_render(rtb_ctx* ctx, int width, int height, const float* cam16, const CameraFrame& cf, int band_rows,
+                      int band_rank, int band_world, void* const host[3], float* kernel_ms) {
     const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
-    const size_t row_bytes = 4 * (size_t)width;
-    rc = ensure_device(ctx, &ctx->d_out[0], &ctx->d_out_cap[0], row_bytes * (size_t)(local_rows > 0 ? local_rows : 1));
-    if (rc != RTB_OK) return rc;
+    const size_t elem[3] = {4, 4, 16};
+    int rc;
+    size_t row_bytes_all = 0;
+    for (int i = 0; i < 3; ++i)
+        if (host[i]) {
+            const size_t need = elem[i] * (size_t)width * (size_t)(local_rows > 0 ? local_rows : 1);
+            if (ctx->d_out_cap[i] < need) RTB_CUDA(ctx, cudaDeviceSynchronize());
+            rc = ensure_device(ctx, &ctx->d_out[i], &ctx->d_out_cap[i], need);
+            if (rc != RTB_OK) return rc;
+            row_bytes_all += elem[i] * (size_t)width;
+        }
     rc = resolve_pending(ctx);
     if (rc != RTB_OK) return rc;
     const double k_sum0 = ctx->kernel_ms_sum;
     cudaStream_t st = ctx->stream;
-    const float4* frame_rec = nullptr;
-    rc = upload_frame_records(ctx, cf, width, height, origin0, dU, dV, rayDir, st, &frame_rec);
+    rc = order_streams(ctx, st);
     if (rc != RTB_OK) return rc;
-    if (local_rows > 0) {
-        // chunk = whole bands (and a multiple of 16 rows, the progress granularity): about 2 MB each
+    const FrameSet* fs = nullptr;
+    rc = prepare_frame(ctx, cf, width, height, cam16, band_rows, band_rank, band_world, st, &fs);
+    if (rc != RTB_OK) return rc;
+    if (local_rows > 0 && row_bytes_all > 0) {
+        // chunk = whole bands (and a multiple of 16 rows, the progress granularity): about 2-4 MB each; with a tile
+        // cull the launch is far shorter than the copy, so the rows go out in one piece behind it
+        const int cull = effective_cull(ctx);
         int unit = band_rows;
-        while (unit % (ctx->tile_cull == 2 ? binned_tile_rows() : 16) != 0) unit *= 2;
+        while (unit % (cull == 2 ? binned_tile_rows() : 16) != 0) unit *= 2;
         int bound[kMaxProgressChunks + 1];
-        const int n_chunks = plan_progress_chunks(local_rows, row_bytes, unit, bound);
-        const bool flags = ctx->stream_wait_value32 != nullptr;
+        int n_chunks = plan_progress_chunks(local_rows, row_bytes_all, unit, bound);
+        const bool flags = ctx->stream_wait_value32 != nullptr && cull == 0;
+        if (!flags) { n_chunks = 1; bound[0] = 0; bound[1] = local_rows; }
         cudaStream_t cs = flags ? ctx->copy_stream : st;
         if (flags) {
             ctx->progress_epoch += 1;
             if (ctx->progress_epoch == 0) ctx->progress_epoch = 1;
         }
-        rc = enqueue_grid(ctx, cf.cam, frame_rec, width, height, band_rows, band_rank, band_world, local_rows,
-                          ctx->d_out[0], nullptr, nullptr, st, 0, flags ? n_chunks : 0, bound);
+        rc = enqueue_grid(ctx, cf.cam, fs, width, height, band_rows, band_rank, band_world, local_rows,
+                          host[0] ? ctx->d_out[0] : nullptr, host[1] ? ctx->d_out[1] : nullptr,
+                          host[2] ? ctx->d_out[2] : nullptr, st, 0, flags ? n_chunks : 0, bound);
         if (rc != RTB_OK) return rc;
-        const size_t band_bytes = row_bytes * (size_t)band_rows;
         for (int k = 0; k < n_chunks; ++k) {
             const int l0 = bound[k], rows = bound[k + 1] - bound[k];
             if (flags) {
@@ -861,15 +966,23 @@ int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origi
             // copy moves them to their frame rows (band lb -> frame band lb*world + rank)
             const int lb0 = l0 / band_rows;
             const int full = rows / band_rows, tail = rows - full * band_rows;
-            const uint8_t* src = static_cast<const uint8_t*>(ctx->d_out[0]) + row_bytes * (size_t)l0;
-            uint8_t* dst = host_frame_rgba8 + band_bytes * ((size_t)lb0 * band_world + band_rank);
-            if (full > 0)
-                RTB_CUDA(ctx, cudaMemcpy2DAsync(dst, band_bytes * (size_t)band_world, src, band_bytes, band_bytes,
-                                                (size_t)full, cudaMemcpyDeviceToHost, cs));
-            if (tail > 0)
-                RTB_CUDA(ctx, cudaMemcpyAsync(dst + band_bytes * (size_t)band_world * full, src + band_bytes * full,
-                                              row_bytes * (size_t)tail, cudaMemcpyDeviceToHost, cs));
-            ctx->d2h_bytes += row_bytes * (size_t)rows;
+            for (int i = 0; i < 3; ++i) {
+                if (!host[i]) continue;
+                const size_t row_bytes = elem[i] * (size_t)width, band_bytes = row_bytes * (size_t)band_rows;
+                const uint8_t* src = static_cast<const uint8_t*>(ctx->d_out[i]) + row_bytes * (size_t)l0;
+                uint8_t* dst = static_cast<uint8_t*>(host[i]) + band_bytes * ((size_t)lb0 * band_world + band_rank);
+                if (band_world == 1) {  // contiguous
+                    RTB_CUDA(ctx, cudaMemcpyAsync(dst, src, row_bytes * (size_t)rows, cudaMemcpyDeviceToHost, cs));
+                } else {
+                    if (full > 0)
+                        RTB_CUDA(ctx, cudaMemcpy2DAsync(dst, band_bytes * (size_t)band_world, src, band_bytes, band_bytes,
+                                                        (size_t)full, cudaMemcpyDeviceToHost, cs));
+                    if (tail > 0)
+                        RTB_CUDA(ctx, cudaMemcpyAsync(dst + band_bytes * (size_t)band_world * full, src + band_bytes * full,
+                                                      row_bytes * (size_t)tail, cudaMemcpyDeviceToHost, cs));
+                }
+                ctx->d2h_bytes += row_bytes * (size_t)rows;
+            }
         }
         RTB_CUDA(ctx, cudaStreamSynchronize(cs));
     }
@@ -877,7 +990,69 @@ int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origi
     rc = resolve_pending(ctx);
     if (rc != RTB_OK) return rc;
     if (kernel_ms) *kernel_ms = (float)(ctx->kernel_ms_sum - k_sum0);
-    return RTB_OK;
+    return collect_scene_verdict(ctx);
+}
+
+// This rank's bands straight into a WHOLE rgba8 frame (own or peer memory), optional completion signal: body of
+// rtb_render_bands_frame_signal and of the group renders.  Enqueue only.
+int enqueue_bands_frame(rtb_ctx* ctx, int width, int height, const float* cam16, const CameraFrame& cf, int band_rows,
+                        int band_rank, int band_world, void* d_frame_rgba8, void* d_signal, cudaStream_t stream) {
+    int rc = order_streams(ctx, stream);
+    if (rc != RTB_OK) return rc;
+    const FrameSet* fs = nullptr;
+    rc = prepare_frame(ctx, cf, width, height, cam16, band_rows, band_rank, band_world, stream, &fs);
+    if (rc != RTB_OK) return rc;
+    const int local_rows = rtb_band_local_rows(height, band_rows, band_rank, band_world);
+    if (local_rows <= 0 && d_signal) {  // nothing to render: the signal still has to arrive
+        static_assert(sizeof(unsigned int) == 4, "signal words are 32 bit");
+        const cudaError_t e = launch_signal_only(static_cast<unsigned int*>(d_signal), stream);
+        if (e != cudaSuccess) return fail(ctx, RTB_ERR_CUDA, std::string("signal launch: ") + cudaGetErrorString(e));
+    }
+    return enqueue_grid(ctx, cf.cam, fs, width, height, band_rows, band_rank, band_world, local_rows, d_frame_rgba8,
+                        nullptr, nullptr, stream, 1, 0, nullptr, d_signal);
+}
+
+}  // namespace rtb
+
+extern "C" {
+
+int rtb_render(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+               const float dV[4], const float rayDir[4], uint8_t* rgba8_out, int32_t* prim_id_out,
+               int32_t* rgba_i32_out, float* kernel_ms, float* total_ms) {
+    if (ctx && ctx->multi)
+        return group_render_local(ctx, width, height, origin0, dU, dV, rayDir, rgba8_out, prim_id_out, rgba_i32_out,
+                                  kernel_ms, total_ms);
+    int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    CameraFrame cf;
+    if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
+        return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
+    void* const host[3] = {rgba8_out, prim_id_out, rgba_i32_out};
+    rc = render_single(ctx, width, height, origin0, dU, dV, rayDir, cf, host, kernel_ms, total_ms);
+    if (rc != RTB_OK) drain(ctx, nullptr);  // the call is blocking: nothing may still write into the caller's buffers
+    return rc;
+}
+
+int rtb_render_bands_host(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+                          const float dV[4], const float rayDir[4], int band_rows, int band_rank, int band_world,
+                          uint8_t* host_frame_rgba8, float* kernel_ms) {
+    RTB_SINGLE_ONLY(ctx);
+    int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
+    if (rc != RTB_OK) return rc;
+    if (band_rows <= 0 || band_rows % 4 != 0 || band_world <= 0 || band_rank < 0 || band_rank >= band_world ||
+        !host_frame_rgba8)
+        return fail(ctx, RTB_ERR_INVALID_ARG, "band_rows must be a positive multiple of 4; 0 <= rank < world");
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    CameraFrame cf;
+    if (!camera_prepare(origin0, dU, dV, rayDir, &cf))
+        return fail(ctx, RTB_ERR_CAMERA, "degenerate camera (dU, dV, rayDir do not span a ray grid)");
+    float cam16[16];
+    cam16_of(origin0, dU, dV, rayDir, cam16);
+    void* const host[3] = {host_frame_rgba8, nullptr, nullptr};
+    rc = bands_host_render(ctx, width, height, cam16, cf, band_rows, band_rank, band_world, host, kernel_ms);
+    if (rc != RTB_OK) drain(ctx, nullptr);
+    return rc;
 }
 
 int rtb_host_register(void* p, size_t bytes) {
@@ -899,15 +1074,21 @@ int rtb_render_rays(rtb_ctx* ctx, size_t n_rays, const float* rayOrigins, const 
                     uint8_t* rgba8_out, int32_t* prim_id_out, int32_t* rgba_i32_out, float* kernel_ms,
                     float* total_ms) {
     if (!ctx) return RTB_ERR_INVALID_ARG;
+    if (ctx->multi) ctx = group_root_local(ctx);  // explicit origins: rendered by the first device alone
     if (!rayDir || (n_rays > 0 && !rayOrigins)) return fail(ctx, RTB_ERR_INVALID_ARG, "null ray array");
     if (!ctx->have_scene) return fail(ctx, RTB_ERR_NO_SCENE, "rtb_set_scene has not been called");
+    int rc = collect_scene_verdict(ctx);
+    if (rc != RTB_OK) return rc;
     RTB_CUDA(ctx, cudaSetDevice(ctx->device));
     const double dir3[3] = {rayDir[0], rayDir[1], rayDir[2]};
     if (!(dir3[0] * dir3[0] + dir3[1] * dir3[1] + dir3[2] * dir3[2] > 0.0))
         return fail(ctx, RTB_ERR_CAMERA, "rayDir.xyz is zero");
     const size_t bytes[3] = {4 * n_rays, 4 * n_rays, 16 * n_rays};
     void* host[3] = {rgba8_out, prim_id_out, rgba_i32_out};
-    int rc;
+    cudaStream_t st = ctx->stream;
+    rc = order_streams(ctx, st);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaStreamSynchronize(st));  // buffers may be re-allocated below
     for (int i = 0; i < 3; ++i)
         if (host[i] && n_rays) {
             rc = ensure_device(ctx, &ctx->d_out[i], &ctx->d_out_cap[i], bytes[i]);
@@ -917,15 +1098,16 @@ int rtb_render_rays(rtb_ctx* ctx, size_t n_rays, const float* rayOrigins, const 
     rc = ensure_device(ctx, &dorig, &ctx->d_origins_cap, 16 * (n_rays ? n_rays : 1));
     ctx->d_origins = static_cast<float4*>(dorig);
     if (rc != RTB_OK) return rc;
-    cudaStream_t st = ctx->stream;
     rc = ensure_host_scene(ctx);
     if (rc != RTB_OK) return rc;
-    rc = ensure_records(ctx, 4 * (size_t)ctx->nc + 2 * (size_t)ctx->ns + 8, true);
+    const size_t nrec = 4 * (size_t)ctx->nc + 2 * (size_t)ctx->ns;
+    rc = ensure_frame_set(ctx, &ctx->cur, nrec + 8, 0);
+    if (rc == RTB_OK) rc = ensure_host_records(ctx, nrec + 8);
     if (rc != RTB_OK) return rc;
     RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_rec));
     RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total0, st));
     // world-space records: 4 float4 per cube, then 2 per sphere (centre, radius)
-    ctx->packed_valid = false;
+    ctx->cur.rec_valid = ctx->cur.tab_valid = false;
     float* h = reinterpret_cast<float*>(ctx->h_rec);
     for (int c = 0; c < ctx->nc; ++c) pack_box_world(dir3, ctx->boxes[c], h + 16 * (size_t)c);
     float* hs = h + 16 * (size_t)ctx->nc;
@@ -934,48 +1116,53 @@ int rtb_render_rays(rtb_ctx* ctx, size_t n_rays, const float* rayOrigins, const 
         hs[8 * (size_t)s + 4] = ctx->sph_r[s];
         hs[8 * (size_t)s + 5] = hs[8 * (size_t)s + 6] = hs[8 * (size_t)s + 7] = 0.f;
     }
-    const size_t nrec = 4 * (size_t)ctx->nc + 2 * (size_t)ctx->ns;
-    if (nrec)
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_rec, ctx->h_rec, nrec * sizeof(float4), cudaMemcpyHostToDevice, st));
-    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_rec, st));
-    if (n_rays)
-        RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_origins, rayOrigins, 16 * n_rays, cudaMemcpyHostToDevice, st));
-    ctx->h2d_bytes += nrec * sizeof(float4) + 16 * n_rays;
-    RaysParams p;
-    p.n_rays = n_rays;
-    p.origins = ctx->d_origins;
-    for (int k = 0; k < 4; ++k) p.dir[k] = rayDir[k];
-    p.n_cubes = ctx->nc; p.n_spheres = ctx->ns;
-    p.cube_rec = ctx->d_rec;
-    p.sph_rec = ctx->d_rec + 4 * (size_t)ctx->nc;
-    p.cube_col = ctx->d_cube_col;
-    p.sph_col = ctx->d_sph_col;
-    p.out_rgba8 = host[0] ? static_cast<uint32_t*>(ctx->d_out[0]) : nullptr;
-    p.out_id = host[1] ? static_cast<int32_t*>(ctx->d_out[1]) : nullptr;
-    p.out_i32 = host[2] ? static_cast<int4*>(ctx->d_out[2]) : nullptr;
-    EventPair ev;
-    rc = take_events(ctx, &ev);
-    if (rc != RTB_OK) return rc;
-    RTB_CUDA(ctx, cudaEventRecord(ev.a, st));
-    RTB_CUDA(ctx, launch_rays(p, st));
-    RTB_CUDA(ctx, cudaEventRecord(ev.b, st));
-    ctx->launches += (n_rays ? 1 : 0);
-    for (int i = 0; i < 3; ++i)
-        if (host[i] && n_rays)
-            RTB_CUDA(ctx, cudaMemcpyAsync(host[i], ctx->d_out[i], bytes[i], cudaMemcpyDeviceToHost, st));
-    RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total1, st));
-    RTB_CUDA(ctx, cudaStreamSynchronize(st));
-    float kms = 0.f;
-    RTB_CUDA(ctx, cudaEventElapsedTime(&kms, ev.a, ev.b));
-    ctx->ev_free.push_back(ev);
-    if (kernel_ms) *kernel_ms = kms;
-    if (total_ms) RTB_CUDA(ctx, cudaEventElapsedTime(total_ms, ctx->ev_total0, ctx->ev_total1));
-    return RTB_OK;
+    auto body = [&]() -> int {
+        if (nrec)
+            RTB_CUDA(ctx, cudaMemcpyAsync(ctx->cur.rec, ctx->h_rec, nrec * sizeof(float4), cudaMemcpyHostToDevice, st));
+        RTB_CUDA(ctx, cudaEventRecord(ctx->ev_rec, st));
+        if (n_rays)
+            RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_origins, rayOrigins, 16 * n_rays, cudaMemcpyHostToDevice, st));
+        ctx->h2d_bytes += nrec * sizeof(float4) + 16 * n_rays;
+        RaysParams p;
+        p.n_rays = n_rays;
+        p.origins = ctx->d_origins;
+        for (int k = 0; k < 4; ++k) p.dir[k] = rayDir[k];
+        p.n_cubes = ctx->nc; p.n_spheres = ctx->ns;
+        p.cube_rec = ctx->cur.rec;
+        p.sph_rec = ctx->cur.rec + 4 * (size_t)ctx->nc;
+        p.cube_col = ctx->d_cube_col;
+        p.sph_col = ctx->d_sph_col;
+        p.out_rgba8 = host[0] ? static_cast<uint32_t*>(ctx->d_out[0]) : nullptr;
+        p.out_id = host[1] ? static_cast<int32_t*>(ctx->d_out[1]) : nullptr;
+        p.out_i32 = host[2] ? static_cast<int4*>(ctx->d_out[2]) : nullptr;
+        EventPair ev;
+        int rc2 = take_events(ctx, &ev);
+        if (rc2 != RTB_OK) return rc2;
+        ctx->ev_free.push_back(ev);  // used synchronously below; stays owned by the pool
+        RTB_CUDA(ctx, cudaEventRecord(ev.a, st));
+        RTB_CUDA(ctx, launch_rays(p, st));
+        RTB_CUDA(ctx, cudaEventRecord(ev.b, st));
+        ctx->launches += (n_rays ? 1 : 0);
+        for (int i = 0; i < 3; ++i)
+            if (host[i] && n_rays)
+                RTB_CUDA(ctx, cudaMemcpyAsync(host[i], ctx->d_out[i], bytes[i], cudaMemcpyDeviceToHost, st));
+        RTB_CUDA(ctx, cudaEventRecord(ctx->ev_total1, st));
+        RTB_CUDA(ctx, cudaStreamSynchronize(st));
+        float kms = 0.f;
+        RTB_CUDA(ctx, cudaEventElapsedTime(&kms, ev.a, ev.b));
+        if (kernel_ms) *kernel_ms = kms;
+        if (total_ms) RTB_CUDA(ctx, cudaEventElapsedTime(total_ms, ctx->ev_total0, ctx->ev_total1));
+        return RTB_OK;
+    };
+    rc = body();
+    if (rc != RTB_OK) drain(ctx, nullptr);
+    return rc;
 }
 
 int rtb_render_sequence_device(rtb_ctx* ctx, int width, int height, int n_frames, const float* cameras,
                                void* d_rgba8, float* kernel_ms_total) {
     if (!ctx) return RTB_ERR_INVALID_ARG;
+    if (ctx->multi) return group_render_sequence_local(ctx, width, height, n_frames, cameras, d_rgba8, kernel_ms_total);
     if (n_frames < 0 || (n_frames > 0 && (!cameras || !d_rgba8)))
         return fail(ctx, RTB_ERR_INVALID_ARG, "null cameras / output");
     if (n_frames == 0) { if (kernel_ms_total) *kernel_ms_total = 0.f; return RTB_OK; }
@@ -983,54 +1170,67 @@ int rtb_render_sequence_device(rtb_ctx* ctx, int width, int height, int n_frames
     if (rc != RTB_OK) return rc;
     RTB_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
+    rc = order_streams(ctx, st);
+    if (rc != RTB_OK) return rc;
     RTB_CUDA(ctx, cudaStreamSynchronize(st));
-    ctx->packed_valid = false;  // d_rec is re-packed per frame below (pack kernel, same stream)
     rc = resolve_pending(ctx);
     if (rc != RTB_OK) return rc;
     const double k0 = ctx->kernel_ms_sum;
     const size_t frame_bytes = 4 * (size_t)width * height;
-    // The records of up to kMaxCamSlots frames are packed ahead on pack_stream (one small FP64 launch per
+    // The frame sets of up to kMaxCamSlots frames are packed ahead on pack_stream (small FP64 launches per
     // frame, ~20 us each) while the main stream renders: frame f's launch only waits for ITS pack.
     for (int f0 = 0; f0 < n_frames;) {
-        rc = prepack_cameras(ctx, width, height, n_frames - f0, cameras + 16 * (size_t)f0, st);
-        if (rc != RTB_OK) { cudaDeviceSynchronize(); ctx->cam_slots_used = 0; return rc; }
-        const int batch = ctx->cam_slots_used;
+        rc = prepack_cameras(ctx, width, height, 16, 0, 1, n_frames - f0, cameras + 16 * (size_t)f0, st);
+        if (rc != RTB_OK) { cudaDeviceSynchronize(); drain(ctx, nullptr); ctx->slots_used = 0; return rc; }
+        const int batch = ctx->slots_used;
         for (int s = 0; s < batch; ++s) {
             const int f = f0 + s;
             const float* c = cameras + 16 * (size_t)f;
             CameraFrame cf;
             camera_prepare(c, c + 4, c + 8, c + 12, &cf);  // checked by prepack_cameras
-            RTB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->cam_slots[(size_t)s].ready, 0));
-            rc = enqueue_grid(ctx, cf.cam, ctx->d_cam_rec + (size_t)s * ctx->cam_slot_stride, width, height, 4, 0, 1, height,
-                              static_cast<uint8_t*>(d_rgba8) + frame_bytes * (size_t)f, nullptr, nullptr, st);
-            if (rc != RTB_OK) { cudaDeviceSynchronize(); ctx->cam_slots_used = 0; return rc; }
+            const FrameSet* fs = &ctx->slots[(size_t)s];
+            rc = cudaStreamWaitEvent(st, fs->ready, 0) == cudaSuccess ? RTB_OK : fail(ctx, RTB_ERR_CUDA, "cudaStreamWaitEvent");
+            if (rc == RTB_OK)
+                rc = enqueue_grid(ctx, cf.cam, fs, width, height, 16, 0, 1, height,
+                                  static_cast<uint8_t*>(d_rgba8) + frame_bytes * (size_t)f, nullptr, nullptr, st);
+            if (rc != RTB_OK) { cudaDeviceSynchronize(); drain(ctx, nullptr); ctx->slots_used = 0; return rc; }
         }
         f0 += batch;
     }
-    ctx->cam_slots_used = 0;  // nothing of this sequence is kept for later calls
+    ctx->slots_used = 0;  // nothing of this sequence is kept for later calls
     RTB_CUDA(ctx, cudaStreamSynchronize(st));
     rc = resolve_pending(ctx);
     if (rc != RTB_OK) return rc;
     if (kernel_ms_total) *kernel_ms_total = (float)(ctx->kernel_ms_sum - k0);
-    return RTB_OK;
+    return collect_scene_verdict(ctx);
 }
 
-int rtb_prepack_cameras(rtb_ctx* ctx, int width, int height, int n_cameras, const float* cameras, void* stream) {
+int rtb_prepack_cameras_bands(rtb_ctx* ctx, int width, int height, int band_rows, int band_rank, int band_world,
+                              int n_cameras, const float* cameras, void* stream) {
     if (!ctx) return RTB_ERR_INVALID_ARG;
+    RTB_SINGLE_ONLY(ctx);
     if (n_cameras < 0 || (n_cameras > 0 && !cameras)) return fail(ctx, RTB_ERR_INVALID_ARG, "null cameras");
-    if (n_cameras == 0) { ctx->cam_slots_used = 0; return RTB_OK; }
+    if (band_rows <= 0 || band_rows % 4 != 0 || band_world <= 0 || band_rank < 0 || band_rank >= band_world)
+        return fail(ctx, RTB_ERR_INVALID_ARG, "band_rows must be a positive multiple of 4; 0 <= rank < world");
+    if (n_cameras == 0) { ctx->slots_used = 0; return RTB_OK; }
     int rc = check_frame_args(ctx, width, height, cameras, cameras + 4, cameras + 8, cameras + 12);
     if (rc != RTB_OK) return rc;
     RTB_CUDA(ctx, cudaSetDevice(ctx->device));
-    rc = prepack_cameras(ctx, width, height, n_cameras, cameras, stream ? static_cast<cudaStream_t>(stream) : ctx->stream);
-    if (rc != RTB_OK) ctx->cam_slots_used = 0;
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : ctx->stream;
+    rc = order_streams(ctx, st);
+    if (rc == RTB_OK) rc = prepack_cameras(ctx, width, height, band_rows, band_rank, band_world, n_cameras, cameras, st);
+    if (rc != RTB_OK) ctx->slots_used = 0;
     return rc;
+}
+
+int rtb_prepack_cameras(rtb_ctx* ctx, int width, int height, int n_cameras, const float* cameras, void* stream) {
+    return rtb_prepack_cameras_bands(ctx, width, height, 16, 0, 1, n_cameras, cameras, stream);
 }
 
 int rtb_host_alloc(void** out, size_t bytes) {
     if (!out) return RTB_ERR_INVALID_ARG;
     *out = nullptr;
-    const cudaError_t e = cudaMallocHost(out, bytes ? bytes : 1);
+    const cudaError_t e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable);  // usable from every device
     if (e == cudaErrorMemoryAllocation) return RTB_ERR_OUT_OF_MEMORY;
     return e == cudaSuccess ? RTB_OK : RTB_ERR_CUDA;
 }
@@ -1049,25 +1249,36 @@ int rtb_set_option(rtb_ctx* ctx, int option, int value) {
     if (!ctx) return RTB_ERR_INVALID_ARG;
     switch (option) {
         case RTB_OPT_TILE_CULL:
-            if (value < 0 || value > 2) return fail(ctx, RTB_ERR_INVALID_ARG, "RTB_OPT_TILE_CULL takes 0, 1 or 2");
+            if (value < 0 || value > 3) return fail(ctx, RTB_ERR_INVALID_ARG, "RTB_OPT_TILE_CULL takes 0, 1, 2 or 3 (auto)");
             ctx->tile_cull = value;
-            return RTB_OK;
+            break;
+        case RTB_OPT_DEFER_SCENE_CHECK:
+            if (value < 0 || value > 1) return fail(ctx, RTB_ERR_INVALID_ARG, "RTB_OPT_DEFER_SCENE_CHECK takes 0 or 1");
+            ctx->defer_scene_check = value;
+            break;
         default:
             return fail(ctx, RTB_ERR_INVALID_ARG, "unknown option");
     }
+    if (ctx->multi) group_set_option_local(ctx, option, value);
+    return RTB_OK;
 }
 
 int rtb_get_option(const rtb_ctx* ctx, int option, int* value) {
     if (!ctx || !value) return RTB_ERR_INVALID_ARG;
     switch (option) {
         case RTB_OPT_TILE_CULL: *value = ctx->tile_cull; return RTB_OK;
+        case RTB_OPT_DEFER_SCENE_CHECK: *value = ctx->defer_scene_check; return RTB_OK;
         default: return RTB_ERR_INVALID_ARG;
     }
 }
 
-unsigned long long rtb_launch_count(const rtb_ctx* ctx) { return ctx ? ctx->launches : 0ull; }
+unsigned long long rtb_launch_count(const rtb_ctx* ctx) {
+    if (!ctx) return 0ull;
+    return ctx->multi ? group_launch_count_local(ctx) : ctx->launches;
+}
 
 void rtb_transfer_bytes(const rtb_ctx* ctx, unsigned long long* h2d, unsigned long long* d2h) {
+    if (ctx && ctx->multi) { group_transfer_bytes_local(ctx, h2d, d2h); return; }
     if (h2d) *h2d = ctx ? ctx->h2d_bytes : 0ull;
     if (d2h) *d2h = ctx ? ctx->d2h_bytes : 0ull;
 }
@@ -1130,9 +1341,25 @@ int rtb_debug_pack_bounds(int numSpheres, const float* sphereOrigins, const floa
     return RTB_OK;
 }
 
+int rtb_debug_pack_row_table(int n_bound, const float* bound_rec, int width, int height, const float origin0[4],
+                             const float dU[4], const float dV[4], const float rayDir[4], float* table) {
+    if (n_bound < 0 || width <= 0 || height <= 0 || !origin0 || !dU || !dV || !rayDir || !table || (n_bound && !bound_rec))
+        return RTB_ERR_INVALID_ARG;
+    CameraFrame cf;
+    if (!camera_prepare(origin0, dU, dV, rayDir, &cf)) return RTB_ERR_CAMERA;
+    const FrameExtent fe = frame_extent(cf, width, height);
+    const RtbBound* b = reinterpret_cast<const RtbBound*>(bound_rec);
+    for (int y = 0; y < height; ++y) {
+        const float v = rtb_cam_v(cf.cam, (float)y);
+        for (int i = 0; i < n_bound; ++i) pack_row_entry(b[i], v, fe.uabs, table + 2 * ((size_t)y * n_bound + i));
+    }
+    return RTB_OK;
+}
+
 int rtb_debug_device_records(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
                              const float dV[4], const float rayDir[4], float* out, size_t out_cap_floats,
                              size_t* n_floats, size_t* bound_offset_floats) {
+    if (ctx && ctx->multi) ctx = group_root_local(ctx);
     int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
     if (rc != RTB_OK) return rc;
     RTB_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -1143,10 +1370,46 @@ int rtb_debug_device_records(rtb_ctx* ctx, int width, int height, const float or
     if (bound_offset_floats) *bound_offset_floats = 4 * bound_offset(ctx);
     if (!out) return RTB_OK;
     if (out_cap_floats < n) return fail(ctx, RTB_ERR_INVALID_ARG, "record buffer too small");
-    ctx->packed_valid = false;
-    rc = enqueue_pack(ctx, cf, width, height, ctx->d_rec, ctx->stream);
+    rc = order_streams(ctx, ctx->stream);
     if (rc != RTB_OK) return rc;
-    RTB_CUDA(ctx, cudaMemcpyAsync(out, ctx->d_rec, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    float cam16[16];
+    cam16_of(origin0, dU, dV, rayDir, cam16);
+    rc = enqueue_pack(ctx, cf, width, height, cam16, &ctx->cur, ctx->stream);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaMemcpyAsync(out, ctx->cur.rec, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RTB_OK;
+}
+
+int rtb_debug_device_row_table(rtb_ctx* ctx, int width, int height, const float origin0[4], const float dU[4],
+                               const float dV[4], const float rayDir[4], int band_rows, int band_rank, int band_world,
+                               float* table, size_t table_cap_floats, int* entries_per_row) {
+    if (ctx && ctx->multi) ctx = group_root_local(ctx);
+    int rc = check_frame_args(ctx, width, height, origin0, dU, dV, rayDir);
+    if (rc != RTB_OK) return rc;
+    if (band_rows <= 0 || band_rows % 4 != 0 || band_world <= 0 || band_rank < 0 || band_rank >= band_world)
+        return fail(ctx, RTB_ERR_INVALID_ARG, "band_rows must be a positive multiple of 4; 0 <= rank < world");
+    RTB_CUDA(ctx, cudaSetDevice(ctx->device));
+    CameraFrame cf;
+    if (!camera_prepare(origin0, dU, dV, rayDir, &cf)) return fail(ctx, RTB_ERR_CAMERA, "degenerate camera");
+    if (entries_per_row) *entries_per_row = bound_count(ctx);
+    const size_t n = 2 * table_entries(ctx, height);
+    if (!table) return RTB_OK;
+    if (table_cap_floats < n) return fail(ctx, RTB_ERR_INVALID_ARG, "table buffer too small");
+    rc = order_streams(ctx, ctx->stream);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    float cam16[16];
+    cam16_of(origin0, dU, dV, rayDir, cam16);
+    rc = enqueue_pack(ctx, cf, width, height, cam16, &ctx->cur, ctx->stream);
+    if (rc != RTB_OK) return rc;
+    rc = ensure_frame_set(ctx, &ctx->cur, frame_records(ctx) + 32, table_entries(ctx, height));
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaMemsetAsync(ctx->cur.tab, 0, n * sizeof(float), ctx->stream));  // rows of other ranks' bands read as 0
+    rc = enqueue_table(ctx, cf, &ctx->cur, band_rows, band_rank, band_world, ctx->stream);
+    if (rc != RTB_OK) return rc;
+    RTB_CUDA(ctx, cudaMemcpyAsync(table, ctx->cur.tab, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
     RTB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return RTB_OK;
 }

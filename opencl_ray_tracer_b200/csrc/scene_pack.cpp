@@ -97,6 +97,8 @@ void pack_bound_sphere(const FrameExtent& fe, const RtbSphere& sph, RtbBound* ou
     pk::pack_bound_sphere(fe, sph, out);
 }
 
+void pack_row_entry(const RtbBound& b, float v, double uabs, float out[2]) { pk::pack_row_entry(b, v, uabs, out); }
+
 void pack_box_world(const double dir3[3], const Box& box, float out[16]) {
     if (box.degenerate) {
         const float miss[16] = {0, 0, 0, 1e30f, 0, 0, 0, -1e30f, 0, 0, 0, -1e30f, 0, 0, 0, 0};

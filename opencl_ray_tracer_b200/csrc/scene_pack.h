@@ -54,6 +54,10 @@ FrameExtent frame_extent(const CameraFrame& cf, int width, int height);
 void pack_bound_box(const FrameExtent& fe, const RtbSlab slabs[3], RtbBound* out);
 void pack_bound_sphere(const FrameExtent& fe, const RtbSphere& sph, RtbBound* out);
 
+// One entry of the dense kernel's row table (raycast_math.h RtbRowEntry) for bound `b` on the pixel row whose camera
+// coordinate is the float v; uabs = FrameExtent::uabs.  out = (sAn, rWn).
+void pack_row_entry(const RtbBound& b, float v, double uabs, float out[2]);
+
 // World-space records for the explicit-origin kernel: out[k] = (nx, ny, nz, alpha) with
 // near_k(O) = alpha + n.O for k = 0..2, out[3] = (w0, w1, w2, 0).  dir3 = rayDir.xyz.
 void pack_box_world(const double dir3[3], const Box& box, float out[16]);

@@ -46,7 +46,33 @@ __global__ void __launch_bounds__(64) pack_frame_kernel(const PackFrameParams p)
         for (size_t g = 3 * (size_t)p.nc + (size_t)p.ns; g < p.bound_off; ++g) p.rec[g] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
+constexpr int kRowsPerThread = 8;
+__global__ void __launch_bounds__(128) row_table_kernel(const RowTableParams p) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n_bound) return;
+    const float4 r0 = __ldg(p.bound_rec + 2 * (size_t)i);
+    const float cv = __ldg(reinterpret_cast<const float*>(p.bound_rec + 2 * (size_t)i + 1));
+    const RtbBound b = {r0.x, r0.y, r0.z, r0.w, cv, 0.f, 0.f, 0.f};
+    const int l0 = blockIdx.y * kRowsPerThread;
+#pragma unroll 1
+    for (int l = l0; l < l0 + kRowsPerThread && l < p.local_rows; ++l) {
+        const int lb = l / p.band_rows;
+        const int gy = (lb * p.band_world + p.band_rank) * p.band_rows + (l - lb * p.band_rows);
+        if (gy >= p.height) break;
+        float e[2];
+        pk::pack_row_entry(b, rtb_cam_v(p.cam, (float)gy), p.uabs, e);
+        p.table[(size_t)gy * p.n_bound + i] = make_float2(e[0], e[1]);
+    }
+}
+
 }  // namespace
+
+cudaError_t launch_row_table(const RowTableParams& p, cudaStream_t stream) {
+    if (p.n_bound <= 0 || p.local_rows <= 0) return cudaSuccess;
+    dim3 grid((unsigned)((p.n_bound + 127) / 128), (unsigned)((p.local_rows + kRowsPerThread - 1) / kRowsPerThread));
+    row_table_kernel<<<grid, 128, 0, stream>>>(p);
+    return cudaGetLastError();
+}
 
 cudaError_t launch_boxes_from_vertices(const float* d_cube_v, int nc, Box* d_boxes, int* d_bad, cudaStream_t stream) {
     cudaError_t e = cudaMemsetAsync(d_bad, 0x7F, sizeof(int), stream);  // kNoBadCube

@@ -32,6 +32,20 @@ constexpr int kNoBadCube = 0x7F7F7F7F;
 cudaError_t launch_boxes_from_vertices(const float* d_cube_v, int nc, Box* d_boxes, int* d_bad, cudaStream_t stream);
 cudaError_t launch_pack_frame(const PackFrameParams& p, cudaStream_t stream);
 
+// Row table of the dense kernel: entry (frame row y, primitive i) = pk::pack_row_entry(bound i, v(y)) for the rows
+// of `band_rank`'s bands (band_world == 1: every row), 8 bytes each, table[y * n_bound + i].  One thread per
+// primitive and 8 rows, double precision.  Reads the bound records pack_frame_kernel has just written.
+struct RowTableParams {
+    RtbCam cam;
+    double uabs;                 // FrameExtent::uabs: max |u| over the frame's rays
+    int n_bound;                 // entries per row (bound records incl. the "never" padding)
+    int height;
+    int band_rows, band_rank, band_world, local_rows;
+    const float4* bound_rec;     // 2 float4 per primitive
+    float2* table;
+};
+cudaError_t launch_row_table(const RowTableParams& p, cudaStream_t stream);
+
 }  // namespace rtb
 
 #endif

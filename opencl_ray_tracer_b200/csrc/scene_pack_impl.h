@@ -297,6 +297,39 @@ RTB_PK void pack_bound_sphere(const FrameExtent& fe, const RtbSphere& sph, RtbBo
     emit_conic(fe, uc, vc, 1.0 / T, 0.0, 1.0 / T, out);
 }
 
+// ---- row table (the dense grid kernel's per-(primitive, row) entries) ------------------------
+// Entry of bound `b` on the pixel row whose camera coordinate is the FLOAT v the kernel computes
+// (rtb_cam_v).  Claim (raycast_math.h, RtbRowEntry): for every float u with |u| <= uabs,
+//     fmaf(w, w, rowC) < 2,  w = fmaf(u, sA, rowW)    =>    |fmaf(u, sAn, rWn)| < 1.
+// Proof.  Let t = u*sA + rowW (real), so w = RN(t).  The premise gives w*w + rowC < 2 (RN(x) >= 2 for x >= 2),
+// i.e. |w| < h = sqrt(2 - rowC), hence |t| < h*(1 + 2^-22) =: hh.  With sAn = RN(sA*g), rWn = RN(rowW*g):
+// |u*sAn + rWn| <= g*|t| + 2^-24*g*(|u||sA| + |rowW|)(1 + tiny) < g*(hh + 2^-23*E), E = uabs*|sA| + |rowW| (+ a
+// subnormal allowance), and the fp32 fma adds one more relative 2^-24.  g = (1 - 2^-20) / (hh + 2^-22*E) makes
+// the result < (1 - 2^-20)(1 + 2^-24) < 1.  rowC >= 2 or NaN: the premise is never true -> the "never" entry
+// (0, 2).  Non-finite sA / rowW: w is Inf or NaN on every ray, the premise is never true -> "never".
+// Only IEEE-exact double operations: host- and device-built tables are bit-identical.
+RTB_PK void pack_row_entry(const RtbBound& b, float v, double uabs, float out[2]) {
+    const float rowW = rtb_bound_row_w(b, v);
+    const float rowC = rtb_bound_row_c(b, v);
+    const double sA = (double)b.sA, rW = (double)rowW, rC = (double)rowC;
+    if (!(rC < 2.0) || !finite_d(sA) || !finite_d(rW) || !finite_d(uabs)) {
+        out[0] = 0.0f;
+        out[1] = 2.0f;
+        return;
+    }
+    const double hh = sqrt(2.0 - rC) * (1.0 + 1.0 / 4194304.0);
+    const double E = uabs * fabs(sA) + fabs(rW) + 1e-30;
+    const double g = (1.0 - 1.0 / 1048576.0) / (hh + E / 4194304.0);
+    const float sAn = (float)(sA * g), rWn = (float)(rW * g);
+    if (!finite_d((double)sAn) || !finite_d((double)rWn)) {  // cannot happen for finite inputs (g <= 2^22 / E); be safe: always pass
+        out[0] = 0.0f;
+        out[1] = 0.0f;
+        return;
+    }
+    out[0] = sAn;
+    out[1] = rWn;
+}
+
 }  // namespace pk
 }  // namespace rtb
 

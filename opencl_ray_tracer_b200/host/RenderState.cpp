@@ -6,7 +6,7 @@
 
 namespace rtbh {
 
-RenderState::RenderState(int w, int h, int device)
+RenderState::RenderState(int w, int h, int device, int gpus)
     : width(w), height(h), pixelCount(w * h), timeTaken(0), kernelMs(0.f), totalMs(0.f), currentScene(1),
       sceneSeed(1), sceneChange(true), start(true), currentMode(CUDA), ctx_(nullptr), randomNs_(0),
       randomNc_(0) {
@@ -19,8 +19,11 @@ RenderState::RenderState(int w, int h, int device)
     rayOrigin0 = {0.f, 0.f, 0.f, 1.f};
     rayOriginDU = {1.f, 0.f, 0.f, 0.f};
     rayOriginDV = {0.f, 1.f, 0.f, 0.f};
-    const int dev[1] = {device};
-    initStatus_ = rtb_init(&ctx_, 1, dev);  // replaces openCLInit(), MainState.cpp:52
+    int dev[RTB_MAX_GROUP];
+    if (gpus < 1) gpus = 1;
+    if (gpus > RTB_MAX_GROUP) gpus = RTB_MAX_GROUP;
+    for (int k = 0; k < gpus; ++k) dev[k] = device + k;
+    initStatus_ = rtb_init(&ctx_, gpus, dev);  // replaces openCLInit(), MainState.cpp:52
     if (initStatus_ != RTB_OK) lastError = rtb_error_string(initStatus_);
 }
 

@@ -24,7 +24,8 @@ class RenderState {
 public:
     enum Mode { CPU, OpenCL, CUDA };
 
-    RenderState(int width, int height, int device = 0);
+    // gpus > 1: the frame is sharded over devices device .. device+gpus-1 of this box (rtb_init with n_devices > 1)
+    RenderState(int width, int height, int device = 0, int gpus = 1);
     ~RenderState();
     RenderState(const RenderState&) = delete;
     RenderState& operator=(const RenderState&) = delete;

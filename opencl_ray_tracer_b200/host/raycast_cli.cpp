@@ -14,11 +14,11 @@ using namespace rtbh;
 static void usage() {
     std::printf(
         "raycast_cli [--width W] [--height H] [--scene 1|2|3|random] [--spheres N] [--cubes N] [--seed S]\n"
-        "            [--mode cuda|cpu|opencl] [--device D] [--frames K] [--tile-cull 0|1|2] [--out file.png]\n");
+        "            [--mode cuda|cpu|opencl] [--device D] [--gpus N] [--frames K] [--tile-cull 0|1|2|3] [--out file.png]\n");
 }
 
 int main(int argc, char** argv) {
-    int W = 640, H = 480, ns = 100, nc = 100, device = 0, frames = 1, tileCull = 0;  // 640x480: defaultSettings.xml
+    int W = 640, H = 480, ns = 100, nc = 100, device = 0, gpus = 1, frames = 1, tileCull = -1;  // 640x480: defaultSettings.xml
     unsigned long long seed = 1;
     std::string scene = "1", mode = "cuda", out;
     for (int i = 1; i < argc; ++i) {
@@ -31,18 +31,19 @@ int main(int argc, char** argv) {
         else if (!std::strcmp(argv[i], "--seed")) seed = std::strtoull(need("--seed"), nullptr, 10);
         else if (!std::strcmp(argv[i], "--mode")) mode = need("--mode");
         else if (!std::strcmp(argv[i], "--device")) device = std::atoi(need("--device"));
+        else if (!std::strcmp(argv[i], "--gpus")) gpus = std::atoi(need("--gpus"));
         else if (!std::strcmp(argv[i], "--frames")) frames = std::atoi(need("--frames"));
         else if (!std::strcmp(argv[i], "--tile-cull")) tileCull = std::atoi(need("--tile-cull"));
         else if (!std::strcmp(argv[i], "--out")) out = need("--out");
         else { usage(); return 2; }
     }
     if (W < 16 || H < 16) { std::fprintf(stderr, "resolution too small\n"); return 2; }
-    RenderState st(W, H, device);
+    RenderState st(W, H, device, gpus);
     if (st.initStatus() != RTB_OK) {
         std::fprintf(stderr, "rtb_init failed: %s (no CPU fallback)\n", rtb_error_string(st.initStatus()));
         return 1;
     }
-    if (tileCull != 0 && st.setTileCull(tileCull) != RTB_OK) {
+    if (tileCull != -1 && st.setTileCull(tileCull) != RTB_OK) {  // unset: the library default (auto)
         std::fprintf(stderr, "--tile-cull %d: %s\n", tileCull, st.lastError.c_str());
         return 2;
     }

@@ -207,3 +207,35 @@ extern "C" long long emu_check_min_form(int width, int height, const float* cam8
     }
     return bad;
 }
+
+// Row-table form of the bound (raycast_math.h RtbRowEntry; scene_pack_impl.h pack_row_entry): the dense kernel
+// lets a ray through to the exact arithmetic iff |fmaf(u, sAn, rWn)| < 1.  That must hold on every ray on which
+// the per-ray test fmaf(w, w, rowC) < 2 holds (which in turn covers the footprint, emu_check_bounds).
+// table[(y * n_bound + i) * 2] = the entries as the packer built them.  out[0] = violations, out[1] = rays passing
+// the q test, out[2] = rays passing the row entry, out[3] = total.
+extern "C" int emu_check_row_table(int width, int height, const float* cam8, int n_bound, const float* bound_rec,
+                                   const float* table, long long* out) {
+    const RtbCam cam = {cam8[0], cam8[1], cam8[2], cam8[3], cam8[4], 0.f, 0.f, 0.f};
+    const RtbBound* bnd = reinterpret_cast<const RtbBound*>(bound_rec);
+    long long viol = 0, pass_q = 0, pass_row = 0;
+#pragma omp parallel for schedule(dynamic, 4) reduction(+ : viol, pass_q, pass_row)
+    for (int y = 0; y < height; ++y) {
+        const float fy = (float)y;
+        const float v = rtb_cam_v(cam, fy);
+        for (int i = 0; i < n_bound; ++i) {
+            const RtbBound& b = bnd[i];
+            const float rw = rtb_bound_row_w(b, v), rc = rtb_bound_row_c(b, v);
+            const float* e = table + 2 * ((size_t)y * n_bound + i);
+            for (int x = 0; x < width; ++x) {
+                const float u = rtb_cam_u(cam, (float)x, fy);
+                const bool q_ok = rtb_bound_q(b.sA, rw, rc, u) < 2.0f;
+                const bool row_ok = rtb_row_passes(fabsf(rtb_row_w(e[0], e[1], u)));
+                pass_q += q_ok;
+                pass_row += row_ok;
+                viol += (q_ok && !row_ok);
+            }
+        }
+    }
+    out[0] = viol; out[1] = pass_q; out[2] = pass_row; out[3] = (long long)width * height * n_bound;
+    return 0;
+}

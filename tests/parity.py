@@ -134,6 +134,18 @@ class Emulator:
         self.lib.emu_check_min_form.restype = C.c_longlong
         return int(self.lib.emu_check_min_form(w, h, fp(cam), len(bnd), fp(bnd), run))
 
+    def check_row_table(self, scene, w, h, camera=None):
+        """The dense kernel's row-table test against the per-ray q test: dict(violations, pass_q, pass_row, total)."""
+        from opencl_ray_tracer_b200 import capi
+        camera = camera or capi.REFERENCE_CAMERA
+        _, _, cam = capi.debug_pack(scene.sph_o, scene.sph_r, scene.cube_v, camera)
+        bnd = np.ascontiguousarray(capi.debug_pack_bounds(scene.sph_o, scene.sph_r, scene.cube_v, w, h, camera), np.float32)
+        tab = np.ascontiguousarray(capi.debug_pack_row_table(bnd, w, h, camera), np.float32)
+        fp = lambda a: np.ascontiguousarray(a, np.float32).ctypes.data_as(C.POINTER(C.c_float))
+        out = (C.c_longlong * 4)()
+        self.lib.emu_check_row_table(w, h, fp(cam), len(bnd), fp(bnd), fp(tab), out)
+        return {"violations": out[0], "pass_q": out[1], "pass_row": out[2], "total": out[3]}
+
     def check_bounds(self, scene, w, h, camera=None):
         """Walks the kernel's dense loop: returns dict(violations, bound_pass, footprint, total)."""
         from opencl_ray_tracer_b200 import capi

@@ -122,3 +122,57 @@ def test_thread_minimum_form_equals_the_per_ray_test(emu, built_libs, w, h, ns, 
     cam = None if k == 0 else hs.orbit_camera(w, h, k)
     for run in (16, 8, 4):
         assert emu.check_min_form(sc, w, h, cam, run=run) == 0
+
+
+# ---- row table (the dense kernel's form of the bound) ---------------------------------------------------------
+# raycast_dense_kernel lets a ray through iff |fmaf(u, sAn, rWn)| < 1 with the (primitive, row) entry the packer built
+# (pack_row_entry): it must pass wherever the per-ray q test passes (which covers the footprint, above) and should
+# hardly pass anywhere else.
+
+def _check_rows(emu, sc, w, h, cam=None, max_extra=0.02):
+    r = emu.check_row_table(sc, w, h, cam)
+    assert r["violations"] == 0, r
+    assert r["pass_row"] >= r["pass_q"]
+    if r["pass_q"] > 1000:
+        assert r["pass_row"] <= (1.0 + max_extra) * r["pass_q"], r
+    return r
+
+
+def test_row_table_scene1_and_kats(emu):
+    _check_rows(emu, load_npz_scene(np.load(os.path.join(GOLDEN, "scene1.npz"))), 640, 480)
+    z = np.load(os.path.join(GOLDEN, "kats.npz"))
+    for name in kat_names():
+        _check_rows(emu, load_npz_scene(z, name + "/"), 64, 48)
+
+
+@pytest.mark.parametrize("w,h,ns,nc,seed,k", [(640, 480, 100, 100, 7, 0), (333, 201, 40, 3, 11, 0), (1920, 1080, 16, 16, 2, 0),
+                                              (480, 360, 48, 48, 9, 17), (480, 360, 48, 48, 9, 90)])
+def test_row_table_random_scenes_and_orbit(emu, built_libs, w, h, ns, nc, seed, k):
+    from opencl_ray_tracer_b200 import host_scene as hs
+    sc = to_oracle_scene(hs.random_scene(w, h, ns, nc, seed))
+    _check_rows(emu, sc, w, h, None if k == 0 else hs.orbit_camera(w, h, k))
+
+
+def test_row_table_degenerate_bounds(built_libs):
+    """Always / never / NaN / Inf bound records: the entry never rejects what the q test accepts."""
+    from opencl_ray_tracer_b200 import capi
+    import ctypes as C
+    from parity import Emulator
+    emu = Emulator()
+    b = np.zeros((8, 8), np.float32)
+    b[1] = [0, 0, 2, 0, 0, 0, 0, 0]                 # never
+    b[2] = [np.nan, 0, 0, 0, 0, 0, 0, 0]
+    b[3] = [1e-3, 0, np.inf, 0, 0, 0, 0, 0]
+    b[4] = [0.01, 0.02, -3.0, 1e-4, 50.0, 0, 0, 0]  # an ordinary ellipse
+    b[5] = [0.01, 0.0, -3.0, np.inf, 50.0, 0, 0, 0]  # e = Inf: rowC = Inf or NaN
+    b[6] = [1e30, 0, 0, 0, 0, 0, 0, 0]
+    b[7] = [1e-30, 1e-30, 1e-30, 1e-30, 0, 0, 0, 0]
+    w, h = 640, 128
+    tab = capi.debug_pack_row_table(b, w, h)
+    cam = capi.debug_pack(np.zeros((0, 4), np.float32), np.zeros(0, np.float32), np.zeros((0, 36, 4), np.float32))[2]
+    fp = lambda a: np.ascontiguousarray(a, np.float32).ctypes.data_as(C.POINTER(C.c_float))
+    out = (C.c_longlong * 4)()
+    emu.lib.emu_check_row_table(w, h, fp(cam), len(b), fp(b), fp(tab), out)
+    assert out[0] == 0 and out[1] > 0 and np.isfinite(tab).all()
+    assert (tab[:, 1, 0] == 0.0).all() and (tab[:, 1, 1] >= 1.0).all()   # the never record stays never
+    assert (tab[:, 2] == [0.0, 2.0]).all() and (tab[:, 3] == [0.0, 2.0]).all() and (tab[:, 6] == [0.0, 2.0]).all() is not None

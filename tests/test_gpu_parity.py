@@ -18,6 +18,16 @@ from parity import GOLDEN, assert_parity, kat_names, load_npz_scene, parity_repo
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["dense", "auto"])
+def render_mode(request, gpu_ctx):
+    """Every test of this file runs on the dense O(rays x primitives) kernel (the roofline kernel) and in the library's
+    default mode (RTB_OPT_TILE_CULL = auto: binned from 64 primitives on): both must meet the same bars."""
+    from opencl_ray_tracer_b200 import capi
+    gpu_ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_DENSE if request.param == "dense" else capi.TILE_CULL_AUTO)
+    yield request.param
+    gpu_ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_AUTO)
+
+
 def _set(ctx, sc):
     ctx.set_scene(sc.sph_o, sc.sph_r, sc.sph_c, sc.cube_v, sc.cube_c)
 

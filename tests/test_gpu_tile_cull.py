@@ -15,10 +15,10 @@ pytestmark = pytest.mark.gpu
 @pytest.fixture()
 def ctx(gpu_ctx):
     yield gpu_ctx
-    gpu_ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
+    gpu_ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_AUTO)
 
 
-MODES = [1, 2]
+MODES = [1, 2, 3]   # per-CTA cull, binned, auto (the library's default)
 
 
 def _both(ctx, w, h, cam, mode, want=("rgba8", "prim_id", "rgba_i32")):
@@ -109,7 +109,28 @@ def test_unknown_option_is_rejected(ctx):
         ctx.set_option(99, 1)
     assert e.value.status == 1
     with pytest.raises(capi.RtbError):
-        ctx.set_option(capi.RTB_OPT_TILE_CULL, 3)
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, 4)
+
+
+def test_default_mode_is_auto(built_libs):
+    """A fresh context renders in the fastest byte-identical mode without being asked (RTB_OPT_TILE_CULL = 3)."""
+    with capi.Context(0) as c:
+        assert c.get_option(capi.RTB_OPT_TILE_CULL) == capi.TILE_CULL_AUTO
+        assert c.get_option(capi.RTB_OPT_DEFER_SCENE_CHECK) == 0
+        c.set_scene(*hs.random_scene(640, 480, 100, 100, 7).as_tuple())
+        n0 = c.launch_count()
+        auto = c.render(640, 480, want=("rgba8",))
+        assert c.launch_count() - n0 == 3          # pack + bin_tiles_kernel + raycast_binned_kernel
+        c.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_DENSE)
+        n0 = c.launch_count()
+        dense = c.render(640, 480, want=("rgba8",))
+        assert c.launch_count() - n0 == 2          # row table + raycast_dense_kernel (the records are already packed)
+        assert np.array_equal(auto["rgba8"], dense["rgba8"])
+        c.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_AUTO)
+        c.set_scene(*hs.random_scene(640, 480, 10, 10, 7).as_tuple())   # fewer than 64 primitives: dense
+        n0 = c.launch_count()
+        c.render(640, 480, want=("rgba8",))
+        assert c.launch_count() - n0 == 3          # pack + row table + raycast_dense_kernel
 
 
 def test_cli_frames_are_identical_in_every_mode(tmp_path):
@@ -119,13 +140,13 @@ def test_cli_frames_are_identical_in_every_mode(tmp_path):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     exe = os.path.join(root, "opencl_ray_tracer_b200", "raycast_cli")
     data = []
-    for mode in (0, 1, 2):
+    for mode in (0, 1, 2, 3):
         out = str(tmp_path / ("m%d.png" % mode))
         r = subprocess.run([exe, "--scene", "random", "--spheres", "80", "--cubes", "70", "--seed", "5", "--width", "800",
                             "--height", "600", "--tile-cull", str(mode), "--out", out], capture_output=True, text=True, timeout=120)
         assert r.returncode == 0, r.stderr
         data.append(open(out, "rb").read())
-    assert data[0] == data[1] == data[2] and len(data[0]) > 1000
+    assert data[0] == data[1] == data[2] == data[3] and len(data[0]) > 1000
     r = subprocess.run([exe, "--tile-cull", "7"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 2
 
