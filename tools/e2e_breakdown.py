@@ -15,7 +15,11 @@ w, h, ns, nc, seed = 3840, 2160, 512, 512, 3
 if "c4" in sys.argv[1:]:
     w, h, ns, nc, seed = 7680, 4320, 2048, 2048, 4
 ctx = capi.Context(0)
-if "binned" in sys.argv[1:]:
+if "defer" in sys.argv[1:]:
+    ctx.set_option(capi.RTB_OPT_DEFER_SCENE_CHECK, 1)
+if "dense" in sys.argv[1:]:
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, 0)
+elif "binned" in sys.argv[1:]:
     ctx.set_option(capi.RTB_OPT_TILE_CULL, 2)
 elif "cull" in sys.argv[1:]:
     ctx.set_option(capi.RTB_OPT_TILE_CULL, 1)
