@@ -252,6 +252,32 @@ int rtb_group_render_host(rtb_group* g, const float origin0[4], const float dU[4
 int rtb_group_prepack(rtb_group* g, int n_cameras, const float* cameras, void* cuda_stream);
 int rtb_group_barrier(rtb_group* g);
 
+/* One frame with NO allocation inside the call (no cudaMalloc / cudaFree / allocating library routine, no context).
+ * This entry point has no counterpart in the reference; it was added for
+ * callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that forbid it.
+ * Inputs and outputs are the CALLER's device buffers on `device` (< 0: the current device): the six scene arrays in
+ * the layout of rtb_set_scene (float4 arrays 16-byte aligned), and any of d_rgba8 / d_prim_id / d_rgba_i32 (nullable,
+ * whole width x height frames).  d_bad_cube (nullable, device int) receives the lowest index of a cube that is not a
+ * box, or 0x7F7F7F7F if every cube is one (the verdict rtb_set_scene returns as RTB_ERR_NOT_A_BOX; reading it is the
+ * caller's business, nothing here waits for the device).  cuda_stream != NULL: the call only enqueues (4 kernels, one
+ * memset, at most one 4-byte copy); NULL: default stream, and the call waits for it.
+ * The binned kernels run (RTB_OPT_TILE_CULL 2: byte-identical to every other mode); their scratch memory -- recovered
+ * boxes, the frame's records, the per-tile primitive words -- is a file-scope static __device__ array of about 0.7 MB
+ * that every GPU which loads the library holds until the process exits.  LIMITS: numSpheres + numCubes <=
+ * RTB_NOALLOC_MAX_PRIMITIVES and ceil(width / 64) * ceil(height / 32) * ceil(primitives / 32) <=
+ * RTB_NOALLOC_MAX_BIN_WORDS (3840 x 2160 at 1024 primitives fits); beyond them the call returns RTB_ERR_INVALID_ARG
+ * with the reason in err.  All calls on a device share the array: calls in one stream are independent (everything
+ * read is rewritten by the call itself), calls that OVERLAP on the GPU (two streams, no event between them) race.
+ * err (nullable, err_cap bytes) receives the detail text of a failure.  (The first call on a device loads the
+ * kernels' code, which the driver may allocate for: make one call before starting a graph capture.) */
+#define RTB_NOALLOC_MAX_PRIMITIVES 1024
+#define RTB_NOALLOC_MAX_BIN_WORDS 131072
+int rtb_render_device_noalloc(int device, int width, int height, const float origin0[4], const float dU[4],
+                              const float dV[4], const float rayDir[4], int numSpheres, const float* d_sphereOrigins,
+                              const float* d_sphereRadius, const float* d_sphereColours, int numCubes,
+                              const float* d_cubeVertices, const float* d_cubeColours, void* d_rgba8, void* d_prim_id,
+                              void* d_rgba_i32, int* d_bad_cube, void* cuda_stream, char* err, size_t err_cap);
+
 /* Pinned host allocations for the e2e path (pageable buffers work too, only slower). */
 int rtb_host_alloc(void** out, size_t bytes);
 void rtb_host_free(void* p);

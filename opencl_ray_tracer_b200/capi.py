@@ -31,7 +31,7 @@ EXPORTED_SYMBOLS = [
     "rtb_peer_frame_signal_offset", "rtb_set_option", "rtb_get_option", "rtb_prepack_cameras",
     "rtb_prepack_cameras_bands", "rtb_debug_pack_row_table", "rtb_debug_device_row_table",
     "rtb_group_join", "rtb_group_leave", "rtb_group_info", "rtb_group_last_error", "rtb_group_render",
-    "rtb_group_render_host", "rtb_group_prepack", "rtb_group_barrier",
+    "rtb_group_render_host", "rtb_group_prepack", "rtb_group_barrier", "rtb_render_device_noalloc",
 ]
 
 RTB_OPT_TILE_CULL = 1
@@ -120,6 +120,8 @@ def load_library(path=None):
     lib.rtb_group_render_host.argtypes = [vp, fp, fp, fp, fp, C.POINTER(vp), fp]
     lib.rtb_group_prepack.argtypes = [vp, C.c_int, fp, vp]
     lib.rtb_group_barrier.argtypes = [vp]
+    lib.rtb_render_device_noalloc.argtypes = [C.c_int, C.c_int, C.c_int, fp, fp, fp, fp, C.c_int, vp, vp, vp, C.c_int, vp, vp,
+                                              vp, vp, vp, vp, vp, C.c_char_p, C.c_size_t]
     if path is None:
         _lib = lib
     return lib
@@ -135,6 +137,25 @@ def _fp(a):
 
 def _vp(a):
     return C.c_void_p(a.ctypes.data) if a is not None else None
+
+
+RTB_NOALLOC_MAX_PRIMITIVES = 1024
+RTB_NOALLOC_MAX_BIN_WORDS = 131072
+
+
+def render_device_noalloc(width, height, camera, ns, d_sph_o, d_sph_r, d_sph_c, nc, d_cube_v, d_cube_c, d_rgba8=0,
+                          d_prim_id=0, d_rgba_i32=0, d_bad_cube=0, stream=0, device=-1):
+    """rtb_render_device_noalloc: every d_* is a device address as an int (torch .data_ptr()); nothing is allocated
+    by the call.  stream = cudaStream_t as int (0: default stream, synchronous)."""
+    lib = load_library()
+    o0, du, dv, d = [_f32(v) for v in camera]
+    err = C.create_string_buffer(512)
+    vpn = lambda a: C.c_void_p(a or None)
+    rc = lib.rtb_render_device_noalloc(device, width, height, _fp(o0), _fp(du), _fp(dv), _fp(d), ns, vpn(d_sph_o),
+                                       vpn(d_sph_r), vpn(d_sph_c), nc, vpn(d_cube_v), vpn(d_cube_c), vpn(d_rgba8),
+                                       vpn(d_prim_id), vpn(d_rgba_i32), vpn(d_bad_cube), vpn(stream), err, len(err))
+    if rc != RTB_OK:
+        raise RtbError(rc, err.value.decode(errors="replace"))
 
 
 # the reference's ray set-up, RayTrace/states/MainState.cpp:37-50
