@@ -26,6 +26,7 @@ sys.path.insert(0, ROOT)
 
 # BASELINE.json configs: name -> (width, height, spheres, cubes, seed)
 WORKLOADS = {
+    "c1": (640, 480, 2, 4, 1),             # the reference's default scene (createScene1) at its window size; `seed` = scene id
     "c2": (1920, 1080, 64, 64, 2),
     "c3": (3840, 2160, 512, 512, 3),       # the roofline point: 4K x 1024 primitives
     "c4": (7680, 4320, 2048, 2048, 4),
@@ -65,8 +66,17 @@ def bench_config(workload, world):
                        "(moving_camera_ms_per_step times the same loop with a new camera every step)"}
 
 
+def make_scene(key):
+    """The workload's scene (host arrays in the reference's layout)."""
+    from opencl_ray_tracer_b200 import host_scene as hs
+    w, h, ns, nc, seed = WORKLOADS[key]
+    return hs.reference_scene(1) if key == "c1" else hs.random_scene(w, h, ns, nc, seed)
+
+
 def workload_name(key):
     w, h, ns, nc, seed = WORKLOADS[key]
+    if key == "c1":
+        return "c1: %dx%d, the reference's default scene (createScene1, MainState.cpp:419-462), reference camera" % (w, h)
     return "%s: %dx%d, %d spheres + %d cubes, createScene3 recipe, seed %d, reference camera" % (key, w, h, ns, nc, seed)
 
 
@@ -196,6 +206,66 @@ def cpu_baseline_port(scene, w, h, target_seconds):
             "tests_per_s": n_rows * w * (scene.ns + scene.nc) / dt}
 
 
+def cpu_faithful_frame(key, scene, w, h, gpu_rgba8):
+    """BASELINE.md s3 `cpu_faithful`: the reference's own ray loop (oracle/_ref: MainState.cpp:941-956 with collide /
+    intersectTri / intersectSphere / Cube compiled from its sources; else the port's faithful mode), ONE thread, the WHOLE
+    frame, timed beside the GPU line; the GPU frame is compared with it.  c1 also goes to PNG: the CPU frame through the
+    reference's lodepng (MainState.cpp:410-417), the GPU frame through the product's writer, both decoded by lodepng."""
+    import tempfile
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from parity import default_origins
+    from oracle.oracle import PortOracle, RefOracle, Scene, ref_available
+    d = np.array([0, 0, -1, -1], np.float32)
+    kind = "reference" if (ref_available() and (key == "c1" or scene.cube_recipes is not None)) else "port"
+    ref = RefOracle() if ref_available() else None
+    if kind == "reference":
+        if key == "c1":
+            ref.build_scene(1)
+        else:
+            ref.clear_scene()
+            for o, r, c in zip(scene.sph_o, scene.sph_r, scene.sph_c):
+                ref.add_sphere(o, r, c)
+            for c, q in zip(scene.cube_c, scene.cube_recipes):   # createScene3's loop body, MainState.cpp:618-638
+                ref.add_cube_ops(c, [("scale", (q[0],) * 3), ("rotate", (0, 0, q[1])), ("rotate", (0, q[2], 0)),
+                                     ("rotate", (q[3], 0, 0)), ("translate", (q[4], q[5], q[6]))])
+        o = default_origins(w, h)
+        t0 = time.perf_counter()
+        rgba = ref.render(o, d, shape=(h, w, 4))
+        dt = time.perf_counter() - t0
+    else:
+        port = PortOracle()
+        t0 = time.perf_counter()
+        rgba = port.render(Scene(*scene.as_tuple()), w, h, faithful=True, threads=1)[0]
+        dt = time.perf_counter() - t0
+    cpu8 = (rgba & 0xFF).astype(np.uint8)
+    diff = np.abs(cpu8[..., :3].astype(np.int32) - gpu_rgba8[..., :3].astype(np.int32))
+    diff = np.minimum(diff, 256 - diff).max(-1)
+    out = {"value": w * h / dt / 1e6, "unit": "Mrays/s", "cores": 1, "kind": kind, "seconds": dt,
+           "sample": "the whole %dx%d frame, 1 thread (the reference is 'Non-Parallel CPU')" % (w, h),
+           "tests_per_s": w * h * (scene.ns + scene.nc) / dt,
+           "gpu_frame_vs_this": {"rgb_within1_frac": float((diff <= 1).mean()), "rgb_exact_frac": float((diff == 0).mean()),
+                                 "pixels_off_by_more": int((diff > 1).sum()), "bar": "tests/parity.py: >= 0.999 within 1, the rest on silhouettes"}}
+    if key == "c1" and ref is not None:
+        from opencl_ray_tracer_b200 import host_scene as hs
+        tmp = tempfile.mkdtemp(prefix="rtb_c1_png_")
+        a, b = os.path.join(tmp, "reference_lodepng.png"), os.path.join(tmp, "product_writer.png")
+        t0 = time.perf_counter()
+        rc = ref.lib.ref_png_encode(a.encode(), np.ascontiguousarray(cpu8).ctypes.data, w, h)
+        t_ref = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        hs.png_write(b, gpu_rgba8)
+        t_own = time.perf_counter() - t0
+        out["png"] = {"what": "CPU frame -> lodepng::encode (the reference's call); GPU frame -> the product's encodePNG; both decoded by lodepng",
+                      "lodepng_rc": int(rc), "lodepng_bytes": os.path.getsize(a), "lodepng_ms": t_ref * 1e3,
+                      "product_bytes": os.path.getsize(b), "product_ms": t_own * 1e3,
+                      "lodepng_file_decodes_to_cpu_frame": bool(np.array_equal(ref.png_decode(a), cpu8)),
+                      "product_file_decodes_to_gpu_frame": bool(np.array_equal(ref.png_decode(b), gpu_rgba8))}
+        for f in (a, b):
+            os.remove(f)
+        os.rmdir(tmp)
+    return out
+
+
 def _setup_dist():
     import torch
     import torch.distributed as dist
@@ -244,7 +314,8 @@ def measure_workload(args, key, ctx, rank, world, local_rank, steps, with_binned
     from opencl_ray_tracer_b200 import capi, host_scene as hs
 
     w, h, ns, nc, seed = WORKLOADS[key]
-    scene = _broadcast_scene(hs.random_scene(w, h, ns, nc, seed), rank, world)
+    scene = _broadcast_scene(make_scene(key), rank, world)
+    ns, nc = scene.ns, scene.nc
     ctx.set_option(capi.RTB_OPT_DEFER_SCENE_CHECK, 0)
     ctx.set_scene(*scene.as_tuple())
     cam = capi.REFERENCE_CAMERA
@@ -386,7 +457,8 @@ def measure_workload(args, key, ctx, rank, world, local_rank, steps, with_binned
         grp.close()
     torch.cuda.set_stream(torch.cuda.default_stream())
     del flush, d_frame
-    return dict(key=key, w=w, h=h, ns=ns, nc=nc, seed=seed, scene=scene, my_rows=my_rows, dense=dense, binned=binned, match=match)
+    return dict(key=key, w=w, h=h, ns=ns, nc=nc, seed=seed, scene=scene, my_rows=my_rows, dense=dense, binned=binned, match=match,
+                host_frame=host_dense)
 
 
 def run_ours(args):
@@ -539,7 +611,11 @@ _REF = {}
 
 def _ref_worker_init(sph_o, sph_r, sph_c, cube_c, recipes, kind):
     from oracle.oracle import PortOracle, RefOracle, Scene
-    if kind == "reference":
+    if kind == "reference" and recipes is None:
+        ref = RefOracle()
+        ref.build_scene(1)             # c1: the reference's own createScene1 (MainState.cpp:419-462)
+        _REF["ref"] = ref
+    elif kind == "reference":
         ref = RefOracle()
         ref.clear_scene()
         for o, r, c in zip(sph_o, sph_r, sph_c):
@@ -598,6 +674,46 @@ def _time_opencl_kernel_on_host(scene, w, h, target_seconds=8.0):
             "sample": "%d of %d rows of the same %dx%d frame, %.1f s" % (len(ys), h, w, h, dt)}
 
 
+class _PlainScene:
+    """Scene arrays of the reference arm (no library of this repo behind them)."""
+
+    def __init__(self, z):
+        self.sph_o, self.sph_r, self.sph_c, self.cube_v, self.cube_c = (z[k] for k in ("sph_o", "sph_r", "sph_c", "cube_v", "cube_c"))
+        self.cube_recipes = z["recipes"] if len(z["recipes"]) == len(self.cube_c) and len(self.cube_c) else None
+        self.ns, self.nc = len(self.sph_r), len(self.cube_c)
+
+    def as_tuple(self):
+        return self.sph_o, self.sph_r, self.sph_c, self.cube_v, self.cube_c
+
+
+def _scene_from_child_process(key):
+    """The workload's scene arrays for the reference arm.  They come from the repo's host mirror (librtb_host.so), which
+    must not be loaded into the process that times the reference: a child python builds them and writes an .npz."""
+    import subprocess
+    import tempfile
+    path = os.path.join(tempfile.mkdtemp(prefix="rtb_ref_scene_"), key + ".npz")
+    code = ("import sys; sys.path.insert(0, %r); import numpy as np, bench; s = bench.make_scene(%r); "
+            "np.savez(%r, sph_o=s.sph_o, sph_r=s.sph_r, sph_c=s.sph_c, cube_v=s.cube_v, cube_c=s.cube_c, "
+            "recipes=(s.cube_recipes if s.cube_recipes is not None else np.zeros((0, 7), np.float32)))" % (ROOT, key, path))
+    subprocess.run([sys.executable, "-c", code], check=True)
+    with np.load(path) as z:
+        sc = _PlainScene({k: z[k] for k in z.files})
+    os.remove(path)
+    return sc
+
+
+def _loaded_libraries(pattern):
+    """Shared objects mapped into this process whose path contains `pattern` (from /proc/self/maps)."""
+    try:
+        return sorted({ln.split()[-1] for ln in open("/proc/self/maps") if pattern in ln and ".so" in ln})
+    except OSError:
+        return []
+
+
+def _ref_worker_libs(_):
+    return _loaded_libraries(ROOT)
+
+
 def run_reference(args):
     """The reference's CPU implementation of the path on this box's host cores: the per-ray code is
     the reference's own (oracle/_ref: MainState::collide / intersectTri / intersectSphere compiled
@@ -606,15 +722,17 @@ def run_reference(args):
     worker process per core, each running the unmodified per-ray loop.  Each step is a bounded
     sample (row segments spread over the frame) sized so that the whole run takes about 90 s."""
     import multiprocessing as mp
-    from opencl_ray_tracer_b200 import host_scene as hs
     from oracle.oracle import ref_available
-    w, h, ns, nc, seed = WORKLOADS[SEQUENCE[args.workload][0] if args.workload in SEQUENCE else args.workload]
-    scene = hs.random_scene(w, h, ns, nc, seed)
-    kind = "reference" if (ref_available() and scene.cube_recipes is not None) else "port"
+    key = SEQUENCE[args.workload][0] if args.workload in SEQUENCE else args.workload
+    w, h = WORKLOADS[key][:2]
+    scene = _scene_from_child_process(key)
+    ns, nc = scene.ns, scene.nc
+    kind = "reference" if (ref_available() and (scene.cube_recipes is not None or key == "c1")) else "port"
     cores = os.cpu_count() or 1
     init = (scene.sph_o, scene.sph_r, scene.sph_c, scene.cube_c, scene.cube_recipes, kind)
     ctxm = mp.get_context("fork")
     with ctxm.Pool(cores, initializer=_ref_worker_init, initargs=init) as pool:
+        worker_libs = sorted({p for libs in pool.map(_ref_worker_libs, range(cores)) for p in libs})
         def step(k, seg_len):
             ys = [int((i + 0.5) * h / cores + 7 * k) % h for i in range(cores)]   # one row per worker, spread
             x0 = (k * seg_len) % max(1, w - seg_len + 1)
@@ -637,16 +755,19 @@ def run_reference(args):
             tot_s += s
     opencl_path = _time_opencl_kernel_on_host(scene, w, h)
     mrays = tot_rays / tot_s / 1e6
-    sample = "%d row segments of %d rays per step (one per worker process, rows spread over the frame), %d steps, of the same %dx%d frame" % (
-        cores, seg_len, args.steps, w, h)
+    sample = ("%d row segments of %d rays per step (one per worker process, rows spread over the frame: a bounded sample, not a "
+              "whole frame), %d steps, of the same %dx%d frame; the reference is single-threaded -- one worker process per host "
+              "core each runs its unmodified per-ray loop, which flatters it by the core count") % (cores, seg_len, args.steps, w, h)
     line = {
         "impl": "reference", "metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot_s * 1e3 / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32 (f64 triangle test)",
         "data": "synthetic",
-        "config": {"workload": (workload_name(args.workload) if args.workload in WORKLOADS else
-                                "%s: frame 0 of the orbit of %s" % (args.workload, workload_name(SEQUENCE[args.workload][0])))},
+        "config": bench_config(args.workload, args.gpus),     # the same dict as our arm's line (the frame and scene are the same;
+                                                              # its parallelism / l2 / records entries describe our arm)
+        "reference_sample_of": (None if args.workload in WORKLOADS else "frame 0 of the orbit"),
         "tests_per_s": mrays * 1e6 * (ns + nc),
+        "libraries_loaded_by_the_workers": worker_libs,
         "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -813,6 +934,8 @@ def main():
             line["c4"] = sub
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_port(m["scene"], m["w"], m["h"], args.cpu_seconds)
+            if args.workload in ("c1", "c2"):   # full-frame single-thread timing of the reference's own loop
+                line["cpu_faithful"] = cpu_faithful_frame(args.workload, m["scene"], m["w"], m["h"], m["host_frame"])
         print(json.dumps(line))
     if world > 1:
         dist.barrier()

@@ -8,7 +8,8 @@
 
 namespace rtbh {
 
-// Valid PNG (8-bit RGBA, filter 0, zlib stream of stored deflate blocks; no compression).
+// 8-bit RGBA PNG: per-scanline adaptive filter (minimum sum of absolute values), zlib stream = one deflate block with
+// the fixed Huffman codes and LZ77 matches from hash chains (32K window).
 unsigned encodePNG(const char* filename, const unsigned char* rgba, unsigned width, unsigned height);
 inline unsigned encodePNG(const char* filename, const std::vector<unsigned char>& imageData, unsigned width,
                           unsigned height) {

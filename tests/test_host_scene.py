@@ -76,8 +76,30 @@ def _png_decode(path):
         pos += 12 + n
     raw = zlib.decompress(idat)
     rows = np.frombuffer(raw, np.uint8).reshape(h, 1 + 4 * w)
-    assert (rows[:, 0] == 0).all()
-    return rows[:, 1:].reshape(h, w, 4)
+    out = np.zeros((h, 4 * w), np.int32)
+    for y in range(h):                      # undo the scanline filters (PNG specification, section 9)
+        f, line = int(rows[y, 0]), rows[y, 1:].astype(np.int32)
+        up = out[y - 1] if y else np.zeros(4 * w, np.int32)
+        cur = out[y]
+        assert 0 <= f <= 4
+        if f == 0:
+            cur[:] = line
+        elif f == 2:
+            cur[:] = (line + up) & 255
+        else:
+            for x in range(4 * w):
+                a = cur[x - 4] if x >= 4 else 0
+                b, c = up[x], (up[x - 4] if x >= 4 else 0)
+                if f == 1:
+                    pred = a
+                elif f == 3:
+                    pred = (a + b) >> 1
+                else:
+                    pp = a + b - c
+                    pa, pb, pc = abs(pp - a), abs(pp - b), abs(pp - c)
+                    pred = a if (pa <= pb and pa <= pc) else (b if pb <= pc else c)
+                cur[x] = (line[x] + pred) & 255
+    return out.astype(np.uint8).reshape(h, w, 4)
 
 
 def test_png_writer_roundtrip(tmp_path, built_libs):
@@ -88,9 +110,34 @@ def test_png_writer_roundtrip(tmp_path, built_libs):
     assert np.array_equal(_png_decode(p), img)
 
 
+def test_png_writer_compresses_a_rendered_frame(tmp_path, port, built_libs):
+    """Scene 1 at 640x480 (1.2 MB of pixels): real deflate, not stored blocks; decodes to the same pixels."""
+    import os
+    from opencl_ray_tracer_b200 import host_scene as hs
+    from parity import to_oracle_scene
+    rgba = port.render(to_oracle_scene(hs.reference_scene(1)), 640, 480)[0]
+    img = (rgba & 0xFF).astype(np.uint8)
+    p = str(tmp_path / "scene1.png")
+    hs.png_write(p, img)
+    assert os.path.getsize(p) < img.nbytes // 20
+    assert np.array_equal(_png_decode(p), img)
+    flat = np.zeros((70, 90, 4), np.uint8)          # long runs: matches of the maximum length, distances of 1 and of a row
+    flat[..., 3] = 255
+    flat[10:40, 20:60, 0] = 200
+    hs.png_write(p, flat)
+    assert np.array_equal(_png_decode(p), flat)
+
+
 def test_png_writer_read_by_reference_lodepng(tmp_path, ref, built_libs):
     from opencl_ray_tracer_b200 import host_scene as hs
     img = np.random.default_rng(1).integers(0, 256, (300, 260, 4), dtype=np.uint8)  # > 65535 B: several stored blocks
     p = str(tmp_path / "b.png")
     hs.png_write(p, img)
     assert np.array_equal(ref.png_decode(p), img)
+    grad = np.zeros((200, 333, 4), np.uint8)      # smooth + flat areas: filters 1-4 and LZ77 matches
+    grad[..., 0] = np.arange(333)[None, :] % 256
+    grad[..., 1] = (np.arange(200)[:, None] * 3) % 256
+    grad[50:120, 40:200, 2] = 77
+    grad[..., 3] = 255
+    hs.png_write(p, grad)
+    assert np.array_equal(ref.png_decode(p), grad)
