@@ -19,6 +19,7 @@
 #include "raycast_kernels.cuh"
 
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 
 namespace rtb {
@@ -322,6 +323,60 @@ __device__ __forceinline__ void shade_and_store(const GridParams& p, PixelState<
     }
 }
 
+// The same for a warp of the 8 x 4 lane layout (dense and cull kernels), called by EVERY lane: when the whole warp lies
+// inside the frame the rgba8 pixels leave as whole 512-byte rows.  A thread's 16 pixels are 64 contiguous bytes, so a
+// per-thread STG.128 writes 32 separate 16-byte pieces per instruction (half sectors, 64 bytes apart); staged through
+// shared memory and read back transposed, one instruction writes 4 rows x 128 contiguous bytes (whole sectors).  For the
+// local L2 this halves the write requests; for a frame in ANOTHER GPU's memory (multi-GPU frames, stores over NVLink)
+// it is the difference between 16-byte and 128-byte write packets.  `stage` = this warp's 4 x 32 uint4 (2 KB).
+template <int PX>
+__device__ __forceinline__ void shade_and_store_warp(const GridParams& p, PixelState<PX>& st, int x0, int lrow, int gy, bool inside,
+                                                     uint4* __restrict__ stage) {
+    static_assert(PX % 4 == 0 && PX <= 16, "the row-staged store handles whole uint4s, at most 4 x 32 of them per warp");
+    constexpr int kRowU4 = 8 * PX / 4;   // uint4 per warp row (8 lanes x PX pixels)
+    const bool full = p.vec_ok && (x0 + PX <= p.width);
+    if (!__all_sync(0xFFFFFFFFu, inside && full && p.out_rgba8 != nullptr && p.out_i32 == nullptr)) {
+        if (inside) shade_and_store<PX>(p, st, x0, lrow, gy);
+        return;
+    }
+    const int lane = threadIdx.x & 31, lx = lane & 7, ly = lane >> 3;
+    int ids[PX];
+#pragma unroll
+    for (int q0 = 0; q0 < PX; q0 += 4) {
+        float4 col[4];
+        uint32_t rgba8[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int q = q0 + i;
+            ids[q] = (st.best[q] == RTB_MISS_T) ? -1 : st.id(q);
+            const float4* src = (ids[q] < p.n_cubes) ? p.cube_col + ids[q] : p.sph_col + (ids[q] - p.n_cubes);
+            col[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ids[q] >= 0) col[i] = __ldg(src);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            int32_t rgba[4];
+            rtb_shade(st.best[q0 + i], col[i].x, col[i].y, col[i].z, rgba);
+            rgba8[i] = rtb_pack_rgba8(rgba);
+        }
+        stage[ly * kRowU4 + lx * (PX / 4) + (q0 >> 2)] = make_uint4(rgba8[0], rgba8[1], rgba8[2], rgba8[3]);
+    }
+    __syncwarp();
+    // the warp's 4 rows are consecutive rows of the output (band_rows is a multiple of 4 and the warp's first row is one)
+    const size_t row0 = (size_t)((p.out_global_rows ? gy : lrow) - ly) * p.width + (size_t)(x0 - lx * PX);
+#pragma unroll
+    for (int r = 0; r < PX / 4; ++r) {
+        const int s = r * 32 + lane, wr = s / kRowU4, c = s - wr * kRowU4;
+        *reinterpret_cast<uint4*>(p.out_rgba8 + row0 + (size_t)wr * p.width + c * 4) = stage[s];
+    }
+    if (p.out_id) {
+        const size_t off = (size_t)(p.out_global_rows ? gy : lrow) * p.width + x0;
+#pragma unroll
+        for (int q = 0; q < PX; q += 4)
+            *reinterpret_cast<int4*>(p.out_id + off + q) = make_int4(ids[q], ids[q + 1], ids[q + 2], ids[q + 3]);
+    }
+}
+
 // ---- completion signals -------------------------------------------------------------------------
 // progress: the launch's rows are cut into chunks [progress_bound[c], progress_bound[c+1]); the last CTA of a chunk
 //   to finish publishes p.progress_epoch in the chunk's flag word, on which the copy stream waits
@@ -413,7 +468,8 @@ __device__ __forceinline__ void dense_group_slow(const GridParams& p, const floa
 // entries of 8 B, cnt a multiple of 8), read as LDS.128 = two primitives, 4 distinct addresses per warp in 4
 // different bank groups.  Groups of 8 primitives share the running minima, one compare and one vote; warp `split`
 // of the S warps of a pixel tile takes groups split, split + S, ...  The next group's entries are requested while
-// the current group is tested.
+// the current group is tested.  (Two groups per trip with the table registers alternating -- no register copies at
+// the end of a trip -- was measured SLOWER: C3 0.5574 -> 0.5663 ms, C4 8.11 -> 8.24 ms.)
 template <int PX, int S>
 __device__ __forceinline__ void dense_chunk(const GridParams& p, const float4* __restrict__ row, int cnt, int first_prim,
                                             int split, float v, PixelState<PX>& st) {
@@ -472,6 +528,7 @@ raycast_dense_kernel(const GridParams p) {
     __shared__ __align__(8) uint64_t full_bar[STAGES];
     __shared__ __align__(8) uint64_t empty_bar[STAGES];
     __shared__ unsigned long long row_src[kTileH];  // entry index of each tile row's first entry in p.row_tab
+    __shared__ __align__(16) uint4 store_stage[kWarps][4 * 32];  // shade_and_store_warp: a warp's rgba8 rows
     float4* tab = reinterpret_cast<float4*>(smem_raw);
 
     const int tid = threadIdx.x;
@@ -487,6 +544,15 @@ raycast_dense_kernel(const GridParams p) {
 
     const int n_pad = p.n_pad;  // entries per table row: a multiple of 8
     const int n_chunks = (n_pad + CHUNK - 1) / CHUNK;
+#ifdef RTB_EXPERIMENTS
+    unsigned long long* trace = p.trace ? p.trace + 4 * ((size_t)blockIdx.y * gridDim.x + blockIdx.x) : nullptr;
+    if (trace && tid == 0) {
+        unsigned long long t; unsigned sm;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+        trace[0] = t; trace[3] = sm;
+    }
+#endif
 
     if (tid < kTileH) {  // the table is indexed by FRAME row; rows past the frame reuse its last row (never stored)
         const int trow = blockIdx.y * kTileH + tid;
@@ -539,6 +605,9 @@ raycast_dense_kernel(const GridParams p) {
     for (int k = 0; k < n_chunks; ++k) {
         const int s = k % STAGES;
         mbar_wait(&full_bar[s], (uint32_t)((k / STAGES) & 1));
+#ifdef RTB_EXPERIMENTS
+        if (trace && tid == 0 && k == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); trace[1] = t; }
+#endif
         const int first = k * CHUNK;
         dense_chunk<PX, S>(p, my_row + s * kStageF4, min(CHUNK, n_pad - first), first, split, v, st);
         __syncwarp();
@@ -584,7 +653,13 @@ raycast_dense_kernel(const GridParams p) {
     }
 
     // ---- nearest-hit shading + stores -------------------------------------------------------
-    if (owner && lrow < p.local_rows && gy < p.height && x0 < p.width) shade_and_store<PX>(p, st, x0, lrow, gy);
+    shade_and_store_warp<PX>(p, st, x0, lrow, gy, owner && lrow < p.local_rows && gy < p.height && x0 < p.width, store_stage[warp]);
+#ifdef RTB_EXPERIMENTS
+    if (trace) {
+        __syncthreads();
+        if (tid == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); trace[2] = t; }
+    }
+#endif
 
     signal_completion(p, kTileH);
 }
@@ -986,9 +1061,9 @@ __global__ void __launch_bounds__(32 * kBinWarps) bin_tiles_kernel(const GridPar
 // the warp is a miss and `st` was never touched: constants only.
 template <int PX>
 __device__ __forceinline__ void store_group(const GridParams& p, size_t px_off, int x, bool full, const uint32_t rgba8[4],
-                                            const int32_t rgba[4][4], const int ids[4]) {
+                                            const int32_t rgba[4][4], const int ids[4], bool with_rgba8 = true) {
     if (full) {
-        if (p.out_rgba8) *reinterpret_cast<uint4*>(p.out_rgba8 + px_off) = make_uint4(rgba8[0], rgba8[1], rgba8[2], rgba8[3]);
+        if (p.out_rgba8 && with_rgba8) *reinterpret_cast<uint4*>(p.out_rgba8 + px_off) = make_uint4(rgba8[0], rgba8[1], rgba8[2], rgba8[3]);
         if (p.out_id) *reinterpret_cast<int4*>(p.out_id + px_off) = make_int4(ids[0], ids[1], ids[2], ids[3]);
         if (p.out_i32) {
 #pragma unroll
@@ -998,7 +1073,7 @@ __device__ __forceinline__ void store_group(const GridParams& p, size_t px_off, 
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             if (x + i < p.width) {
-                if (p.out_rgba8) p.out_rgba8[px_off + i] = rgba8[i];
+                if (p.out_rgba8 && with_rgba8) p.out_rgba8[px_off + i] = rgba8[i];
                 if (p.out_id) p.out_id[px_off + i] = ids[i];
                 if (p.out_i32) {
                     int32_t* o = reinterpret_cast<int32_t*>(p.out_i32) + 4 * (px_off + i);
@@ -1011,21 +1086,47 @@ __device__ __forceinline__ void store_group(const GridParams& p, size_t px_off, 
 
 // Called by EVERY lane of the warp (the per-group vote needs them all); `inside` false = this thread's pixels
 // lie outside the frame or the launch's rows and nothing is stored for it.
-template <int PX>
+// Row-staged rgba8 stores (LX = 2 lanes x 16 rows per warp, `stage` = the warp's 16 x 8 uint4 = 2 KB, nullptr = off):
+// a thread's 16 pixels are 64 contiguous bytes, so its STG.128 per group of four pixels writes, warp-wide, 32 separate
+// 16-byte pieces; with the whole warp inside the frame the groups go to shared memory instead and leave at the end as
+// 4 instructions of 4 rows x 128 contiguous bytes each (whole sectors: half the L2 write requests, and 128-byte
+// instead of 16-byte packets when the frame lives in another GPU's memory).
+template <int PX, int LX>
 __device__ __forceinline__ void shade_store_groups(const GridParams& p, PixelState<PX>& st, bool hit, bool inside, int x0,
-                                                   int lrow, int gy) {
+                                                   int lrow, int gy, uint4* __restrict__ stage) {
     const size_t row_off = (size_t)(p.out_global_rows ? gy : lrow) * p.width + x0;
     const bool full = p.vec_ok && (x0 + PX <= p.width);
     int32_t miss[4];
     rtb_shade(RTB_MISS_T, 0.f, 0.f, 0.f, miss);
     const uint32_t miss8 = rtb_pack_rgba8(miss);
+    const int lane = threadIdx.x & 31, lx = lane % LX, ly = lane / LX;
+    const bool rows = PX == 16 && LX == 2 && stage != nullptr && p.out_rgba8 != nullptr &&
+                      __all_sync(0xFFFFFFFFu, inside && full);
+    // the transposed store of instruction r: this lane writes uint4 (r * 32 + lane) of the warp's 16 rows x 8 uint4
+    auto row_store = [&](int r, const uint4 val) {
+        const int s = r * 32 + lane, wr = s >> 3, c = s & 7;
+        const int l = lrow - ly + wr;                               // local row of warp row wr
+        int orow = l;
+        if (p.out_global_rows) {
+            const int lb = l / p.band_rows;
+            orow = (lb * p.band_world + p.band_rank) * p.band_rows + (l - lb * p.band_rows);
+        }
+        *reinterpret_cast<uint4*>(p.out_rgba8 + (size_t)orow * p.width + (size_t)(x0 - lx * PX) + c * 4) = val;
+    };
     if (!hit) {
         const uint32_t rgba8[4] = {miss8, miss8, miss8, miss8};
         const int ids[4] = {-1, -1, -1, -1};
         int32_t rgba[4][4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) { rgba[i][0] = miss[0]; rgba[i][1] = miss[1]; rgba[i][2] = miss[2]; rgba[i][3] = miss[3]; }
-        if (inside) {
+        if (rows) {
+#pragma unroll
+            for (int r = 0; r < 4; ++r) row_store(r, make_uint4(miss8, miss8, miss8, miss8));
+            if (p.out_id || p.out_i32) {
+#pragma unroll 1
+                for (int q0 = 0; q0 < PX; q0 += 4) store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids, false);
+            }
+        } else if (inside) {
 #pragma unroll 1
             for (int q0 = 0; q0 < PX; q0 += 4) store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids);
         }
@@ -1045,26 +1146,29 @@ __device__ __forceinline__ void shade_store_groups(const GridParams& p, PixelSta
                 ids[i] = -1; rgba8[i] = miss8;
                 rgba[i][0] = miss[0]; rgba[i][1] = miss[1]; rgba[i][2] = miss[2]; rgba[i][3] = miss[3];
             }
-            if (inside) store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids);
+        } else {
 #pragma unroll
-            for (int i = 0; i + 4 < PX; ++i) st.best[i] = st.best[i + 4];
-            continue;
-        }
+            for (int i = 0; i < 4; ++i) {
+                ids[i] = (st.best[i] == RTB_MISS_T) ? -1 : st.id(q0 + i);
+                const float4* src = (ids[i] < p.n_cubes) ? p.cube_col + ids[i] : p.sph_col + (ids[i] - p.n_cubes);
+                col[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (ids[i] >= 0) col[i] = __ldg(src);
+            }
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            ids[i] = (st.best[i] == RTB_MISS_T) ? -1 : st.id(q0 + i);
-            const float4* src = (ids[i] < p.n_cubes) ? p.cube_col + ids[i] : p.sph_col + (ids[i] - p.n_cubes);
-            col[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ids[i] >= 0) col[i] = __ldg(src);
+            for (int i = 0; i < 4; ++i) {
+                rtb_shade(st.best[i], col[i].x, col[i].y, col[i].z, rgba[i]);
+                rgba8[i] = rtb_pack_rgba8(rgba[i]);
+            }
         }
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            rtb_shade(st.best[i], col[i].x, col[i].y, col[i].z, rgba[i]);
-            rgba8[i] = rtb_pack_rgba8(rgba[i]);
-        }
-        if (inside) store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids);
+        if (rows) stage[ly * 8 + lx * 4 + (q0 >> 2)] = make_uint4(rgba8[0], rgba8[1], rgba8[2], rgba8[3]);
+        if (inside) store_group<PX>(p, row_off + q0, x0 + q0, full, rgba8, rgba, ids, !rows);  // rows: rgba8 leaves at the end
 #pragma unroll
         for (int i = 0; i + 4 < PX; ++i) st.best[i] = st.best[i + 4];
+    }
+    if (rows) {
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < 4; ++r) row_store(r, stage[r * 32 + lane]);
     }
 }
 
@@ -1083,6 +1187,7 @@ raycast_binned_kernel(const GridParams p) {
     __shared__ __align__(16) float4 s_rec[kCap][5];  // bound record (2) + exact records (cube 3, sphere 1)
     __shared__ int s_prim[kCap];
     __shared__ int s_wsum[2][kWarps];
+    __shared__ __align__(16) uint4 store_stage[kWarps][16 * 8];  // shade_store_groups: a warp's rgba8 rows (LX = 2)
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -1187,7 +1292,8 @@ raycast_binned_kernel(const GridParams p) {
         }
     }
 
-    shade_store_groups<PX>(p, st, warp_hit, lrow < p.local_rows && gy < p.height && x0 < p.width, x0, lrow, gy);
+    shade_store_groups<PX, LX>(p, st, warp_hit, lrow < p.local_rows && gy < p.height && x0 < p.width, x0, lrow, gy,
+                               LX == 2 ? store_stage[warp] : nullptr);
     signal_completion(p, kTileH);
 }
 
@@ -1248,41 +1354,41 @@ GridLaunchShape shape_of(int width, int local_rows) {
 
 }  // namespace
 
-// Tilings of the dense kernel: rays per thread, warp tiles per CTA (x, y), warps per warp tile (primitive
-// split), and the cost per ray-primitive test relative to the first.
-struct Tiling { int px, wx, wy, split; double cost; };
+// Tilings of the dense kernel: rays per thread, warp tiles per CTA (x, y), warps per warp tile (primitive split).
+// The product uses the first for every launch: 256 x 4 pixels, TWO warps, 8 CTAs per SM.  Measured on C2 / C3 / C4 for one
+// rank's rows at world 1 / 2 / 4 / 8 (profiles/r02_dense_sweep_t3.jsonl, r02_dense_sweep_c2_t3.jsonl) it is the fastest or
+// within 2 % of the fastest everywhere: the work per warp is that of the 4-warp CTA (same table traffic, same loop), in
+// CTAs of half the size, so that a launch of few waves spreads evenly over the SMs (C3 at world 8: 0.0905 ms against
+// 0.0921 for 4-warp CTAs and 0.0954 for the primitive-split variant; C4 at world 8: 1.053 against 1.135 ms).  The CTA
+// timeline (tools/cta_trace.py, profiles/r02_cta_trace_c3.jsonl) shows what is left: CTA lifetimes spread from 35 to
+// 112 us around a median of 71 us (the exact updates behind the votes), so the SMs run dry over the last ~20 us of
+// any launch.  The other tilings exist in the experiments build only (RTB_DENSE_TILING = 1 / 2 / 3).
+struct Tiling { int px, wx, wy, split; };
 static const Tiling kTilings[] = {
-    {16, 2, 2, 1, 1.00},  // 256 x 8 pixels, 4 warps
-    {16, 2, 1, 2, 1.03},  // 256 x 4 pixels, 4 warps, two per warp tile: nearest-hit merge, table rows read by half as many rays
-    {16, 1, 1, 4, 1.06},  // 128 x 4 pixels, 4 warps on one warp tile: short band sets (8-GPU frames), small frames
+    {16, 2, 1, 1},  // 256 x 4 pixels, 2 warps
+#ifdef RTB_EXPERIMENTS
+    {16, 2, 2, 1},  // 256 x 8 pixels, 4 warps (round 1's and v10's CTA)
+    {16, 2, 1, 2},  // 256 x 4 pixels, 4 warps, two per warp tile: nearest-hit merge through shared memory
+    {16, 1, 1, 4},  // 128 x 4 pixels, 4 warps on one warp tile
+    {8, 2, 1, 1},   // 128 x 4 pixels, 2 warps, 8 rays per thread: half the work per CTA
+#endif
 };
 
-// The CTA scheduler spreads a grid evenly over the SMs and a CTA's warps over the 4 schedulers of
-// its SM; a launch lasts about (warps on the fullest scheduler) x (work per warp):
-//   ceil(CTAs / SMs * warps per CTA / 4) * (32 * px / split) * cost.   Pick the tiling minimising it.
 GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count) {
-    GridLaunchShape best;
-    double best_t = 0.0;
-    if (sm_count <= 0) sm_count = 1;
+    (void)sm_count;
+    int pick = 0;
+#ifdef RTB_EXPERIMENTS
     static const int forced = [] { const char* e = std::getenv("RTB_DENSE_TILING"); return e ? std::atoi(e) : -1; }();
-    for (int i = 0; i < (int)(sizeof kTilings / sizeof kTilings[0]); ++i) {
-        const Tiling& t = kTilings[i];
-        const int tw = t.wx * 8 * t.px, th = t.wy * 4;
-        GridLaunchShape s;
-        s.px = t.px; s.wx = t.wx; s.wy = t.wy; s.split = t.split;
-        s.block = dim3(32 * t.wx * t.wy * t.split);
-        s.grid = dim3((width + tw - 1) / tw, (local_rows + th - 1) / th);
-        s.smem = 0;
-        const double ctas = (double)s.grid.x * s.grid.y;
-        const double warps_per_sched = std::ceil(ctas / sm_count * (t.wx * t.wy * t.split) / 4.0 - 1e-9);
-        const double est = warps_per_sched * (32.0 * t.px / t.split) * t.cost;
-        if (i == forced) return s;
-        if (i == 0 || est < best_t * 0.97) {  // 3 % hysteresis in favour of the earlier entry
-            best = s;
-            best_t = est;
-        }
-    }
-    return best;
+    if (forced >= 0 && forced < (int)(sizeof kTilings / sizeof kTilings[0])) pick = forced;
+#endif
+    const Tiling& t = kTilings[pick];
+    const int tw = t.wx * 8 * t.px, th = t.wy * 4;
+    GridLaunchShape s;
+    s.px = t.px; s.wx = t.wx; s.wy = t.wy; s.split = t.split;
+    s.block = dim3(32 * t.wx * t.wy * t.split);
+    s.grid = dim3((width + tw - 1) / tw, (local_rows + th - 1) / th);
+    s.smem = 0;
+    return s;
 }
 
 // Launch of one instantiation: the id columns are dynamic shared memory (PX x threads ints); the opt-in
@@ -1309,6 +1415,17 @@ cudaError_t launch_dense_instance(const GridParams& p, dim3 grid, cudaStream_t s
         if (e != cudaSuccess) return e;
         configured_device = dev;
     }
+#ifdef RTB_EXPERIMENTS
+    // occupancy experiment: RTB_DENSE_EXTRA_SMEM bytes of unused dynamic shared memory per CTA (fewer resident CTAs)
+    static const int extra = [] { const char* x = std::getenv("RTB_DENSE_EXTRA_SMEM"); return x ? std::atoi(x) : 0; }();
+    if (extra > 0) {
+        e = cudaFuncSetAttribute(raycast_dense_kernel<PX, WX, WY, S, STAGES, CHUNK, MINB>,
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, kDyn + extra);
+        if (e != cudaSuccess) return e;
+        raycast_dense_kernel<PX, WX, WY, S, STAGES, CHUNK, MINB><<<grid, dim3(kThreads), kDyn + extra, stream>>>(p);
+        return cudaGetLastError();
+    }
+#endif
     raycast_dense_kernel<PX, WX, WY, S, STAGES, CHUNK, MINB><<<grid, dim3(kThreads), kDyn, stream>>>(p);
     return cudaGetLastError();
 }
@@ -1405,6 +1522,35 @@ static cudaError_t launch_binned(const GridParams& p, cudaStream_t stream) {
     return cudaLaunchKernelEx(&cfg, raycast_binned_kernel<PX, LX, WX, WY, MINB>, p);
 }
 
+#ifdef RTB_EXPERIMENTS
+namespace { unsigned long long* g_trace = nullptr; size_t g_trace_cap = 0; }
+unsigned long long* cta_trace_buffer(size_t ctas) {
+    if (!std::getenv("RTB_CTA_TRACE")) return nullptr;
+    if (g_trace_cap < ctas) {
+        if (g_trace) cudaFree(g_trace);
+        g_trace_cap = ctas;
+        if (cudaMalloc(&g_trace, 32 * ctas) != cudaSuccess) { g_trace = nullptr; g_trace_cap = 0; return nullptr; }
+    }
+    cudaMemset(g_trace, 0, 32 * ctas);
+    return g_trace;
+}
+int cta_trace_dump(size_t ctas) {
+    const char* path = std::getenv("RTB_CTA_TRACE");
+    if (!path || !g_trace) return 0;
+    if (cudaDeviceSynchronize() != cudaSuccess) return 1;
+    unsigned long long* h = new unsigned long long[4 * ctas];
+    cudaMemcpy(h, g_trace, 32 * ctas, cudaMemcpyDeviceToHost);
+    FILE* f = std::fopen(path, "a");
+    if (f) {
+        std::fprintf(f, "launch %zu\n", ctas);
+        for (size_t i = 0; i < ctas; ++i) std::fprintf(f, "%llu %llu %llu %llu\n", h[4 * i], h[4 * i + 1], h[4 * i + 2], h[4 * i + 3]);
+        std::fclose(f);
+    }
+    delete[] h;
+    return 0;
+}
+#endif
+
 cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) {
     if (p.tile_cull == 2) return launch_binned<16, 2, 2, 2, 8>(p, stream);  // 64 registers, 8 CTAs/SM
     if (p.tile_cull) return launch_cull_instance<16, 2, 2, 4>(p, stream);
@@ -1422,9 +1568,22 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) 
     if (p.row_tab == nullptr) return cudaErrorInvalidValue;
     const GridLaunchShape s = grid_launch_shape(p.width, p.local_rows, sm_count);
     if (s.grid.x == 0 || s.grid.y == 0) return cudaSuccess;
-    if (s.split == 1) return launch_dense_instance<16, 2, 2, 1, kDenseStages, kDenseChunk, 4>(p, s.grid, stream);
-    if (s.split == 2) return launch_dense_instance<16, 2, 1, 2, kDenseStages, kDenseChunk, 4>(p, s.grid, stream);
-    return launch_dense_instance<16, 1, 1, 4, kDenseStages, kDenseChunk, 4>(p, s.grid, stream);
+#ifdef RTB_EXPERIMENTS
+    GridParams q = p;
+    const size_t ctas = (size_t)s.grid.x * s.grid.y;
+    const bool traced = std::getenv("RTB_CTA_TRACE") != nullptr;
+    q.trace = traced ? cta_trace_buffer(ctas) : nullptr;
+    cudaError_t e;
+    if (s.px == 8) e = launch_dense_instance<8, 2, 1, 1, kDenseStages, kDenseChunk, 10>(q, s.grid, stream);
+    else if (s.split == 1 && s.wy == 1) e = launch_dense_instance<16, 2, 1, 1, kDenseStages, kDenseChunk, 8>(q, s.grid, stream);
+    else if (s.split == 1) e = launch_dense_instance<16, 2, 2, 1, kDenseStages, kDenseChunk, 4>(q, s.grid, stream);
+    else if (s.split == 2) e = launch_dense_instance<16, 2, 1, 2, kDenseStages, kDenseChunk, 4>(q, s.grid, stream);
+    else e = launch_dense_instance<16, 1, 1, 4, kDenseStages, kDenseChunk, 4>(q, s.grid, stream);
+    if (traced) cta_trace_dump(ctas);
+    return e;
+#else
+    return launch_dense_instance<16, 2, 1, 1, kDenseStages, kDenseChunk, 8>(p, s.grid, stream);
+#endif
 }
 
 cudaError_t launch_rays(const RaysParams& p, cudaStream_t stream) {

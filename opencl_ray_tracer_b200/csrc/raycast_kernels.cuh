@@ -56,7 +56,16 @@ struct GridParams {
     uint32_t* bins;                         // tile_cull == 2: [bin_words][tiles] words, grid_bin_words() of them
     int bin_words;                          // ceil(n_bound / 32)
     RtbCam cam;
+#ifdef RTB_EXPERIMENTS
+    // CTA timeline of the dense kernel (tools/cta_trace.py): 4 words per CTA = globaltimer at CTA start, after the wait
+    // for the first table chunk, at CTA end, and the SM id.  nullptr = off.  Experiments build only.
+    unsigned long long* trace;
+#endif
 };
+#ifdef RTB_EXPERIMENTS
+unsigned long long* cta_trace_buffer(size_t ctas);  // RTB_CTA_TRACE set: a device buffer of 4 words per CTA, else nullptr
+int cta_trace_dump(size_t ctas);                    // after the launch: synchronises and appends the words to $RTB_CTA_TRACE
+#endif
 
 // Explicit-origin ("rays") form: world-space records, one thread per ray.
 struct RaysParams {

@@ -265,6 +265,13 @@ int init_single(rtb_ctx** out, int dev) {
                 ctx->stream_write_value32 = reinterpret_cast<CUresult (*)(CUstream, CUdeviceptr, cuuint32_t, unsigned int)>(fn);
             else
                 (void)cudaGetLastError();
+            fn = nullptr;
+            if (cudaGetDriverEntryPoint("cuStreamBatchMemOp", &fn, cudaEnableDefault, &qr) == cudaSuccess &&
+                qr == cudaDriverEntryPointSuccess && fn)
+                ctx->stream_batch_memop =
+                    reinterpret_cast<CUresult (*)(CUstream, unsigned int, CUstreamBatchMemOpParams*, unsigned int)>(fn);
+            else
+                (void)cudaGetLastError();
         }
     }
     *out = ctx;
@@ -574,6 +581,9 @@ int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const FrameSet* fs, int width,
                  cudaStream_t stream, int out_global_rows, int progress_chunks, const int* progress_bound,
                  void* done_signal) {
     GridParams p;
+#ifdef RTB_EXPERIMENTS
+    p.trace = nullptr;
+#endif
     p.out_global_rows = out_global_rows;
     static const int fence_sys = [] { const char* e = std::getenv("RTB_PROGRESS_FENCE_SYSTEM"); return (e && e[0] == '1') ? 1 : 0; }();
     p.fence_system = fence_sys;

@@ -29,6 +29,7 @@
 #include <chrono>
 #include <condition_variable>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <mutex>
@@ -146,6 +147,8 @@ struct rtb_group {
     unsigned int** d_credit_ptrs = nullptr;                // device copy of credit_at0 (rank 0's device)
     unsigned long long frame_no[RTB_MAX_GROUP] = {0};      // frames enqueued so far by rank r
     unsigned long long host_frame_no = 0;
+    cudaStream_t release_stream = nullptr;                 // rank 0: credits are written off the frame's stream
+    cudaEvent_t ev_release = nullptr;
     // process group
     std::string shm_name, host_name;
     GroupShm* shm = nullptr;
@@ -198,8 +201,17 @@ int group_enqueue_rank(rtb_group* g, int r, const float* cam16, const CameraFram
     if (r == 0) {
         // rank 0 is done with frame f-1 (whatever the caller enqueued on this stream since the last call has run
         // by the time this kernel does): hand its slot back to the ranks
+        // -- on a side stream behind an event of this one: the frame's stream does not spend a launch on it
         if (f > 0 && g->world > 1) {
-            release_credits_kernel<<<1, 32, 0, stream>>>(g->d_credit_ptrs, g->world, (unsigned int)f);
+            if (!g->release_stream) {
+                int lo = 0, hi = 0;
+                RTB_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+                RTB_CUDA(ctx, cudaStreamCreateWithPriority(&g->release_stream, cudaStreamNonBlocking, hi));
+                RTB_CUDA(ctx, cudaEventCreateWithFlags(&g->ev_release, cudaEventDisableTiming));
+            }
+            RTB_CUDA(ctx, cudaEventRecord(g->ev_release, stream));
+            RTB_CUDA(ctx, cudaStreamWaitEvent(g->release_stream, g->ev_release, 0));
+            release_credits_kernel<<<1, 32, 0, g->release_stream>>>(g->d_credit_ptrs, g->world, (unsigned int)f);
             RTB_CUDA(ctx, cudaGetLastError());
             ctx->launches += 1;
         }
@@ -210,11 +222,38 @@ int group_enqueue_rank(rtb_group* g, int r, const float* cam16, const CameraFram
             CUDA_SUCCESS)
             return fail(ctx, RTB_ERR_CUDA, "cuStreamWaitValue32 (credit) failed");
     }
+    // "this rank's bands of frame f have landed": a stream write of the rank's done word (in rank 0's memory) behind the
+    // launch -- the word is written once the kernel and its stores have completed, and the launch carries no fences.
+    // RTB_GROUP_STREAM_SIGNAL=0 (or no stream memory operations): the launch's last CTA bumps the word itself, behind a
+    // system-scope fence per CTA.  Measured on C3 at 2 GPUs: rank 1's kernel 0.3048 ms against 0.3183 ms with the
+    // in-kernel signal (binned frame: 0.0405 against 0.0511 ms); the step, which pays ~4 us for the stream write,
+    // 0.3181 against 0.3275 ms (profiles/r02_ab_signal_n2.txt).
+    static const bool stream_signal = [] { const char* e = std::getenv("RTB_GROUP_STREAM_SIGNAL"); return !(e && e[0] == '0'); }();
+    const bool by_stream = stream_signal && ctx->stream_write_value32 != nullptr && r != 0;
     rc = enqueue_bands_frame(ctx, g->width, g->height, cam16, cf, g->band_rows, r, g->world, frame,
-                             r == 0 ? nullptr : done_word(g, r, r), stream);
+                             (r == 0 || by_stream) ? nullptr : done_word(g, r, r), stream);
     if (rc != RTB_OK) return rc;
+    if (by_stream && ctx->stream_write_value32(stream, reinterpret_cast<CUdeviceptr>(done_word(g, r, r)), (unsigned int)(f + 1ull),
+                                               CU_STREAM_WRITE_VALUE_DEFAULT) != CUDA_SUCCESS)
+        return fail(ctx, RTB_ERR_CUDA, "cuStreamWriteValue32 (done) failed");
     if (r == 0) {
-        for (int q = 1; q < g->world; ++q)  // every other rank's bands of frame f have landed in rank 0's memory
+        // every other rank's bands of frame f have landed in rank 0's memory: one wait per rank's done word, submitted
+        // as ONE batch (a stream wait costs 2-4 us of the stream's time each when issued on its own: 7 of them were
+        // 26 us of an 8-GPU frame's 123 us); RTB_GROUP_BATCH_WAIT=0 or no cuStreamBatchMemOp: one call per word
+        static const bool batch = [] { const char* e = std::getenv("RTB_GROUP_BATCH_WAIT"); return !(e && e[0] == '0'); }();
+        bool done = false;
+        if (batch && ctx->stream_batch_memop && g->world > 2) {
+            CUstreamBatchMemOpParams ops[RTB_MAX_GROUP];
+            std::memset(ops, 0, sizeof ops);
+            for (int q = 1; q < g->world; ++q) {
+                ops[q - 1].waitValue.operation = CU_STREAM_MEM_OP_WAIT_VALUE_32;
+                ops[q - 1].waitValue.address = reinterpret_cast<CUdeviceptr>(done_word(g, 0, q));
+                ops[q - 1].waitValue.value = (cuuint32_t)(f + 1ull);
+                ops[q - 1].waitValue.flags = CU_STREAM_WAIT_VALUE_GEQ;
+            }
+            done = ctx->stream_batch_memop(stream, (unsigned int)(g->world - 1), ops, 0) == CUDA_SUCCESS;
+        }
+        for (int q = 1; q < g->world && !done; ++q)
             if (ctx->stream_wait_value32(stream, reinterpret_cast<CUdeviceptr>(done_word(g, 0, q)), (unsigned int)(f + 1ull),
                                          CU_STREAM_WAIT_VALUE_GEQ) != CUDA_SUCCESS)
                 return fail(ctx, RTB_ERR_CUDA, "cuStreamWaitValue32 (done) failed");
@@ -568,6 +607,11 @@ int rtb_group_leave(rtb_group* g) {
     if (g->host_frame) {
         if (g->host_registered) cudaHostUnregister(g->host_frame);
         munmap(g->host_frame, g->host_frame_bytes);
+    }
+    if (g->release_stream) {
+        cudaStreamSynchronize(g->release_stream);
+        cudaStreamDestroy(g->release_stream);
+        cudaEventDestroy(g->ev_release);
     }
     if (g->rank == 0) {
         for (int r = 1; r < g->world; ++r)

@@ -48,6 +48,7 @@ struct rtb_ctx {
     unsigned int progress_epoch = 0;
     CUresult (*stream_wait_value32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int) = nullptr;
     CUresult (*stream_write_value32)(CUstream, CUdeviceptr, cuuint32_t, unsigned int) = nullptr;
+    CUresult (*stream_batch_memop)(CUstream, unsigned int, CUstreamBatchMemOpParams*, unsigned int) = nullptr;
     std::string last_error;
 
     // scene: resident on the device in the reference's layout + the boxes recovered from the cubes

@@ -2,7 +2,7 @@
 (what each GPU of an N-GPU job executes per frame), L2 flushed between launches, for the tilings behind
 RTB_DENSE_TILING (-1 = the cost model's pick) and -- with librtb_exp.so (RTB_BUILD_EXP=1 build.sh) -- the round-1
 kernel behind RTB_GRID_VARIANT.  One process per configuration; every frame is hashed so that tilings can be compared.
-  python tools/dense_sweep.py [--workloads c3,c4,c2] [--tilings -1,0,1,2] [--old 10,20]"""
+  python tools/dense_sweep.py [--workloads c3,c4,c2] [--tilings 0,1,2,3]  (experiments build: 0 = the product's 2-warp CTA, 1 = 4-warp, 2 = split 2, 3 = split 4) [--old 10,20]"""
 import argparse
 import hashlib
 import json
@@ -63,8 +63,9 @@ if __name__ == "__main__":
     if a.child:
         child(a.workloads.split(","), [int(x) for x in a.worlds.split(",")])
     else:
-        runs = [dict(RTB_DENSE_TILING=t) for t in a.tilings.split(",") if t]
         exp = os.path.join(ROOT, "opencl_ray_tracer_b200", "librtb_exp.so")
+        # the product has ONE tiling (0); the others are compiled into the experiments build only
+        runs = [dict(RTB_DENSE_TILING=t, **({} if t in ("-1", "0") else {"RTB_LIB": exp})) for t in a.tilings.split(",") if t]
         runs += [dict(RTB_GRID_VARIANT=v, RTB_LIB=exp) for v in a.old.split(",") if v]
         runs += [dict(RTB_LIB=os.path.join(ROOT, "opencl_ray_tracer_b200", "librtb_%s.so" % n)) for n in a.libs.split(",") if n]
         for env in runs:
