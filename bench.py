@@ -489,7 +489,8 @@ def run_ours(args):
 
 def run_sequence(args):
     """BASELINE config 5: the 120-frame orbiting-camera sequence at C3's size.  One step = the whole
-    sequence, frames device-resident (N = 1: rtb_render_sequence_device; N > 1: every frame sharded as
+    sequence, frames device-resident (N = 1: rtb_render_sequence_device, consecutive frames on two alternating
+    streams of the context so that a frame's ragged end overlaps the next frame's start; N > 1: every frame sharded as
     row bands, every rank's kernels storing into rank 0's sequence buffer over NVLink, ONE fence at the
     end).  e2e = every frame delivered into a pinned / shared host frame (rtb_render, rtb_render_bands_host)."""
     import torch
@@ -564,6 +565,7 @@ def run_sequence(args):
         device_step()
         binned_s = timed(device_step, steps) / steps
         ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_DENSE)
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_AUTO)   # e2e: the library's default options, as in the single-frame lines
     e2e_step()
     e2e_steps = max(1, steps // 4)
     h2d0, d2h0 = ctx.transfer_bytes()
@@ -598,7 +600,7 @@ def run_sequence(args):
                     "frames_per_s": n_frames * e2e_steps / e2e_s,
                     "h2d_bytes_per_step": float(tb[0].item()) / e2e_steps, "d2h_bytes_per_step": float(tb[1].item()) / e2e_steps,
                     "ms_per_step": e2e_s * 1e3 / e2e_steps,
-                    "what": "every frame rendered and delivered into a pinned (N = 1) / shared page-locked (N > 1) host frame; the scene stays resident, the step's input is the camera sequence"},
+                    "what": "every frame rendered with the library's default options (RTB_OPT_TILE_CULL = auto) and delivered into a pinned (N = 1) / shared page-locked (N > 1) host frame by one blocking call per frame; the scene stays resident, the step's input is the camera sequence"},
             "gpu_launches": launches,
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None,
                          "traffic": None, "kernel": "raycast_dense_kernel", "kernel_ms": k_avg_ms, "kernel_launches_timed": k_n,

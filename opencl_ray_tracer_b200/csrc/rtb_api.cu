@@ -187,6 +187,10 @@ void rtb_shutdown(rtb_ctx* ctx) {
     cudaFree(ctx->d_bad);
     cudaFree(ctx->d_progress);
     cudaFree(ctx->d_bins);
+    cudaFree(ctx->d_bins_seq);
+    if (ctx->seq_stream) cudaStreamDestroy(ctx->seq_stream);
+    if (ctx->ev_seq_fork) cudaEventDestroy(ctx->ev_seq_fork);
+    if (ctx->ev_seq_join) cudaEventDestroy(ctx->ev_seq_join);
     if (ctx->pack_stream) cudaStreamDestroy(ctx->pack_stream);
     if (ctx->ev_prepack) cudaEventDestroy(ctx->ev_prepack);
     if (ctx->h_bad) cudaFreeHost(ctx->h_bad);
@@ -579,7 +583,7 @@ int plan_progress_chunks(int rows, size_t row_bytes, int unit, int bound[kMaxPro
 int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const FrameSet* fs, int width, int height, int band_rows,
                  int band_rank, int band_world, int local_rows, void* d_rgba8, void* d_id, void* d_i32,
                  cudaStream_t stream, int out_global_rows, int progress_chunks, const int* progress_bound,
-                 void* done_signal) {
+                 void* done_signal, int bins_lane) {
     GridParams p;
 #ifdef RTB_EXPERIMENTS
     p.trace = nullptr;
@@ -593,10 +597,12 @@ int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const FrameSet* fs, int width,
     if (p.tile_cull == 2) {
         const int n_bound = bound_count(ctx);
         const size_t words = grid_bin_words(width, local_rows, n_bound);
-        if (ctx->d_bins_cap < (words ? words : 1) * sizeof(uint32_t)) RTB_CUDA(ctx, cudaDeviceSynchronize());  // an earlier launch may read the old buffer
-        const int rc = ensure_device(ctx, &ctx->d_bins, &ctx->d_bins_cap, (words ? words : 1) * sizeof(uint32_t));
+        void** bins = bins_lane ? &ctx->d_bins_seq : &ctx->d_bins;
+        size_t* bins_cap = bins_lane ? &ctx->d_bins_seq_cap : &ctx->d_bins_cap;
+        if (*bins_cap < (words ? words : 1) * sizeof(uint32_t)) RTB_CUDA(ctx, cudaDeviceSynchronize());  // an earlier launch may read the old buffer
+        const int rc = ensure_device(ctx, bins, bins_cap, (words ? words : 1) * sizeof(uint32_t));
         if (rc != RTB_OK) return rc;
-        p.bins = static_cast<uint32_t*>(ctx->d_bins);
+        p.bins = static_cast<uint32_t*>(*bins);
         p.bin_words = (n_bound + 31) / 32;
     }
     p.done_counter = ctx->d_progress + 2 * kMaxProgressChunks;
@@ -1188,22 +1194,42 @@ int rtb_render_sequence_device(rtb_ctx* ctx, int width, int height, int n_frames
     const double k0 = ctx->kernel_ms_sum;
     const size_t frame_bytes = 4 * (size_t)width * height;
     // The frame sets of up to kMaxCamSlots frames are packed ahead on pack_stream (small FP64 launches per
-    // frame, ~20 us each) while the main stream renders: frame f's launch only waits for ITS pack.
+    // frame, ~20 us each) while the frames render: frame f's launch only waits for ITS pack.  Consecutive frames go
+    // to alternating lanes (the context's stream / seq_stream, each with its own bin words): frames are independent,
+    // so the next frame's first CTAs run in the SMs the current frame's ragged end leaves idle, and a binned frame's
+    // bin launch overlaps the previous frame's render (RTB_SEQ_LANES=1: one lane, as before).
+    static const bool two_lanes = [] { const char* e = std::getenv("RTB_SEQ_LANES"); return !(e && e[0] == '1'); }();
+    if (two_lanes && !ctx->seq_stream) {
+        RTB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->seq_stream, cudaStreamNonBlocking));
+        RTB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_seq_fork, cudaEventDisableTiming));
+        RTB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_seq_join, cudaEventDisableTiming));
+    }
     for (int f0 = 0; f0 < n_frames;) {
         rc = prepack_cameras(ctx, width, height, 16, 0, 1, n_frames - f0, cameras + 16 * (size_t)f0, st);
         if (rc != RTB_OK) { cudaDeviceSynchronize(); drain(ctx, nullptr); ctx->slots_used = 0; return rc; }
         const int batch = ctx->slots_used;
+        if (two_lanes) {  // lane 1 starts behind whatever the context's stream holds
+            RTB_CUDA(ctx, cudaEventRecord(ctx->ev_seq_fork, st));
+            RTB_CUDA(ctx, cudaStreamWaitEvent(ctx->seq_stream, ctx->ev_seq_fork, 0));
+        }
         for (int s = 0; s < batch; ++s) {
             const int f = f0 + s;
             const float* c = cameras + 16 * (size_t)f;
             CameraFrame cf;
             camera_prepare(c, c + 4, c + 8, c + 12, &cf);  // checked by prepack_cameras
             const FrameSet* fs = &ctx->slots[(size_t)s];
-            rc = cudaStreamWaitEvent(st, fs->ready, 0) == cudaSuccess ? RTB_OK : fail(ctx, RTB_ERR_CUDA, "cudaStreamWaitEvent");
+            const int lane = two_lanes ? (f & 1) : 0;
+            cudaStream_t ls = lane ? ctx->seq_stream : st;
+            rc = cudaStreamWaitEvent(ls, fs->ready, 0) == cudaSuccess ? RTB_OK : fail(ctx, RTB_ERR_CUDA, "cudaStreamWaitEvent");
             if (rc == RTB_OK)
                 rc = enqueue_grid(ctx, cf.cam, fs, width, height, 16, 0, 1, height,
-                                  static_cast<uint8_t*>(d_rgba8) + frame_bytes * (size_t)f, nullptr, nullptr, st);
+                                  static_cast<uint8_t*>(d_rgba8) + frame_bytes * (size_t)f, nullptr, nullptr, ls, 0, 0, nullptr,
+                                  nullptr, lane);
             if (rc != RTB_OK) { cudaDeviceSynchronize(); drain(ctx, nullptr); ctx->slots_used = 0; return rc; }
+        }
+        if (two_lanes) {  // the next batch's packs (and the caller) see both lanes through the context's stream
+            RTB_CUDA(ctx, cudaEventRecord(ctx->ev_seq_join, ctx->seq_stream));
+            RTB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_seq_join, 0));
         }
         f0 += batch;
     }

@@ -101,6 +101,13 @@ struct rtb_ctx {
     int tile_cull = 3;             // RTB_OPT_TILE_CULL (3 = auto)
     void* d_bins = nullptr;        // binned mode: per-tile primitive bit words of the launch in flight, grow-only
     size_t d_bins_cap = 0;
+    // rtb_render_sequence_device renders consecutive frames on alternating lanes (lane 0 = the context's stream and
+    // d_bins; lane 1 = seq_stream and its own bin words), so that a frame's ragged end / second launch overlaps the
+    // next frame's start.
+    cudaStream_t seq_stream = nullptr;
+    cudaEvent_t ev_seq_fork = nullptr, ev_seq_join = nullptr;
+    void* d_bins_seq = nullptr;
+    size_t d_bins_seq_cap = 0;
     // Frame sets packed ahead of their frames (rtb_prepack_cameras, rtb_render_sequence_device) on pack_stream.
     std::vector<FrameSet> slots;   // buffers and events are created once and reused
     int slots_used = 0;
@@ -141,7 +148,7 @@ int prepare_frame(rtb_ctx* ctx, const CameraFrame& cf, int width, int height, co
 int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const FrameSet* fs, int width, int height, int band_rows,
                  int band_rank, int band_world, int local_rows, void* d_rgba8, void* d_id, void* d_i32,
                  cudaStream_t stream, int out_global_rows = 0, int progress_chunks = 0,
-                 const int* progress_bound = nullptr, void* done_signal = nullptr);
+                 const int* progress_bound = nullptr, void* done_signal = nullptr, int bins_lane = 0);
 int bands_host_render(rtb_ctx* ctx, int width, int height, const float* cam16, const CameraFrame& cf, int band_rows,
                       int band_rank, int band_world, void* const host[3], float* kernel_ms);
 int enqueue_bands_frame(rtb_ctx* ctx, int width, int height, const float* cam16, const CameraFrame& cf, int band_rows,
