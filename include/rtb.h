@@ -223,13 +223,15 @@ int rtb_prepack_cameras_bands(rtb_ctx* ctx, int width, int height, int band_rows
  * The ranks of a job (all on one box) meet in a POSIX shared-memory control block called `name` (any string unique
  * to the job; rank 0 creates it).  Rank 0 owns a ring of `slots` frame slots in its device memory, mapped into every
  * rank (CUDA IPC).  rtb_group_render enqueues, on the caller's stream (NULL = the context's, then it also waits):
- *   every rank   wait for its credit word (slot free again) -> [record pack] -> dense / binned launch whose stores
- *                go straight into rank 0's slot over NVLink and whose last CTA bumps this rank's done word there;
- *   rank 0       additionally: credits for the previous frame's slot (a 1-warp kernel writing every rank's credit
- *                word through the peer mapping), and after its own launch one stream wait per other rank's done
- *                word.  *d_frame_out (rank 0) = the slot: complete in stream order behind this call, valid until
- *                rank 0's NEXT rtb_group_render call is reached in stream order (whatever rank 0 enqueues on the
- *                stream in between -- a copy, a consumer kernel -- runs before the slot is handed back).
+ *   every rank   wait for its credit word (slot free again) -> [record pack] -> dense / binned launch whose row stores
+ *                go straight into rank 0's slot over NVLink -> a stream write of this rank's done word in rank 0's memory
+ *                (ordered behind the launch and its stores; without cuStreamWriteValue32 the launch's last CTA bumps it);
+ *   rank 0       additionally: after its own launch ONE batched stream wait on every other rank's done word (one word per
+ *                rank: a rank that runs ahead cannot stand in for one that lags), and -- on a side stream, behind an event
+ *                of this one -- the credits for the previous frame's slot (a 1-warp kernel writing every rank's credit
+ *                word through the peer mapping).  *d_frame_out (rank 0) = the slot: complete in stream order behind this
+ *                call, valid until rank 0's NEXT rtb_group_render call is reached in stream order (whatever rank 0
+ *                enqueues on the stream in between -- a copy, a consumer kernel -- runs before the slot is handed back).
  * With slots >= 2 the other ranks run up to slots-1 frames ahead of rank 0's consumer.  Every rank must call it
  * once per frame with the same camera.  Replaces, for the sharded frame, the per-render sequence of
  * MainState.cpp:641-934 (and round 1's Python loop with an NCCL all-reduce per frame).
