@@ -470,6 +470,12 @@ __device__ __forceinline__ void dense_group_slow(const GridParams& p, const floa
 // of the S warps of a pixel tile takes groups split, split + S, ...  The next group's entries are requested while
 // the current group is tested.  (Two groups per trip with the table registers alternating -- no register copies at
 // the end of a trip -- was measured SLOWER: C3 0.5574 -> 0.5663 ms, C4 8.11 -> 8.24 ms.)
+// Measured (profiles/r02_dense_sweep_v16.jsonl), vote per 16 against vote per 8: C4 8.117 -> 7.927 ms (92 % of the issue
+// bound), one rank's C4 rows at world 8 1.055 -> 1.030 ms, C3 0.5619 -> 0.5613 ms (its launch is short enough for the
+// doubled cold path to eat the gain), C2 0.0381 -> 0.0388 ms.  -DRTB_DENSE_VOTE16=0 builds the vote-per-8 loop.
+#ifndef RTB_DENSE_VOTE16
+#define RTB_DENSE_VOTE16 1
+#endif
 template <int PX, int S>
 __device__ __forceinline__ void dense_chunk(const GridParams& p, const float4* __restrict__ row, int cnt, int first_prim,
                                             int split, float v, PixelState<PX>& st) {
@@ -478,6 +484,47 @@ __device__ __forceinline__ void dense_chunk(const GridParams& p, const float4* _
     if (j >= cnt) return;
     const float4* t = row + (j >> 1);
     float4 a0 = t[0], a1 = t[1], a2 = t[2], a3 = t[3];
+#if RTB_DENSE_VOTE16
+    // Two groups of 8 per trip share the running minima, ONE compare and ONE vote; the table registers alternate
+    // (a -> b -> a), so nothing is copied at the end of a trip.  A trip whose second group lies past the end tests the
+    // chunk's last group again (harmless: minima and exact updates are idempotent).
+#pragma unroll 1
+    for (; j < cnt; j += 2 * S * G) {
+        float m[kMinChains];
+#pragma unroll
+        for (int k = 0; k < kMinChains; ++k) m[k] = __int_as_float(0x7f800000);
+        const int jb = min(j + S * G, cnt - G);
+        const float4* tb = row + (jb >> 1);
+        row_min<PX>(a0.x, a0.y, m, st);
+        row_min<PX>(a0.z, a0.w, m, st);
+        const float4 b0 = tb[0], b1 = tb[1];
+        row_min<PX>(a1.x, a1.y, m, st);
+        row_min<PX>(a1.z, a1.w, m, st);
+        const float4 b2 = tb[2], b3 = tb[3];
+        row_min<PX>(a2.x, a2.y, m, st);
+        row_min<PX>(a2.z, a2.w, m, st);
+        row_min<PX>(a3.x, a3.y, m, st);
+        row_min<PX>(a3.z, a3.w, m, st);
+        const int jn = min(j + 2 * S * G, cnt - G);
+        const float4* tn = row + (jn >> 1);
+        row_min<PX>(b0.x, b0.y, m, st);
+        row_min<PX>(b0.z, b0.w, m, st);
+        a0 = tn[0]; a1 = tn[1];
+        row_min<PX>(b1.x, b1.y, m, st);
+        row_min<PX>(b1.z, b1.w, m, st);
+        a2 = tn[2]; a3 = tn[3];
+        row_min<PX>(b2.x, b2.y, m, st);
+        row_min<PX>(b2.z, b2.w, m, st);
+        row_min<PX>(b3.x, b3.y, m, st);
+        row_min<PX>(b3.z, b3.w, m, st);
+        if (__any_sync(0xFFFFFFFFu, rtb_row_passes(min_of_chains(m)))) {
+#pragma unroll 1
+            for (int hgrp = 0; hgrp < 2; ++hgrp)
+                dense_group_slow<PX>(p, reinterpret_cast<const float2*>(hgrp ? tb : t), first_prim + (hgrp ? jb : j), v, st);
+        }
+        t = tn;
+    }
+#else
 #pragma unroll 1
     for (; j < cnt; j += S * G) {
         float m[kMinChains];
@@ -501,6 +548,7 @@ __device__ __forceinline__ void dense_chunk(const GridParams& p, const float4* _
         a0 = b0; a1 = b1; a2 = b2; a3 = b3;
         t = tn;
     }
+#endif
 }
 
 // Tile = (WARPS_X * 8 * PX) x (WARPS_Y * 4) pixels.  S > 1: S warps share one 8*PX x 4 warp tile and split the
