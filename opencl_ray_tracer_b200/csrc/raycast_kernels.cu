@@ -448,19 +448,25 @@ __device__ __forceinline__ float min_of_chains(const float (&m)[kMinChains]) {
 
 constexpr int kDenseGroup = 8;  // primitives per compare + warp vote
 
-// Behind the vote (a few per mille of the groups): which of the group's primitives was it?  Per primitive the
-// same test once more, then the reference-exact update for the rays of the warp.  Rolled: this is cold code.
+// Behind the vote (a few per mille of the groups): which of the group's primitives was it?  Per primitive the SPAN form
+// of the same test (raycast_math.h, rtb_bound_span_m: w' at the thread's two end rays bounds every w' between them, u
+// and w' being monotone along the run; the distance from 0 to that interval is min |w'| unless the run straddles 0) --
+// one FFMA2 and three FMNMX per primitive instead of 8 + 8: it accepts every run the per-ray test accepts, so the warp
+// still runs the reference-exact update wherever it has to, and the exact update is a no-op elsewhere.  Rolled: cold
+// code, but it is what makes crowded tiles slow (CTA lifetimes 35 .. 112 us around a median of 71 at C3).
 template <int PX>
 __device__ __forceinline__ void dense_group_slow(const GridParams& p, const float2* __restrict__ ent, int first_prim, float v,
                                                  PixelState<PX>& st) {
+    float u_first, u_last, unused;
+    unpack2(st.u2[0], u_first, unused);
+    unpack2(st.u2[PX / 2 - 1], unused, u_last);
+    const uint64_t u_ends = pack2(u_first, u_last);
 #pragma unroll 1
     for (int g = 0; g < kDenseGroup; ++g) {
         const float2 e = ent[g];
-        float m[kMinChains];
-#pragma unroll
-        for (int k = 0; k < kMinChains; ++k) m[k] = __int_as_float(0x7f800000);
-        row_min<PX>(e.x, e.y, m, st);
-        if (__any_sync(0xFFFFFFFFu, rtb_row_passes(min_of_chains(m)))) exact_update<PX>(p, first_prim + g, v, st);
+        float wa, wb;
+        unpack2(ffma2(u_ends, pack2(e.x, e.x), pack2(e.y, e.y)), wa, wb);
+        if (__any_sync(0xFFFFFFFFu, rtb_row_passes(rtb_bound_span_m(wa, wb)))) exact_update<PX>(p, first_prim + g, v, st);
     }
 }
 
