@@ -1,3 +1,5 @@
+# A/B of the multi-GPU frame fence on an N-GPU box: RTB_GROUP_STREAM_SIGNAL = 0 (in-kernel signal) / 1 (stream write, the default)
+#   /usr/local/graft/bin/gpurun --gpus 2 --timeout 600 -- 'bash tools/gpu_ab2.sh 2'
 set -x
 mkdir -p gpurun_out
 for v in 0 1; do

@@ -1,3 +1,5 @@
+# Per-rank breakdown of the host-frame call at N GPUs (tools/e2e_breakdown_group.py), dense and binned:
+#   /usr/local/graft/bin/gpurun --gpus 8 --timeout 900 -- 'bash tools/gpu_bd.sh "8 2"'
 set -x
 mkdir -p gpurun_out
 for n in $1; do for m in dense binned; do

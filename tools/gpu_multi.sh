@@ -1,3 +1,8 @@
+# The round's multi-GPU measurements (on an 8-GPU box, from the repo root):
+#   /usr/local/graft/bin/gpurun --gpus 8 --timeout 1800 -- 'bash tools/gpu_multi.sh'
+# bench lines at 8 / 4 / 2 GPUs the way the driver launches them, C5 at 8 and 1 GPUs, and the single-process
+# multi-device context (rtb_init with n_devices = 1, 2, 4, 8).  A/B of the frame fence: tools/gpu_ab2.sh; per-rank
+# breakdown of the host-frame call: tools/gpu_bd.sh; host topology: tools/numa_probe.py.
 set -x
 mkdir -p gpurun_out
 bash tools/gpu_scale.sh "8 4 2" r02 v12
