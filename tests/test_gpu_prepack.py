@@ -75,3 +75,24 @@ def test_sequence_equals_frame_by_frame(gpu_ctx, mode):
         assert np.array_equal(ctx.render(W, H, cams[1], want=("rgba8",))["rgba8"], got[1])   # context still usable
     finally:
         ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_AUTO)
+
+
+@pytest.mark.parametrize("mode", [0, 2])
+def test_long_sequence_on_two_lanes(gpu_ctx, mode):
+    """rtb_render_sequence_device: more frames than camera slots (256), consecutive frames on alternating streams with
+    their own bin words; every 23rd frame (and the last) must equal the single-frame render of its camera."""
+    import torch
+    ctx = gpu_ctx
+    w, h, nf = 200, 120, 300
+    ctx.set_option(capi.RTB_OPT_TILE_CULL, mode)
+    try:
+        ctx.set_scene(*hs.random_scene(w, h, 70, 30, 5).as_tuple())
+        cams = [hs.orbit_camera(w, h, k % 120) for k in range(nf)]
+        out = torch.zeros((nf, h, w, 4), dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        ctx.render_sequence_device(w, h, _flat(cams), out.data_ptr())
+        seq = out.cpu().numpy()
+        for k in list(range(0, nf, 23)) + [nf - 2, nf - 1]:
+            assert np.array_equal(seq[k], ctx.render(w, h, cams[k], want=("rgba8",))["rgba8"]), k
+    finally:
+        ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_AUTO)
