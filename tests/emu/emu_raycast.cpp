@@ -234,6 +234,16 @@ extern "C" int emu_check_row_table(int width, int height, const float* cam8, int
                 pass_row += row_ok;
                 viol += (q_ok && !row_ok);
             }
+            // the dense kernel's cold path (dense_group_slow): behind a vote a thread re-tests its run of 16 rays in the
+            // span form -- w' at the run's two end rays; it must accept every run in which a ray passes the row entry
+            for (int x0 = 0; x0 < width; x0 += 16) {
+                bool any = false;
+                for (int x = x0; x < x0 + 16; ++x)  // past the frame's edge like the kernel's threads
+                    any = any || rtb_row_passes(fabsf(rtb_row_w(e[0], e[1], rtb_cam_u(cam, (float)x, fy))));
+                const float wa = rtb_row_w(e[0], e[1], rtb_cam_u(cam, (float)x0, fy));
+                const float wb = rtb_row_w(e[0], e[1], rtb_cam_u(cam, (float)(x0 + 15), fy));
+                viol += (any && !rtb_row_passes(rtb_bound_span_m(wa, wb)));
+            }
         }
     }
     out[0] = viol; out[1] = pass_q; out[2] = pass_row; out[3] = (long long)width * height * n_bound;
