@@ -591,7 +591,8 @@ raycast_dense_kernel(const GridParams p) {
     const int wx = tile_warp % WARPS_X, wy = tile_warp / WARPS_X;
     const int lx = lane & 7, ly = lane >> 3;
     const int x0 = blockIdx.x * kTileW + (wx * 8 + lx) * PX;
-    const int lrow = blockIdx.y * kTileH + wy * 4 + ly;  // row in the packed (local) output
+    const int tile_y = (int)blockIdx.y + p.tile_y0;          // tile row within the launch set of this frame
+    const int lrow = tile_y * kTileH + wy * 4 + ly;  // row in the packed (local) output
     // interleaved row bands: local band lb -> global band lb*world + rank
     const int lb = lrow / p.band_rows;
     const int gy = (lb * p.band_world + p.band_rank) * p.band_rows + (lrow - lb * p.band_rows);
@@ -609,7 +610,7 @@ raycast_dense_kernel(const GridParams p) {
 #endif
 
     if (tid < kTileH) {  // the table is indexed by FRAME row; rows past the frame reuse its last row (never stored)
-        const int trow = blockIdx.y * kTileH + tid;
+        const int trow = tile_y * kTileH + tid;
         const int tlb = trow / p.band_rows;
         int tgy = (tlb * p.band_world + p.band_rank) * p.band_rows + (trow - tlb * p.band_rows);
         tgy = min(tgy, p.height - 1);
@@ -1605,7 +1606,7 @@ int cta_trace_dump(size_t ctas) {
 }
 #endif
 
-cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) {
+cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream, const TailLane* tail) {
     if (p.tile_cull == 2) return launch_binned<16, 2, 2, 2, 8>(p, stream);  // 64 registers, 8 CTAs/SM
     if (p.tile_cull) return launch_cull_instance<16, 2, 2, 4>(p, stream);
 #ifdef RTB_EXPERIMENTS
@@ -1636,7 +1637,37 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream) 
     if (traced) cta_trace_dump(ctas);
     return e;
 #else
-    return launch_dense_instance<16, 2, 1, 1, kDenseStages, kDenseChunk, 8>(p, s.grid, stream);
+    // Short tail.  The CTAs of a launch live ~70 us each (C3) and run out of phase, so when the grid is exhausted the
+    // SM slots go idle one by one over a whole CTA lifetime: ~35 us per slot, 6 % of a C3 frame, 12 % of one rank's
+    // half of it.  With a tail lane the last tile rows (one wave's worth of work, at most half of the rows) go to CTAs
+    // of 8 rays per thread -- half the lifetime, ~6 % more instructions per test -- launched on a second, low-priority
+    // stream at the same time: the block scheduler starts them when the body's grid is exhausted, and the frame's
+    // stream joins them.  Measured on one rank's rows of C3 at world 1 / 2 / 4: 0.5558 -> 0.5438, 0.2956 -> 0.2878,
+    // 0.1663 -> 0.1581 ms; C4 (4096 primitives: the 8-ray CTAs cost 8 % there and re-read twice the table) 7.948 -> 7.949,
+    // 3.991 -> 4.000, 2.040 -> 2.052, 1.031 -> 1.066 ms (profiles/r02_dense_tail_sweep.txt): used up to 2048 primitives.
+    // Only for launches of more than 1.25 waves without in-kernel progress / completion signals (their counters count
+    // the CTAs of one grid).  RTB_DENSE_TAIL=0 switches it off.
+    static const bool tail_on = [] { const char* e = std::getenv("RTB_DENSE_TAIL"); return !(e && e[0] == '0'); }();
+    const int slots = 8 * (sm_count > 0 ? sm_count : 1);
+    const int strips = (int)s.grid.y;
+    int tail_strips = (tail && tail_on && p.progress == nullptr && p.done_signal == nullptr && p.n_pad <= 2048)
+                          ? (slots + (int)s.grid.x - 1) / (int)s.grid.x : 0;
+    if (tail_strips <= 0 || (long long)strips * s.grid.x <= (long long)slots + slots / 4 || p.width <= 128)
+        return launch_dense_instance<16, 2, 1, 1, kDenseStages, kDenseChunk, 8>(p, s.grid, stream);
+    if (tail_strips > strips / 2) tail_strips = strips / 2;
+    cudaError_t e = cudaEventRecord(tail->fork, stream);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(tail->stream, tail->fork, 0);
+    if (e != cudaSuccess) return e;
+    GridParams body = p, tl = p;
+    body.tile_y0 = 0;
+    tl.tile_y0 = strips - tail_strips;
+    e = launch_dense_instance<16, 2, 1, 1, kDenseStages, kDenseChunk, 8>(body, dim3(s.grid.x, (unsigned)(strips - tail_strips)), stream);
+    if (e != cudaSuccess) return e;
+    e = launch_dense_instance<8, 2, 1, 1, kDenseStages, kDenseChunk, 10>(tl, dim3((unsigned)((p.width + 127) / 128), (unsigned)tail_strips), tail->stream);
+    if (e != cudaSuccess) return e;
+    e = cudaEventRecord(tail->join, tail->stream);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(stream, tail->join, 0);
+    return e;
 #endif
 }
 

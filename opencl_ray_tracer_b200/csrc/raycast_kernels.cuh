@@ -55,6 +55,8 @@ struct GridParams {
                                             // 2: bin_tiles_kernel + raycast_binned_kernel (the cull made once per frame)
     uint32_t* bins;                         // tile_cull == 2: [bin_words][tiles] words, grid_bin_words() of them
     int bin_words;                          // ceil(n_bound / 32)
+    int tile_y0;                            // dense kernel: this launch's first tile row (launch_grid splits a frame's rows
+                                            // into a body and a tail of shorter-lived CTAs); 0 otherwise
     RtbCam cam;
 #ifdef RTB_EXPERIMENTS
     // CTA timeline of the dense kernel (tools/cta_trace.py): 4 words per CTA = globaltimer at CTA start, after the wait
@@ -102,7 +104,10 @@ GridLaunchShape grid_launch_shape(int width, int local_rows, int sm_count);
 size_t grid_bin_words(int width, int local_rows, int n_bound);
 // Pixel rows of a tile of the binned render (a multiple of 16); progress chunks must not cut a tile.
 int binned_tile_rows();
-cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream);
+// One frame's launch(es).  `tail` (nullable): a second stream plus two events of the caller's, which let a dense launch
+// of more than one wave put its last tile rows into CTAs of half the lifetime on that stream (see launch_grid).
+struct TailLane { cudaStream_t stream; cudaEvent_t fork, join; };
+cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream, const TailLane* tail = nullptr);
 cudaError_t launch_rays(const RaysParams& p, cudaStream_t stream);
 cudaError_t launch_signal_only(unsigned int* d_signal, cudaStream_t stream);  // a rank with no rows still signals
 

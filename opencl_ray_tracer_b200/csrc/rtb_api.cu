@@ -188,6 +188,9 @@ void rtb_shutdown(rtb_ctx* ctx) {
     cudaFree(ctx->d_progress);
     cudaFree(ctx->d_bins);
     cudaFree(ctx->d_bins_seq);
+    if (ctx->tail_lane.stream) cudaStreamDestroy(ctx->tail_lane.stream);
+    if (ctx->tail_lane.fork) cudaEventDestroy(ctx->tail_lane.fork);
+    if (ctx->tail_lane.join) cudaEventDestroy(ctx->tail_lane.join);
     if (ctx->seq_stream) cudaStreamDestroy(ctx->seq_stream);
     if (ctx->ev_seq_fork) cudaEventDestroy(ctx->ev_seq_fork);
     if (ctx->ev_seq_join) cudaEventDestroy(ctx->ev_seq_join);
@@ -588,6 +591,7 @@ int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const FrameSet* fs, int width,
 #ifdef RTB_EXPERIMENTS
     p.trace = nullptr;
 #endif
+    p.tile_y0 = 0;
     p.out_global_rows = out_global_rows;
     static const int fence_sys = [] { const char* e = std::getenv("RTB_PROGRESS_FENCE_SYSTEM"); return (e && e[0] == '1') ? 1 : 0; }();
     p.fence_system = fence_sys;
@@ -632,7 +636,14 @@ int enqueue_grid(rtb_ctx* ctx, const RtbCam& cam, const FrameSet* fs, int width,
     const int rc = take_events(ctx, &ev);
     if (rc != RTB_OK) return rc;
     RTB_CUDA(ctx, cudaEventRecord(ev.a, stream));
-    RTB_CUDA(ctx, launch_grid(p, ctx->sm_count, stream));
+    if (!ctx->tail_lane.stream) {  // a low-priority stream for the short-lived tail CTAs of a dense launch
+        int lo = 0, hi = 0;
+        RTB_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        RTB_CUDA(ctx, cudaStreamCreateWithPriority(&ctx->tail_lane.stream, cudaStreamNonBlocking, lo));
+        RTB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->tail_lane.fork, cudaEventDisableTiming));
+        RTB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->tail_lane.join, cudaEventDisableTiming));
+    }
+    RTB_CUDA(ctx, launch_grid(p, ctx->sm_count, stream, &ctx->tail_lane));
     RTB_CUDA(ctx, cudaEventRecord(ev.b, stream));
     ctx->ev_pending.push_back(ev);
     ctx->launches += (p.tile_cull == 2 && p.bin_words > 0) ? 2 : 1;  // bin_tiles_kernel + raycast_binned_kernel

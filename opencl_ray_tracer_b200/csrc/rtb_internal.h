@@ -104,6 +104,7 @@ struct rtb_ctx {
     // rtb_render_sequence_device renders consecutive frames on alternating lanes (lane 0 = the context's stream and
     // d_bins; lane 1 = seq_stream and its own bin words), so that a frame's ragged end / second launch overlaps the
     // next frame's start.
+    rtb::TailLane tail_lane = {nullptr, nullptr, nullptr};   // dense launches of more than one wave: see launch_grid
     cudaStream_t seq_stream = nullptr;
     cudaEvent_t ev_seq_fork = nullptr, ev_seq_join = nullptr;
     void* d_bins_seq = nullptr;
