@@ -1645,14 +1645,22 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream, 
     // stream joins them.  Measured on one rank's rows of C3 at world 1 / 2 / 4: 0.5558 -> 0.5438, 0.2956 -> 0.2878,
     // 0.1663 -> 0.1581 ms; C4 (4096 primitives: the 8-ray CTAs cost 8 % there and re-read twice the table) 7.948 -> 7.949,
     // 3.991 -> 4.000, 2.040 -> 2.052, 1.031 -> 1.066 ms (profiles/r02_dense_tail_sweep.txt): used up to 2048 primitives.
-    // Only for launches of more than 1.25 waves without in-kernel progress / completion signals (their counters count
-    // the CTAs of one grid).  RTB_DENSE_TAIL=0 switches it off.
+    // Only for launches without in-kernel progress / completion signals (their counters count the CTAs of one grid).
+    // RTB_DENSE_TAIL=0 switches it off.
     static const bool tail_on = [] { const char* e = std::getenv("RTB_DENSE_TAIL"); return !(e && e[0] == '0'); }();
     const int slots = 8 * (sm_count > 0 ? sm_count : 1);
     const int strips = (int)s.grid.y;
     int tail_strips = (tail && tail_on && p.progress == nullptr && p.done_signal == nullptr && p.n_pad <= 2048)
                           ? (slots + (int)s.grid.x - 1) / (int)s.grid.x : 0;
-    if (tail_strips <= 0 || (long long)strips * s.grid.x <= (long long)slots + slots / 4 || p.width <= 128)
+    const long long ctas16 = (long long)strips * s.grid.x;
+    if (tail_strips > 0 && ctas16 <= (long long)slots + slots / 4) {
+        // A launch of about one wave or less: every CTA starts at once and the SMs hold 6 or 7 of them.  Between half a
+        // wave and one, as many tile rows as the free slots allow become 8-ray CTAs (two per tile): every SM then holds
+        // 8 CTAs of two sizes and the load evens out (one rank's 272 rows of C3 at world 8: 0.0917 -> 0.0847 ms;
+        // profiles/r02_dense_tail_sweep.txt).  Not worth a second launch for short kernels (few primitives).
+        tail_strips = (ctas16 >= slots / 2 && ctas16 < slots && p.n_pad >= 512) ? (int)((slots - ctas16) / s.grid.x) : 0;
+    }
+    if (tail_strips <= 0 || p.width <= 128)
         return launch_dense_instance<16, 2, 1, 1, kDenseStages, kDenseChunk, 8>(p, s.grid, stream);
     if (tail_strips > strips / 2) tail_strips = strips / 2;
     cudaError_t e = cudaEventRecord(tail->fork, stream);
