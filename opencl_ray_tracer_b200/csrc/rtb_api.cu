@@ -50,6 +50,8 @@ int resolve_pending(rtb_ctx* ctx) {
 void drain(rtb_ctx* ctx, cudaStream_t extra) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+    if (ctx->seq_stream) cudaStreamSynchronize(ctx->seq_stream);
+    if (ctx->tail_lane.stream) cudaStreamSynchronize(ctx->tail_lane.stream);
     if (extra) cudaStreamSynchronize(extra);
     for (const EventPair& e : ctx->ev_pending) ctx->ev_free.push_back(e);  // timings of a failed call are dropped
     ctx->ev_pending.clear();
