@@ -178,13 +178,9 @@ void rtb_shutdown(rtb_ctx* ctx) {
     if (ctx->ev_rec) cudaEventDestroy(ctx->ev_rec);
     if (ctx->ev_state) cudaEventDestroy(ctx->ev_state);
     if (ctx->ev_scene) cudaEventDestroy(ctx->ev_scene);
-    cudaFree(ctx->d_cube_col);
-    cudaFree(ctx->d_sph_col);
     free_frame_set(&ctx->cur);
     for (auto& fs : ctx->slots) free_frame_set(&fs);
-    cudaFree(ctx->d_cube_v);
-    cudaFree(ctx->d_sph_o);
-    cudaFree(ctx->d_sph_r);
+    cudaFree(ctx->d_scene);
     cudaFree(ctx->d_boxes);
     cudaFree(ctx->d_bad);
     cudaFree(ctx->d_progress);
@@ -313,53 +309,50 @@ int set_scene_single(rtb_ctx* ctx, int numSpheres, const float* sphereOrigins, c
     int rc = order_streams(ctx, st);  // frames of the previous scene may still be reading the buffers
     if (rc != RTB_OK) return rc;
     const size_t nc = (size_t)numCubes, ns = (size_t)numSpheres;
-    {
-        void* p[6] = {ctx->d_cube_v, ctx->d_sph_o, ctx->d_sph_r, ctx->d_boxes, ctx->d_cube_col, ctx->d_sph_col};
-        size_t cap[6] = {ctx->d_scene_cap[0], ctx->d_scene_cap[1], ctx->d_scene_cap[2], ctx->d_scene_cap[3],
-                         ctx->d_col_cap[0] * sizeof(float4), ctx->d_col_cap[1] * sizeof(float4)};
-        const size_t need[6] = {144 * sizeof(float) * (nc ? nc : 1), sizeof(float4) * (ns ? ns : 1),
-                                sizeof(float) * (ns ? ns : 1), sizeof(Box) * (nc ? nc : 1),
-                                sizeof(float4) * (nc ? nc : 1), sizeof(float4) * (ns ? ns : 1)};
-        bool grow = false;
-        for (int k = 0; k < 6; ++k) grow = grow || cap[k] < need[k];
-        if (grow) RTB_CUDA(ctx, cudaDeviceSynchronize());  // cudaFree below: nothing may still read the old buffers
-        int rc0 = RTB_OK;
-        for (int k = 0; k < 6 && rc0 == RTB_OK; ++k) rc0 = ensure_device(ctx, &p[k], &cap[k], need[k]);
-        ctx->d_cube_v = static_cast<float*>(p[0]);
-        ctx->d_sph_o = static_cast<float4*>(p[1]);
-        ctx->d_sph_r = static_cast<float*>(p[2]);
-        ctx->d_boxes = static_cast<Box*>(p[3]);
-        ctx->d_cube_col = static_cast<float4*>(p[4]);
-        ctx->d_sph_col = static_cast<float4*>(p[5]);
-        for (int k = 0; k < 4; ++k) ctx->d_scene_cap[k] = cap[k];
-        ctx->d_col_cap[0] = cap[4] / sizeof(float4);
-        ctx->d_col_cap[1] = cap[5] / sizeof(float4);
-        if (rc0 != RTB_OK) return rc0;
-    }
-    // The caller may free its arrays on return: they are staged in the context's pinned buffer (one host
-    // memcpy) and go to the device from there, exactly as the reference lays them out (the 6 arrays of
-    // MainState.cpp:677-839); the boxes are recovered from the vertices on the device.  Nothing here waits for
-    // the GPU unless the staging area is still being read by the previous rtb_set_scene.
+    // The caller may free its arrays on return: they are staged in the context's pinned buffer (one host memcpy each)
+    // and go to the device from there in ONE copy, into a device block with the same layout -- the 5 arrays of
+    // MainState.cpp:677-839 as the reference lays them out, each 256-byte aligned; the boxes are recovered from the
+    // vertices on the device.  Nothing here waits for the GPU unless the staging area is still being read by the
+    // previous rtb_set_scene.
     const size_t bytes[5] = {144 * sizeof(float) * nc, sizeof(float4) * nc, sizeof(float4) * ns, sizeof(float) * ns,
                              sizeof(float4) * ns};
     const void* src[5] = {cubeVertices, cubeColours, sphereOrigins, sphereRadius, sphereColours};
-    void* dst[5] = {ctx->d_cube_v, ctx->d_cube_col, ctx->d_sph_o, ctx->d_sph_r, ctx->d_sph_col};
     size_t total = 0, off[5];
     for (int k = 0; k < 5; ++k) { off[k] = total; total += (bytes[k] + 255) & ~(size_t)255; }
+    if (total == 0) total = 256;
+    {
+        const size_t need_boxes = sizeof(Box) * (nc ? nc : 1);
+        if (ctx->d_scene_cap < total || ctx->d_boxes_cap < need_boxes)
+            RTB_CUDA(ctx, cudaDeviceSynchronize());  // cudaFree below: nothing may still read the old buffers
+        void* blk = ctx->d_scene;
+        int rc0 = ensure_device(ctx, &blk, &ctx->d_scene_cap, total);
+        ctx->d_scene = static_cast<unsigned char*>(blk);
+        void* bx = ctx->d_boxes;
+        if (rc0 == RTB_OK) rc0 = ensure_device(ctx, &bx, &ctx->d_boxes_cap, need_boxes);
+        ctx->d_boxes = static_cast<Box*>(bx);
+        if (rc0 != RTB_OK) return rc0;
+        ctx->d_cube_v = reinterpret_cast<float*>(ctx->d_scene + off[0]);
+        ctx->d_cube_col = reinterpret_cast<float4*>(ctx->d_scene + off[1]);
+        ctx->d_sph_o = reinterpret_cast<float4*>(ctx->d_scene + off[2]);
+        ctx->d_sph_r = reinterpret_cast<float*>(ctx->d_scene + off[3]);
+        ctx->d_sph_col = reinterpret_cast<float4*>(ctx->d_scene + off[4]);
+    }
     if (ctx->scene_check_pending) RTB_CUDA(ctx, cudaEventSynchronize(ctx->ev_scene));  // staging area and h_bad free again
     ctx->scene_check_pending = false;
     if (ctx->h_scene_cap < total) {
         if (ctx->h_scene) RTB_CUDA(ctx, cudaFreeHost(ctx->h_scene));
         ctx->h_scene = nullptr;
         ctx->h_scene_cap = 0;
-        RTB_CUDA(ctx, cudaMallocHost(&ctx->h_scene, total ? total : 256));
-        ctx->h_scene_cap = total ? total : 256;
+        RTB_CUDA(ctx, cudaMallocHost(&ctx->h_scene, total));
+        ctx->h_scene_cap = total;
     }
+    size_t used = 0;
     for (int k = 0; k < 5; ++k)
         if (bytes[k]) {
             std::memcpy(ctx->h_scene + off[k], src[k], bytes[k]);
-            RTB_CUDA(ctx, cudaMemcpyAsync(dst[k], ctx->h_scene + off[k], bytes[k], cudaMemcpyHostToDevice, st));
+            used = off[k] + bytes[k];
         }
+    if (used) RTB_CUDA(ctx, cudaMemcpyAsync(ctx->d_scene, ctx->h_scene, used, cudaMemcpyHostToDevice, st));
     RTB_CUDA(ctx, launch_boxes_from_vertices(ctx->d_cube_v, numCubes, ctx->d_boxes, ctx->d_bad, st));
     if (nc) ctx->launches += 1;
     RTB_CUDA(ctx, cudaMemcpyAsync(ctx->h_bad, ctx->d_bad, sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -58,7 +58,10 @@ struct rtb_ctx {
     float4* d_sph_o = nullptr;
     float* d_sph_r = nullptr;
     rtb::Box* d_boxes = nullptr;
-    size_t d_scene_cap[4] = {0, 0, 0, 0};  // bytes: cube_v, sph_o, sph_r, boxes
+    // the five scene arrays are sub-ranges of ONE device block (d_scene), laid out like the pinned staging buffer: one
+    // host-to-device copy per rtb_set_scene instead of five; the boxes have their own buffer
+    unsigned char* d_scene = nullptr;
+    size_t d_scene_cap = 0, d_boxes_cap = 0;
     int* d_bad = nullptr;          // lowest index of a cube that is not a box (boxes_from_vertices_kernel)
     int* h_bad = nullptr;          // pinned
     // rtb_set_scene stages the caller's arrays in pinned memory and returns; ev_scene = staging consumed + verdict
@@ -81,7 +84,6 @@ struct rtb_ctx {
     size_t h_rec_cap = 0;
     void* d_out[3] = {nullptr, nullptr, nullptr};  // rgba8, id, i32 frame buffers, grow-only
     size_t d_out_cap[3] = {0, 0, 0};
-    size_t d_col_cap[2] = {0, 0};  // cube / sphere colour capacity in float4
     unsigned long long h2d_bytes = 0, d2h_bytes = 0;  // bytes this context copied over PCIe
     float4* d_origins = nullptr;   // rays path
     size_t d_origins_cap = 0;
