@@ -9,10 +9,12 @@
 // and a lane's PX RGBA8 results leave as 128-bit stores.  The per-(pixel row, primitive) entries of the
 // conservative bound -- the row table, 8 B each, built once per frame by row_table_kernel
 // (scene_pack_device.cu) -- are staged global->shared in chunks with 1-D TMA bulk copies (cp.async.bulk +
-// mbarrier complete_tx) through a 4-stage ring with full / empty mbarriers: no CTA-wide barrier in the
-// loop.  Per ray pair and primitive: 1 FFMA2 (w' = sAn*u + rWn) + 1 FMNMX3 (running min of |w'| over the
-// thread's rays AND over 8 primitives); per 8 primitives one compare (min < 1), one warp vote.  The
-// reference-exact slab / sphere update (raycast_math.h) runs only behind the vote.
+// mbarrier complete_tx) through a 2-stage ring of 256-primitive chunks with full / empty mbarriers: no CTA-wide
+// barrier in the loop.  Per ray pair and primitive: 1 FFMA2 (w' = sAn*u + rWn) + 1 FMNMX3 (running min of |w'| over
+// the thread's rays AND over 16 primitives); per 16 primitives one compare (min < 1), one warp vote.  The
+// reference-exact slab / sphere update (raycast_math.h) runs only behind the vote.  A CTA is two such warps
+// (256 x 4 pixels, 8 CTAs per SM); the last tile rows of a launch run in CTAs of 8 rays per thread on a second
+// stream (launch_grid), and a warp's rgba8 pixels leave as whole rows through shared memory (shade_and_store_warp).
 //
 // Compiled with -fmad=false: every FMA is an explicit fmaf() from raycast_math.h so the scalar
 // emulator in tests/emu reproduces the kernel bit for bit.
