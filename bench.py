@@ -147,10 +147,10 @@ class ClockSampler(threading.Thread):
 
 def ncu_traffic_bytes(workload, key=None):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel (key = "binned": of the
-    two launches of a binned frame), from the committed ncu --set full captures (profiles/r01_ncu_traffic.json);
+    two launches of a binned frame), from the committed ncu --set full captures (profiles/r02_ncu_traffic.json);
     None for other workloads."""
     try:
-        j = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))
+        j = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")))
         if j.get("workload") == workload:
             if key:
                 j = j[key]
