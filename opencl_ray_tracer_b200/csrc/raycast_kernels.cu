@@ -1662,9 +1662,9 @@ cudaError_t launch_grid(const GridParams& p, int sm_count, cudaStream_t stream, 
         // profiles/r02_dense_tail_sweep.txt).  Not worth a second launch for short kernels (few primitives).
         tail_strips = (ctas16 >= slots / 2 && ctas16 < slots && p.n_pad >= 512) ? (int)((slots - ctas16) / s.grid.x) : 0;
     }
+    if (tail_strips > strips / 2) tail_strips = strips / 2;
     if (tail_strips <= 0 || p.width <= 128)
         return launch_dense_instance<16, 2, 1, 1, kDenseStages, kDenseChunk, 8>(p, s.grid, stream);
-    if (tail_strips > strips / 2) tail_strips = strips / 2;
     cudaError_t e = cudaEventRecord(tail->fork, stream);
     if (e == cudaSuccess) e = cudaStreamWaitEvent(tail->stream, tail->fork, 0);
     if (e != cudaSuccess) return e;
