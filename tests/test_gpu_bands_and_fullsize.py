@@ -52,6 +52,27 @@ def test_band_sharding_reassembles_exactly(gpu_ctx, w, h, band_rows):
         assert np.array_equal(fid, whole["prim_id"]), world
 
 
+@pytest.mark.parametrize("w,h,band_rows", [(2300, 2206, 4), (3000, 1500, 16)])
+def test_dense_bands_with_a_short_tail_reassemble_exactly(gpu_ctx, w, h, band_rows):
+    """Dense kernel, device-resident launches: more than 1.25 waves of CTAs, so the last tile rows of every launch run
+    in 8-ray CTAs on a second stream (launch_grid); ragged widths, rows and bands.  rtb_render (one launch with progress
+    flags, no tail) is the frame they must re-assemble to."""
+    from opencl_ray_tracer_b200 import capi, host_scene as hs
+    s = hs.random_scene(w, h, 70, 50, 33)
+    _set(gpu_ctx, s)
+    gpu_ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_DENSE)
+    try:
+        whole = gpu_ctx.render(w, h, want=("rgba8", "prim_id"))
+        for world in (1, 2, 3):
+            f8, fid = _render_bands(gpu_ctx, w, h, capi.REFERENCE_CAMERA, band_rows, world)
+            assert np.array_equal(f8, whole["rgba8"]), world
+            assert np.array_equal(fid, whole["prim_id"]), world
+    finally:
+        gpu_ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_AUTO)
+    binned = gpu_ctx.render(w, h, want=("rgba8", "prim_id"))
+    assert np.array_equal(binned["rgba8"], whole["rgba8"]) and np.array_equal(binned["prim_id"], whole["prim_id"])
+
+
 def test_sequence_equals_single_frames(gpu_ctx):
     import torch
     from opencl_ray_tracer_b200 import host_scene as hs

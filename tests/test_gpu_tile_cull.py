@@ -38,6 +38,9 @@ def _both(ctx, w, h, cam, mode, want=("rgba8", "prim_id", "rgba_i32")):
     (250, 40, 900, 131, 19, 7),
     (96, 40, 3000, 2000, 23, 0),   # 5000 primitives: more words than a CTA has threads, many passes
     (1000, 700, 1, 0, 29, 0), (64, 48, 0, 1, 31, 0),
+    # dense launches with a short tail (more than 1.25 waves of CTAs: the last tile rows run in 8-ray CTAs on a second
+    # stream) whose body and tail both end in partial tiles: width not a multiple of 4 / of 128, rows not a multiple of 4
+    (2001, 1203, 90, 60, 37, 0), (2500, 1102, 60, 70, 41, 9), (1924, 1440, 100, 50, 43, 0),
 ])
 @pytest.mark.parametrize("mode", MODES)
 def test_culled_frame_is_the_dense_frame(ctx, mode, w, h, ns, nc, seed, k):
