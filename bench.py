@@ -91,6 +91,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-c4", action="store_true", help="skip the BASELINE config 4 sub-record of a c3 run")
     ap.add_argument("--no-binned", action="store_true", help="skip the second pass with the binned tile cull (RTB_OPT_TILE_CULL = 2)")
+    ap.add_argument("--lanes", type=int, default=2, help="c5 at N > 1: contexts (+ groups, streams) per rank that the frames alternate between")
     return ap.parse_args()
 
 
@@ -510,6 +511,15 @@ def run_sequence(args):
     sptr = stream.cuda_stream
     # N > 1: a ring of 8 frame slots on rank 0 (the ranks run up to 7 frames ahead of rank 0's stream)
     grp = capi.Group(ctx, _group_name("c5", rank, world), rank, world, w, h, BAND_ROWS, 8) if world > 1 else None
+    # N > 1, --lanes 2 (default): a SECOND context + group + stream per rank; frames alternate between the two, so a
+    # frame's ragged end, its NVLink drain into rank 0 and its stream operations overlap the next frame's kernel (what
+    # rtb_render_sequence_device does inside one context for N = 1).  Each lane is the plain public API.
+    lanes = [(ctx, grp, stream)]
+    if world > 1 and args.lanes >= 2:
+        ctx2 = capi.Context(local_rank)
+        ctx2.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_DENSE)
+        ctx2.set_scene(*scene.as_tuple())
+        lanes.append((ctx2, capi.Group(ctx2, _group_name("c5b", rank, world), rank, world, w, h, BAND_ROWS, 8), torch.cuda.Stream()))
     d_out = torch.empty((n_frames, h, w, 4), dtype=torch.uint8, device="cuda") if world == 1 else None
     h_frame = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory().numpy() if world == 1 else None
     token = torch.zeros(1, dtype=torch.int32, device="cuda")
@@ -518,10 +528,14 @@ def run_sequence(args):
         if world == 1:
             ctx.render_sequence_device(w, h, flat, d_out.data_ptr())     # blocking
             return
-        grp.prepack(flat, sptr)        # the frames' records (this rank's bands) are packed ahead on the context's side stream
+        nl = len(lanes)
+        for k, (_, g, st) in enumerate(lanes):   # the frames' records (this rank's bands) are packed ahead on each context's side stream
+            g.prepack(flat[k::nl], st.cuda_stream)
         for f in range(n_frames):
-            grp.render(cams[f], sptr)  # one C call per frame and rank; rank 0's stream holds every frame's completion
-        stream.synchronize()
+            _, g, st = lanes[f % nl]
+            g.render(cams[f], st.cuda_stream)    # one C call per frame and rank; the lane's stream holds the frame's completion
+        for _, _, st in lanes:
+            st.synchronize()
 
     def e2e_step():
         for f in range(n_frames):
@@ -549,22 +563,27 @@ def run_sequence(args):
     steps = max(1, args.steps)
     for _ in range(max(1, min(args.warmup, 3))):
         device_step()
-    ctx.kernel_ms_avg(reset=True)
+    for c, _, _ in lanes:
+        c.kernel_ms_avg(reset=True)
     sampler = ClockSampler(local_rank)
     sampler.start()
-    n_launch0 = ctx.launch_count()
+    n_launch0 = sum(c.launch_count() for c, _, _ in lanes)
     dev_s = timed(device_step, steps)
-    launches = ctx.launch_count() - n_launch0
+    launches = sum(c.launch_count() for c, _, _ in lanes) - n_launch0
     sampler.stop_flag = True
     sampler.join()
-    k_avg_ms, k_n = ctx.kernel_ms_avg(reset=True)
+    k_pairs = [c.kernel_ms_avg(reset=True) for c, _, _ in lanes]
+    k_n = sum(n for _, n in k_pairs)
+    k_avg_ms = sum(a * n for a, n in k_pairs) / k_n if k_n else 0.0
     # the same sequence with the binned tile cull (RTB_OPT_TILE_CULL = 2, byte-identical frames), device-resident
     binned_s = None
     if not args.no_binned:
-        ctx.set_option(capi.RTB_OPT_TILE_CULL, 2)
+        for c, _, _ in lanes:
+            c.set_option(capi.RTB_OPT_TILE_CULL, 2)
         device_step()
         binned_s = timed(device_step, steps) / steps
-        ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_DENSE)
+        for c, _, _ in lanes:
+            c.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_DENSE)
     ctx.set_option(capi.RTB_OPT_TILE_CULL, capi.TILE_CULL_AUTO)   # e2e: the library's default options, as in the single-frame lines
     e2e_step()
     e2e_steps = max(1, steps // 4)
@@ -592,7 +611,9 @@ def run_sequence(args):
             "config": dict(bench_config(args.workload, world),
                            l2="each step writes %d frames = %.1f GB of output (larger than L2); a step is timed as a whole (wall clock around blocking calls, max over ranks)" % (
                                n_frames, n_frames * 4 * n_px / 1e9),
-                           records="moving camera: every frame's records and row table are packed (ahead, on a side stream)"),
+                           records="moving camera: every frame's records and row table are packed (ahead, on a side stream)",
+                           lanes=("%d contexts (+ groups, streams) per rank, frames alternate between them" % len(lanes)) if world > 1 else
+                                 "one context; rtb_render_sequence_device alternates two streams inside it"),
             "frames_per_s": n_frames / s_step, "ms_per_frame": s_step * 1e3 / n_frames,
             "tests_per_s": n_frames * n_px * (ns + nc) / s_step,
             "clocks": sampler.result(),
@@ -615,7 +636,8 @@ def run_sequence(args):
         print(json.dumps(line))
     if world > 1:
         dist.barrier()
-        grp.close()
+        for _, g, _ in lanes:
+            g.close()
         dist.destroy_process_group()
 
 
