@@ -93,3 +93,13 @@ def test_product_package_never_imports_oracle():
                                   r"|-loracle|oracle/_ref/|oracle\.py)", text)
                 hits = [h for h in hits if not (f.endswith((".cpp", ".h")) and h == "oracle/_ref/")]
                 assert not hits, (os.path.join(dirpath, f), hits)
+
+
+def test_header_is_plain_c(tmp_path):
+    """include/rtb.h is the boundary a C or C++ host binds: it must compile as C99 and as C++11 on its own."""
+    import subprocess
+    src = tmp_path / "hdr.c"
+    src.write_text('#include "rtb.h"\nint main(void) { rtb_ctx* c = 0; (void)c; return RTB_OK; }\n')
+    inc = os.path.join(ROOT, "include")
+    subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-I", inc, "-fsyntax-only", str(src)], check=True)
+    subprocess.run(["g++", "-std=c++11", "-Wall", "-Werror", "-I", inc, "-fsyntax-only", "-x", "c++", str(src)], check=True)
